@@ -1,0 +1,408 @@
+#!/usr/bin/env python
+"""bench.py - RS(255,223) batched encode + decode throughput (BASELINE.json metric) on N B200s.
+
+Contract (see the task brief): `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0.
+
+Workload (BASELINE.json configs[1]): per GPU, 16 Mi RS(255,223) codewords as packed 255-byte records;
+one step = encode all messages (223 B -> 32 B parity) + decode all corrupted codewords (0-16 random byte
+errors each, uniform; positions over data and parity; corrected in place).  Inputs are resident in HBM
+when the timed region starts (`value`); `e2e` is the same step through the host-pointer C API
+(poporon_encode_batch / poporon_decode_batch on page-locked host buffers, copies inside the timed region).
+
+Each GPU owns a contiguous slice of the codeword index space (weak scaling, no data-path collective:
+codewords are independent - SURVEY 8e); torch.distributed is used only for the barrier and the
+max-over-ranks of the elapsed time.
+
+`--impl reference` times the reference's own CPU implementation (oracle/_ref/libpoporon_ref.so = the
+unmodified reference compiled by oracle/Makefile; falls back to the oracle port when it is absent) with one
+independent poporon_t per host core on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "rs255_223_encode_decode_payload_GBps"
+UNIT = "GB/s"
+K_MSG, K_PAR, K_CW = 223, 32, 255
+SEED_MSG, SEED_ERR = 0x5EED0001, 0x5EED0002
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--ncw", type=int, default=16 * 1024 * 1024, help="codewords per GPU per step")
+    ap.add_argument("--emax", type=int, default=16, help="errors per codeword are uniform in [0, emax]")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="codewords in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--mem-budget-gb", type=float, default=140.0)
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples SM clock and throttle reasons of one GPU during the timed region (pynvml)."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ----------------------------------------------------------------------------------------- CPU arms
+def cpu_workload(n, emax, seed=1234):
+    """Synthetic codewords of the same distribution as the GPU workload, generated with numpy."""
+    import numpy as np
+
+    rng = np.random.default_rng(seed)
+    msg = rng.integers(0, 256, (n, K_MSG), dtype=np.uint8)
+    e = rng.integers(0, emax + 1, n)
+    order = np.argsort(rng.random((n, K_CW)), axis=1)[:, :max(emax, 1)]
+    mags = rng.integers(1, 256, (n, max(emax, 1)), dtype=np.uint8)
+    return msg, e, order, mags
+
+
+def time_cpu(lib, msg, e, order, mags, threads):
+    """One CPU step on the sample: encode then decode; returns seconds."""
+    import numpy as np
+
+    n = len(msg)
+    t0 = time.perf_counter()
+    par = lib.rs_encode(msg, threads=threads)
+    t1 = time.perf_counter()
+    cw = np.concatenate([msg, par], 1)
+    rows = np.arange(n)
+    for k in range(order.shape[1]):
+        sel = e > k
+        cw[rows[sel], order[sel, k]] ^= mags[sel, k]
+    d, p = np.ascontiguousarray(cw[:, :K_MSG]), np.ascontiguousarray(cw[:, K_MSG:])
+    t2 = time.perf_counter()
+    out = lib.rs_decode(d, p, threads=threads)
+    t3 = time.perf_counter()
+    assert out[2].all(), "CPU baseline failed to decode a correctable codeword"
+    return (t1 - t0) + (t3 - t2)
+
+
+def load_cpu_lib():
+    from oraclelib import Oracle, have_reference
+
+    if have_reference():
+        return Oracle("reference"), "reference"
+    return Oracle("port"), "port"
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    lib, kind = load_cpu_lib()
+    cores = os.cpu_count() or 1
+    sample = args.cpu_sample or min(args.ncw, cores * 20000)
+    msg, e, order, mags = cpu_workload(sample, args.emax)
+    for _ in range(min(args.warmup, 1)):
+        time_cpu(lib, msg[: max(1, sample // 8)], e[: max(1, sample // 8)], order[: max(1, sample // 8)],
+                 mags[: max(1, sample // 8)], cores)
+    total = 0.0
+    for _ in range(args.steps):
+        total += time_cpu(lib, msg, e, order, mags, cores)
+    per_step = total / max(args.steps, 1)
+    value = 2 * sample * K_MSG / per_step / 1e9
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(args, sample_per_step=sample),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{sample} codewords per step (encode + decode), one handle per thread"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, **extra):
+    cfg = {"workload": "RS(255,223) batched encode+decode, 0-%d random byte errors per codeword "
+                       "(BASELINE configs[1])" % args.emax,
+           "codewords_per_gpu": args.ncw, "record_bytes": K_CW, "layout": "packed 255-byte records",
+           "errors": f"uniform 0..{args.emax} per codeword, distinct positions over data+parity",
+           "cache": "inputs larger than L2 (%.2f GB per pass vs 126 MB L2)" % (args.ncw * K_CW / 1e9)}
+    cfg.update(extra)
+    return cfg
+
+
+# ----------------------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import libpoporon_b200.api as api
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.ncw
+    i0 = rank * n  # this rank's slice of the global codeword index space
+    K, W = args.steps, args.warmup
+    rec_bytes = n * K_CW
+    nbuf = max(1, min(K + W, int(args.mem_budget_gb * 1e9 // rec_bytes) - 1))
+    reinject = nbuf < K + W
+    stream = torch.cuda.current_stream().cuda_stream
+
+    h = api.Poporon.rs_default()
+    assert h.use_devices([local])
+
+    clean = torch.empty(rec_bytes, dtype=torch.uint8, device=dev)
+    api.synth_fill(local, clean.data_ptr(), K_CW, K_MSG, n, SEED_MSG, i0, stream)
+    assert h.encode_batch_async(clean.data_ptr(), K_CW, K_MSG, clean.data_ptr() + K_MSG, K_CW, n, stream)
+    bufs, dirty = [], []
+
+    def corrupt(b):
+        """XOR buffer b's deterministic error pattern in (a second application would remove it again)"""
+        api.synth_inject(local, bufs[b].data_ptr(), K_CW, K_CW, n, SEED_ERR + b, i0, 0, 0, args.emax, 0, stream)
+        dirty[b] = not dirty[b]
+
+    for b in range(nbuf):
+        bufs.append(clean.clone())
+        dirty.append(False)
+        corrupt(b)
+    ok = torch.empty(n, dtype=torch.uint8, device=dev)
+    cor = torch.empty(n, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+
+    def step(s, ev=None):
+        buf = bufs[s % nbuf]
+        if not dirty[s % nbuf]:  # only when K + W exceeds the buffer ring (reported as reinject_in_timed_region)
+            corrupt(s % nbuf)
+        dirty[s % nbuf] = False  # the decode below restores it
+        if ev:
+            ev[0].record()
+        assert h.encode_batch_async(clean.data_ptr(), K_CW, K_MSG, clean.data_ptr() + K_MSG, K_CW, n, stream)
+        if ev:
+            ev[1].record()
+        assert h.decode_batch_async(buf.data_ptr(), K_CW, K_MSG, buf.data_ptr() + K_MSG, K_CW, n, ok.data_ptr(),
+                                    cor.data_ptr(), stream=stream)
+        if ev:
+            ev[2].record()
+
+    for s in range(W):
+        step(s)
+    torch.cuda.synchronize()
+    # correctness gate on the last warm-up buffer: everything decodable, restored to the clean records
+    if W > 0:
+        last = bufs[(W - 1) % nbuf]
+        assert bool(ok.all().item()), "a correctable codeword failed to decode"
+        assert torch.equal(last, clean), "decoded records differ from the encoded records"
+
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    sampler = ClockSampler(local)
+    launches0 = h.launches
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    t_start = torch.cuda.Event(enable_timing=True)
+    t_stop = torch.cuda.Event(enable_timing=True)
+    t_start.record()
+    for s in range(K):
+        step(W + s, evs[s])
+    t_stop.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    if world > 1:
+        dist.barrier()
+    launches = h.launches - launches0
+    elapsed_ms = t_start.elapsed_time(t_stop)
+    enc_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / K
+    dec_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / K
+    tt = torch.tensor([elapsed_ms, enc_ms, dec_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    elapsed_ms, enc_ms, dec_ms = (float(x) for x in tt.tolist())
+    ms_per_step = elapsed_ms / K
+    payload_step = 2 * n * K_MSG * world
+    value = payload_step / (ms_per_step * 1e-3) / 1e9
+
+    # mean errors per codeword (algorithmic write bytes of the decode)
+    mean_err = float(cor.float().mean().item())
+    peak, peak_src = peaks()
+    enc_alg = n * (K_MSG + K_PAR)
+    dec_alg = n * (K_CW + 5 + mean_err)
+    if dec_ms >= enc_ms:
+        roof = {"kernel": "rs decode (screen + correction pipeline)", "bound": "hbm",
+                "achieved": dec_alg / (dec_ms * 1e-3) / 1e9, "bytes_per_codeword": dec_alg / n}
+    else:
+        roof = {"kernel": "rs encode", "bound": "hbm", "achieved": enc_alg / (enc_ms * 1e-3) / 1e9,
+                "bytes_per_codeword": enc_alg / n}
+    roof.update({"peak": peak, "unit": "GB/s", "frac": roof["achieved"] / peak, "traffic": None, "peak_source": peak_src})
+    phases = {"encode_ms": enc_ms, "decode_ms": dec_ms,
+              "encode_payload_GBps": n * K_MSG / (enc_ms * 1e-3) / 1e9,
+              "decode_payload_GBps": n * K_MSG / (dec_ms * 1e-3) / 1e9,
+              "encode_hbm_frac": enc_alg / (enc_ms * 1e-3) / 1e9 / peak,
+              "decode_hbm_frac": dec_alg / (dec_ms * 1e-3) / 1e9 / peak}
+
+    # ---- e2e: host-pointer API on page-locked buffers, copies inside the timed region -------------
+    e2e = None
+    if not args.no_e2e:
+        hmsg = torch.empty(n * K_MSG, dtype=torch.uint8).pin_memory()
+        hpar = torch.empty(n * K_PAR, dtype=torch.uint8).pin_memory()
+        hrec = torch.empty(rec_bytes, dtype=torch.uint8).pin_memory()
+        hok = torch.empty(n, dtype=torch.uint8).pin_memory()
+        hcor = torch.empty(n, dtype=torch.int32).pin_memory()
+        hmsg.view(n, K_MSG).copy_(clean.view(n, K_CW)[:, :K_MSG])
+        e2e_steps = max(1, args.e2e_steps)
+        tot = 0.0
+        for s in range(e2e_steps + 1):  # first pass is a warm-up (allocates the staging slots)
+            src = bufs[s % nbuf]
+            if not dirty[s % nbuf]:  # decoded in place during the timed loop: corrupt it again (untimed)
+                corrupt(s % nbuf)
+            hrec.copy_(src)
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            assert h.encode_batch(hmsg.data_ptr(), K_MSG, K_MSG, hpar.data_ptr(), K_PAR, n)
+            assert h.decode_batch(hrec.data_ptr(), K_CW, K_MSG, hrec.data_ptr() + K_MSG, K_CW, n, hok.data_ptr(),
+                                  hcor.data_ptr())
+            dt = time.perf_counter() - t0
+            if s > 0:
+                tot += dt
+        assert bool(hok.all().item())
+        assert torch.equal(hrec.view(n, K_CW)[:, K_MSG:], hpar.view(n, K_PAR)), "e2e parity mismatch"
+        tmax = torch.tensor([tot / e2e_steps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        e2e_s = float(tmax.item())
+        e2e = {"value": payload_step / e2e_s / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": n * (K_MSG + K_CW), "d2h_bytes_per_step": n * (K_PAR + K_CW + 5),
+               "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
+               "api": "poporon_encode_batch + poporon_decode_batch on page-locked host buffers"}
+
+    # ---- CPU baseline next to it (rank 0, N = 1 only) ------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        lib, kind = load_cpu_lib()
+        cores = os.cpu_count() or 1
+        sample = args.cpu_sample or min(n, cores * 20000)
+        rec = clean.view(n, K_CW)[:sample].cpu().numpy()
+        if not dirty[0]:
+            corrupt(0)
+        torch.cuda.synchronize()
+        badh = bufs[0].view(n, K_CW)[:sample].cpu().numpy()
+        t0 = time.perf_counter()
+        par = lib.rs_encode(np.ascontiguousarray(rec[:, :K_MSG]), threads=cores)
+        out = lib.rs_decode(np.ascontiguousarray(badh[:, :K_MSG]), np.ascontiguousarray(badh[:, K_MSG:]),
+                            threads=cores)
+        dt = time.perf_counter() - t0
+        assert (par == rec[:, K_MSG:]).all() and out[2].all() and (out[0] == rec[:, :K_MSG]).all(), \
+            "CPU baseline and GPU disagree on the sample"
+        cpu = {"value": 2 * sample * K_MSG / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": f"first {sample} codewords of the GPU batch (encode + decode), one handle per thread; "
+                         "outputs compared with the GPU's"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": workload_config(args, corrupted_buffers=nbuf, reinject_in_timed_region=reinject,
+                                      mean_errors_per_codeword=mean_err),
+            "roofline": roof, "phases": phases, "clocks": clocks, "gpu_launches": int(launches),
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

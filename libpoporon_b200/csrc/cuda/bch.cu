@@ -1,0 +1,245 @@
+// bch.cu — binary BCH(n <= 31) encode/decode kernels, one thread per codeword.
+//
+// The reference keeps the whole codeword in a uint32_t (src/bch.c:352-435) and wraps it in
+// big-endian byte packing (src/encode.c:199-234, src/decode.c:542-594).  A codeword is 1-4 data
+// bytes + 1-4 parity bytes, so these kernels are pure ALU work on registers; field tables sit in
+// shared memory (512 B per CTA).
+//
+// Decode mirrors the reference step by step so that miscorrections of > t errors and the
+// "found != L" / re-syndrome rejections come out identical:
+//   syndromes  src/bch.c:25-51     BM  src/bch.c:78-142    Chien  src/bch.c:144-166
+//   accept/reject rules  src/bch.c:403-426
+#include "common.cuh"
+#include "bch.cuh"
+
+namespace ppcu {
+
+namespace {
+
+constexpr int kArr = 64; // fixed work-array length of the reference (src/bch.c:12)
+
+struct BchParams {
+    int m, nn, n, k, parity_bits, t;
+    uint32_t gen;
+    int gen_deg;
+};
+
+struct BchSmem {
+    uint8_t alpha_to[256];
+    uint8_t index_of[256];
+};
+
+__device__ __forceinline__ void bch_load_tables(BchSmem &s, const uint8_t *g)
+{
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(g);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&s);
+    for (int i = threadIdx.x; i < 128; i += blockDim.x)
+        dst[i] = src[i];
+    __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t pack_be(const uint8_t *p, int nbytes)
+{
+    uint32_t v = 0;
+    for (int i = 0; i < nbytes && i < 4; i++)
+        v |= (uint32_t)p[i] << (8 * (nbytes - 1 - i));
+    return v;
+}
+
+__device__ __forceinline__ uint32_t low_mask(int bits)
+{
+    return bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
+}
+
+__global__ void __launch_bounds__(256)
+bch_encode_kernel(BchParams P, const uint8_t *__restrict__ data, size_t data_stride, size_t size,
+                  uint8_t *__restrict__ parity, size_t parity_stride, size_t n, uint8_t *__restrict__ ok)
+{
+    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cw >= n)
+        return;
+    const int db = (P.k + 7) / 8, pb = (P.parity_bits + 7) / 8;
+    bool good = false;
+    if (size >= (size_t)db) {
+        uint32_t d = pack_be(data + cw * data_stride, db) & low_mask(P.k);
+        // systematic encoding: remainder of d * x^p by g (src/bch.c:352-380)
+        const uint32_t shifted = d << P.parity_bits;
+        uint32_t rem = shifted;
+        for (int i = P.n - 1; i >= P.gen_deg; i--)
+            if (rem & (1u << i))
+                rem ^= P.gen << (i - P.gen_deg);
+        const uint32_t pv = (shifted ^ rem) & low_mask(P.parity_bits);
+        uint8_t *p = parity + cw * parity_stride;
+        for (int i = 0; i < pb; i++)
+            p[i] = 0;
+        for (int i = 0; i < pb && i < 4; i++)
+            p[pb - 1 - i] = (uint8_t)(pv >> (8 * i));
+        good = true;
+    }
+    if (ok)
+        ok[cw] = good ? 1 : 0;
+}
+
+__device__ bool bch_syndromes(const BchParams &P, const BchSmem &T, uint32_t w, uint8_t *s)
+{
+    bool any = false;
+    for (int i = 0; i < 2 * P.t; i++) {
+        uint8_t acc = 0;
+        uint32_t bits = w;
+        while (bits) {
+            const int j = __ffs(bits) - 1;
+            bits &= bits - 1;
+            acc ^= T.alpha_to[((i + 1) * j) % P.nn];
+        }
+        s[i] = acc;
+        any |= (acc != 0);
+    }
+    return any;
+}
+
+__device__ bool bch_decode_word(const BchParams &P, const BchSmem &T, uint32_t received, uint32_t &fixed_out,
+                                int &num_errors)
+{
+    uint8_t s[kArr], cur[kArr], prev[kArr], keep[kArr];
+    received &= low_mask(P.n);
+    fixed_out = received;
+    num_errors = 0;
+    for (int i = 0; i < kArr; i++)
+        s[i] = 0;
+    if (!bch_syndromes(P, T, received, s))
+        return true;
+
+    for (int i = 0; i < kArr; i++)
+        cur[i] = prev[i] = 0;
+    cur[0] = prev[0] = 1;
+    int L = 0, shift = 1;
+    uint8_t dprev = 1;
+    for (int it = 0; it < 2 * P.t; it++) {
+        uint8_t d = s[it];
+        for (int i = 1; i <= L; i++)
+            if (cur[i] != 0 && s[it - i] != 0)
+                d ^= T.alpha_to[(T.index_of[cur[i]] + T.index_of[s[it - i]]) % P.nn];
+        if (d == 0) {
+            shift++;
+            continue;
+        }
+        const uint8_t mult = T.alpha_to[(P.nn - T.index_of[dprev] + T.index_of[d]) % P.nn];
+        const bool grow = (2 * L <= it);
+        if (grow)
+            for (int i = 0; i < kArr; i++)
+                keep[i] = cur[i];
+        for (int i = 0; i < kArr - shift; i++)
+            if (prev[i] != 0)
+                cur[i + shift] ^= T.alpha_to[(T.index_of[prev[i]] + T.index_of[mult]) % P.nn];
+        if (grow) {
+            for (int i = 0; i < kArr; i++)
+                prev[i] = keep[i];
+            L = it + 1 - L;
+            dprev = d;
+            shift = 1;
+        } else {
+            shift++;
+        }
+    }
+    if (L > P.t)
+        return false;
+
+    uint32_t flips = 0;
+    int found = 0;
+    for (int i = 0; i < P.n; i++) {
+        // sigma evaluated at alpha^{-i}; position i is in error when it vanishes
+        const int lx = T.index_of[T.alpha_to[(P.nn - i) % P.nn]];
+        uint8_t acc = 0;
+        for (int j = 0; j <= L; j++)
+            if (cur[j] != 0)
+                acc ^= T.alpha_to[(T.index_of[cur[j]] + (lx * j) % P.nn) % P.nn];
+        if (acc == 0) {
+            flips ^= 1u << i;
+            if (++found >= L)
+                break;
+        }
+    }
+    if (found != L)
+        return false;
+    const uint32_t fixed = received ^ flips;
+    if (bch_syndromes(P, T, fixed, s))
+        return false;
+    fixed_out = fixed;
+    num_errors = found;
+    return true;
+}
+
+__global__ void __launch_bounds__(128)
+bch_decode_kernel(BchParams P, const uint8_t *__restrict__ gtab, uint8_t *data, size_t data_stride, size_t size,
+                  const uint8_t *__restrict__ parity, size_t parity_stride, size_t n, uint8_t *__restrict__ ok,
+                  uint32_t *__restrict__ corrected)
+{
+    __shared__ BchSmem T;
+    bch_load_tables(T, gtab);
+    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cw >= n)
+        return;
+    const int db = (P.k + 7) / 8, pb = (P.parity_bits + 7) / 8;
+    bool good = false;
+    uint32_t nc = 0;
+    if (size != 0 && size >= (size_t)db) {
+        uint8_t *d = data + cw * data_stride;
+        const uint32_t dv = pack_be(d, db) & low_mask(P.k);
+        const uint32_t pv = pack_be(parity + cw * parity_stride, pb) & low_mask(P.parity_bits);
+        uint32_t fixed;
+        int ne;
+        if (bch_decode_word(P, T, (dv << P.parity_bits) | pv, fixed, ne)) {
+            const uint32_t out = (fixed >> P.parity_bits) & low_mask(P.k);
+            for (int i = 0; i < db && i < 4; i++)
+                d[db - 1 - i] = (uint8_t)(out >> (8 * i));
+            nc = ne > 0 ? (uint32_t)ne : 0;
+            good = true;
+        }
+    }
+    if (ok)
+        ok[cw] = good ? 1 : 0;
+    if (corrected)
+        corrected[cw] = nc;
+}
+
+BchParams params_of(const poporon_cuda_bch *ctx)
+{
+    BchParams P;
+    P.m = ctx->m;
+    P.nn = ctx->nn;
+    P.n = ctx->n;
+    P.k = ctx->k;
+    P.parity_bits = ctx->parity_bits;
+    P.t = ctx->t;
+    P.gen = ctx->gen;
+    P.gen_deg = ctx->parity_bits;
+    return P;
+}
+
+} // namespace
+
+int launch_bch_encode(poporon_cuda_bch *ctx, const uint8_t *data, size_t data_stride, size_t size, uint8_t *parity,
+                      size_t parity_stride, size_t n, uint8_t *ok, cudaStream_t stream)
+{
+    if (n == 0)
+        return 0;
+    const int threads = 256;
+    bch_encode_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, stream>>>(
+        params_of(ctx), data, data_stride, size, parity, parity_stride, n, ok);
+    ctx->launches++;
+    return check(cudaGetLastError(), "bch_encode launch");
+}
+
+int launch_bch_decode(poporon_cuda_bch *ctx, uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
+                      size_t parity_stride, size_t n, uint8_t *ok, uint32_t *corrected, cudaStream_t stream)
+{
+    if (n == 0)
+        return 0;
+    const int threads = 128;
+    bch_decode_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, stream>>>(
+        params_of(ctx), ctx->d_tables, data, data_stride, size, parity, parity_stride, n, ok, corrected);
+    ctx->launches++;
+    return check(cudaGetLastError(), "bch_decode launch");
+}
+
+} // namespace ppcu

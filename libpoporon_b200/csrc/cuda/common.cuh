@@ -1,0 +1,86 @@
+// common.cuh — shared declarations of the libpoporon_cuda translation units.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "poporon_cuda.h"
+
+namespace ppcu {
+
+void set_error(const char *fmt, ...);
+int check(cudaError_t e, const char *what);
+
+#define PP_CUDA_TRY(expr)                                   \
+    do {                                                    \
+        int _rc = ::ppcu::check((expr), #expr);             \
+        if (_rc != 0)                                       \
+            return _rc;                                     \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess)
+            prev = -1;
+        ok = (prev == dev) || (cudaSetDevice(dev) == cudaSuccess);
+    }
+    ~DeviceGuard()
+    {
+        if (prev >= 0)
+            cudaSetDevice(prev);
+    }
+};
+
+// Field + code tables as the generic kernels see them (device global memory, copied to shared
+// memory by each CTA).  All entries fit a byte for m <= 8: the log of zero is nn <= 255.
+struct RsTables {
+    uint8_t alpha_to[256];
+    uint8_t index_of[256];
+    uint8_t genpoly[256]; // index form, nroots+1 entries
+};
+
+struct RsCode {
+    int m;
+    int nn;
+    int nroots;
+    uint16_t fcr, prim, iprim;
+};
+
+static inline int sm_count_of(int device)
+{
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess)
+        return 148;
+    return n;
+}
+
+} // namespace ppcu
+
+// Context layouts (opaque to C callers).
+struct poporon_cuda_rs {
+    int device;
+    int sm_count;
+    ppcu::RsCode code;
+    ppcu::RsTables *d_tables; // device copy
+    bool fast255;             // RS(255,223), 0x11D, fcr = 1, prim = 1: bitsliced kernels apply
+    bool force_generic;
+    uint64_t launches;
+    // scratch for the staged decode pipeline (grow-only, owned)
+    uint32_t *d_queue;        // dirty-codeword indices
+    uint8_t *d_rem;           // per-dirty-codeword remainder / syndromes
+    uint32_t *d_counters;     // [0] = dirty count
+    size_t queue_cap;
+};
+
+struct poporon_cuda_bch {
+    int device;
+    int sm_count;
+    int m, nn, n, k, parity_bits, t;
+    uint32_t gen;
+    uint8_t *d_tables; // alpha_to[256] | index_of[256]
+    uint64_t launches;
+};

@@ -1,0 +1,408 @@
+// poporon_cuda.cu — the extern "C" shim of libpoporon_cuda.so (see include/poporon_cuda.h).
+// Device/stream/memory helpers, context lifecycle and dispatch to the kernel families.
+#include "common.cuh"
+#include "bch.cuh"
+#include "rs_generic.cuh"
+#include "rs255.cuh"
+
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+namespace ppcu {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+int check(cudaError_t e, const char *what)
+{
+    if (e == cudaSuccess)
+        return POPORON_CUDA_OK;
+    set_error("%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+    if (e == cudaErrorMemoryAllocation)
+        return POPORON_CUDA_ERR_NOMEM;
+    return POPORON_CUDA_ERR_DEVICE;
+}
+
+} // namespace ppcu
+
+using namespace ppcu;
+
+#define GUARD(dev)                                                   \
+    DeviceGuard _guard(dev);                                         \
+    if (!_guard.ok)                                                  \
+    return check(cudaErrorInvalidDevice, "cudaSetDevice")
+
+extern "C" {
+
+const char *poporon_cuda_last_error(void)
+{
+    return g_err;
+}
+
+int poporon_cuda_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        check(e, "cudaGetDeviceCount");
+        (void)cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int poporon_cuda_device_sm_count(int device)
+{
+    int n = 0;
+    if (check(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device), "sm count") != 0)
+        return POPORON_CUDA_ERR_DEVICE;
+    return n;
+}
+
+int poporon_cuda_malloc(int device, size_t bytes, void **dptr)
+{
+    GUARD(device);
+    if (!dptr)
+        return POPORON_CUDA_ERR_ARG;
+    *dptr = nullptr;
+    if (bytes == 0)
+        return 0;
+    return check(cudaMalloc(dptr, bytes), "cudaMalloc");
+}
+
+int poporon_cuda_free(int device, void *dptr)
+{
+    GUARD(device);
+    return dptr ? check(cudaFree(dptr), "cudaFree") : 0;
+}
+
+int poporon_cuda_host_alloc(size_t bytes, void **hptr)
+{
+    if (!hptr)
+        return POPORON_CUDA_ERR_ARG;
+    *hptr = nullptr;
+    return check(cudaHostAlloc(hptr, bytes ? bytes : 1, cudaHostAllocPortable), "cudaHostAlloc");
+}
+
+int poporon_cuda_host_free(void *hptr)
+{
+    return hptr ? check(cudaFreeHost(hptr), "cudaFreeHost") : 0;
+}
+
+int poporon_cuda_stream_create(int device, void **stream)
+{
+    GUARD(device);
+    cudaStream_t s;
+    PP_CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *stream = (void *)s;
+    return 0;
+}
+
+int poporon_cuda_stream_destroy(int device, void *stream)
+{
+    GUARD(device);
+    return check(cudaStreamDestroy((cudaStream_t)stream), "cudaStreamDestroy");
+}
+
+int poporon_cuda_stream_sync(int device, void *stream)
+{
+    GUARD(device);
+    return check(cudaStreamSynchronize((cudaStream_t)stream), "cudaStreamSynchronize");
+}
+
+int poporon_cuda_memcpy_h2d(int device, void *dst, const void *src, size_t bytes, void *stream)
+{
+    GUARD(device);
+    if (bytes == 0)
+        return 0;
+    return check(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream), "memcpy h2d");
+}
+
+int poporon_cuda_memcpy_d2h(int device, void *dst, const void *src, size_t bytes, void *stream)
+{
+    GUARD(device);
+    if (bytes == 0)
+        return 0;
+    return check(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream), "memcpy d2h");
+}
+
+int poporon_cuda_memcpy2d_h2d(int device, void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
+                              size_t height, void *stream)
+{
+    GUARD(device);
+    if (width == 0 || height == 0)
+        return 0;
+    return check(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, cudaMemcpyHostToDevice,
+                                   (cudaStream_t)stream),
+                 "memcpy2d h2d");
+}
+
+int poporon_cuda_memcpy2d_d2h(int device, void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
+                              size_t height, void *stream)
+{
+    GUARD(device);
+    if (width == 0 || height == 0)
+        return 0;
+    return check(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, cudaMemcpyDeviceToHost,
+                                   (cudaStream_t)stream),
+                 "memcpy2d d2h");
+}
+
+int poporon_cuda_memset(int device, void *dst, int value, size_t bytes, void *stream)
+{
+    GUARD(device);
+    if (bytes == 0)
+        return 0;
+    return check(cudaMemsetAsync(dst, value, bytes, (cudaStream_t)stream), "memset");
+}
+
+int poporon_cuda_pointer_kind(const void *p, int *device)
+{
+    cudaPointerAttributes a;
+    cudaError_t e = cudaPointerGetAttributes(&a, p);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    if (device)
+        *device = a.device;
+    switch (a.type) {
+    case cudaMemoryTypeHost:
+        return 1;
+    case cudaMemoryTypeDevice:
+    case cudaMemoryTypeManaged:
+        return 2;
+    default:
+        return 0;
+    }
+}
+
+int poporon_cuda_event_create(int device, void **event)
+{
+    GUARD(device);
+    cudaEvent_t ev;
+    PP_CUDA_TRY(cudaEventCreate(&ev));
+    *event = (void *)ev;
+    return 0;
+}
+
+int poporon_cuda_event_destroy(int device, void *event)
+{
+    GUARD(device);
+    return check(cudaEventDestroy((cudaEvent_t)event), "cudaEventDestroy");
+}
+
+int poporon_cuda_event_record(int device, void *event, void *stream)
+{
+    GUARD(device);
+    return check(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream), "cudaEventRecord");
+}
+
+int poporon_cuda_event_elapsed_ms(int device, void *start, void *stop, float *ms)
+{
+    GUARD(device);
+    PP_CUDA_TRY(cudaEventSynchronize((cudaEvent_t)stop));
+    return check(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop), "cudaEventElapsedTime");
+}
+
+/* ------------------------------------------------------------------------------------------ RS */
+
+int poporon_cuda_rs_create(const poporon_cuda_rs_desc_t *d, int device, poporon_cuda_rs_t **out)
+{
+    if (!d || !out || !d->alpha_to || !d->index_of || !d->genpoly_index)
+        return POPORON_CUDA_ERR_ARG;
+    *out = nullptr;
+    if (d->symbol_size < 1 || d->symbol_size > 8 || d->nn != (1u << d->symbol_size) - 1u)
+        return POPORON_CUDA_ERR_UNSUPP;
+    if (d->nroots < 1 || d->nroots >= d->nn || d->prim == 0)
+        return POPORON_CUDA_ERR_UNSUPP;
+    GUARD(device);
+
+    RsTables h;
+    memset(&h, 0, sizeof h);
+    for (unsigned i = 0; i <= d->nn; i++) {
+        h.alpha_to[i] = (uint8_t)d->alpha_to[i];
+        h.index_of[i] = (uint8_t)d->index_of[i];
+    }
+    for (unsigned i = 0; i <= d->nroots; i++)
+        h.genpoly[i] = (uint8_t)d->genpoly_index[i];
+
+    poporon_cuda_rs *ctx = (poporon_cuda_rs *)calloc(1, sizeof *ctx);
+    if (!ctx)
+        return POPORON_CUDA_ERR_NOMEM;
+    ctx->device = device;
+    ctx->sm_count = sm_count_of(device);
+    ctx->code.m = d->symbol_size;
+    ctx->code.nn = d->nn;
+    ctx->code.nroots = d->nroots;
+    ctx->code.fcr = d->fcr;
+    ctx->code.prim = d->prim;
+    ctx->code.iprim = d->iprim;
+    ctx->fast255 = rs255_matches(d);
+    int rc = check(cudaMalloc((void **)&ctx->d_tables, sizeof h), "cudaMalloc tables");
+    if (rc == 0)
+        rc = check(cudaMemcpy(ctx->d_tables, &h, sizeof h, cudaMemcpyHostToDevice), "upload tables");
+    if (rc == 0 && ctx->fast255)
+        rc = rs255_init(ctx);
+    if (rc != 0) {
+        poporon_cuda_rs_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return 0;
+}
+
+void poporon_cuda_rs_destroy(poporon_cuda_rs_t *ctx)
+{
+    if (!ctx)
+        return;
+    DeviceGuard g(ctx->device);
+    cudaFree(ctx->d_tables);
+    cudaFree(ctx->d_queue);
+    cudaFree(ctx->d_rem);
+    cudaFree(ctx->d_counters);
+    free(ctx);
+}
+
+int poporon_cuda_rs_device(const poporon_cuda_rs_t *ctx)
+{
+    return ctx ? ctx->device : POPORON_CUDA_ERR_ARG;
+}
+
+void poporon_cuda_rs_force_generic(poporon_cuda_rs_t *ctx, int on)
+{
+    if (ctx)
+        ctx->force_generic = on != 0;
+}
+
+uint64_t poporon_cuda_rs_launch_count(const poporon_cuda_rs_t *ctx)
+{
+    return ctx ? ctx->launches : 0;
+}
+
+int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, size_t data_stride, size_t size, size_t parity_stride)
+{
+    if (!ctx)
+        return POPORON_CUDA_ERR_ARG;
+    return (ctx->fast255 && !ctx->force_generic && rs255_shape_ok(data_stride, size, parity_stride)) ? 1 : 0;
+}
+
+int poporon_cuda_rs_encode_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size_t data_stride, size_t size,
+                               uint8_t *parity, size_t parity_stride, size_t n, uint8_t *ok, void *stream)
+{
+    if (!ctx || (n && (!data || !parity)))
+        return POPORON_CUDA_ERR_ARG;
+    if (size >= 65536) /* the reference's loop counter is a uint16_t (src/encode.c:121) */
+        return POPORON_CUDA_ERR_UNSUPP;
+    GUARD(ctx->device);
+    if (poporon_cuda_rs_path(ctx, data_stride, size, parity_stride) == 1)
+        return rs255_encode(ctx, data, data_stride, size, parity, parity_stride, n, ok, (cudaStream_t)stream);
+    return launch_rs_encode_generic(ctx, data, data_stride, size, parity, parity_stride, n, ok, (cudaStream_t)stream);
+}
+
+int poporon_cuda_rs_decode_dev(poporon_cuda_rs_t *ctx, int mode, uint8_t *data, size_t data_stride, size_t size,
+                               uint8_t *parity, size_t parity_stride, size_t n, const uint32_t *pos,
+                               size_t pos_stride, const uint32_t *cnt, const uint16_t *syn, uint8_t *ok,
+                               uint32_t *corrected, void *stream)
+{
+    if (!ctx || (n && (!data || !parity)))
+        return POPORON_CUDA_ERR_ARG;
+    if (mode == POPORON_CUDA_MODE_ERASURE && n && (!pos || !cnt || pos_stride < (size_t)ctx->code.nroots))
+        return POPORON_CUDA_ERR_ARG;
+    if (mode == POPORON_CUDA_MODE_EXTSYN && n && !syn)
+        return POPORON_CUDA_ERR_ARG;
+    if (mode < 0 || mode > 2)
+        return POPORON_CUDA_ERR_ARG;
+    GUARD(ctx->device);
+    if (mode != POPORON_CUDA_MODE_EXTSYN && poporon_cuda_rs_path(ctx, data_stride, size, parity_stride) == 1)
+        return rs255_decode(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt, ok,
+                            corrected, (cudaStream_t)stream);
+    return launch_rs_decode_generic(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt,
+                                    syn, ok, corrected, (cudaStream_t)stream);
+}
+
+/* ------------------------------------------------------------------------------------------ BCH */
+
+int poporon_cuda_bch_create(const poporon_cuda_bch_desc_t *d, int device, poporon_cuda_bch_t **out)
+{
+    if (!d || !out || !d->alpha_to || !d->index_of)
+        return POPORON_CUDA_ERR_ARG;
+    *out = nullptr;
+    /* the reference's word arithmetic is only defined for n <= 31 (src/bch.c:39,396) */
+    if (d->symbol_size < 3 || d->symbol_size > 5 || d->n != (1u << d->symbol_size) - 1u || d->n > 31)
+        return POPORON_CUDA_ERR_UNSUPP;
+    if (d->t < 1 || d->t > 16 || d->parity_bits > d->n || d->k + d->parity_bits != d->n)
+        return POPORON_CUDA_ERR_UNSUPP;
+    GUARD(device);
+    uint8_t h[512];
+    memset(h, 0, sizeof h);
+    for (unsigned i = 0; i <= d->nn; i++) {
+        h[i] = (uint8_t)d->alpha_to[i];
+        h[256 + i] = (uint8_t)d->index_of[i];
+    }
+    poporon_cuda_bch *ctx = (poporon_cuda_bch *)calloc(1, sizeof *ctx);
+    if (!ctx)
+        return POPORON_CUDA_ERR_NOMEM;
+    ctx->device = device;
+    ctx->sm_count = sm_count_of(device);
+    ctx->m = d->symbol_size;
+    ctx->nn = d->nn;
+    ctx->n = d->n;
+    ctx->k = d->k;
+    ctx->parity_bits = d->parity_bits;
+    ctx->t = d->t;
+    ctx->gen = d->gen_poly;
+    int rc = check(cudaMalloc((void **)&ctx->d_tables, sizeof h), "cudaMalloc bch tables");
+    if (rc == 0)
+        rc = check(cudaMemcpy(ctx->d_tables, h, sizeof h, cudaMemcpyHostToDevice), "upload bch tables");
+    if (rc != 0) {
+        poporon_cuda_bch_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return 0;
+}
+
+void poporon_cuda_bch_destroy(poporon_cuda_bch_t *ctx)
+{
+    if (!ctx)
+        return;
+    DeviceGuard g(ctx->device);
+    cudaFree(ctx->d_tables);
+    free(ctx);
+}
+
+uint64_t poporon_cuda_bch_launch_count(const poporon_cuda_bch_t *ctx)
+{
+    return ctx ? ctx->launches : 0;
+}
+
+int poporon_cuda_bch_encode_dev(poporon_cuda_bch_t *ctx, const uint8_t *data, size_t data_stride, size_t size,
+                                uint8_t *parity, size_t parity_stride, size_t n, uint8_t *ok, void *stream)
+{
+    if (!ctx || (n && (!data || !parity)))
+        return POPORON_CUDA_ERR_ARG;
+    GUARD(ctx->device);
+    return launch_bch_encode(ctx, data, data_stride, size, parity, parity_stride, n, ok, (cudaStream_t)stream);
+}
+
+int poporon_cuda_bch_decode_dev(poporon_cuda_bch_t *ctx, uint8_t *data, size_t data_stride, size_t size,
+                                const uint8_t *parity, size_t parity_stride, size_t n, uint8_t *ok,
+                                uint32_t *corrected, void *stream)
+{
+    if (!ctx || (n && (!data || !parity)))
+        return POPORON_CUDA_ERR_ARG;
+    GUARD(ctx->device);
+    return launch_bch_decode(ctx, data, data_stride, size, parity, parity_stride, n, ok, corrected,
+                             (cudaStream_t)stream);
+}
+
+} /* extern "C" */

@@ -1,0 +1,371 @@
+// rs_generic.cu — table-driven Reed-Solomon kernels for ANY code the reference accepts
+// (GF(2^m), m <= 8, arbitrary primitive polynomial, fcr, prim, nroots, shortened sizes).
+//
+// One thread owns one codeword.  These kernels are the general-parameter path behind
+// poporon_cuda_rs_encode_dev / poporon_cuda_rs_decode_dev; the RS(255,223) default code takes the
+// bitsliced kernels in rs255_*.cu instead.  Log/antilog tables and the generator live in shared
+// memory (768 B per CTA); per-codeword polynomials live in thread-local arrays.
+//
+// Semantics follow the reference exactly, including its integer widths where they are observable
+// (paths relative to the reference tree):
+//   encoder ................. src/encode.c:120-144
+//   syndromes ............... src/decode.c:375-415
+//   locator init / BM ....... src/decode.c:31-96
+//   degree, Chien ........... src/decode.c:98-145
+//   omega, Forney ........... src/decode.c:147-191
+//   re-syndrome check ....... src/decode.c:193-209
+//   apply ................... src/decode.c:211-227
+//   glue / outcome table .... src/decode.c:418-487, 596-600   
+#include "common.cuh"
+#include "rs_generic.cuh"
+
+namespace ppcu {
+
+namespace {
+
+struct SmemTables {
+    uint8_t alpha_to[256];
+    uint8_t index_of[256];
+    uint8_t genpoly[256];
+};
+
+__device__ __forceinline__ void load_tables(SmemTables &s, const RsTables *g)
+{
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(g);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&s);
+    for (int i = threadIdx.x; i < (int)(sizeof(SmemTables) / 4); i += blockDim.x)
+        dst[i] = src[i];
+    __syncthreads();
+}
+
+// v mod nn for a 16-bit v (what the reference's fold loop computes, src/internal/common.h:102-110)
+__device__ __forceinline__ uint32_t redc(uint32_t v16, int nn)
+{
+    return (v16 & 0xFFFFu) % (uint32_t)nn;
+}
+
+template <int MAXR>
+__global__ void __launch_bounds__(128)
+rs_encode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, const uint8_t *__restrict__ data,
+                         size_t data_stride, size_t size, uint8_t *__restrict__ parity, size_t parity_stride,
+                         size_t n, uint8_t *__restrict__ ok)
+{
+    __shared__ SmemTables T;
+    load_tables(T, gtab);
+    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cw >= n)
+        return;
+    const int nr = c.nroots, nn = c.nn;
+    uint8_t ring[MAXR]; // circular LFSR state: logical p[j] = ring[(head + j) mod nr]
+    for (int j = 0; j < nr; j++)
+        ring[j] = 0;
+    int head = 0;
+    const uint8_t *d = data + cw * data_stride;
+    for (size_t i = 0; i < size; i++) {
+        const uint32_t fb = T.index_of[(d[i] & nn) ^ ring[head]];
+        if (fb != (uint32_t)nn) {
+            int pos = head;
+            for (int j = 1; j < nr; j++) {
+                pos = (pos + 1 == nr) ? 0 : pos + 1;
+                uint32_t e = fb + T.genpoly[nr - j];
+                e = e >= (uint32_t)nn ? e - nn : e;
+                ring[pos] ^= T.alpha_to[e];
+            }
+            uint32_t e0 = fb + T.genpoly[0];
+            e0 = e0 >= (uint32_t)nn ? e0 - nn : e0;
+            ring[head] = T.alpha_to[e0];
+        } else {
+            ring[head] = 0;
+        }
+        head = (head + 1 == nr) ? 0 : head + 1;
+    }
+    uint8_t *p = parity + cw * parity_stride;
+    for (int j = 0; j < nr; j++) {
+        int pos = head + j;
+        pos = pos >= nr ? pos - nr : pos;
+        p[j] = ring[pos];
+    }
+    if (ok)
+        ok[cw] = 1;
+}
+
+// The correction stage, shared by all three decode modes.  Returns the reference's bool and sets
+// ncorr when the reference would have set *errors_corrected.
+template <int MAXR>
+__device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, size_t size, uint8_t *parity,
+                           const uint8_t *syn /* index form */, uint32_t ecount, const uint32_t *epos,
+                           size_t pos_stride, bool erasure_apply, int16_t pad, uint32_t &ncorr)
+{
+    const int nr = c.nroots, nn = c.nn;
+    const uint8_t A0 = (uint8_t)nn;
+    uint8_t lambda[MAXR + 1], b[MAXR + 1], t[MAXR + 1], omega[MAXR + 1];
+    uint8_t root[MAXR + 1], loc[MAXR + 1], reg[MAXR + 1];
+
+    for (int i = 0; i <= nr; i++)
+        lambda[i] = 0;
+    lambda[0] = 1;
+    if (ecount > 0) {
+        lambda[1] = T.alpha_to[redc((uint32_t)c.prim * (uint32_t)(nn - 1 - (epos[0] + (uint32_t)(int32_t)pad)), nn)];
+        for (int i = 1; (uint32_t)i < ecount; i++) {
+            const uint32_t term =
+                redc((uint32_t)c.prim * (uint32_t)(nn - 1 - (epos[i] + (uint32_t)(int32_t)pad)), nn) & 0xFF;
+            for (int j = i + 1; j > 0; j--) {
+                const uint8_t lg = T.index_of[lambda[j - 1]];
+                if (lg != A0)
+                    lambda[j] ^= T.alpha_to[redc(term + lg, nn)];
+            }
+        }
+    }
+    for (int i = 0; i <= nr; i++)
+        b[i] = T.index_of[lambda[i]];
+
+    uint32_t r = ecount, el = ecount;
+    while (++r <= (uint32_t)nr) {
+        uint8_t disc = 0;
+        for (uint32_t i = 0; i < r; i++) {
+            const uint8_t s = syn[r - i - 1];
+            if (lambda[i] != 0 && s != A0)
+                disc ^= T.alpha_to[redc((uint32_t)T.index_of[lambda[i]] + s, nn)];
+        }
+        disc = T.index_of[disc];
+        if (disc == A0) {
+            for (int i = nr; i > 0; i--)
+                b[i] = b[i - 1];
+            b[0] = A0;
+        } else {
+            t[0] = lambda[0];
+            for (int i = 0; i < nr; i++)
+                t[i + 1] = (b[i] != A0) ? (uint8_t)(lambda[i + 1] ^ T.alpha_to[redc((uint32_t)disc + b[i], nn)])
+                                        : lambda[i + 1];
+            if (2 * el <= r + ecount - 1) {
+                el = r + ecount - el;
+                for (int i = 0; i <= nr; i++)
+                    b[i] = (lambda[i] == 0) ? A0
+                                            : (uint8_t)redc((uint32_t)T.index_of[lambda[i]] - disc + nn, nn);
+            } else {
+                for (int i = nr; i > 0; i--)
+                    b[i] = b[i - 1];
+                b[0] = A0;
+            }
+            for (int i = 0; i <= nr; i++)
+                lambda[i] = t[i];
+        }
+    }
+
+    int deg = 0;
+    for (int i = 0; i <= nr; i++) {
+        lambda[i] = T.index_of[lambda[i]];
+        if (lambda[i] != A0)
+            deg = i;
+    }
+    if (deg == 0)
+        return false;
+
+    for (int i = 1; i <= nr; i++)
+        reg[i] = lambda[i];
+    int count = 0;
+    {
+        int16_t k = (int16_t)(c.iprim - 1);
+        for (int i = 1; i <= nn; i++, k = (int16_t)redc((uint32_t)(int32_t)(k + c.iprim), nn)) {
+            uint8_t q = 1;
+            for (int j = deg; j > 0; j--) {
+                if (reg[j] != A0) {
+                    reg[j] = (uint8_t)redc((uint32_t)reg[j] + j, nn);
+                    q ^= T.alpha_to[reg[j]];
+                }
+            }
+            if (q != 0)
+                continue;
+            if (k < pad)
+                return false;
+            root[count] = (uint8_t)i;
+            loc[count] = (uint8_t)k;
+            if (++count == deg)
+                break;
+        }
+    }
+    if (deg != count)
+        return false;
+
+    for (int i = 0; i < deg; i++) {
+        uint8_t acc = 0;
+        for (int j = i; j >= 0; j--) {
+            if (syn[i - j] != A0 && lambda[j] != A0)
+                acc ^= T.alpha_to[redc((uint32_t)syn[i - j] + lambda[j], nn)];
+        }
+        omega[i] = T.index_of[acc];
+    }
+
+    ncorr = 0;
+    for (int j = count - 1; j >= 0; j--) {
+        uint8_t num1 = 0, den = 0;
+        for (int i = deg - 1; i >= 0; i--) {
+            if (omega[i] != A0)
+                num1 ^= T.alpha_to[redc((uint32_t)omega[i] + (uint32_t)(i * root[j]), nn)];
+        }
+        if (num1 == 0) {
+            b[j] = 0;
+            continue;
+        }
+        const uint8_t num2 = T.alpha_to[redc((uint32_t)root[j] * ((uint32_t)c.fcr - 1u) + (uint32_t)nn, nn)];
+        for (int i = (deg < nr - 1 ? deg : nr - 1) & ~1; i >= 0; i -= 2) {
+            if (lambda[i + 1] != A0)
+                den ^= T.alpha_to[redc((uint32_t)lambda[i + 1] + (uint32_t)(i * root[j]), nn)];
+        }
+        b[j] = T.alpha_to[redc((uint32_t)T.index_of[num1] + T.index_of[num2] + nn - T.index_of[den], nn)];
+        ncorr++;
+    }
+
+    for (int i = 0; i < nr; i++) {
+        uint8_t acc = 0;
+        for (int j = 0; j < count; j++) {
+            if (b[j] == 0)
+                continue;
+            // the reference forms this product in int, stores it to an int16_t and adds it back in int
+            // before truncating to 16 bits: only the low 16 bits of the sum survive, so wrap-around
+            // unsigned arithmetic gives the same value
+            const uint32_t k16 = (uint32_t)(c.fcr + i) * (uint32_t)c.prim * (uint32_t)(nn - loc[j] - 1);
+            acc ^= T.alpha_to[redc((uint32_t)T.index_of[b[j]] + k16, nn)];
+        }
+        if (acc != T.alpha_to[syn[i]])
+            return false;
+    }
+
+    if (erasure_apply) {
+        for (int i = 0; i < count; i++) {
+            // slot i of the caller's row, in Chien order (src/decode.c:211-214); slots past the row or
+            // positions past the message are outside the reference's defined behaviour and are skipped
+            if ((size_t)i < pos_stride) {
+                const uint32_t p = epos[i];
+                if (p < size)
+                    data[p] ^= b[i];
+            }
+        }
+    } else {
+        for (int i = 0; i < count; i++) {
+            const int32_t p = (int32_t)loc[i] - (int32_t)pad;
+            if (p >= 0 && p < (int32_t)size)
+                data[p] ^= b[i];
+            else if (p >= (int32_t)size && p < (int32_t)(size + nr))
+                parity[p - size] ^= b[i];
+            else
+                return false;
+        }
+    }
+    return true;
+}
+
+template <int MAXR>
+__global__ void __launch_bounds__(128)
+rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint8_t *data, size_t data_stride,
+                         size_t size, uint8_t *parity, size_t parity_stride, size_t n,
+                         const uint32_t *__restrict__ pos, size_t pos_stride, const uint32_t *__restrict__ cnt,
+                         const uint16_t *__restrict__ extsyn, uint8_t *__restrict__ ok,
+                         uint32_t *__restrict__ corrected)
+{
+    __shared__ SmemTables T;
+    load_tables(T, gtab);
+    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cw >= n)
+        return;
+    const int nr = c.nroots, nn = c.nn;
+    const uint8_t A0 = (uint8_t)nn;
+    uint8_t *d = data + cw * data_stride;
+    uint8_t *p = parity + cw * parity_stride;
+    uint8_t syn[MAXR + 1];
+    uint32_t ncorr = 0;
+    bool success = false;
+
+    const int16_t pad = (int16_t)(uint16_t)((size_t)nn - (size_t)nr - size); // src/decode.c:418-429
+    if (size != 0 && !(pad < 0 || pad >= (int16_t)(nn - nr))) {
+        if (mode == POPORON_CUDA_MODE_EXTSYN) {
+            bool dirty = false;
+            for (int i = 0; i < nr; i++) {
+                const uint16_t s = extsyn[cw * (size_t)nr + i];
+                // index-form values above nn cannot be produced by the reference's own tables; clamp
+                // them into the table (they would index out of bounds there)
+                syn[i] = (uint8_t)(s > (uint16_t)nn ? nn : s);
+                dirty |= (s != (uint16_t)nn);
+            }
+            success = !dirty || rs_correct<MAXR>(c, T, d, size, p, syn, 0, nullptr, 0, false, pad, ncorr);
+        } else {
+            // Horner over data || parity at the generator roots
+            const uint32_t first = d[0] & nn;
+            for (int i = 0; i < nr; i++)
+                syn[i] = (uint8_t)first;
+            const size_t total = size + (size_t)nr;
+            for (size_t j = 1; j < total; j++) {
+                const uint32_t sym = (j < size ? d[j] : p[j - size]) & nn;
+                for (int i = 0; i < nr; i++) {
+                    const uint8_t s = syn[i];
+                    syn[i] = (s == 0) ? (uint8_t)sym
+                                      : (uint8_t)(sym ^ T.alpha_to[redc((uint32_t)T.index_of[s] +
+                                                                            (uint32_t)(c.fcr + i) * (uint32_t)c.prim,
+                                                                        nn)]);
+                }
+            }
+            uint32_t any = 0;
+            for (int i = 0; i < nr; i++) {
+                any |= syn[i];
+                syn[i] = T.index_of[syn[i]];
+            }
+            if (!any) {
+                success = true;
+            } else if (mode == POPORON_CUDA_MODE_ERASURE) {
+                const uint32_t ec = cnt[cw];
+                if (ec <= (uint32_t)nr) // > nroots erasures overrun the reference's scratch: report failure
+                    success = rs_correct<MAXR>(c, T, d, size, p, syn, ec, pos + cw * pos_stride, pos_stride, true,
+                                               pad, ncorr);
+            } else {
+                success = rs_correct<MAXR>(c, T, d, size, p, syn, 0, nullptr, 0, false, pad, ncorr);
+            }
+        }
+    }
+    (void)A0;
+    if (ok)
+        ok[cw] = success ? 1 : 0;
+    if (corrected)
+        corrected[cw] = ncorr;
+}
+
+} // namespace
+
+int launch_rs_encode_generic(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, size_t size,
+                             uint8_t *parity, size_t parity_stride, size_t n, uint8_t *ok, cudaStream_t stream)
+{
+    if (n == 0)
+        return 0;
+    const int threads = 128;
+    const unsigned blocks = (unsigned)((n + threads - 1) / threads);
+    if (ctx->code.nroots <= 32)
+        rs_encode_generic_kernel<32><<<blocks, threads, 0, stream>>>(ctx->code, ctx->d_tables, data, data_stride, size,
+                                                                     parity, parity_stride, n, ok);
+    else
+        rs_encode_generic_kernel<255><<<blocks, threads, 0, stream>>>(ctx->code, ctx->d_tables, data, data_stride,
+                                                                      size, parity, parity_stride, n, ok);
+    ctx->launches++;
+    return check(cudaGetLastError(), "rs_encode_generic launch");
+}
+
+int launch_rs_decode_generic(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stride, size_t size,
+                             uint8_t *parity, size_t parity_stride, size_t n, const uint32_t *pos, size_t pos_stride,
+                             const uint32_t *cnt, const uint16_t *syn, uint8_t *ok, uint32_t *corrected,
+                             cudaStream_t stream)
+{
+    if (n == 0)
+        return 0;
+    const int threads = 128;
+    const unsigned blocks = (unsigned)((n + threads - 1) / threads);
+    if (ctx->code.nroots <= 32)
+        rs_decode_generic_kernel<32><<<blocks, threads, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride,
+                                                                     size, parity, parity_stride, n, pos, pos_stride,
+                                                                     cnt, syn, ok, corrected);
+    else
+        rs_decode_generic_kernel<255><<<blocks, threads, 0, stream>>>(ctx->code, ctx->d_tables, mode, data,
+                                                                      data_stride, size, parity, parity_stride, n, pos,
+                                                                      pos_stride, cnt, syn, ok, corrected);
+    ctx->launches++;
+    return check(cudaGetLastError(), "rs_decode_generic launch");
+}
+
+} // namespace ppcu

@@ -1,0 +1,490 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI (libpoporon.so -> libpoporon_cuda.so),
+against the CPU oracle (oracle/liboracle.so, the restatement pinned in test_oracle.py) and the committed
+golden fixtures.  Bar: bit-exact - corrected bytes, corrected_num and the success flag, including
+uncorrectable codewords and the reference's erasure-mode quirks.
+
+Nothing here reads /root/reference."""
+import ctypes as C
+
+import numpy as np
+import pytest
+from conftest import golden
+from oraclelib import MODE_ERASURE, MODE_EXTSYN, MODE_PLAIN, RS_DEFAULT
+from test_oracle import BCH_GOLDEN, RS_GOLDEN
+
+import libpoporon_b200.api as api
+
+pytestmark = pytest.mark.gpu
+
+
+def _rs(params, **kw):
+    m, poly, fcr, prim, nr = params
+    return api.Poporon.rs(m, poly, fcr, prim, nr, **kw)
+
+
+def _inject(rng, cw, nn, emax):
+    n, L = cw.shape
+    for i in range(n):
+        e = int(rng.integers(0, min(L, emax) + 1))
+        pos = rng.choice(L, e, replace=False)
+        cw[i, pos] ^= rng.integers(1, nn + 1, e, dtype=np.uint8)
+
+
+def _gpu_encode(h, msg, nr):
+    n, size = msg.shape
+    msg = np.ascontiguousarray(msg)
+    par = np.full((n, nr), 0xEE, np.uint8)
+    assert h.encode_batch(msg, size, size, par, nr, n)
+    return par
+
+
+def _gpu_decode(h, rx_d, rx_p, mode=MODE_PLAIN, pos=None, cnt=None, syn=None):
+    d = np.array(rx_d, np.uint8, order="C", copy=True)
+    p = np.array(rx_p, np.uint8, order="C", copy=True)
+    n, size = d.shape
+    ok = np.full(n, 7, np.uint8)
+    cor = np.full(n, 0xFFFFFFFF, np.uint32)
+    if mode == MODE_ERASURE:
+        pos = np.ascontiguousarray(pos, np.uint32)
+        cnt = np.ascontiguousarray(cnt, np.uint32)
+        assert h.decode_batch_erasure(d, size, size, p, p.shape[1], n, pos, pos.shape[1], cnt, ok, cor)
+    elif mode == MODE_EXTSYN:
+        syn = np.ascontiguousarray(syn, np.uint16)
+        assert h.decode_batch_syndrome(d, size, size, p, p.shape[1], n, syn, ok, cor)
+    else:
+        assert h.decode_batch(d, size, size, p, p.shape[1], n, ok, cor)
+    return d, p, ok, cor
+
+
+def _assert_same(got, want, tag=""):
+    names = ("data", "parity", "ok", "corrected")
+    for name, a, b in zip(names, got, want):
+        if not (a == b).all():
+            bad = np.nonzero((a != b).reshape(len(a), -1).any(1))[0]
+            raise AssertionError(f"{tag}: {name} differs at codewords {bad[:8]} ({len(bad)} total)")
+
+
+# ------------------------------------------------------------------------------------ golden fixtures
+@pytest.mark.parametrize("name", RS_GOLDEN)
+def test_rs_golden_fixture(gpu_device, name):
+    g = golden(name)
+    params = tuple(int(x) for x in g["params"])
+    mode = int(g["mode"])
+    with _rs(params) as h:
+        assert (_gpu_encode(h, g["msg"], params[4]) == g["parity"]).all()
+        kw = {}
+        if mode == MODE_ERASURE:
+            kw = dict(pos=g["pos"], cnt=g["cnt"])
+        if mode == MODE_EXTSYN:
+            kw = dict(syn=g["syn"])
+        got = _gpu_decode(h, g["rx_data"], g["rx_parity"], mode, **kw)
+        _assert_same(got, (g["out_data"], g["out_parity"], g["ok"], g["corrected"]), name)
+
+
+@pytest.mark.parametrize("name", BCH_GOLDEN)
+def test_bch_golden_fixture(gpu_device, name):
+    g = golden(name)
+    m, poly, t, n, k, p = (int(x) for x in g["params"])
+    with api.Poporon.bch(m, poly, t) as h:
+        assert h.info_size == (k + 7) // 8 and h.parity_size == (p + 7) // 8
+        pb = (p + 7) // 8
+        if "msg" in g:
+            msg = np.ascontiguousarray(g["msg"])
+            par = np.full((len(msg), pb), 0xEE, np.uint8)
+            assert h.encode_batch(msg, msg.shape[1], msg.shape[1], par, pb, len(msg))
+            assert (par == g["parity"]).all()
+        d = np.array(g["rx_data"], np.uint8, order="C", copy=True)
+        pp = np.ascontiguousarray(g["rx_parity"])
+        N = len(d)
+        ok = np.full(N, 7, np.uint8)
+        cor = np.full(N, 0xFFFFFFFF, np.uint32)
+        assert h.decode_batch(d, d.shape[1], d.shape[1], pp, pb, N, ok, cor)
+        assert (ok == g["ok"]).all() and (cor == g["corrected"]).all() and (d == g["out_data"]).all()
+        assert (pp == g["rx_parity"]).all()  # BCH decode never rewrites parity
+
+
+# ------------------------------------------------------------------------------------ oracle differential
+@pytest.mark.parametrize("size", [223, 222, 100, 64, 33, 2, 1])
+def test_rs_default_random_vs_oracle(gpu_device, orc, size):
+    rng = np.random.default_rng(1000 + size)
+    n = 6000 if size == 223 else 1500
+    msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        par = _gpu_encode(h, msg, 32)
+        assert (par == orc.rs_encode(msg)).all()
+        cw = np.concatenate([msg, par], 1)
+        _inject(rng, cw, 255, 20)
+        got = _gpu_decode(h, cw[:, :size], cw[:, size:])
+        _assert_same(got, orc.rs_decode(cw[:, :size], cw[:, size:]), f"size {size}")
+        assert h.launches > 0
+
+
+def test_rs_default_error_count_sweep(gpu_device, orc):
+    """exactly e errors for e = 0..20: corrected_num == e and data restored for e <= 16, failure above
+    (reference tests/test_codec.c:170-233)"""
+    rng = np.random.default_rng(7)
+    per = 200
+    msg = rng.integers(0, 256, (21 * per, 223), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        par = _gpu_encode(h, msg, 32)
+        cw = np.concatenate([msg, par], 1)
+        clean = cw.copy()
+        for i in range(len(cw)):
+            e = i // per
+            pos = rng.choice(255, e, replace=False)
+            cw[i, pos] ^= rng.integers(1, 256, e, dtype=np.uint8)
+        d, p, ok, cor = got = _gpu_decode(h, cw[:, :223], cw[:, 223:])
+        _assert_same(got, orc.rs_decode(cw[:, :223], cw[:, 223:]), "sweep")
+        for e in range(21):
+            sl = slice(e * per, (e + 1) * per)
+            if e <= 16:
+                assert ok[sl].all() and (cor[sl] == e).all()
+                assert (np.concatenate([d[sl], p[sl]], 1) == clean[sl]).all()
+            else:
+                assert not ok[sl].any() and (cor[sl] == 0).all()
+                assert (np.concatenate([d[sl], p[sl]], 1) == cw[sl]).all()
+
+
+def test_rs_default_erasures_vs_oracle(gpu_device, orc):
+    """sorted / unsorted rows, stale slots, zero magnitudes, extra unknown errors, 2v + c > 32"""
+    rng = np.random.default_rng(11)
+    n, size = 6000, 223
+    msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        par = _gpu_encode(h, msg, 32)
+        cw = np.concatenate([msg, par], 1)
+        pos = np.zeros((n, 32), np.uint32)
+        cnt = np.zeros(n, np.uint32)
+        for i in range(n):
+            c = int(rng.integers(0, 33))
+            pp = rng.choice(size, c, replace=False)
+            pos[i, :c] = np.sort(pp) if rng.random() < 0.7 else pp
+            cnt[i] = c
+            if rng.random() < 0.25:
+                pos[i, c:] = rng.integers(0, size, 32 - c)
+            cw[i, pp] ^= rng.integers(0, 256, c, dtype=np.uint8)
+            v = int(rng.choice([0, 0, 0, 0, 1, 2, 3]))
+            vp = rng.choice(255, v, replace=False)
+            cw[i, vp] ^= rng.integers(1, 256, v, dtype=np.uint8)
+        got = _gpu_decode(h, cw[:, :size], cw[:, size:], MODE_ERASURE, pos, cnt)
+        want = orc.rs_decode(cw[:, :size], cw[:, size:], RS_DEFAULT, MODE_ERASURE, pos, cnt)
+        _assert_same(got, want, "erasure")
+        assert (want[2] == 0).any() and ((want[2] == 0) & (want[3] != 0)).any()  # the A.5 corner is exercised
+
+
+def test_rs_default_extsyn_vs_oracle(gpu_device, orc):
+    rng = np.random.default_rng(13)
+    n, size = 3000, 223
+    msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        par = _gpu_encode(h, msg, 32)
+        syn = np.full((n, 32), 255, np.uint16)
+        for i in range(n):
+            if rng.random() < 0.7:
+                q = int(rng.integers(1, 33))
+                syn[i, rng.choice(32, q, replace=False)] = rng.integers(0, 255, q)
+        # a block of genuine single-error syndrome sets: error magnitude alpha^a at location L gives
+        # S_i = a + (1+i)*(254-L) in index form
+        for i in range(500):
+            L, a = int(rng.integers(0, 255)), int(rng.integers(0, 255))
+            syn[i] = (a + (1 + np.arange(32)) * (254 - L)) % 255
+        got = _gpu_decode(h, msg, par, MODE_EXTSYN, syn=syn)
+        _assert_same(got, orc.rs_decode(msg, par, RS_DEFAULT, MODE_EXTSYN, syn=syn), "extsyn")
+        assert got[2][:500].all() and (got[3][:500] == 1).all()
+
+
+@pytest.mark.parametrize("params", [(8, 0x187, 112, 11, 32), (8, 0x11D, 0, 1, 16), (8, 0x11D, 1, 2, 16),
+                                    (8, 0x11D, 1, 1, 127), (8, 0x11D, 2, 1, 4), (8, 0x11D, 1, 1, 10),
+                                    (4, 0x13, 1, 2, 8), (5, 0x25, 3, 3, 6), (7, 0x89, 1, 1, 20),
+                                    (8, 0x11D, 300, 7, 33), (8, 0x11D, 1, 1, 254), (3, 0xB, 1, 1, 2),
+                                    (8, 0x11D, 65535, 1, 8)])
+def test_rs_general_parameters_vs_oracle(gpu_device, orc, params):
+    m, _, _, _, nr = params
+    nn = (1 << m) - 1
+    K = nn - nr
+    rng = np.random.default_rng(hash(params) & 0xFFFF)
+    with _rs(params) as h:
+        assert h.parity_size == nr and h.info_size == K and h.fec_type == api.FEC_RS
+        for size in sorted({K, max(1, K // 2), 1}):
+            n = 500
+            msg = rng.integers(0, 256, (n, size), dtype=np.uint8)  # bits above m are masked by the codec
+            par = _gpu_encode(h, msg, nr)
+            assert (par == orc.rs_encode(msg, params)).all()
+            cw = np.concatenate([msg & nn, par], 1)
+            _inject(rng, cw, nn, nr // 2 + 3)
+            _assert_same(_gpu_decode(h, cw[:, :size], cw[:, size:]),
+                         orc.rs_decode(cw[:, :size], cw[:, size:], params), f"{params} size {size}")
+            W = max(32, nr)
+            pos = np.zeros((n, W), np.uint32)
+            cnt = np.zeros(n, np.uint32)
+            cw = np.concatenate([msg & nn, par], 1)
+            for i in range(n):
+                c = int(rng.integers(0, min(nr, size) + 1))
+                pp = rng.choice(size, c, replace=False)
+                pos[i, :c] = np.sort(pp) if rng.random() < 0.6 else pp
+                cnt[i] = c
+                cw[i, pp] ^= rng.integers(0, nn + 1, c, dtype=np.uint8)
+                v = int(rng.choice([0, 0, 1, 2]))
+                vp = rng.choice(size + nr, v, replace=False)
+                cw[i, vp] ^= rng.integers(1, nn + 1, v, dtype=np.uint8)
+            _assert_same(_gpu_decode(h, cw[:, :size], cw[:, size:], MODE_ERASURE, pos, cnt),
+                         orc.rs_decode(cw[:, :size], cw[:, size:], params, MODE_ERASURE, pos, cnt),
+                         f"{params} erasure size {size}")
+
+
+def test_rs_bad_sizes(gpu_device, orc):
+    with api.Poporon.rs_default() as h:
+        for size in (224, 230, 255, 300):
+            msg = np.arange(4 * size, dtype=np.uint32).astype(np.uint8).reshape(4, size)
+            par = _gpu_encode(h, msg, 32)  # encode does not validate the size
+            assert (par == orc.rs_encode(msg)).all()
+            d, p, ok, cor = _gpu_decode(h, msg, par)
+            assert not ok.any() and not cor.any() and (d == msg).all() and (p == par).all()
+
+
+def test_packed_records_and_gaps_roundtrip(gpu_device, orc):
+    """packed 255-byte records (parity = data + size) and a strided layout with gaps that must survive"""
+    rng = np.random.default_rng(21)
+    n = 3000
+    msg = rng.integers(0, 256, (n, 223), dtype=np.uint8)
+    want_par = orc.rs_encode(msg)
+    with api.Poporon.rs_default() as h:
+        rec = np.zeros((n, 255), np.uint8)
+        rec[:, :223] = msg
+        assert h.encode_batch(rec.ctypes.data, 255, 223, rec.ctypes.data + 223, 255, n)
+        assert (rec[:, 223:] == want_par).all() and (rec[:, :223] == msg).all()
+        _inject(rng, rec, 255, 18)
+        want = orc.rs_decode(rec[:, :223], rec[:, 223:])
+        ok = np.zeros(n, np.uint8)
+        cor = np.zeros(n, np.uint32)
+        assert h.decode_batch(rec.ctypes.data, 255, 223, rec.ctypes.data + 223, 255, n, ok, cor)
+        _assert_same((rec[:, :223], rec[:, 223:], ok, cor), want, "packed")
+        # strided with gaps: data stride 300, parity stride 40, gaps hold a canary
+        dbuf = np.full((n, 300), 0xC3, np.uint8)
+        pbuf = np.full((n, 40), 0x3C, np.uint8)
+        dbuf[:, :223] = msg
+        assert h.encode_batch(dbuf, 300, 223, pbuf, 40, n)
+        assert (pbuf[:, :32] == want_par).all() and (pbuf[:, 32:] == 0x3C).all() and (dbuf[:, 223:] == 0xC3).all()
+
+
+def test_device_pointer_path_matches_host_path(gpu_device, orc):
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(23)
+    n = 5000
+    msg = rng.integers(0, 256, (n, 223), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        rec = torch.zeros((n, 255), dtype=torch.uint8, device="cuda:0")
+        rec[:, :223] = torch.from_numpy(msg).cuda()
+        stream = torch.cuda.current_stream().cuda_stream
+        assert h.encode_batch_async(rec.data_ptr(), 255, 223, rec.data_ptr() + 223, 255, n, stream=stream)
+        torch.cuda.synchronize()
+        cw = rec.cpu().numpy()
+        assert (cw[:, 223:] == orc.rs_encode(msg)).all()
+        _inject(rng, cw, 255, 19)
+        rec.copy_(torch.from_numpy(cw))
+        ok = torch.full((n,), 9, dtype=torch.uint8, device="cuda:0")
+        cor = torch.full((n,), -1, dtype=torch.int32, device="cuda:0")
+        assert h.decode_batch_async(rec.data_ptr(), 255, 223, rec.data_ptr() + 223, 255, n, ok.data_ptr(),
+                                    cor.data_ptr(), stream=stream)
+        torch.cuda.synchronize()
+        out = rec.cpu().numpy()
+        want = orc.rs_decode(cw[:, :223], cw[:, 223:])
+        _assert_same((out[:, :223], out[:, 223:], ok.cpu().numpy(), cor.cpu().numpy().astype(np.uint32)), want, "dev")
+        # synchronous device-pointer form
+        rec.copy_(torch.from_numpy(cw))
+        assert h.decode_batch(rec.data_ptr(), 255, 223, rec.data_ptr() + 223, 255, n, ok.data_ptr(), cor.data_ptr())
+        assert (rec.cpu().numpy() == out).all()
+
+
+# ------------------------------------------------------------------------------------ single-instance API
+def test_config1_hello_reed_solomon(gpu_device):
+    """BASELINE config 1 / SURVEY B.2 through poporon_encode / poporon_decode"""
+    with api.Poporon.rs_default() as h:
+        assert h.fec_type == api.FEC_RS and h.parity_size == 32 and h.info_size == 223
+        data = np.zeros(64, np.uint8)
+        msg = b"Hello, Reed-Solomon!"
+        data[:len(msg)] = np.frombuffer(msg, np.uint8)
+        parity = np.zeros(32, np.uint8)
+        assert h.encode(data, parity)
+        assert parity.tobytes().hex() == "31e6a711c1fc30242fd40fa62307b796856794fff72ac6a79c6fb63e70086d5b"
+        rx = data.copy()
+        rx[0] ^= 0xFF
+        rx[10] ^= 0xAA
+        ok, cnt = h.decode(rx, parity)
+        assert ok and cnt == 2 and (rx == data).all()
+        ok, cnt = h.decode(rx, parity)
+        assert ok and cnt == 0
+        ok, _ = h.decode(rx, parity, want_count=False)  # corrected_num may be NULL
+        assert ok
+
+
+def test_single_api_null_and_size_rules(gpu_device):
+    """reference tests/test_codec.c:72-75,223-226 and SURVEY A.5 outcome table"""
+    with api.Poporon.rs_default() as h:
+        d = np.zeros(64, np.uint8)
+        p = np.zeros(32, np.uint8)
+        host = api.host
+        assert not host.poporon_encode(None, d.ctypes.data, 64, p.ctypes.data)
+        assert not host.poporon_encode(h.ptr, None, 64, p.ctypes.data)
+        assert not host.poporon_encode(h.ptr, d.ctypes.data, 64, None)
+        assert h.encode(d, p)
+        cnt = C.c_size_t(12345)
+        assert not host.poporon_decode(None, d.ctypes.data, 64, p.ctypes.data, C.byref(cnt))
+        assert not host.poporon_decode(h.ptr, None, 64, p.ctypes.data, C.byref(cnt))
+        assert not host.poporon_decode(h.ptr, d.ctypes.data, 64, None, C.byref(cnt))
+        assert not host.poporon_decode(h.ptr, d.ctypes.data, 0, p.ctypes.data, C.byref(cnt))
+        assert cnt.value == 12345  # untouched on NULL / size 0
+        big = np.zeros(224, np.uint8)
+        assert not host.poporon_decode(h.ptr, big.ctypes.data, 224, p.ctypes.data, C.byref(cnt))
+        assert cnt.value == 0  # bad size: false, corrected_num = 0
+        # 17 errors: failure, corrected_num = 0, buffers untouched
+        rng = np.random.default_rng(5)
+        d = rng.integers(0, 256, 223, dtype=np.uint8)
+        assert h.encode(d, p)
+        rx = d.copy()
+        rx[rng.choice(223, 17, replace=False)] ^= 0xFF
+        keep = rx.copy()
+        ok, c = h.decode(rx, p)
+        assert not ok and c == 0 and (rx == keep).all()
+
+
+def test_single_api_erasure_object(gpu_device, orc):
+    """reference tests/test_codec.c:123-168, tests/test_unified.c:82-112 and SURVEY B.6"""
+    er = api.Erasure(32, 16)
+    with api.Poporon.rs(erasure=er) as h:
+        rng = np.random.default_rng(9)
+        data = rng.integers(0, 256, 64, dtype=np.uint8)
+        parity = np.zeros(32, np.uint8)
+        assert h.encode(data, parity)
+        for count in (16, 20):
+            er.reset()
+            rx = data.copy()
+            for pos in rng.choice(64, count, replace=False):  # unsorted, constant magnitude like tests/util.h
+                rx[pos] ^= 0xFF
+                er.add(int(pos))
+            ok, c = h.decode(rx, parity)
+            assert ok and c == count and (rx == data).all()
+        # B.6 quirk: unsorted positions with distinct magnitudes
+        d3 = ((7 * np.arange(223) + 3) & 0xFF).astype(np.uint8)
+        p3 = np.zeros(32, np.uint8)
+        assert h.encode(d3, p3)
+        rx = d3.copy()
+        rx[200] ^= 1
+        rx[100] ^= 2
+        rx[3] ^= 3
+        er.reset()
+        for pos in (200, 100, 3):
+            er.add(pos)
+        ok, c = h.decode(rx, p3)
+        assert ok and c == 3
+        assert rx[3] ^ d3[3] == 2 and rx[100] ^ d3[100] == 0 and rx[200] ^ d3[200] == 2
+        # empty list + one unknown error: applied at slot 0's stale position (here 200)
+        rx = d3.copy()
+        rx[50] ^= 0x21
+        er.reset()
+        ok, c = h.decode(rx, p3)
+        pos = np.zeros((1, 32), np.uint32)
+        pos[0, :3] = [200, 100, 3]
+        bad = d3.copy()
+        bad[50] ^= 0x21
+        wd, wp, wok, wc = orc.rs_decode(bad[None], p3[None], RS_DEFAULT, MODE_ERASURE, pos, np.zeros(1, np.uint32))
+        assert ok == bool(wok[0]) and c == wc[0] and (rx == wd[0]).all()
+    er.close()
+
+
+def test_single_api_ext_syndrome(gpu_device):
+    """reference tests/test_codec.c:78-121: all-0xFF syndromes decode as clean"""
+    syn = np.full(32, 0xFF, np.uint16)
+    with api.Poporon.rs(syndrome=syn) as h:
+        data = np.arange(64, dtype=np.uint8)
+        parity = np.zeros(32, np.uint8)
+        assert h.encode(data, parity)
+        rx = data.copy()
+        ok, c = h.decode(rx, parity)
+        assert ok and c == 0 and (rx == data).all()
+        syn[:] = np.arange(254, 222, -1)  # single error of magnitude 1 at location 0 (padding for size 64)
+        ok, c = h.decode(rx, parity)
+        assert not ok and c == 0 and (rx == data).all()
+
+
+def test_bch_default_single_api(gpu_device):
+    """reference tests/test_unified.c:366-389 and SURVEY B.8"""
+    with api.Poporon.bch_default() as h:
+        assert h.fec_type == api.FEC_BCH and h.info_size == 1 and h.parity_size == 2
+        for dval, hexpar in [(0, "0000"), (7, "02b2"), (14, "0053"), (21, "0247"), (28, "00a6"), (0xF5, "0247")]:
+            d = np.array([dval], np.uint8)
+            p = np.zeros(2, np.uint8)
+            assert h.encode(d, p) and p.tobytes().hex() == hexpar and d[0] == dval
+        d = np.array([0x15], np.uint8)
+        p = np.zeros(2, np.uint8)
+        assert h.encode(d, p)
+        ok, c = h.decode(d, p)
+        assert ok and c == 0 and d[0] == 0x15
+        d[0] = 0xF5
+        ok, c = h.decode(d, p)
+        assert ok and c == 0 and d[0] == 0x15  # pad bits forced to zero even on the clean path
+        d[0] = 21 ^ 0x0A
+        ok, c = h.decode(d, p)
+        assert ok and c == 2 and d[0] == 21
+        bad_p = p.copy()
+        bad_p[1] ^= 0x07  # three parity-bit flips: corrected count 3, parity buffer left corrupted
+        ok, c = h.decode(d, bad_p)
+        assert ok and c == 3 and d[0] == 21 and (bad_p != p).any()
+        d[0] = 21 ^ 0x1F
+        ok, c = h.decode(d, p)
+        assert not ok and c is None and d[0] == 21 ^ 0x1F  # failure: data and corrected_num untouched
+
+
+def test_bch_word_level_api(gpu_device, orc):
+    """poporon_bch_encode/decode/extract_data as used by reference tests/test_bch.c:61-187,251-305"""
+    host = api.host
+    for (m, poly, t, datas) in [(4, 0x13, 3, [0, 7, 21, 31]), (5, 0x25, 2, [0, 1, 0x12345, 0x1FFFFF])]:
+        b = host.poporon_bch_create(m, poly, t)
+        n = host.poporon_bch_get_codeword_length(b)
+        k = host.poporon_bch_get_data_length(b)
+        for data in datas:
+            cw = C.c_uint32(0)
+            assert host.poporon_bch_encode(b, data, C.byref(cw))
+            fixed, ne = C.c_uint32(0), C.c_int32(-5)
+            assert host.poporon_bch_decode(b, cw.value, C.byref(fixed), C.byref(ne))
+            assert fixed.value == cw.value and ne.value == 0
+            assert host.poporon_bch_extract_data(b, fixed.value) == data
+            for bit in range(n):  # every single-bit error
+                assert host.poporon_bch_decode(b, cw.value ^ (1 << bit), C.byref(fixed), C.byref(ne))
+                assert fixed.value == cw.value and ne.value == 1
+            for b1 in range(0, n, 3):  # a spread of double-bit errors
+                for b2 in range(b1 + 1, n, 4):
+                    assert host.poporon_bch_decode(b, cw.value ^ (1 << b1) ^ (1 << b2), C.byref(fixed), C.byref(ne))
+                    assert fixed.value == cw.value and ne.value == 2
+        assert not host.poporon_bch_encode(b, 1 << k, C.byref(cw))  # data >= 2^k
+        host.poporon_bch_destroy(b)
+
+
+def test_unsupported_long_bch_reports_failure(gpu_device):
+    """n >= 63 is undefined in the reference: handles exist, codec calls report false"""
+    with api.Poporon.bch(6, 0x43, 2) as h:
+        d = np.zeros(8, np.uint8)
+        p = np.zeros(8, np.uint8)
+        assert not h.encode(d, p)
+        ok, _ = h.decode(d, p)
+        assert not ok
+
+
+def test_use_devices_and_large_host_batch(gpu_device, orc):
+    """host-pointer batch larger than one staging chunk, through the multi-lane planner"""
+    rng = np.random.default_rng(31)
+    n = 300_000
+    msg = rng.integers(0, 256, (n, 223), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        assert h.use_devices(None)  # all visible devices
+        par = _gpu_encode(h, msg, 32)
+        sample = rng.choice(n, 4000, replace=False)
+        assert (par[sample] == orc.rs_encode(msg[sample])).all()
+        cw = np.concatenate([msg, par], 1)
+        hit = rng.choice(n, 30_000, replace=False)
+        for i in hit[:3000]:
+            e = int(rng.integers(1, 17))
+            cw[i, rng.choice(255, e, replace=False)] ^= rng.integers(1, 256, e, dtype=np.uint8)
+        d, p, ok, cor = _gpu_decode(h, cw[:, :223], cw[:, 223:])
+        assert ok.all() and (d == msg).all() and (p == par).all()
+        assert int((cor > 0).sum()) == 3000
