@@ -117,9 +117,12 @@ int poporon_cuda_rs_create(const poporon_cuda_rs_desc_t *desc, int device, popor
 void poporon_cuda_rs_destroy(poporon_cuda_rs_t *ctx);
 int poporon_cuda_rs_device(const poporon_cuda_rs_t *ctx);
 
-/* Which kernel family a call with these arguments would take: 0 = generic table kernels,
- * 1 = RS(255,223)/0x11D bitsliced fast path.  Introspection for tests and the bench. */
-int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, size_t data_stride, size_t size, size_t parity_stride);
+/* Which kernel family a call with these arguments would take: 0 = general-parameter table kernels,
+ * 1 = RS(255,223)/0x11D bitsliced fast path (encode: any strides, data 16-byte aligned; decode: packed
+ * records, i.e. parity == data + size and equal strides, data 16-byte aligned).  op: 0 encode, 1 decode.
+ * Introspection for tests and the bench. */
+int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, int op, const uint8_t *data, size_t data_stride, size_t size,
+                         const uint8_t *parity, size_t parity_stride);
 /* Force the generic kernels even where the fast path applies (tests compare the two). */
 void poporon_cuda_rs_force_generic(poporon_cuda_rs_t *ctx, int on);
 

@@ -288,11 +288,14 @@ uint64_t poporon_cuda_rs_launch_count(const poporon_cuda_rs_t *ctx)
     return ctx ? ctx->launches : 0;
 }
 
-int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, size_t data_stride, size_t size, size_t parity_stride)
+int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, int op, const uint8_t *data, size_t data_stride, size_t size,
+                         const uint8_t *parity, size_t parity_stride)
 {
     if (!ctx)
         return POPORON_CUDA_ERR_ARG;
-    return (ctx->fast255 && !ctx->force_generic && rs255_shape_ok(data_stride, size, parity_stride)) ? 1 : 0;
+    return (ctx->fast255 && !ctx->force_generic && rs255_shape_ok(op, data, data_stride, size, parity, parity_stride))
+               ? 1
+               : 0;
 }
 
 int poporon_cuda_rs_encode_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size_t data_stride, size_t size,
@@ -303,7 +306,7 @@ int poporon_cuda_rs_encode_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size
     if (size >= 65536) /* the reference's loop counter is a uint16_t (src/encode.c:121) */
         return POPORON_CUDA_ERR_UNSUPP;
     GUARD(ctx->device);
-    if (poporon_cuda_rs_path(ctx, data_stride, size, parity_stride) == 1)
+    if (poporon_cuda_rs_path(ctx, 0, data, data_stride, size, parity, parity_stride) == 1)
         return rs255_encode(ctx, data, data_stride, size, parity, parity_stride, n, ok, (cudaStream_t)stream);
     return launch_rs_encode_generic(ctx, data, data_stride, size, parity, parity_stride, n, ok, (cudaStream_t)stream);
 }
@@ -322,7 +325,8 @@ int poporon_cuda_rs_decode_dev(poporon_cuda_rs_t *ctx, int mode, uint8_t *data, 
     if (mode < 0 || mode > 2)
         return POPORON_CUDA_ERR_ARG;
     GUARD(ctx->device);
-    if (mode != POPORON_CUDA_MODE_EXTSYN && poporon_cuda_rs_path(ctx, data_stride, size, parity_stride) == 1)
+    if (mode != POPORON_CUDA_MODE_EXTSYN && n < ((size_t)1 << 30) &&
+        poporon_cuda_rs_path(ctx, 1, data, data_stride, size, parity, parity_stride) == 1)
         return rs255_decode(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt, ok,
                             corrected, (cudaStream_t)stream);
     return launch_rs_decode_generic(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt,

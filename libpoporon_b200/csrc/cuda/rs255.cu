@@ -1,18 +1,615 @@
-// rs255.cu — placeholder until the bitsliced kernels land: reports "no fast path".
+// rs255.cu — bitsliced sm_100a kernels for the reference's default code RS(255,223), GF(2^8)/0x11D,
+// fcr = 1, prim = 1 (reference src/poporon.c:281-284).
+//
+// What replaces what (paths relative to the reference tree):
+//   rs_encode (src/encode.c:17-145) ............ rs255_lfsr_kernel<ENCODE>: systematic parity
+//   calculate_syndrome_u8 (src/decode.c:232-416)  rs255_lfsr_kernel<SCREEN>: "is the codeword clean" + the
+//                                                 32 syndromes of dirty codewords
+//   error_correction_u8 (src/decode.c:17-230) ... rs255_correct_kernel on a compacted queue of dirty
+//                                                 codewords (rs_correct.cuh)
+//
+// Data layout.  A bit-plane is one 32-bit register holding the same bit of the same symbol of 32
+// codewords.  A multiplication by a field CONSTANT is then an 8x8 GF(2) matrix = a fixed XOR network,
+// and the LFSR step "state <- state * x + fb * g" for 32 codewords costs one LOP3 (3-input XOR) per state
+// bit: every state bit is updated with a subset-XOR of the 8 feedback planes, looked up in two 16-entry
+// tables of 4-bit subset XORs that live in registers (the four-Russians trick; the subset is a
+// compile-time constant from gf256_consts.cuh).
+//
+// 256 state planes (32 parity symbols x 8 bits) exceed one thread's registers, so g(x) is split into two
+// degree-16 factors and each warp of a CTA (a "role") runs the LFSR of one factor on the same 1024
+// codewords (lane l owns codewords {tile*1024 + 32*i + l}).  See gf256_consts.cuh for the algebra.
+//
+// Memory.  Codeword streams are fetched with 16-byte cp.async into a 3-stage shared-memory ring
+// (one 16-byte chunk per codeword per stage) shared by the two roles, one round = 16 symbols ahead of
+// use; a lane's 32 codewords share the same byte alignment inside their chunks, so re-alignment is one
+// PRMT per word with a loop-invariant selector.  Bytes -> bit-planes is a 32x32 bit-matrix transpose in
+// registers (2 PRMT stages + 3 shift/LOP3 stages).
+//
+// The kernels are bound by the integer ALU pipe (LOP3/PRMT at 64 lanes/clk/SM measured, tools/ubench_pipes.cu),
+// not by HBM: DESIGN.md has the op count per symbol.
 #include "rs255.cuh"
 
+#include <utility>
+
+#include "gf256_consts.cuh"
+#include "rs_correct.cuh"
+
 namespace ppcu {
-bool rs255_matches(const poporon_cuda_rs_desc_t *) { return false; }
-bool rs255_shape_ok(size_t, size_t, size_t) { return false; }
-int rs255_init(poporon_cuda_rs *) { return 0; }
-int rs255_encode(poporon_cuda_rs *, const uint8_t *, size_t, size_t, uint8_t *, size_t, size_t, uint8_t *,
-                 cudaStream_t)
+
+namespace {
+
+constexpr int kMsg = 223, kPar = 32;
+constexpr int kTile = 1024;              // codewords per CTA tile
+constexpr int kRingBytes = 32 * 3 * 512; // [i = 32][stage = 3][lane = 32][16 B]
+
+enum { MODE_ENCODE = 0, MODE_SCREEN = 1 };
+
+template <int ROLE>
+struct Masks {
+    static constexpr gf256::LfsrMasks<ROLE> lfsr = gf256::make_lfsr_masks<ROLE>();
+};
+
+// encoder recombination: output half OH (parity bytes 16*OH .. 16*OH+15) from the state of role SRC
+template <int SRC>
+struct CrtM {
+    static constexpr gf256::CrtMasks<SRC> v = gf256::make_crt_masks<SRC>();
+};
+
+// syndrome map of a role: V_q = s(alpha^(1 + 16*ROLE + q)) = sum_k s[k] * alpha^(j*(15-k))
+template <int ROLE>
+struct SynM {
+    uint8_t m[16][16][8];
+};
+template <int ROLE>
+constexpr SynM<ROLE> make_synm()
 {
-    return POPORON_CUDA_ERR_UNSUPP;
+    SynM<ROLE> r{};
+    for (int k = 0; k < 16; k++)
+        for (int q = 0; q < 16; q++)
+            for (int t = 0; t < 8; t++)
+                r.m[k][q][t] = gf256::rowmask(gf256::pow_alpha((1 + 16 * ROLE + q) * (15 - k)), t);
+    return r;
 }
-int rs255_decode(poporon_cuda_rs *, int, uint8_t *, size_t, size_t, uint8_t *, size_t, size_t, const uint32_t *,
-                 size_t, const uint32_t *, uint8_t *, uint32_t *, cudaStream_t)
+template <int ROLE>
+struct SynMasks {
+    static constexpr SynM<ROLE> v = make_synm<ROLE>();
+};
+
+// ---------------------------------------------------------------------------------------------------
+// small device helpers
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
 {
-    return POPORON_CUDA_ERR_UNSUPP;
+    return (uint32_t)__cvta_generic_to_shared(p);
 }
+
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void *gaddr, uint32_t src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(saddr), "l"(gaddr), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit()
+{
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t saddr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(v) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t saddr, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(saddr), "r"(v) : "memory");
+}
+
+// 32x32 bit-matrix transpose in registers: x[r] bit c  <->  x[c] bit r.  An involution, used in both
+// directions (bytes -> planes on the way in, planes -> bytes on the way out).
+__device__ __forceinline__ void transpose32(uint32_t (&x)[32])
+{
+#pragma unroll
+    for (int r = 0; r < 16; r++) { // column bit 4 <-> row bit 4: half-word exchange
+        const uint32_t a = x[r], b = x[r + 16];
+        x[r] = __byte_perm(a, b, 0x5410);
+        x[r + 16] = __byte_perm(a, b, 0x7632);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) { // bit 3: byte exchange
+        if (r & 8)
+            continue;
+        const uint32_t a = x[r], b = x[r + 8];
+        x[r] = __byte_perm(a, b, 0x6240);
+        x[r + 8] = __byte_perm(a, b, 0x7351);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) { // bit 2: nibble exchange
+        if (r & 4)
+            continue;
+        const uint32_t a = x[r], b = x[r + 4];
+        x[r] = (a & 0x0F0F0F0Fu) | ((b << 4) & 0xF0F0F0F0u);
+        x[r + 4] = ((a >> 4) & 0x0F0F0F0Fu) | (b & 0xF0F0F0F0u);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) { // bit 1
+        if (r & 2)
+            continue;
+        const uint32_t a = x[r], b = x[r + 2];
+        x[r] = (a & 0x33333333u) | ((b << 2) & 0xCCCCCCCCu);
+        x[r + 2] = ((a >> 2) & 0x33333333u) | (b & 0xCCCCCCCCu);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) { // bit 0
+        if (r & 1)
+            continue;
+        const uint32_t a = x[r], b = x[r + 1];
+        x[r] = (a & 0x55555555u) | ((b << 1) & 0xAAAAAAAAu);
+        x[r + 1] = ((a >> 1) & 0x55555555u) | (b & 0xAAAAAAAAu);
+    }
+}
+
+// all 16 subset-XORs of four planes: T[s] = xor of b_k over the bits k set in s (11 XORs)
+__device__ __forceinline__ void subset_table(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3, uint32_t (&T)[16])
+{
+    T[0] = 0;
+    T[1] = b0;
+    T[2] = b1;
+    T[3] = b0 ^ b1;
+    T[4] = b2;
+    T[5] = b2 ^ b0;
+    T[6] = b2 ^ b1;
+    T[7] = b2 ^ T[3];
+    T[8] = b3;
+    T[9] = b3 ^ b0;
+    T[10] = b3 ^ b1;
+    T[11] = b3 ^ T[3];
+    T[12] = b3 ^ b2;
+    T[13] = T[12] ^ b0;
+    T[14] = T[12] ^ b1;
+    T[15] = T[12] ^ T[3];
+}
+
+// ---- one LFSR step for 32 codewords: 8 + 22 + 128 three-input XORs --------------------------------
+template <int ROLE, int JT>
+__device__ __forceinline__ void lfsr_update_one(uint32_t (&P)[16][8], const uint32_t (&T1)[16],
+                                                const uint32_t (&T2)[16])
+{
+    constexpr int J = JT >> 3, T = JT & 7;
+    constexpr unsigned m = Masks<ROLE>::lfsr.m[J][T];
+    if constexpr (J < 15)
+        P[J][T] = P[J + 1][T] ^ T1[m & 15] ^ T2[m >> 4];
+    else
+        P[J][T] = T1[m & 15] ^ T2[m >> 4];
+}
+
+template <int ROLE, int... JT>
+__device__ __forceinline__ void lfsr_update_all(uint32_t (&P)[16][8], const uint32_t (&T1)[16],
+                                                const uint32_t (&T2)[16], std::integer_sequence<int, JT...>)
+{
+    (lfsr_update_one<ROLE, JT>(P, T1, T2), ...);
+}
+
+template <int ROLE>
+__device__ __forceinline__ void lfsr_step(uint32_t (&P)[16][8], const uint32_t *d /* 8 planes of the symbol */)
+{
+    uint32_t T1[16], T2[16];
+    subset_table(d[0] ^ P[0][0], d[1] ^ P[0][1], d[2] ^ P[0][2], d[3] ^ P[0][3], T1);
+    subset_table(d[4] ^ P[0][4], d[5] ^ P[0][5], d[6] ^ P[0][6], d[7] ^ P[0][7], T2);
+    lfsr_update_all<ROLE>(P, T1, T2, std::make_integer_sequence<int, 128>{});
+}
+
+// ---- constant linear map on bit-planes: acc[q] ^= in * c[k][q] for 16 outputs ------------------------
+template <class M, int K, int OBASE, int QT>
+__device__ __forceinline__ void linmap_one(uint32_t (&acc)[16][8], const uint32_t (&T1)[16], const uint32_t (&T2)[16])
+{
+    constexpr int Q = QT >> 3, T = QT & 7;
+    constexpr unsigned m = M::v.m[K][OBASE + Q][T];
+    acc[Q][T] ^= T1[m & 15] ^ T2[m >> 4];
+}
+template <class M, int K, int OBASE, int... QT>
+__device__ __forceinline__ void linmap_all(uint32_t (&acc)[16][8], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
+                                           std::integer_sequence<int, QT...>)
+{
+    (linmap_one<M, K, OBASE, QT>(acc, T1, T2), ...);
+}
+// input symbol k of a 16-symbol vector stored in shared memory as [plane = 8k + t][lane] words
+template <class M, int OBASE, int K>
+__device__ __forceinline__ void linmap_k(uint32_t (&acc)[16][8], uint32_t sbase /* smem addr of plane 0, this lane */)
+{
+    uint32_t in[8], T1[16], T2[16];
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        in[t] = lds32(sbase + (uint32_t)((8 * K + t) * 128));
+    subset_table(in[0], in[1], in[2], in[3], T1);
+    subset_table(in[4], in[5], in[6], in[7], T2);
+    linmap_all<M, K, OBASE>(acc, T1, T2, std::make_integer_sequence<int, 128>{});
+}
+template <class M, int OBASE, int... K>
+__device__ __forceinline__ void linmap_vec(uint32_t (&acc)[16][8], uint32_t sbase, std::integer_sequence<int, K...>)
+{
+    (linmap_k<M, OBASE, K>(acc, sbase), ...);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// the LFSR kernel: one CTA = two warps (roles) x one tile of 1024 codewords at a time
+// ---------------------------------------------------------------------------------------------------
+struct LfsrArgs {
+    const uint8_t *stream; // first byte of codeword 0's stream (data for ENCODE, packed record for SCREEN)
+    size_t stride;         // bytes between consecutive codewords' streams
+    int len;               // symbols fed to the LFSR (size, or size + 32 for SCREEN)
+    size_t n;              // codewords
+    const uint8_t *gend;   // one past the last readable byte of the stream buffer
+    // ENCODE outputs
+    uint8_t *parity;
+    size_t parity_stride;
+    uint8_t *ok;
+    // SCREEN outputs
+    uint32_t *dmask; // [2 * groups]: per (group, role) 32-bit "state != 0" mask; group = tile*32 + lane
+    uint8_t *syn;    // [n][32]: raw evaluations V_q of the role's final state at its 16 roots
+};
+
+template <int MODE, int ROLE>
+__device__ __forceinline__ void lfsr_role(const LfsrArgs &A, uint8_t *ring)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t ring_s = smem_u32(ring);
+    const uint32_t lane_s = ring_s + (uint32_t)lane * 16u;
+    const size_t ntiles = (A.n + kTile - 1) / kTile;
+
+    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const size_t cw0 = tile * kTile + (size_t)lane;
+        const uint8_t *s0 = A.stream + cw0 * A.stride; // stream of (i = 0)
+        const uint32_t o = (uint32_t)((uintptr_t)s0 & 15u);
+        const uint8_t *a0 = s0 - o; // 16-byte aligned
+        const size_t istride = 32 * A.stride;
+        const int nchunks = (int)((o + (uint32_t)A.len + 15u) >> 4);
+        const int rounds = (A.len + 15) >> 4;
+        const uint32_t sel = 0x3210u + 0x1111u * (o & 3u); // PRMT selector re-aligning (lo, hi) words
+        const uint32_t wbase = o >> 2;
+
+        // this role fetches chunk `k` of its half of the codewords (i in [16*ROLE, 16*ROLE + 16))
+        auto fetch = [&](int k) {
+            if (k < nchunks) {
+                const uint32_t stage = (uint32_t)(k % 3);
+#pragma unroll
+                for (int ii = 0; ii < 16; ii++) {
+                    const int i = 16 * ROLE + ii;
+                    const uint8_t *g = a0 + (size_t)i * istride + (size_t)k * 16;
+                    uint32_t nbytes = 0;
+                    if (cw0 + 32 * (size_t)i < A.n && g < A.gend) {
+                        const size_t left = (size_t)(A.gend - g);
+                        nbytes = left >= 16 ? 16u : (uint32_t)left;
+                    }
+                    cp_async16(lane_s + (uint32_t)((i * 3 + stage) * 512), nbytes ? g : A.stream, nbytes);
+                }
+            }
+            cp_async_commit();
+        };
+
+        uint32_t P[16][8];
+#pragma unroll
+        for (int j = 0; j < 16; j++)
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                P[j][t] = 0;
+
+        __syncthreads(); // the previous tile's epilogue is done with the ring memory
+        fetch(0);
+        fetch(1);
+        for (int r = 0; r < rounds; r++) {
+            cp_async_wait_all();
+            __syncthreads(); // chunks <= r+1 of BOTH roles are visible; both roles are done with chunk r-1
+            fetch(r + 2);
+#pragma unroll 1
+            for (int win = 0; win < 4; win++) {
+                const int W = 4 * r + win;
+                if (4 * W >= A.len)
+                    break;
+                const uint32_t jlo = wbase + (uint32_t)W, jhi = jlo + 1;
+                const uint32_t off_lo = ((jlo >> 2) % 3u) * 512u + (jlo & 3u) * 4u;
+                const uint32_t off_hi = ((jhi >> 2) % 3u) * 512u + (jhi & 3u) * 4u;
+                uint32_t X[32];
+#pragma unroll
+                for (int i = 0; i < 32; i++) {
+                    const uint32_t lo = lds32(lane_s + (uint32_t)(i * 1536) + off_lo);
+                    const uint32_t hi = lds32(lane_s + (uint32_t)(i * 1536) + off_hi);
+                    X[i] = __byte_perm(lo, hi, sel);
+                }
+                transpose32(X); // X[8*y + t] = plane of bit t of symbol 4W + y
+#pragma unroll
+                for (int y = 0; y < 4; y++) {
+                    if (4 * W + y < A.len)
+                        lfsr_step<ROLE>(P, &X[8 * y]);
+                }
+            }
+        }
+        cp_async_wait_all();
+        __syncthreads(); // both roles finished reading the ring: it becomes epilogue scratch
+
+        // spill the state planes: [role][plane = 8j + t][lane]
+        const uint32_t st_s = ring_s + (uint32_t)(ROLE * 16384) + (uint32_t)lane * 4u;
+#pragma unroll
+        for (int j = 0; j < 16; j++)
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                sts32(st_s + (uint32_t)((8 * j + t) * 128), P[j][t]);
+
+        uint32_t acc[16][8];
+#pragma unroll
+        for (int q = 0; q < 16; q++)
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                acc[q][t] = 0;
+
+        if (MODE == MODE_ENCODE) {
+            __syncthreads(); // both states are in shared memory
+            // parity bytes [16*ROLE, 16*ROLE + 16) = (sA * FA + sB * FB) restricted to those coefficients
+            linmap_vec<CrtM<0>, 16 * ROLE>(acc, ring_s + (uint32_t)lane * 4u, std::make_integer_sequence<int, 16>{});
+            linmap_vec<CrtM<1>, 16 * ROLE>(acc, ring_s + 16384u + (uint32_t)lane * 4u,
+                                           std::make_integer_sequence<int, 16>{});
+        } else {
+            uint32_t nz = 0;
+#pragma unroll
+            for (int j = 0; j < 16; j++)
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    nz |= P[j][t];
+            A.dmask[2 * (tile * 32 + (size_t)lane) + ROLE] = nz;
+            if (!__any_sync(0xFFFFFFFFu, nz != 0))
+                continue; // every codeword of the tile is clean for this role: its 16 syndromes are zero
+            __syncwarp();
+            linmap_vec<SynMasks<ROLE>, 0>(acc, st_s, std::make_integer_sequence<int, 16>{});
+        }
+
+        // planes -> bytes: four 32x32 transposes give, for every codeword i, 16 output bytes as 4 words
+        uint32_t *flat = &acc[0][0];
+        uint32_t B[4][32];
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+#pragma unroll
+            for (int c = 0; c < 32; c++)
+                B[w][c] = flat[32 * w + c];
+            transpose32(B[w]);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+            const size_t cw = cw0 + 32 * (size_t)i;
+            if (cw >= A.n)
+                continue;
+            const uint4 v = make_uint4(B[0][i], B[1][i], B[2][i], B[3][i]);
+            if (MODE == MODE_ENCODE) {
+                uint8_t *p = A.parity + cw * A.parity_stride + 16 * ROLE;
+                if (((uintptr_t)p & 15u) == 0) {
+                    *reinterpret_cast<uint4 *>(p) = v;
+                } else if (((uintptr_t)p & 3u) == 0) {
+                    reinterpret_cast<uint32_t *>(p)[0] = v.x;
+                    reinterpret_cast<uint32_t *>(p)[1] = v.y;
+                    reinterpret_cast<uint32_t *>(p)[2] = v.z;
+                    reinterpret_cast<uint32_t *>(p)[3] = v.w;
+                } else {
+                    const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int b = 0; b < 16; b++)
+                        p[b] = (uint8_t)(w4[b >> 2] >> (8 * (b & 3)));
+                }
+                if (ROLE == 0 && A.ok)
+                    A.ok[cw] = 1;
+            } else {
+                *reinterpret_cast<uint4 *>(A.syn + cw * 32 + 16 * ROLE) = v;
+            }
+        }
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(64, 4) rs255_lfsr_kernel(LfsrArgs A)
+{
+    extern __shared__ __align__(16) uint8_t ring[];
+    if ((threadIdx.x >> 5) == 0)
+        lfsr_role<MODE, 0>(A, ring);
+    else
+        lfsr_role<MODE, 1>(A, ring);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// compaction: clean codewords get their status here and cost nothing further; dirty ones are queued
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+rs255_compact_kernel(const uint32_t *__restrict__ dmask, size_t n, uint32_t *__restrict__ queue,
+                     uint32_t *__restrict__ counter, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+{
+    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t flags = 0;
+    if (cw < n) {
+        const size_t tile = cw / kTile;
+        const uint32_t within = (uint32_t)(cw % kTile);
+        const uint32_t i = within >> 5, l = within & 31;
+        const uint2 m = reinterpret_cast<const uint2 *>(dmask)[tile * 32 + l];
+        flags = ((m.x >> i) & 1u) | (((m.y >> i) & 1u) << 1);
+        if (!flags) {
+            if (ok)
+                ok[cw] = 1;
+            if (corrected)
+                corrected[cw] = 0;
+        }
+    }
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, flags != 0);
+    if (ballot) {
+        const int lane = threadIdx.x & 31;
+        uint32_t base = 0;
+        if (lane == 0)
+            base = atomicAdd(counter, (uint32_t)__popc(ballot));
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (flags)
+            queue[base + __popc(ballot & ((1u << lane) - 1u))] = (uint32_t)cw | (flags << 30);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// correction of the queued codewords: one thread per dirty codeword (rs_correct.cuh)
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint8_t *data, size_t data_stride,
+                     size_t size, uint8_t *parity, size_t parity_stride, const uint32_t *__restrict__ queue,
+                     const uint32_t *__restrict__ counter, const uint8_t *__restrict__ syn_raw,
+                     const uint32_t *__restrict__ pos, size_t pos_stride, const uint32_t *__restrict__ cnt,
+                     uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+{
+    __shared__ SmemTables T;
+    load_tables(T, gtab);
+    const uint32_t total = *counter;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
+        const uint32_t entry = queue[q];
+        const size_t cw = entry & 0x3FFFFFFFu;
+        const uint32_t flags = entry >> 30;
+        uint8_t syn[33];
+        // raw[q'] = state(alpha^j) = c(alpha^j) * alpha^(16 j)  ->  S_j in index form
+        const uint4 *raw4 = reinterpret_cast<const uint4 *>(syn_raw + cw * 32);
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+            uint32_t w[4] = {0, 0, 0, 0};
+            if (flags & (1u << half)) {
+                const uint4 v = raw4[half];
+                w[0] = v.x, w[1] = v.y, w[2] = v.z, w[3] = v.w;
+            }
+#pragma unroll
+            for (int b = 0; b < 16; b++) {
+                const int j = 1 + 16 * half + b;
+                const uint32_t val = (w[b >> 2] >> (8 * (b & 3))) & 0xFFu;
+                uint32_t lg = T.index_of[val];
+                if (val != 0) {
+                    lg += 255u - (uint32_t)((16 * j) % 255);
+                    lg = lg >= 255u ? lg - 255u : lg;
+                }
+                syn[j - 1] = (uint8_t)lg;
+            }
+        }
+        uint8_t *d = data + cw * data_stride;
+        uint8_t *p = parity + cw * parity_stride;
+        const int16_t pad = (int16_t)(255 - 32 - (int)size);
+        uint32_t ncorr = 0;
+        bool success;
+        if (mode == POPORON_CUDA_MODE_ERASURE) {
+            const uint32_t ec = cnt[cw];
+            success = ec <= 32u && rs_correct<32>(c, T, d, size, p, syn, ec, pos + cw * pos_stride, pos_stride, true,
+                                                  pad, ncorr);
+        } else {
+            success = rs_correct<32>(c, T, d, size, p, syn, 0, nullptr, 0, false, pad, ncorr);
+        }
+        if (ok)
+            ok[cw] = success ? 1 : 0;
+        if (corrected)
+            corrected[cw] = ncorr;
+    }
+}
+
+int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
+{
+    if (n <= ctx->queue_cap)
+        return 0;
+    cudaFree(ctx->d_queue);
+    cudaFree(ctx->d_rem);
+    cudaFree(ctx->d_counters);
+    ctx->d_queue = nullptr;
+    ctx->d_rem = nullptr;
+    ctx->d_counters = nullptr;
+    ctx->queue_cap = 0;
+    const size_t tiles = (n + kTile - 1) / kTile;
+    // queue [n rounded up to 4] | dmask [tiles * 64]
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64) * sizeof(uint32_t)));
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32));
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, 64));
+    ctx->queue_cap = n;
+    return 0;
+}
+
+} // namespace
+
+bool rs255_matches(const poporon_cuda_rs_desc_t *d)
+{
+    return d->symbol_size == 8 && d->gfpoly == 0x11D && d->fcr == 1 && d->prim == 1 && d->nroots == 32;
+}
+
+bool rs255_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
+                    size_t parity_stride)
+{
+    // Any message size 1..223.  A lane's 32 codewords must be equally aligned inside their 16-byte chunks,
+    // which 32 * stride = 0 (mod 16) guarantees for every stride once the base is 16-byte aligned.
+    if (size < 1 || size > (size_t)kMsg || data_stride < size || ((uintptr_t)data & 15u) != 0)
+        return false;
+    if (op == 1) // the screen kernel reads ONE contiguous stream per codeword: packed records only
+        return parity == data + size && parity_stride == data_stride;
+    return true;
+}
+
+int rs255_init(poporon_cuda_rs *ctx)
+{
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_ENCODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kRingBytes));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kRingBytes));
+    (void)ctx;
+    return 0;
+}
+
+static unsigned lfsr_grid(const poporon_cuda_rs *ctx, size_t n)
+{
+    const size_t tiles = (n + kTile - 1) / kTile;
+    const size_t cap = (size_t)ctx->sm_count * 4; // 4 CTAs (8 warps) per SM, persistent over tiles
+    return (unsigned)(tiles < cap ? tiles : cap);
+}
+
+int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, size_t size, uint8_t *parity,
+                 size_t parity_stride, size_t n, uint8_t *ok, cudaStream_t stream)
+{
+    if (n == 0)
+        return 0;
+    LfsrArgs A{};
+    A.stream = data;
+    A.stride = data_stride;
+    A.len = (int)size;
+    A.n = n;
+    A.gend = data + (n - 1) * data_stride + size;
+    A.parity = parity;
+    A.parity_stride = parity_stride;
+    A.ok = ok;
+    rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64, kRingBytes, stream>>>(A);
+    ctx->launches++;
+    return check(cudaGetLastError(), "rs255 encode launch");
+}
+
+int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stride, size_t size, uint8_t *parity,
+                 size_t parity_stride, size_t n, const uint32_t *pos, size_t pos_stride, const uint32_t *cnt,
+                 uint8_t *ok, uint32_t *corrected, cudaStream_t stream)
+{
+    if (n == 0)
+        return 0;
+    int rc = ensure_scratch(ctx, n);
+    if (rc != 0)
+        return rc;
+    const size_t tiles = (n + kTile - 1) / kTile;
+    uint32_t *dmask = ctx->d_queue + ((n + 3) & ~(size_t)3);
+    PP_CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 64, stream));
+    LfsrArgs A{};
+    A.stream = data;
+    A.stride = data_stride;
+    A.len = (int)size + kPar;
+    A.n = n;
+    A.gend = data + (n - 1) * data_stride + size + kPar;
+    A.dmask = dmask;
+    A.syn = ctx->d_rem;
+    rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64, kRingBytes, stream>>>(A);
+    rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(dmask, n, ctx->d_queue,
+                                                                                    ctx->d_counters, ok, corrected);
+    const unsigned cblocks = (unsigned)ctx->sm_count * 8;
+    rs255_correct_kernel<<<cblocks, 128, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride, size, parity,
+                                                      parity_stride, ctx->d_queue, ctx->d_counters, ctx->d_rem, pos,
+                                                      pos_stride, cnt, ok, corrected);
+    ctx->launches += 3;
+    return check(cudaGetLastError(), "rs255 decode launch");
+}
+
 } // namespace ppcu

@@ -1,0 +1,204 @@
+// rs_correct.cuh — the per-codeword error/erasure correction stage (locator, Berlekamp-Massey, Chien,
+// Forney, re-syndrome verification, in-place apply) shared by the general-parameter decode kernel
+// (rs_generic.cu) and the RS(255,223) dirty-queue kernel (rs255.cu).  One thread owns one codeword.
+//
+// Semantics follow the reference exactly, including its integer widths where they are observable
+// (paths relative to the reference tree):
+//   locator init / BM ....... src/decode.c:31-96
+//   degree, Chien ........... src/decode.c:98-145
+//   omega, Forney ........... src/decode.c:147-191
+//   re-syndrome check ....... src/decode.c:193-209
+//   apply ................... src/decode.c:211-227        outcome table: SURVEY Appendix A.5
+#pragma once
+#include "common.cuh"
+
+namespace ppcu {
+
+struct SmemTables {
+    uint8_t alpha_to[256];
+    uint8_t index_of[256];
+    uint8_t genpoly[256];
+};
+
+__device__ __forceinline__ void load_tables(SmemTables &s, const RsTables *g)
+{
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(g);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&s);
+    for (int i = threadIdx.x; i < (int)(sizeof(SmemTables) / 4); i += blockDim.x)
+        dst[i] = src[i];
+    __syncthreads();
+}
+
+// v mod nn for a 16-bit v (what the reference's fold loop computes, src/internal/common.h:102-110)
+__device__ __forceinline__ uint32_t redc(uint32_t v16, int nn)
+{
+    return (v16 & 0xFFFFu) % (uint32_t)nn;
+}
+
+// The correction stage, shared by all three decode modes.  Returns the reference's bool and sets
+// ncorr when the reference would have set *errors_corrected.
+template <int MAXR>
+__device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, size_t size, uint8_t *parity,
+                           const uint8_t *syn /* index form */, uint32_t ecount, const uint32_t *epos,
+                           size_t pos_stride, bool erasure_apply, int16_t pad, uint32_t &ncorr)
+{
+    const int nr = c.nroots, nn = c.nn;
+    const uint8_t A0 = (uint8_t)nn;
+    uint8_t lambda[MAXR + 1], b[MAXR + 1], t[MAXR + 1], omega[MAXR + 1];
+    uint8_t root[MAXR + 1], loc[MAXR + 1], reg[MAXR + 1];
+
+    for (int i = 0; i <= nr; i++)
+        lambda[i] = 0;
+    lambda[0] = 1;
+    if (ecount > 0) {
+        lambda[1] = T.alpha_to[redc((uint32_t)c.prim * (uint32_t)(nn - 1 - (epos[0] + (uint32_t)(int32_t)pad)), nn)];
+        for (int i = 1; (uint32_t)i < ecount; i++) {
+            const uint32_t term =
+                redc((uint32_t)c.prim * (uint32_t)(nn - 1 - (epos[i] + (uint32_t)(int32_t)pad)), nn) & 0xFF;
+            for (int j = i + 1; j > 0; j--) {
+                const uint8_t lg = T.index_of[lambda[j - 1]];
+                if (lg != A0)
+                    lambda[j] ^= T.alpha_to[redc(term + lg, nn)];
+            }
+        }
+    }
+    for (int i = 0; i <= nr; i++)
+        b[i] = T.index_of[lambda[i]];
+
+    uint32_t r = ecount, el = ecount;
+    while (++r <= (uint32_t)nr) {
+        uint8_t disc = 0;
+        for (uint32_t i = 0; i < r; i++) {
+            const uint8_t s = syn[r - i - 1];
+            if (lambda[i] != 0 && s != A0)
+                disc ^= T.alpha_to[redc((uint32_t)T.index_of[lambda[i]] + s, nn)];
+        }
+        disc = T.index_of[disc];
+        if (disc == A0) {
+            for (int i = nr; i > 0; i--)
+                b[i] = b[i - 1];
+            b[0] = A0;
+        } else {
+            t[0] = lambda[0];
+            for (int i = 0; i < nr; i++)
+                t[i + 1] = (b[i] != A0) ? (uint8_t)(lambda[i + 1] ^ T.alpha_to[redc((uint32_t)disc + b[i], nn)])
+                                        : lambda[i + 1];
+            if (2 * el <= r + ecount - 1) {
+                el = r + ecount - el;
+                for (int i = 0; i <= nr; i++)
+                    b[i] = (lambda[i] == 0) ? A0
+                                            : (uint8_t)redc((uint32_t)T.index_of[lambda[i]] - disc + nn, nn);
+            } else {
+                for (int i = nr; i > 0; i--)
+                    b[i] = b[i - 1];
+                b[0] = A0;
+            }
+            for (int i = 0; i <= nr; i++)
+                lambda[i] = t[i];
+        }
+    }
+
+    int deg = 0;
+    for (int i = 0; i <= nr; i++) {
+        lambda[i] = T.index_of[lambda[i]];
+        if (lambda[i] != A0)
+            deg = i;
+    }
+    if (deg == 0)
+        return false;
+
+    for (int i = 1; i <= nr; i++)
+        reg[i] = lambda[i];
+    int count = 0;
+    {
+        int16_t k = (int16_t)(c.iprim - 1);
+        for (int i = 1; i <= nn; i++, k = (int16_t)redc((uint32_t)(int32_t)(k + c.iprim), nn)) {
+            uint8_t q = 1;
+            for (int j = deg; j > 0; j--) {
+                if (reg[j] != A0) {
+                    reg[j] = (uint8_t)redc((uint32_t)reg[j] + j, nn);
+                    q ^= T.alpha_to[reg[j]];
+                }
+            }
+            if (q != 0)
+                continue;
+            if (k < pad)
+                return false;
+            root[count] = (uint8_t)i;
+            loc[count] = (uint8_t)k;
+            if (++count == deg)
+                break;
+        }
+    }
+    if (deg != count)
+        return false;
+
+    for (int i = 0; i < deg; i++) {
+        uint8_t acc = 0;
+        for (int j = i; j >= 0; j--) {
+            if (syn[i - j] != A0 && lambda[j] != A0)
+                acc ^= T.alpha_to[redc((uint32_t)syn[i - j] + lambda[j], nn)];
+        }
+        omega[i] = T.index_of[acc];
+    }
+
+    ncorr = 0;
+    for (int j = count - 1; j >= 0; j--) {
+        uint8_t num1 = 0, den = 0;
+        for (int i = deg - 1; i >= 0; i--) {
+            if (omega[i] != A0)
+                num1 ^= T.alpha_to[redc((uint32_t)omega[i] + (uint32_t)(i * root[j]), nn)];
+        }
+        if (num1 == 0) {
+            b[j] = 0;
+            continue;
+        }
+        const uint8_t num2 = T.alpha_to[redc((uint32_t)root[j] * ((uint32_t)c.fcr - 1u) + (uint32_t)nn, nn)];
+        for (int i = (deg < nr - 1 ? deg : nr - 1) & ~1; i >= 0; i -= 2) {
+            if (lambda[i + 1] != A0)
+                den ^= T.alpha_to[redc((uint32_t)lambda[i + 1] + (uint32_t)(i * root[j]), nn)];
+        }
+        b[j] = T.alpha_to[redc((uint32_t)T.index_of[num1] + T.index_of[num2] + nn - T.index_of[den], nn)];
+        ncorr++;
+    }
+
+    for (int i = 0; i < nr; i++) {
+        uint8_t acc = 0;
+        for (int j = 0; j < count; j++) {
+            if (b[j] == 0)
+                continue;
+            // the reference forms this product in int, stores it to an int16_t and adds it back in int
+            // before truncating to 16 bits: only the low 16 bits of the sum survive, so wrap-around
+            // unsigned arithmetic gives the same value
+            const uint32_t k16 = (uint32_t)(c.fcr + i) * (uint32_t)c.prim * (uint32_t)(nn - loc[j] - 1);
+            acc ^= T.alpha_to[redc((uint32_t)T.index_of[b[j]] + k16, nn)];
+        }
+        if (acc != T.alpha_to[syn[i]])
+            return false;
+    }
+
+    if (erasure_apply) {
+        for (int i = 0; i < count; i++) {
+            // slot i of the caller's row, in Chien order (src/decode.c:211-214); slots past the row or
+            // positions past the message are outside the reference's defined behaviour and are skipped
+            if ((size_t)i < pos_stride) {
+                const uint32_t p = epos[i];
+                if (p < size)
+                    data[p] ^= b[i];
+            }
+        }
+    } else {
+        for (int i = 0; i < count; i++) {
+            const int32_t p = (int32_t)loc[i] - (int32_t)pad;
+            if (p >= 0 && p < (int32_t)size)
+                data[p] ^= b[i];
+            else if (p >= (int32_t)size && p < (int32_t)(size + nr))
+                parity[p - size] ^= b[i];
+            else
+                return false;
+        }
+    }
+    return true;
+}
+
+} // namespace ppcu

@@ -53,6 +53,21 @@ def _gpu_decode(h, rx_d, rx_p, mode=MODE_PLAIN, pos=None, cnt=None, syn=None):
         assert h.decode_batch_syndrome(d, size, size, p, p.shape[1], n, syn, ok, cor)
     else:
         assert h.decode_batch(d, size, size, p, p.shape[1], n, ok, cor)
+    if mode != MODE_EXTSYN:
+        # the same batch as packed records (message immediately followed by parity): for the default code this
+        # takes the bitsliced fast path, the split layout above takes the general-parameter kernels
+        nr = p.shape[1]
+        rec = np.ascontiguousarray(np.concatenate([np.asarray(rx_d, np.uint8), np.asarray(rx_p, np.uint8)], 1))
+        ok2 = np.full(n, 7, np.uint8)
+        cor2 = np.full(n, 0xFFFFFFFF, np.uint32)
+        st = size + nr
+        if mode == MODE_ERASURE:
+            assert h.decode_batch_erasure(rec.ctypes.data, st, size, rec.ctypes.data + size, st, n, pos, pos.shape[1],
+                                          cnt, ok2, cor2)
+        else:
+            assert h.decode_batch(rec.ctypes.data, st, size, rec.ctypes.data + size, st, n, ok2, cor2)
+        assert (ok2 == ok).all() and (cor2 == cor).all(), "packed and split layouts disagree (status)"
+        assert (rec[:, :size] == d).all() and (rec[:, size:] == p).all(), "packed and split layouts disagree (bytes)"
     return d, p, ok, cor
 
 
@@ -169,7 +184,22 @@ def test_rs_default_erasures_vs_oracle(gpu_device, orc):
         got = _gpu_decode(h, cw[:, :size], cw[:, size:], MODE_ERASURE, pos, cnt)
         want = orc.rs_decode(cw[:, :size], cw[:, size:], RS_DEFAULT, MODE_ERASURE, pos, cnt)
         _assert_same(got, want, "erasure")
-        assert (want[2] == 0).any() and ((want[2] == 0) & (want[3] != 0)).any()  # the A.5 corner is exercised
+        assert (want[2] == 0).any()
+        # the "false with corrected_num != 0" corner of SURVEY A.5: 28 sorted erasures + 3 unknown errors
+        m2 = 4000
+        cw2 = np.concatenate([msg[:m2], par[:m2]], 1)
+        pos2 = np.zeros((m2, 32), np.uint32)
+        for i in range(m2):
+            pp = np.sort(rng.choice(size, 28, replace=False))
+            pos2[i, :28] = pp
+            cw2[i, pp] ^= rng.integers(0, 256, 28, dtype=np.uint8)
+            vp = rng.choice(255, 3, replace=False)
+            cw2[i, vp] ^= rng.integers(1, 256, 3, dtype=np.uint8)
+        cnt2 = np.full(m2, 28, np.uint32)
+        got2 = _gpu_decode(h, cw2[:, :size], cw2[:, size:], MODE_ERASURE, pos2, cnt2)
+        want2 = orc.rs_decode(cw2[:, :size], cw2[:, size:], RS_DEFAULT, MODE_ERASURE, pos2, cnt2)
+        _assert_same(got2, want2, "erasure 28+3")
+        assert ((want2[2] == 0) & (want2[3] != 0)).any()
 
 
 def test_rs_default_extsyn_vs_oracle(gpu_device, orc):
