@@ -33,6 +33,7 @@
 
 #include "gf256_consts.cuh"
 #include "rs_correct.cuh"
+#include "rs255_solve_core.h"
 
 namespace ppcu {
 
@@ -506,6 +507,114 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// bitsliced solver for the queued codewords (plain mode): rs255_solve_core.h, one warp per CTA, each lane
+// owns 32 queue entries (slot c of lane l = entry 1024*group + 32*c + l).  Shared memory per lane:
+// 256 words of syndromes (later the per-codeword root lists) + 136 words of BM scratch (later the
+// evaluator terms and root counters), word-interleaved over the lanes (bank = lane: conflict-free).
+// Codewords the solver declines (register length > 16 or a vanishing leading coefficient - uncorrectable
+// words only) are appended to a second queue for the literal per-codeword stage.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kSolveWords = bs::kWordsS + bs::kWordsB;
+constexpr int kSolveSmem = kSolveWords * 128;
+
+template <int W>
+__device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], const uint8_t *__restrict__ syn_raw,
+                                                     const bs::Mem<32> S)
+{
+    if constexpr (W < 8) {
+        uint32_t X[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++) {
+            const uint32_t e = ent[c];
+            // a half whose LFSR state was zero has no row written by the screen kernel: its 16 values are 0
+            const bool live = e != 0xFFFFFFFFu && ((e >> (30 + (W >> 2))) & 1u);
+            X[c] = live ? __ldg(reinterpret_cast<const uint32_t *>(syn_raw) + (size_t)(e & 0x3FFFFFFFu) * 8 + W) : 0u;
+        }
+        transpose32(X); // X[8*y + t] = plane t of raw byte 4W + y = state(alpha^j), j = 1 + 4W + y
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            // S_j = state(alpha^j) * alpha^(-16 j)
+            uint32_t(&in)[8] = *reinterpret_cast<uint32_t(*)[8]>(&X[8 * y]);
+            uint32_t s[8];
+            if (y == 0) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 0))>(in, s);
+            if (y == 1) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 1))>(in, s);
+            if (y == 2) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 2))>(in, s);
+            if (y == 3) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 3))>(in, s);
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                S.st(8 * (4 * W + y) + t, s[t]);
+        }
+        solve_load_syndromes<W + 1>(ent, syn_raw, S);
+    }
+}
+
+__global__ void __launch_bounds__(32, 4)
+rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *parity, size_t parity_stride,
+                   const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+                   const uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2,
+                   uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+{
+    extern __shared__ __align__(16) uint32_t solve_smem[];
+    const int lane = threadIdx.x;
+    const bs::Mem<32> S{solve_smem + lane};
+    const bs::Mem<32> B{solve_smem + bs::kWordsS * 32 + lane};
+    const uint32_t total = *counter;
+    const int pad = kMsg - (int)size;
+
+    for (uint32_t g0 = blockIdx.x * 1024u; g0 < total; g0 += gridDim.x * 1024u) {
+        {
+            uint32_t ent[32];
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+                const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
+                ent[c] = q < total ? queue[q] : 0xFFFFFFFFu;
+            }
+            solve_load_syndromes<0>(ent, syn_raw, S);
+        }
+        bs::LaneOut out;
+        bs::solve_lane<32>(S, B, pad, out);
+
+#pragma unroll 1
+        for (int c = 0; c < 32; c++) {
+            const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
+            if (q >= total)
+                continue;
+            const uint32_t entry = queue[q];
+            const size_t cw = entry & 0x3FFFFFFFu;
+            int nroots = 0;
+            const int st = bs::classify<32>(B, out, c, nroots);
+            if (st == bs::kDeclined) {
+                queue2[atomicAdd(counter2, 1u)] = entry;
+                continue;
+            }
+            uint32_t nnz = 0;
+            if (st == bs::kOk) {
+                uint8_t *d = data + cw * data_stride;
+                uint8_t *p = parity + cw * parity_stride;
+                for (int e = 0; e < nroots; e++) {
+                    const uint32_t v = (S.ld(8 * c + (e >> 1)) >> (16 * (e & 1))) & 0xFFFFu;
+                    const uint32_t mag = v >> 8;
+                    const int pos = (int)(v & 0xFFu) - pad; // >= 0: no root fell into the padding
+                    if (mag) {
+                        nnz++;
+                        if (pos < (int)size)
+                            d[pos] ^= (uint8_t)mag;
+                        else
+                            p[pos - (int)size] ^= (uint8_t)mag;
+                    }
+                }
+            }
+            if (ok)
+                ok[cw] = st == bs::kOk ? 1 : 0;
+            if (corrected)
+                corrected[cw] = nnz;
+        }
+        __syncwarp();
+    }
+}
+
 int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
 {
     if (n <= ctx->queue_cap)
@@ -518,8 +627,8 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
     ctx->d_counters = nullptr;
     ctx->queue_cap = 0;
     const size_t tiles = (n + kTile - 1) / kTile;
-    // queue [n rounded up to 4] | dmask [tiles * 64]
-    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64) * sizeof(uint32_t)));
+    // queue [n rounded up to 4] | dmask [tiles * 64] | queue2 [n]
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64 + n) * sizeof(uint32_t)));
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32));
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, 64));
     ctx->queue_cap = n;
@@ -551,6 +660,7 @@ int rs255_init(poporon_cuda_rs *ctx)
                                      kRingBytes));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      kRingBytes));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
     (void)ctx;
     return 0;
 }
@@ -605,9 +715,22 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(dmask, n, ctx->d_queue,
                                                                                     ctx->d_counters, ok, corrected);
     const unsigned cblocks = (unsigned)ctx->sm_count * 8;
+    const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
+    if (mode == POPORON_CUDA_MODE_PLAIN) {
+        // bitsliced solver first; what it declines lands in queue2 for the literal stage below
+        uint32_t *queue2 = dmask + tiles * 64;
+        const size_t groups = (n + 1023) / 1024;
+        const size_t cap = (size_t)ctx->sm_count * 4;
+        rs255_solve_kernel<<<(unsigned)(groups < cap ? groups : cap), 32, kSolveSmem, stream>>>(
+            data, data_stride, size, parity, parity_stride, ctx->d_queue, ctx->d_counters, ctx->d_rem, queue2,
+            ctx->d_counters + 1, ok, corrected);
+        cq = queue2;
+        cc = ctx->d_counters + 1;
+        ctx->launches++;
+    }
     rs255_correct_kernel<<<cblocks, 128, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride, size, parity,
-                                                      parity_stride, ctx->d_queue, ctx->d_counters, ctx->d_rem, pos,
-                                                      pos_stride, cnt, ok, corrected);
+                                                      parity_stride, cq, cc, ctx->d_rem, pos, pos_stride, cnt, ok,
+                                                      corrected);
     ctx->launches += 3;
     return check(cudaGetLastError(), "rs255 decode launch");
 }

@@ -1,0 +1,436 @@
+// rs255_solve_core.h — bitsliced error solver for RS(255,223)/0x11D, fcr = 1, prim = 1, plain mode.
+//
+// Replaces the reference's error_correction_u8 (src/decode.c:17-230) for the common case: the key-equation
+// solver (Berlekamp-Massey, src/decode.c:53-96), the Chien search (:117-141), the error evaluator
+// (:147-158) and Forney's formula (:159-191), for 32 codewords at once per thread ("lane"): every value is
+// held as 8 bit-planes, one 32-bit word per plane, bit c of a word belonging to codeword c of the lane.
+// There are no table look-ups and no data-dependent branches in the arithmetic:
+//
+//   * a variable x variable GF(2^8) product is 64 AND-XOR (LOP3) into 15 partial planes + a 16-op reduction
+//     modulo x^8 + x^4 + x^3 + x^2 + 1; products that are summed share one reduction;
+//   * a product by a compile-time constant is a fixed XOR network;
+//   * the reference's Karn-style BM divides by the discrepancy (b = lambda / delta, src/decode.c:84-90).
+//     Here the inversion-free form is used: T = gamma*Lambda + Delta*x*B;  on a length change B = Lambda,
+//     gamma = Delta.  With identical branch conditions (Delta != 0, 2*el <= r - 1) every polynomial is a
+//     non-zero scalar multiple of the reference's, so degree, roots, L and the Forney ratio are identical;
+//   * the length test runs on a bitsliced counter k = r - 1 - 2*el (k >= 0  <=>  2*el <= r - 1;
+//     length change: k <- -k - 1 = ~k; otherwise k <- k + 1);
+//   * Chien + Forney are one sweep over the 255 locations: per location the 16 locator terms and 16
+//     evaluator terms are advanced by constant multipliers, the locator value tested for zero, and the
+//     magnitude x*Omega(x) / (x*Lambda'(x)) formed with an x^254 inversion chain (4 products, 7 squarings).
+//
+// Domain.  The solver keeps 17 locator coefficients: it is exact for every codeword whose final register
+// length L is <= 16 and whose locator has degree L.  Anything else (L > 16, or a vanishing leading
+// coefficient - both only happen for uncorrectable words) is reported as "declined" and is decoded by the
+// general per-codeword stage (rs_correct.cuh), which restates the reference literally.  For accepted
+// codewords the reference's outcome is: roots found == L and none in the padding ->
+// true, corrected = number of non-zero magnitudes; otherwise false, 0.  (The re-syndrome verification,
+// src/decode.c:193-209, cannot fail when L distinct roots of a length-L connection polynomial were found.)
+//
+// The code is plain C++ (uint32_t logic only) so that the same functions run under nvcc for sm_100a and,
+// for unit tests, on the host (tests/host_solver.cpp emulates one lane at a time).
+#pragma once
+#include <stdint.h>
+
+#include "gf256_consts.cuh"
+
+#if defined(__CUDACC__)
+#define BS_FN __host__ __device__ __forceinline__
+#else
+#define BS_FN inline __attribute__((always_inline))
+#endif
+
+namespace bs {
+
+constexpr int kT = 16;      // correctable errors
+constexpr int kNL = kT + 1; // locator coefficients kept
+constexpr int kNS = 32;     // syndromes
+
+// "memory" = an array of 32-bit words with a fixed word stride: shared memory [word][lane] on the device
+// (stride 32), a plain array on the host (stride 1)
+template <int STRIDE>
+struct Mem {
+    uint32_t *base;
+    BS_FN uint32_t ld(int idx) const { return base[idx * STRIDE]; }
+    BS_FN void st(int idx, uint32_t v) const { base[idx * STRIDE] = v; }
+};
+
+// ---- variable x variable -------------------------------------------------------------------------------
+BS_FN void mac(uint32_t (&acc)[15], const uint32_t (&a)[8], const uint32_t (&b)[8])
+{
+#pragma unroll
+    for (int s = 0; s < 8; s++)
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            acc[s + t] ^= a[s] & b[t];
+}
+
+BS_FN void clear15(uint32_t (&acc)[15])
+{
+#pragma unroll
+    for (int i = 0; i < 15; i++)
+        acc[i] = 0;
+}
+
+// x^8 = x^4 + x^3 + x^2 + 1  (0x11D)
+BS_FN void reduce(uint32_t (&acc)[15], uint32_t (&out)[8])
+{
+#pragma unroll
+    for (int k = 14; k >= 8; k--) {
+        const uint32_t v = acc[k];
+        acc[k - 8] ^= v;
+        acc[k - 6] ^= v;
+        acc[k - 5] ^= v;
+        acc[k - 4] ^= v;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+        out[i] = acc[i];
+}
+
+BS_FN void mul(const uint32_t (&a)[8], const uint32_t (&b)[8], uint32_t (&out)[8])
+{
+    uint32_t acc[15];
+    clear15(acc);
+    mac(acc, a, b);
+    reduce(acc, out);
+}
+
+// ---- fixed linear maps -----------------------------------------------------------------------------------
+// out[t] = xor of in[s] over the bits s set in M[t]
+template <unsigned M>
+BS_FN uint32_t xor_subset(const uint32_t (&in)[8])
+{
+    uint32_t v = 0;
+    if constexpr ((M & 1u) != 0) v ^= in[0];
+    if constexpr ((M & 2u) != 0) v ^= in[1];
+    if constexpr ((M & 4u) != 0) v ^= in[2];
+    if constexpr ((M & 8u) != 0) v ^= in[3];
+    if constexpr ((M & 16u) != 0) v ^= in[4];
+    if constexpr ((M & 32u) != 0) v ^= in[5];
+    if constexpr ((M & 64u) != 0) v ^= in[6];
+    if constexpr ((M & 128u) != 0) v ^= in[7];
+    return v;
+}
+
+// multiply by the constant C
+template <uint8_t C>
+BS_FN void cmul(const uint32_t (&in)[8], uint32_t (&out)[8])
+{
+    uint32_t r[8];
+    r[0] = xor_subset<gf256::rowmask(C, 0)>(in);
+    r[1] = xor_subset<gf256::rowmask(C, 1)>(in);
+    r[2] = xor_subset<gf256::rowmask(C, 2)>(in);
+    r[3] = xor_subset<gf256::rowmask(C, 3)>(in);
+    r[4] = xor_subset<gf256::rowmask(C, 4)>(in);
+    r[5] = xor_subset<gf256::rowmask(C, 5)>(in);
+    r[6] = xor_subset<gf256::rowmask(C, 6)>(in);
+    r[7] = xor_subset<gf256::rowmask(C, 7)>(in);
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+        out[i] = r[i];
+}
+
+// squaring is GF(2)-linear: row t collects the input bits s whose square (2^s)^2 has bit t
+constexpr uint8_t sq_rowmask(int t)
+{
+    unsigned m = 0;
+    for (int s = 0; s < 8; s++) {
+        const uint8_t e = (uint8_t)(1u << s);
+        if (gf256::mul(e, e) & (1u << t))
+            m |= 1u << s;
+    }
+    return (uint8_t)m;
+}
+
+BS_FN void sqr(const uint32_t (&in)[8], uint32_t (&out)[8])
+{
+    uint32_t r[8];
+    r[0] = xor_subset<sq_rowmask(0)>(in);
+    r[1] = xor_subset<sq_rowmask(1)>(in);
+    r[2] = xor_subset<sq_rowmask(2)>(in);
+    r[3] = xor_subset<sq_rowmask(3)>(in);
+    r[4] = xor_subset<sq_rowmask(4)>(in);
+    r[5] = xor_subset<sq_rowmask(5)>(in);
+    r[6] = xor_subset<sq_rowmask(6)>(in);
+    r[7] = xor_subset<sq_rowmask(7)>(in);
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+        out[i] = r[i];
+}
+
+// a^254 = a^-1 (0 -> 0): 4 products, 7 squarings
+BS_FN void inv(const uint32_t (&a)[8], uint32_t (&out)[8])
+{
+    uint32_t a2[8], a3[8], a12[8], a15[8], t[8];
+    sqr(a, a2);
+    mul(a2, a, a3);
+    sqr(a3, t);
+    sqr(t, a12);
+    mul(a12, a3, a15);
+    sqr(a15, t);
+    sqr(t, t);
+    sqr(t, t);
+    sqr(t, t); // a^240
+    mul(t, a12, t); // a^252
+    mul(t, a2, out); // a^254
+}
+
+BS_FN uint32_t or8(const uint32_t (&a)[8])
+{
+    return (a[0] | a[1] | a[2]) | (a[3] | a[4] | a[5]) | (a[6] | a[7]);
+}
+
+// ---- inversion-free Berlekamp-Massey ---------------------------------------------------------------------
+// S: 32 syndromes, word (8*m + t) = plane t of S_{m+1}.  B: scratch of kNL*8 words.
+// On return L[i] is the locator (a non-zero multiple of the reference's lambda), K the counter planes after
+// the last iteration (k = 32 - 2*el, two's complement, 7 planes).
+template <int STRIDE>
+BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kNL][8], uint32_t (&K)[7])
+{
+    uint32_t gamma[8];
+#pragma unroll
+    for (int i = 0; i < kNL; i++)
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            L[i][t] = (i == 0 && t == 0) ? 0xFFFFFFFFu : 0u;
+            B.st(8 * i + t, (i == 0 && t == 0) ? 0xFFFFFFFFu : 0u);
+        }
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        gamma[t] = t == 0 ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+    for (int b = 0; b < 7; b++)
+        K[b] = 0;
+
+#pragma unroll 1
+    for (int r = 1; r <= kNS; r++) {
+        // discrepancy: sum_{i < r, i <= 16} L_i * S_{r-i}     (S_{r-i} is word block r-1-i)
+        uint32_t acc[15], delta[8];
+        clear15(acc);
+#pragma unroll
+        for (int i = 0; i < kNL; i++) {
+            if (i < r) {
+                uint32_t s[8];
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    s[t] = S.ld(8 * (r - 1 - i) + t);
+                mac(acc, L[i], s);
+            }
+        }
+        reduce(acc, delta);
+        const uint32_t chg = or8(delta) & ~K[6]; // delta != 0 and k >= 0
+
+        // T_i = gamma*L_i + delta*B_{i-1};  B_i <- chg ? L_i : B_{i-1}    (descending i: in place)
+#pragma unroll
+        for (int i = kNL - 1; i >= 0; i--) {
+            if (i <= r) {
+                uint32_t bp[8], tacc[15];
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    bp[t] = i > 0 ? B.ld(8 * (i - 1) + t) : 0u;
+                clear15(tacc);
+                mac(tacc, gamma, L[i]);
+                if (i > 0)
+                    mac(tacc, delta, bp);
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    B.st(8 * i + t, (chg & L[i][t]) | (~chg & bp[t]));
+                reduce(tacc, L[i]);
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            gamma[t] = (chg & delta[t]) | (~chg & gamma[t]);
+        uint32_t carry = 0xFFFFFFFFu;
+#pragma unroll
+        for (int b = 0; b < 7; b++) {
+            const uint32_t inc = K[b] ^ carry;
+            carry &= K[b];
+            K[b] = (chg & ~K[b]) | (~chg & inc);
+        }
+    }
+}
+
+// ---- evaluator: Omega_i = sum_{j <= i} S_{i-j+1} * L_j, i = 0..15 (src/decode.c:147-158) -------------------
+// Stored to O as word block i, already advanced to "location 0" form is NOT done here (see sweep_init).
+template <int STRIDE>
+BS_FN void omega(const Mem<STRIDE> S, const uint32_t (&L)[kNL][8], const Mem<STRIDE> O)
+{
+#pragma unroll
+    for (int i = 0; i < kT; i++) {
+        uint32_t acc[15], o[8];
+        clear15(acc);
+#pragma unroll
+        for (int j = 0; j <= i; j++) {
+            uint32_t s[8];
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                s[t] = S.ld(8 * (i - j) + t);
+            mac(acc, L[j], s);
+        }
+        reduce(acc, o);
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            O.st(8 * i + t, o[t]);
+    }
+}
+
+// ---- Chien / Forney sweep -----------------------------------------------------------------------------------
+// Location k = 0..254 corresponds to the root alpha^(k+1) (src/decode.c:117-141 with prim = 1: k = i - 1).
+// Before location k is examined every term is advanced once:
+//     L_j <- L_j * alpha^j        (j = 1..16)   so that L_j holds lambda_j * alpha^(j*(k+1))
+//     O_j <- O_j * alpha^(j+1)    (j = 0..15)   so that sum O_j = x * Omega(x) at x = alpha^(k+1)
+template <int J>
+BS_FN void advance_L(uint32_t (&L)[kNL][8])
+{
+    if constexpr (J <= kT) {
+        cmul<gf256::pow_alpha(J)>(L[J], L[J]);
+        advance_L<J + 1>(L);
+    }
+}
+
+template <int STRIDE, int J>
+BS_FN void advance_O(const Mem<STRIDE> O, uint32_t (&num)[8])
+{
+    if constexpr (J < kT) {
+        uint32_t o[8];
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            o[t] = O.ld(8 * J + t);
+        cmul<gf256::pow_alpha(J + 1)>(o, o);
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            O.st(8 * J + t, o[t]);
+            num[t] ^= o[t];
+        }
+        advance_O<STRIDE, J + 1>(O, num);
+    }
+}
+
+// One location.  Returns the root mask; mag = error magnitude planes (zero where the location is no root).
+template <int STRIDE>
+BS_FN uint32_t sweep_step(uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_t (&mag)[8])
+{
+    advance_L<1>(L);
+    uint32_t even[8], odd[8], num[8];
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        uint32_t e = L[0][t], o = 0;
+#pragma unroll
+        for (int j = 1; j <= kT; j++) {
+            if (j & 1)
+                o ^= L[j][t];
+            else
+                e ^= L[j][t];
+        }
+        even[t] = e;
+        odd[t] = o;
+        num[t] = 0;
+    }
+    uint32_t nz = 0;
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        nz |= even[t] ^ odd[t];
+    const uint32_t root = ~nz;
+    advance_O<STRIDE, 0>(O, num);
+    // magnitude = x*Omega(x) / (x*Lambda'(x)); x*Lambda'(x) = sum of the odd terms (src/decode.c:159-191, fcr = 1)
+    uint32_t di[8], m[8];
+    inv(odd, di);
+    mul(num, di, m);
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        mag[t] = m[t] & root;
+    return root;
+}
+
+} // namespace bs
+
+// ---- one lane, start to finish ----------------------------------------------------------------------------
+namespace bs {
+
+#if defined(__CUDA_ARCH__)
+#define BS_CTZ(x) (__ffs((int)(x)) - 1)
+#else
+#define BS_CTZ(x) __builtin_ctz(x)
+#endif
+
+constexpr int kWordsS = 8 * kNS;      // 256: syndromes in, per-codeword root lists out
+constexpr int kWordsB = 8 * kNL;      // 136: BM scratch, then evaluator terms (128) + root counters (8)
+constexpr int kCntBase = 8 * kT;      // word offset of the packed root counters inside the B area
+
+struct LaneOut {
+    uint32_t K[7];       // k = 32 - 2*L per codeword (bit-planes, two's complement)
+    uint32_t nzL[kNL];   // nzL[j] bit c: locator coefficient j of codeword c is non-zero
+    uint32_t padfail;    // bit c: a root fell into the zero padding (k < pad), src/decode.c:132-134
+};
+
+// Root list of codeword c: up to 16 entries (location | magnitude << 8) as half-words, words [8c, 8c+8) of
+// the S area; root counter of codeword c: byte (c & 3) of word kCntBase + (c >> 2) of the B area.
+template <int STRIDE>
+BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, LaneOut &out)
+{
+    uint32_t L[kNL][8];
+    ribm<STRIDE>(S, B, L, out.K);
+    omega<STRIDE>(S, L, B); // evaluator terms replace the BM scratch (words 0..127)
+#pragma unroll
+    for (int j = 0; j < kNL; j++)
+        out.nzL[j] = or8(L[j]);
+    for (int w = 0; w < kWordsS; w++)
+        S.st(w, 0u);
+    for (int w = 0; w < 8; w++)
+        B.st(kCntBase + w, 0u);
+    uint32_t padfail = 0;
+#pragma unroll 1
+    for (int k = 0; k < 255; k++) {
+        uint32_t mag[8];
+        uint32_t m = sweep_step<STRIDE>(L, B, mag);
+        if (k < pad)
+            padfail |= m;
+        while (m) {
+            const int c = BS_CTZ(m);
+            m &= m - 1;
+            uint32_t v = 0;
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                v |= ((mag[t] >> c) & 1u) << t;
+            const int sh = 8 * (c & 3);
+            const uint32_t cw = B.ld(kCntBase + (c >> 2));
+            const uint32_t e = (cw >> sh) & 0xFFu;
+            B.st(kCntBase + (c >> 2), cw + (1u << sh));
+            if (e < (uint32_t)kT) {
+                const int idx = 8 * c + (int)(e >> 1);
+                S.st(idx, S.ld(idx) | (((uint32_t)k | (v << 8)) << (16 * (e & 1u))));
+            }
+        }
+    }
+    out.padfail = padfail;
+}
+
+enum { kDeclined = 0, kFail = 1, kOk = 2 };
+
+// Outcome of codeword c of a lane (see the header comment for the rules).  nroots = roots found.
+template <int STRIDE>
+BS_FN int classify(const Mem<STRIDE> B, const LaneOut &o, int c, int &nroots)
+{
+    int k = 0;
+#pragma unroll
+    for (int b = 0; b < 7; b++)
+        k |= (int)((o.K[b] >> c) & 1u) << b;
+    if (k & 64)
+        return kDeclined; // k < 0: L > 16
+    const int el = (32 - k) >> 1;
+    uint32_t lead = 0;
+#pragma unroll
+    for (int j = 0; j < kNL; j++)
+        if (j == el)
+            lead = (o.nzL[j] >> c) & 1u;
+    if (!lead || el == 0)
+        return kDeclined; // degree below the register length: leave it to the literal stage
+    nroots = (int)((B.ld(kCntBase + (c >> 2)) >> (8 * (c & 3))) & 0xFFu);
+    if (nroots != el || ((o.padfail >> c) & 1u))
+        return kFail;
+    return kOk;
+}
+
+} // namespace bs

@@ -518,3 +518,23 @@ def test_use_devices_and_large_host_batch(gpu_device, orc):
         d, p, ok, cor = _gpu_decode(h, cw[:, :223], cw[:, 223:])
         assert ok.all() and (d == msg).all() and (p == par).all()
         assert int((cor > 0).sum()) == 3000
+
+
+@pytest.mark.parametrize("size,elo,ehi,n", [(223, 14, 40, 40_000), (223, 0, 16, 70_000), (120, 10, 24, 20_000)])
+def test_rs_default_solver_heavy_loads(gpu_device, orc, size, elo, ehi, n):
+    """the bitsliced solver (rs255_solve_core.h) and its hand-over of declined codewords (register length
+    > 16, vanishing leading coefficient) to the literal stage: many uncorrectable words, several queue groups"""
+    rng = np.random.default_rng(size * 1000 + ehi)
+    msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+    cw = np.concatenate([msg, orc.rs_encode(msg, threads=8)], 1)
+    L = size + 32
+    e = rng.integers(elo, ehi + 1, n)
+    order = np.argsort(rng.random((n, L)), axis=1)[:, :ehi]
+    mags = rng.integers(1, 256, (n, ehi), dtype=np.uint8)
+    rows = np.arange(n)
+    for k in range(ehi):
+        sel = e > k
+        cw[rows[sel], order[sel, k]] ^= mags[sel, k]
+    with api.Poporon.rs_default() as h:
+        got = _gpu_decode(h, cw[:, :size], cw[:, size:])
+    _assert_same(got, orc.rs_decode(cw[:, :size], cw[:, size:], threads=8), f"heavy {size} {elo}-{ehi}")

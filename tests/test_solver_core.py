@@ -1,0 +1,124 @@
+"""CPU test of the bitsliced RS(255,223) solver arithmetic (libpoporon_b200/csrc/cuda/rs255_solve_core.h).
+
+The header is plain C++; tests/native/host_solver.cpp runs it on the host one lane (32 codewords) at a
+time.  Here its outcome (status, root count, locations, magnitudes) is compared with the oracle's
+poporon_decode on the same received words: for every codeword the solver accepts, applying its error list
+must reproduce the oracle's corrected bytes, corrected_num and success flag; codewords it declines are
+counted (they go to the literal per-codeword stage on the device) and must be rare."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+from oraclelib import Oracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "native", "host_solver.cpp")
+INC = os.path.join(ROOT, "libpoporon_b200", "csrc", "cuda")
+OUT = os.path.join(ROOT, "build", "tests", "host_solver.so")
+
+
+@pytest.fixture(scope="module")
+def solver():
+    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+    subprocess.run(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", f"-I{INC}", "-o", OUT, SRC], check=True)
+    lib = C.CDLL(OUT)
+    P = C.POINTER
+    lib.host_solve.argtypes = [P(C.c_uint8), C.c_size_t, C.c_int, P(C.c_int8), P(C.c_uint8), P(C.c_uint16)]
+    return lib
+
+
+def gf_tables():
+    exp = np.zeros(512, np.int64)
+    log = np.zeros(256, np.int64)
+    x = 1
+    for i in range(255):
+        exp[i] = x
+        log[x] = i
+        x <<= 1
+        if x & 0x100:
+            x ^= 0x11D
+    exp[255:510] = exp[0:255]
+    return exp, log
+
+
+def syndromes(cw):
+    """S_j = r(alpha^j), j = 1..32, first byte = highest degree."""
+    exp, log = gf_tables()
+    n, length = cw.shape
+    out = np.zeros((n, 32), np.uint8)
+    powers = (length - 1 - np.arange(length))
+    nz = cw != 0
+    lg = log[cw]
+    for j in range(1, 33):
+        e = (lg + (j * powers)[None, :]) % 255
+        v = np.where(nz, exp[e], 0)
+        out[:, j - 1] = np.bitwise_xor.reduce(v, axis=1)
+    return out
+
+
+def run_case(solver, orc, rng, n, size, emin, emax):
+    msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+    par = orc.rs_encode(msg)
+    cw = np.concatenate([msg, par], 1)
+    length = size + 32
+    for i in range(n):
+        e = int(rng.integers(emin, emax + 1))
+        pos = rng.choice(length, e, replace=False)
+        cw[i, pos] ^= rng.integers(1, 256, e, dtype=np.uint8)
+    wd, wp, wok, wcor = orc.rs_decode(cw[:, :size], cw[:, size:])
+    syn = np.ascontiguousarray(syndromes(cw))
+    dirty = syn.any(axis=1)
+    status = np.zeros(n, np.int8)
+    nroots = np.zeros(n, np.uint8)
+    lists = np.zeros((n, 16), np.uint16)
+    pad = 223 - size
+    P = C.POINTER
+    solver.host_solve(syn.ctypes.data_as(P(C.c_uint8)), n, pad, status.ctypes.data_as(P(C.c_int8)),
+                      nroots.ctypes.data_as(P(C.c_uint8)), lists.ctypes.data_as(P(C.c_uint16)))
+    declined = 0
+    for i in range(n):
+        if not dirty[i]:
+            assert wok[i] == 1 and wcor[i] == 0
+            continue
+        if status[i] == 0:
+            declined += 1
+            continue
+        if status[i] == 1:
+            assert wok[i] == 0 and wcor[i] == 0, (i, wok[i], wcor[i])
+            assert (wd[i] == cw[i, :size]).all() and (wp[i] == cw[i, size:]).all()
+            continue
+        assert wok[i] == 1, i
+        fixed = cw[i].copy()
+        nnz = 0
+        for e in range(nroots[i]):
+            loc, mag = int(lists[i, e]) & 0xFF, int(lists[i, e]) >> 8
+            assert loc >= pad
+            fixed[loc - pad] ^= mag
+            nnz += mag != 0
+        assert nnz == wcor[i], (i, nnz, wcor[i])
+        assert (fixed[:size] == wd[i]).all() and (fixed[size:] == wp[i]).all(), i
+    return declined, int(dirty.sum())
+
+
+def test_solver_core_correctable(solver):
+    orc = Oracle("port")
+    rng = np.random.default_rng(11)
+    declined, dirty = run_case(solver, orc, rng, 640, 223, 0, 16)
+    assert declined == 0 and dirty > 500
+
+
+def test_solver_core_uncorrectable(solver):
+    orc = Oracle("port")
+    rng = np.random.default_rng(12)
+    declined, dirty = run_case(solver, orc, rng, 960, 223, 15, 40)
+    assert dirty == 960
+    assert declined < 0.15 * dirty  # L > 16 happens for ~6 % of random uncorrectable words
+
+
+def test_solver_core_shortened(solver):
+    orc = Oracle("port")
+    rng = np.random.default_rng(13)
+    for size in (1, 17, 64, 200):
+        run_case(solver, orc, rng, 256, size, 0, 19)
