@@ -517,7 +517,8 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 // words only) are appended to a second queue for the literal per-codeword stage.
 // ---------------------------------------------------------------------------------------------------
 constexpr int kSolveWords = bs::kWordsS + bs::kWordsB;
-constexpr int kSolveSmem = kSolveWords * 128;
+constexpr int kSolveSmem = kSolveWords * 128 + 512; // + log[256] | exp[256]
+__constant__ gf256::ExpLog c_explog = gf256::kExpLog;
 
 template <int W>
 __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], const uint8_t *__restrict__ syn_raw,
@@ -562,6 +563,12 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
     const bs::Mem<32> B{solve_smem + bs::kWordsS * 32 + lane};
     const uint32_t total = *counter;
     const int pad = kMsg - (int)size;
+    uint8_t *logt = reinterpret_cast<uint8_t *>(solve_smem + kSolveWords * 32), *expt = logt + 256;
+    for (int i = lane; i < 256; i += 32) {
+        logt[i] = c_explog.log[i];
+        expt[i] = c_explog.exp[i];
+    }
+    __syncwarp();
 
     for (uint32_t g0 = blockIdx.x * 1024u; g0 < total; g0 += gridDim.x * 1024u) {
         {
@@ -574,7 +581,7 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
             solve_load_syndromes<0>(ent, syn_raw, S);
         }
         bs::LaneOut out;
-        bs::solve_lane<32>(S, B, pad, out);
+        bs::solve_lane<32>(S, B, pad, logt, expt, out);
 
 #pragma unroll 1
         for (int c = 0; c < 32; c++) {

@@ -16,8 +16,9 @@
 //   * the length test runs on a bitsliced counter k = r - 1 - 2*el (k >= 0  <=>  2*el <= r - 1;
 //     length change: k <- -k - 1 = ~k; otherwise k <- k + 1);
 //   * Chien + Forney are one sweep over the 255 locations: per location the 16 locator terms and 16
-//     evaluator terms are advanced by constant multipliers, the locator value tested for zero, and the
-//     magnitude x*Omega(x) / (x*Lambda'(x)) formed with an x^254 inversion chain (4 products, 7 squarings).
+//     evaluator terms are advanced by constant multipliers and the locator value tested for zero; where it
+//     is zero (about one codeword per lane and location) x*Omega(x) and x*Lambda'(x) are gathered from the
+//     planes and divided with a 512-byte log/antilog table.
 //
 // Domain.  The solver keeps 17 locator coefficients: it is exact for every codeword whose final register
 // length L is <= 16 and whose locator has degree L.  Anything else (L > 16, or a vanishing leading
@@ -40,6 +41,14 @@
 #define BS_FN inline __attribute__((always_inline))
 #endif
 
+// Compiler-level fence: keeps nvcc from hoisting every shared-memory load of a long unrolled sequence to the
+// top (which costs more registers than the kernel has); loads are software-pipelined one term ahead instead.
+#if defined(__CUDA_ARCH__)
+#define BS_FENCE() asm volatile("" ::: "memory")
+#else
+#define BS_FENCE() ((void)0)
+#endif
+
 namespace bs {
 
 constexpr int kT = 16;      // correctable errors
@@ -54,6 +63,27 @@ struct Mem {
     BS_FN uint32_t ld(int idx) const { return base[idx * STRIDE]; }
     BS_FN void st(int idx, uint32_t v) const { base[idx * STRIDE] = v; }
 };
+
+template <int STRIDE>
+BS_FN void ld8(const Mem<STRIDE> M, int blk, uint32_t (&v)[8])
+{
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        v[t] = M.ld(8 * blk + t);
+}
+template <int STRIDE>
+BS_FN void st8(const Mem<STRIDE> M, int blk, const uint32_t (&v)[8])
+{
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        M.st(8 * blk + t, v[t]);
+}
+BS_FN void cp8(uint32_t (&d)[8], const uint32_t (&s)[8])
+{
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        d[t] = s[t];
+}
 
 // ---- variable x variable -------------------------------------------------------------------------------
 BS_FN void mac(uint32_t (&acc)[15], const uint32_t (&a)[8], const uint32_t (&b)[8])
@@ -194,7 +224,8 @@ BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kNL][8],
 #pragma unroll
         for (int t = 0; t < 8; t++) {
             L[i][t] = (i == 0 && t == 0) ? 0xFFFFFFFFu : 0u;
-            B.st(8 * i + t, (i == 0 && t == 0) ? 0xFFFFFFFFu : 0u);
+            if (i < kT)
+                B.st(8 * i + t, (i == 0 && t == 0) ? 0xFFFFFFFFu : 0u);
         }
 #pragma unroll
     for (int t = 0; t < 8; t++)
@@ -206,37 +237,54 @@ BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kNL][8],
 #pragma unroll 1
     for (int r = 1; r <= kNS; r++) {
         // discrepancy: sum_{i < r, i <= 16} L_i * S_{r-i}     (S_{r-i} is word block r-1-i)
-        uint32_t acc[15], delta[8];
+        uint32_t acc[15], delta[8], s[8], sn[8];
         clear15(acc);
+        ld8(S, r - 1, s);
 #pragma unroll
         for (int i = 0; i < kNL; i++) {
             if (i < r) {
-                uint32_t s[8];
-#pragma unroll
-                for (int t = 0; t < 8; t++)
-                    s[t] = S.ld(8 * (r - 1 - i) + t);
+                if (i + 1 < kNL && i + 1 < r)
+                    ld8(S, r - 2 - i, sn);
+                BS_FENCE();
                 mac(acc, L[i], s);
+                cp8(s, sn);
             }
         }
         reduce(acc, delta);
         const uint32_t chg = or8(delta) & ~K[6]; // delta != 0 and k >= 0
 
         // T_i = gamma*L_i + delta*B_{i-1};  B_i <- chg ? L_i : B_{i-1}    (descending i: in place)
+        {
+            uint32_t bp[8], bn[8];
+            const int top = r < kNL - 1 ? r : kNL - 1; // highest coefficient that can be non-zero
+            if (top > 0)
+                ld8(B, top - 1, bp);
 #pragma unroll
-        for (int i = kNL - 1; i >= 0; i--) {
-            if (i <= r) {
-                uint32_t bp[8], tacc[15];
+            for (int i = kNL - 1; i >= 0; i--) {
+                if (i <= r) {
+                    uint32_t tacc[15];
+                    if (i == 0) {
 #pragma unroll
-                for (int t = 0; t < 8; t++)
-                    bp[t] = i > 0 ? B.ld(8 * (i - 1) + t) : 0u;
-                clear15(tacc);
-                mac(tacc, gamma, L[i]);
-                if (i > 0)
-                    mac(tacc, delta, bp);
+                        for (int t = 0; t < 8; t++)
+                            bp[t] = 0u;
+                    }
+                    if (i >= 2)
+                        ld8(B, i - 2, bn);
+                    BS_FENCE();
+                    clear15(tacc);
+                    mac(tacc, gamma, L[i]);
+                    if (i > 0)
+                        mac(tacc, delta, bp);
+                    if (i < kT) { // B_16 is never read again
+                        uint32_t nb[8];
 #pragma unroll
-                for (int t = 0; t < 8; t++)
-                    B.st(8 * i + t, (chg & L[i][t]) | (~chg & bp[t]));
-                reduce(tacc, L[i]);
+                        for (int t = 0; t < 8; t++)
+                            nb[t] = (chg & L[i][t]) | (~chg & bp[t]);
+                        st8(B, i, nb);
+                    }
+                    reduce(tacc, L[i]);
+                    cp8(bp, bn);
+                }
             }
         }
 #pragma unroll
@@ -291,29 +339,33 @@ BS_FN void advance_L(uint32_t (&L)[kNL][8])
 }
 
 template <int STRIDE, int J>
-BS_FN void advance_O(const Mem<STRIDE> O, uint32_t (&num)[8])
+BS_FN void advance_O(const Mem<STRIDE> O, uint32_t (&cur)[8], uint32_t (&num)[8])
 {
     if constexpr (J < kT) {
-        uint32_t o[8];
+        uint32_t nxt[8];
+        if constexpr (J + 1 < kT)
+            ld8(O, J + 1, nxt);
+        BS_FENCE();
+        cmul<gf256::pow_alpha(J + 1)>(cur, cur);
+        st8(O, J, cur);
 #pragma unroll
         for (int t = 0; t < 8; t++)
-            o[t] = O.ld(8 * J + t);
-        cmul<gf256::pow_alpha(J + 1)>(o, o);
-#pragma unroll
-        for (int t = 0; t < 8; t++) {
-            O.st(8 * J + t, o[t]);
-            num[t] ^= o[t];
-        }
-        advance_O<STRIDE, J + 1>(O, num);
+            num[t] ^= cur[t];
+        if constexpr (J + 1 < kT)
+            cp8(cur, nxt);
+        advance_O<STRIDE, J + 1>(O, cur, num);
     }
 }
 
-// One location.  Returns the root mask; mag = error magnitude planes (zero where the location is no root).
+// One location.  Returns the root mask; num = x*Omega(x), odd = x*Lambda'(x) at this location's root
+// (bit-planes, all 32 codewords; only the bits under the root mask are meaningful to the caller).
 template <int STRIDE>
-BS_FN uint32_t sweep_step(uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_t (&mag)[8])
+BS_FN uint32_t sweep_step(uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_t (&num)[8], uint32_t (&odd)[8])
 {
+    uint32_t cur[8];
+    ld8(O, 0, cur);
     advance_L<1>(L);
-    uint32_t even[8], odd[8], num[8];
+    uint32_t nz = 0;
 #pragma unroll
     for (int t = 0; t < 8; t++) {
         uint32_t e = L[0][t], o = 0;
@@ -324,24 +376,12 @@ BS_FN uint32_t sweep_step(uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_t (
             else
                 e ^= L[j][t];
         }
-        even[t] = e;
         odd[t] = o;
+        nz |= e ^ o;
         num[t] = 0;
     }
-    uint32_t nz = 0;
-#pragma unroll
-    for (int t = 0; t < 8; t++)
-        nz |= even[t] ^ odd[t];
-    const uint32_t root = ~nz;
-    advance_O<STRIDE, 0>(O, num);
-    // magnitude = x*Omega(x) / (x*Lambda'(x)); x*Lambda'(x) = sum of the odd terms (src/decode.c:159-191, fcr = 1)
-    uint32_t di[8], m[8];
-    inv(odd, di);
-    mul(num, di, m);
-#pragma unroll
-    for (int t = 0; t < 8; t++)
-        mag[t] = m[t] & root;
-    return root;
+    advance_O<STRIDE, 0>(O, cur, num);
+    return ~nz;
 }
 
 } // namespace bs
@@ -365,17 +405,27 @@ struct LaneOut {
     uint32_t padfail;    // bit c: a root fell into the zero padding (k < pad), src/decode.c:132-134
 };
 
+// bit c of 8 planes -> one byte
+BS_FN uint32_t gather_byte(const uint32_t (&p)[8], int c)
+{
+    uint32_t v = 0;
+#pragma unroll
+    for (int t = 7; t >= 0; t--)
+        v = (v << 1) | ((p[t] >> c) & 1u);
+    return v;
+}
+
 // Root list of codeword c: up to 16 entries (location | magnitude << 8) as half-words, words [8c, 8c+8) of
 // the S area; root counter of codeword c: byte (c & 3) of word kCntBase + (c >> 2) of the B area.
+// Forney's quotient (src/decode.c:159-191, num2 = 1 for fcr = 1) is formed per root with the log/antilog
+// tables logt[256] / expt[256] (a root is rare: ~1 per lane and location, so this stays off the bit-plane path).
 template <int STRIDE>
-BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, LaneOut &out)
+BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, const uint8_t *logt, const uint8_t *expt,
+                      LaneOut &out)
 {
     uint32_t L[kNL][8];
     ribm<STRIDE>(S, B, L, out.K);
     omega<STRIDE>(S, L, B); // evaluator terms replace the BM scratch (words 0..127)
-#pragma unroll
-    for (int j = 0; j < kNL; j++)
-        out.nzL[j] = or8(L[j]);
     for (int w = 0; w < kWordsS; w++)
         S.st(w, 0u);
     for (int w = 0; w < 8; w++)
@@ -383,17 +433,20 @@ BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, LaneOut
     uint32_t padfail = 0;
 #pragma unroll 1
     for (int k = 0; k < 255; k++) {
-        uint32_t mag[8];
-        uint32_t m = sweep_step<STRIDE>(L, B, mag);
+        uint32_t num[8], odd[8];
+        uint32_t m = sweep_step<STRIDE>(L, B, num, odd);
         if (k < pad)
             padfail |= m;
         while (m) {
             const int c = BS_CTZ(m);
             m &= m - 1;
+            const uint32_t nb = gather_byte(num, c), db = gather_byte(odd, c);
             uint32_t v = 0;
-#pragma unroll
-            for (int t = 0; t < 8; t++)
-                v |= ((mag[t] >> c) & 1u) << t;
+            if (nb != 0) { // a zero numerator is a zero magnitude, not counted (src/decode.c:167-170)
+                uint32_t lg = (uint32_t)logt[nb] + 255u - (uint32_t)logt[db];
+                lg = lg >= 255u ? lg - 255u : lg;
+                v = expt[lg];
+            }
             const int sh = 8 * (c & 3);
             const uint32_t cw = B.ld(kCntBase + (c >> 2));
             const uint32_t e = (cw >> sh) & 0xFFu;
@@ -405,6 +458,10 @@ BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, LaneOut
         }
     }
     out.padfail = padfail;
+    // the sweep multiplied every coefficient by non-zero constants only: zero-ness is that of the locator
+#pragma unroll
+    for (int j = 0; j < kNL; j++)
+        out.nzL[j] = or8(L[j]);
 }
 
 enum { kDeclined = 0, kFail = 1, kOk = 2 };
