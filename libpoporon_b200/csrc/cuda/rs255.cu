@@ -517,8 +517,7 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 // words only) are appended to a second queue for the literal per-codeword stage.
 // ---------------------------------------------------------------------------------------------------
 constexpr int kSolveWords = bs::kWordsS + bs::kWordsB;
-constexpr int kSolveSmem = kSolveWords * 128 + 512; // + log[256] | exp[256]
-__constant__ gf256::ExpLog c_explog = gf256::kExpLog;
+constexpr int kSolveSmem = kSolveWords * 128;
 
 template <int W>
 __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], const uint8_t *__restrict__ syn_raw,
@@ -563,12 +562,6 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
     const bs::Mem<32> B{solve_smem + bs::kWordsS * 32 + lane};
     const uint32_t total = *counter;
     const int pad = kMsg - (int)size;
-    uint8_t *logt = reinterpret_cast<uint8_t *>(solve_smem + kSolveWords * 32), *expt = logt + 256;
-    for (int i = lane; i < 256; i += 32) {
-        logt[i] = c_explog.log[i];
-        expt[i] = c_explog.exp[i];
-    }
-    __syncwarp();
 
     for (uint32_t g0 = blockIdx.x * 1024u; g0 < total; g0 += gridDim.x * 1024u) {
         {
@@ -581,14 +574,19 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
             solve_load_syndromes<0>(ent, syn_raw, S);
         }
         bs::LaneOut out;
-        bs::solve_lane<32>(S, B, pad, logt, expt, out);
+        bs::solve_lane<32>(S, B, pad, out);
 
+        // Corrections are applied with word-wide atomic XORs (RED.XOR, no return value): nothing in this loop
+        // waits on memory, and bytes of neighbouring records that share a word cannot be lost.
+        uint32_t next_entry = g0 + (uint32_t)lane < total ? queue[g0 + (uint32_t)lane] : 0u;
 #pragma unroll 1
         for (int c = 0; c < 32; c++) {
             const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
+            const uint32_t entry = next_entry;
+            if (c + 1 < 32 && q + 32u < total)
+                next_entry = queue[q + 32u];
             if (q >= total)
                 continue;
-            const uint32_t entry = queue[q];
             const size_t cw = entry & 0x3FFFFFFFu;
             int nroots = 0;
             const int st = bs::classify<32>(B, out, c, nroots);
@@ -606,10 +604,9 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
                     const int pos = (int)(v & 0xFFu) - pad; // >= 0: no root fell into the padding
                     if (mag) {
                         nnz++;
-                        if (pos < (int)size)
-                            d[pos] ^= (uint8_t)mag;
-                        else
-                            p[pos - (int)size] ^= (uint8_t)mag;
+                        uint8_t *a = pos < (int)size ? d + pos : p + (pos - (int)size);
+                        const uintptr_t ua = (uintptr_t)a;
+                        atomicXor(reinterpret_cast<unsigned int *>(ua & ~(uintptr_t)3), mag << (8u * (unsigned)(ua & 3u)));
                     }
                 }
             }

@@ -62,6 +62,16 @@ struct Mem {
     uint32_t *base;
     BS_FN uint32_t ld(int idx) const { return base[idx * STRIDE]; }
     BS_FN void st(int idx, uint32_t v) const { base[idx * STRIDE] = v; }
+    // half-word h (0/1) and byte b (0..3) of word idx (little endian, as the GPU sees them)
+    BS_FN void st_half(int idx, int h, uint32_t v) const
+    {
+        reinterpret_cast<uint16_t *>(base + idx * STRIDE)[h] = (uint16_t)v;
+    }
+    BS_FN uint32_t ld_byte(int idx, int b) const { return reinterpret_cast<const uint8_t *>(base + idx * STRIDE)[b]; }
+    BS_FN void st_byte(int idx, int b, uint32_t v) const
+    {
+        reinterpret_cast<uint8_t *>(base + idx * STRIDE)[b] = (uint8_t)v;
+    }
 };
 
 template <int STRIDE>
@@ -324,11 +334,63 @@ BS_FN void omega(const Mem<STRIDE> S, const uint32_t (&L)[kNL][8], const Mem<STR
     }
 }
 
-// ---- Chien / Forney sweep -----------------------------------------------------------------------------------
+// ---- 32x32 bit-matrix transpose: x[r] bit c <-> x[c] bit r (an involution) ---------------------------------
+BS_FN void transpose32(uint32_t (&x)[32])
+{
+#pragma unroll
+    for (int r = 0; r < 16; r++) {
+        const uint32_t a = x[r], b = x[r + 16];
+#if defined(__CUDA_ARCH__)
+        x[r] = __byte_perm(a, b, 0x5410);
+        x[r + 16] = __byte_perm(a, b, 0x7632);
+#else
+        x[r] = (a & 0x0000FFFFu) | (b << 16);
+        x[r + 16] = (a >> 16) | (b & 0xFFFF0000u);
+#endif
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 8)
+            continue;
+        const uint32_t a = x[r], b = x[r + 8];
+#if defined(__CUDA_ARCH__)
+        x[r] = __byte_perm(a, b, 0x6240);
+        x[r + 8] = __byte_perm(a, b, 0x7351);
+#else
+        x[r] = (a & 0x00FF00FFu) | ((b << 8) & 0xFF00FF00u);
+        x[r + 8] = ((a >> 8) & 0x00FF00FFu) | (b & 0xFF00FF00u);
+#endif
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 4)
+            continue;
+        const uint32_t a = x[r], b = x[r + 4];
+        x[r] = (a & 0x0F0F0F0Fu) | ((b << 4) & 0xF0F0F0F0u);
+        x[r + 4] = ((a >> 4) & 0x0F0F0F0Fu) | (b & 0xF0F0F0F0u);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 2)
+            continue;
+        const uint32_t a = x[r], b = x[r + 2];
+        x[r] = (a & 0x33333333u) | ((b << 2) & 0xCCCCCCCCu);
+        x[r + 2] = ((a >> 2) & 0x33333333u) | (b & 0xCCCCCCCCu);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 1)
+            continue;
+        const uint32_t a = x[r], b = x[r + 1];
+        x[r] = (a & 0x55555555u) | ((b << 1) & 0xAAAAAAAAu);
+        x[r + 1] = ((a >> 1) & 0x55555555u) | (b & 0xAAAAAAAAu);
+    }
+}
+
+// ---- Chien search -------------------------------------------------------------------------------------------
 // Location k = 0..254 corresponds to the root alpha^(k+1) (src/decode.c:117-141 with prim = 1: k = i - 1).
-// Before location k is examined every term is advanced once:
-//     L_j <- L_j * alpha^j        (j = 1..16)   so that L_j holds lambda_j * alpha^(j*(k+1))
-//     O_j <- O_j * alpha^(j+1)    (j = 0..15)   so that sum O_j = x * Omega(x) at x = alpha^(k+1)
+// Before location k is examined every term is advanced once, L_j <- L_j * alpha^j (j = 1..16), so that L_j
+// holds lambda_j * alpha^(j*(k+1)).  After all 255 locations every term is back at lambda_j (alpha^255 = 1).
 template <int J>
 BS_FN void advance_L(uint32_t (&L)[kNL][8])
 {
@@ -338,57 +400,62 @@ BS_FN void advance_L(uint32_t (&L)[kNL][8])
     }
 }
 
-template <int STRIDE, int J>
-BS_FN void advance_O(const Mem<STRIDE> O, uint32_t (&cur)[8], uint32_t (&num)[8])
+// one location: returns the mask of codewords whose locator vanishes there
+BS_FN uint32_t chien_step(uint32_t (&L)[kNL][8])
 {
-    if constexpr (J < kT) {
-        uint32_t nxt[8];
-        if constexpr (J + 1 < kT)
-            ld8(O, J + 1, nxt);
-        BS_FENCE();
-        cmul<gf256::pow_alpha(J + 1)>(cur, cur);
-        st8(O, J, cur);
-#pragma unroll
-        for (int t = 0; t < 8; t++)
-            num[t] ^= cur[t];
-        if constexpr (J + 1 < kT)
-            cp8(cur, nxt);
-        advance_O<STRIDE, J + 1>(O, cur, num);
-    }
-}
-
-// One location.  Returns the root mask; num = x*Omega(x), odd = x*Lambda'(x) at this location's root
-// (bit-planes, all 32 codewords; only the bits under the root mask are meaningful to the caller).
-template <int STRIDE>
-BS_FN uint32_t sweep_step(uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_t (&num)[8], uint32_t (&odd)[8])
-{
-    uint32_t cur[8];
-    ld8(O, 0, cur);
     advance_L<1>(L);
     uint32_t nz = 0;
 #pragma unroll
     for (int t = 0; t < 8; t++) {
-        uint32_t e = L[0][t], o = 0;
+        uint32_t v = L[0][t];
 #pragma unroll
-        for (int j = 1; j <= kT; j++) {
-            if (j & 1)
-                o ^= L[j][t];
-            else
-                e ^= L[j][t];
-        }
-        odd[t] = o;
-        nz |= e ^ o;
-        num[t] = 0;
+        for (int j = 1; j <= kT; j++)
+            v ^= L[j][t];
+        nz |= v;
     }
-    advance_O<STRIDE, 0>(O, cur, num);
     return ~nz;
 }
 
-} // namespace bs
+// ---- Forney on one list slot ----------------------------------------------------------------------------------
+// x = the root alpha^(k+1) found for each of the 32 codewords (planes).  Magnitude (src/decode.c:159-191,
+// fcr = 1 so num2 = 1):  Omega(x) / Lambda'(x)  =  x*Omega(x) / (sum of the odd-degree locator terms at x).
+// A vanishing numerator gives magnitude 0 (the reference does not count such a root either).
+template <int STRIDE>
+BS_FN void forney_slot(const uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_t (&x)[8])
+{
+    uint32_t num[8], odd[8], x2[8], o[8], on[8];
+    // Horner: Omega_15, then acc <- acc*x + Omega_j
+    ld8(O, kT - 1, num);
+    ld8(O, kT - 2, o);
+#pragma unroll
+    for (int j = kT - 2; j >= 0; j--) {
+        uint32_t acc[15];
+        if (j > 0)
+            ld8(O, j - 1, on);
+        BS_FENCE();
+        clear15(acc);
+        cp8(*reinterpret_cast<uint32_t(*)[8]>(&acc[0]), o);
+        mac(acc, num, x);
+        reduce(acc, num);
+        cp8(o, on);
+    }
+    mul(num, x, num);
+    sqr(x, x2);
+    cp8(odd, L[kT - 1]);
+#pragma unroll
+    for (int j = kT - 3; j >= 1; j -= 2) {
+        uint32_t acc[15];
+        clear15(acc);
+        cp8(*reinterpret_cast<uint32_t(*)[8]>(&acc[0]), L[j]);
+        mac(acc, odd, x2);
+        reduce(acc, odd);
+    }
+    mul(odd, x, odd);
+    inv(odd, odd);
+    mul(num, odd, x);
+}
 
 // ---- one lane, start to finish ----------------------------------------------------------------------------
-namespace bs {
-
 #if defined(__CUDA_ARCH__)
 #define BS_CTZ(x) (__ffs((int)(x)) - 1)
 #else
@@ -396,8 +463,8 @@ namespace bs {
 #endif
 
 constexpr int kWordsS = 8 * kNS;      // 256: syndromes in, per-codeword root lists out
-constexpr int kWordsB = 8 * kNL;      // 136: BM scratch, then evaluator terms (128) + root counters (8)
-constexpr int kCntBase = 8 * kT;      // word offset of the packed root counters inside the B area
+constexpr int kWordsB = 8 * kNL;      // 136: BM scratch (128), then evaluator terms (128) + root counters (8)
+constexpr int kCntBase = 8 * kT;      // word offset of the root counters (one byte per codeword) in the B area
 
 struct LaneOut {
     uint32_t K[7];       // k = 32 - 2*L per codeword (bit-planes, two's complement)
@@ -405,63 +472,61 @@ struct LaneOut {
     uint32_t padfail;    // bit c: a root fell into the zero padding (k < pad), src/decode.c:132-134
 };
 
-// bit c of 8 planes -> one byte
-BS_FN uint32_t gather_byte(const uint32_t (&p)[8], int c)
-{
-    uint32_t v = 0;
-#pragma unroll
-    for (int t = 7; t >= 0; t--)
-        v = (v << 1) | ((p[t] >> c) & 1u);
-    return v;
-}
-
-// Root list of codeword c: up to 16 entries (location | magnitude << 8) as half-words, words [8c, 8c+8) of
-// the S area; root counter of codeword c: byte (c & 3) of word kCntBase + (c >> 2) of the B area.
-// Forney's quotient (src/decode.c:159-191, num2 = 1 for fcr = 1) is formed per root with the log/antilog
-// tables logt[256] / expt[256] (a root is rare: ~1 per lane and location, so this stays off the bit-plane path).
+// Root list of codeword c: up to 16 half-word entries in words [8c, 8c+8) of the S area.  The Chien sweep
+// writes (location | root << 8); the Forney pass turns the high byte into the error magnitude.
+// Root counter of codeword c: byte c of the 8 words at kCntBase of the B area.
 template <int STRIDE>
-BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, const uint8_t *logt, const uint8_t *expt,
-                      LaneOut &out)
+BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, LaneOut &out)
 {
     uint32_t L[kNL][8];
     ribm<STRIDE>(S, B, L, out.K);
-    omega<STRIDE>(S, L, B); // evaluator terms replace the BM scratch (words 0..127)
+    omega<STRIDE>(S, L, B); // evaluator coefficients replace the BM scratch (words 0..127)
     for (int w = 0; w < kWordsS; w++)
         S.st(w, 0u);
     for (int w = 0; w < 8; w++)
         B.st(kCntBase + w, 0u);
+
     uint32_t padfail = 0;
+    uint32_t xr = 1; // alpha^(k+1) after the update below
 #pragma unroll 1
     for (int k = 0; k < 255; k++) {
-        uint32_t num[8], odd[8];
-        uint32_t m = sweep_step<STRIDE>(L, B, num, odd);
+        xr <<= 1;
+        if (xr & 0x100u)
+            xr ^= gf256::kPoly;
+        uint32_t m = chien_step(L);
         if (k < pad)
             padfail |= m;
         while (m) {
             const int c = BS_CTZ(m);
             m &= m - 1;
-            const uint32_t nb = gather_byte(num, c), db = gather_byte(odd, c);
-            uint32_t v = 0;
-            if (nb != 0) { // a zero numerator is a zero magnitude, not counted (src/decode.c:167-170)
-                uint32_t lg = (uint32_t)logt[nb] + 255u - (uint32_t)logt[db];
-                lg = lg >= 255u ? lg - 255u : lg;
-                v = expt[lg];
-            }
-            const int sh = 8 * (c & 3);
-            const uint32_t cw = B.ld(kCntBase + (c >> 2));
-            const uint32_t e = (cw >> sh) & 0xFFu;
-            B.st(kCntBase + (c >> 2), cw + (1u << sh));
-            if (e < (uint32_t)kT) {
-                const int idx = 8 * c + (int)(e >> 1);
-                S.st(idx, S.ld(idx) | (((uint32_t)k | (v << 8)) << (16 * (e & 1u))));
-            }
+            const uint32_t e = B.ld_byte(kCntBase + (c >> 2), c & 3);
+            B.st_byte(kCntBase + (c >> 2), c & 3, e + 1);
+            if (e < (uint32_t)kT)
+                S.st_half(8 * c + (int)(e >> 1), (int)(e & 1u), (uint32_t)k | (xr << 8));
         }
     }
     out.padfail = padfail;
-    // the sweep multiplied every coefficient by non-zero constants only: zero-ness is that of the locator
+    // every term is back at its coefficient (alpha^(255 j) = 1)
 #pragma unroll
     for (int j = 0; j < kNL; j++)
         out.nzL[j] = or8(L[j]);
+
+    // Forney, two list slots per pass: word w of every codeword's list holds slots 2w and 2w+1; a transpose
+    // turns the 32 codewords' words into planes (bytes 1 and 3 = the roots), and back afterwards
+#pragma unroll 1
+    for (int w = 0; w < 8; w++) {
+        uint32_t X[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            X[c] = S.ld(8 * c + w);
+        transpose32(X);
+        forney_slot<STRIDE>(L, B, *reinterpret_cast<uint32_t(*)[8]>(&X[8]));
+        forney_slot<STRIDE>(L, B, *reinterpret_cast<uint32_t(*)[8]>(&X[24]));
+        transpose32(X);
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            S.st(8 * c + w, X[c]);
+    }
 }
 
 enum { kDeclined = 0, kFail = 1, kOk = 2 };
@@ -484,7 +549,7 @@ BS_FN int classify(const Mem<STRIDE> B, const LaneOut &o, int c, int &nroots)
             lead = (o.nzL[j] >> c) & 1u;
     if (!lead || el == 0)
         return kDeclined; // degree below the register length: leave it to the literal stage
-    nroots = (int)((B.ld(kCntBase + (c >> 2)) >> (8 * (c & 3))) & 0xFFu);
+    nroots = (int)B.ld_byte(kCntBase + (c >> 2), c & 3);
     if (nroots != el || ((o.padfail >> c) & 1u))
         return kFail;
     return kOk;

@@ -22,7 +22,7 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
                     if ((syn[(g + c) * 32 + m] >> t) & 1)
                         S[8 * m + t] |= 1u << c;
         bs::LaneOut out;
-        bs::solve_lane<1>(bs::Mem<1>{S}, bs::Mem<1>{B}, pad, gf256::kExpLog.log, gf256::kExpLog.exp, out);
+        bs::solve_lane<1>(bs::Mem<1>{S}, bs::Mem<1>{B}, pad, out);
         for (size_t c = 0; c < cnt; c++) {
             int nr = 0;
             status[g + c] = (int8_t)bs::classify<1>(bs::Mem<1>{B}, out, (int)c, nr);
