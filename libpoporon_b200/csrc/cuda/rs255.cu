@@ -108,6 +108,15 @@ __device__ __forceinline__ void sts32(uint32_t saddr, uint32_t v)
     asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(saddr), "r"(v) : "memory");
 }
 
+// (a & m) | (b & ~m) in ONE LOP3 (immLut 0xE4).  Written as PTX because the optimiser otherwise "unfolds" the
+// masked merge into ((a ^ b) & m) ^ b plus separate ANDs: 4+ instructions per word instead of 1.
+__device__ __forceinline__ uint32_t merge_bits(uint32_t a, uint32_t b, uint32_t m)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(d) : "r"(a), "r"(b), "r"(m));
+    return d;
+}
+
 // 32x32 bit-matrix transpose in registers: x[r] bit c  <->  x[c] bit r.  An involution, used in both
 // directions (bytes -> planes on the way in, planes -> bytes on the way out).
 __device__ __forceinline__ void transpose32(uint32_t (&x)[32])
@@ -131,25 +140,35 @@ __device__ __forceinline__ void transpose32(uint32_t (&x)[32])
         if (r & 4)
             continue;
         const uint32_t a = x[r], b = x[r + 4];
-        x[r] = (a & 0x0F0F0F0Fu) | ((b << 4) & 0xF0F0F0F0u);
-        x[r + 4] = ((a >> 4) & 0x0F0F0F0Fu) | (b & 0xF0F0F0F0u);
+        x[r] = merge_bits(a, b << 4, 0x0F0F0F0Fu);
+        x[r + 4] = merge_bits(a >> 4, b, 0x0F0F0F0Fu);
     }
 #pragma unroll
     for (int r = 0; r < 32; r++) { // bit 1
         if (r & 2)
             continue;
         const uint32_t a = x[r], b = x[r + 2];
-        x[r] = (a & 0x33333333u) | ((b << 2) & 0xCCCCCCCCu);
-        x[r + 2] = ((a >> 2) & 0x33333333u) | (b & 0xCCCCCCCCu);
+        x[r] = merge_bits(a, b << 2, 0x33333333u);
+        x[r + 2] = merge_bits(a >> 2, b, 0x33333333u);
     }
 #pragma unroll
     for (int r = 0; r < 32; r++) { // bit 0
         if (r & 1)
             continue;
         const uint32_t a = x[r], b = x[r + 1];
-        x[r] = (a & 0x55555555u) | ((b << 1) & 0xAAAAAAAAu);
-        x[r + 1] = ((a >> 1) & 0x55555555u) | (b & 0xAAAAAAAAu);
+        x[r] = merge_bits(a, b << 1, 0x55555555u);
+        x[r + 1] = merge_bits(a >> 1, b, 0x55555555u);
     }
+}
+
+// a ^ b ^ c as ONE LOP3, spelled in PTX: given plain C xors ptxas re-associates "P ^ T1[a] ^ T2[b]" into chains
+// over the input planes (it does not see that the table entries are shared) and spends 213 instead of 158
+// instructions per LFSR step
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
 }
 
 // all 16 subset-XORs of four planes: T[s] = xor of b_k over the bits k set in s (11 XORs)
@@ -181,7 +200,7 @@ __device__ __forceinline__ void lfsr_update_one(uint32_t (&P)[16][8], const uint
     constexpr int J = JT >> 3, T = JT & 7;
     constexpr unsigned m = Masks<ROLE>::lfsr.m[J][T];
     if constexpr (J < 15)
-        P[J][T] = P[J + 1][T] ^ T1[m & 15] ^ T2[m >> 4];
+        P[J][T] = xor3(P[J + 1][T], T1[m & 15], T2[m >> 4]);
     else
         P[J][T] = T1[m & 15] ^ T2[m >> 4];
 }
@@ -208,7 +227,7 @@ __device__ __forceinline__ void linmap_one(uint32_t (&acc)[16][8], const uint32_
 {
     constexpr int Q = QT >> 3, T = QT & 7;
     constexpr unsigned m = M::v.m[K][OBASE + Q][T];
-    acc[Q][T] ^= T1[m & 15] ^ T2[m >> 4];
+    acc[Q][T] = xor3(acc[Q][T], T1[m & 15], T2[m >> 4]);
 }
 template <class M, int K, int OBASE, int... QT>
 __device__ __forceinline__ void linmap_all(uint32_t (&acc)[16][8], const uint32_t (&T1)[16], const uint32_t (&T2)[16],

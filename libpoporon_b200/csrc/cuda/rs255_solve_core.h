@@ -334,6 +334,18 @@ BS_FN void omega(const Mem<STRIDE> S, const uint32_t (&L)[kNL][8], const Mem<STR
     }
 }
 
+// (a & m) | (b & ~m): one LOP3 on the device (the optimiser would otherwise unfold the masked merge)
+BS_FN uint32_t merge_bits(uint32_t a, uint32_t b, uint32_t m)
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(d) : "r"(a), "r"(b), "r"(m));
+    return d;
+#else
+    return (a & m) | (b & ~m);
+#endif
+}
+
 // ---- 32x32 bit-matrix transpose: x[r] bit c <-> x[c] bit r (an involution) ---------------------------------
 BS_FN void transpose32(uint32_t (&x)[32])
 {
@@ -366,24 +378,24 @@ BS_FN void transpose32(uint32_t (&x)[32])
         if (r & 4)
             continue;
         const uint32_t a = x[r], b = x[r + 4];
-        x[r] = (a & 0x0F0F0F0Fu) | ((b << 4) & 0xF0F0F0F0u);
-        x[r + 4] = ((a >> 4) & 0x0F0F0F0Fu) | (b & 0xF0F0F0F0u);
+        x[r] = merge_bits(a, b << 4, 0x0F0F0F0Fu);
+        x[r + 4] = merge_bits(a >> 4, b, 0x0F0F0F0Fu);
     }
 #pragma unroll
     for (int r = 0; r < 32; r++) {
         if (r & 2)
             continue;
         const uint32_t a = x[r], b = x[r + 2];
-        x[r] = (a & 0x33333333u) | ((b << 2) & 0xCCCCCCCCu);
-        x[r + 2] = ((a >> 2) & 0x33333333u) | (b & 0xCCCCCCCCu);
+        x[r] = merge_bits(a, b << 2, 0x33333333u);
+        x[r + 2] = merge_bits(a >> 2, b, 0x33333333u);
     }
 #pragma unroll
     for (int r = 0; r < 32; r++) {
         if (r & 1)
             continue;
         const uint32_t a = x[r], b = x[r + 1];
-        x[r] = (a & 0x55555555u) | ((b << 1) & 0xAAAAAAAAu);
-        x[r + 1] = ((a >> 1) & 0x55555555u) | (b & 0xAAAAAAAAu);
+        x[r] = merge_bits(a, b << 1, 0x55555555u);
+        x[r + 1] = merge_bits(a >> 1, b, 0x55555555u);
     }
 }
 
