@@ -41,7 +41,6 @@ namespace {
 
 constexpr int kMsg = 223, kPar = 32;
 constexpr int kTile = 1024;              // codewords per CTA tile
-constexpr int kRingBytes = 32 * 3 * 512; // [i = 32][stage = 3][lane = 32][16 B]
 
 enum { MODE_ENCODE = 0, MODE_SCREEN = 1 };
 
@@ -254,59 +253,136 @@ __device__ __forceinline__ void linmap_vec(uint32_t (&acc)[16][8], uint32_t sbas
 }
 
 // ---------------------------------------------------------------------------------------------------
-// the LFSR kernel: one CTA = two warps (roles) x one tile of 1024 codewords at a time
+// the stream kernel: one CTA = two warps (roles) x one tile of 1024 codewords at a time
 // ---------------------------------------------------------------------------------------------------
+// Tile geometry.  Codewords are taken in blocks of 4096; a block is four tiles ("groups" G = 0..3).  Lane l of
+// the tile owns the 32 codewords  cw = 4096*block + 512*(l >> 2) + 16*i + r,  i = 0..31, where r is one of the
+// four residues (mod 16) of the group.  Consecutive i are 16 codewords apart, so all 32 streams of a lane
+// have the same byte offset o inside their 16-byte chunks whatever the stride is; and the host sorts the 16
+// residues by (o >> 2) before cutting them into groups, so (o >> 2) - the word offset - is the same for the
+// WHOLE tile.  That makes the chunk schedule uniform per CTA and a two-stage ring sufficient.
 struct LfsrArgs {
     const uint8_t *stream; // first byte of codeword 0's stream (data for ENCODE, packed record for SCREEN)
     size_t stride;         // bytes between consecutive codewords' streams
     int len;               // symbols fed to the LFSR (size, or size + 32 for SCREEN)
     size_t n;              // codewords
     const uint8_t *gend;   // one past the last readable byte of the stream buffer
+    uint64_t perm;         // nibble p: residue (codeword index mod 16) in slot p; group G = slots 4G..4G+3
+    uint32_t wbs;          // 2 bits per group: word offset (o >> 2) of the group's streams
     // ENCODE outputs
     uint8_t *parity;
     size_t parity_stride;
     uint8_t *ok;
     // SCREEN outputs
-    uint32_t *dmask; // [2 * groups]: per (group, role) 32-bit "state != 0" mask; group = tile*32 + lane
+    uint32_t *dmask; // [2 * groups]: per (tile, lane, role) 32-bit "state != 0" mask over i
     uint8_t *syn;    // [n][32]: raw evaluations V_q of the role's final state at its 16 roots
 };
 
-template <int MODE, int ROLE>
-__device__ __forceinline__ void lfsr_role(const LfsrArgs &A, uint8_t *ring)
+constexpr int kRingStage = 16384;          // [i = 32][lane = 32][16 B]
+constexpr int kRingBytes2 = 2 * kRingStage; // two stages
+constexpr int kWinBytes = 4096;            // one window of 4 symbols: [plane = 32][lane = 32] words
+constexpr int kSmemEncode = kRingBytes2 + 3 * kWinBytes;
+constexpr int kSmemScreen = kRingBytes2 + 2 * kWinBytes;
+
+__device__ __forceinline__ size_t tile_cw0(const LfsrArgs &A, size_t tile, int lane)
 {
+    const unsigned slot = 4u * (unsigned)(tile & 3) + (unsigned)(lane & 3);
+    const unsigned r = (unsigned)(A.perm >> (4u * slot)) & 15u;
+    return (tile >> 2) * 4096 + 512u * (unsigned)(lane >> 2) + r;
+}
+
+// one update of a role's 16-symbol register with the multiplier symbol u (8 planes):
+// P[j] <- P[j+1] ^ u * g_{15-j}
+template <int ROLE>
+__device__ __forceinline__ void lfsr_update(uint32_t (&P)[16][8], const uint32_t (&u)[8])
+{
+    uint32_t T1[16], T2[16];
+    subset_table(u[0], u[1], u[2], u[3], T1);
+    subset_table(u[4], u[5], u[6], u[7], T2);
+    lfsr_update_all<ROLE>(P, T1, T2, std::make_integer_sequence<int, 128>{});
+}
+
+// KIND 0: divider      u = d ^ P[0]                       (screen roles, encoder role 1)
+// KIND 1: divider that also emits the quotient symbol e = d ^ P[0] in place of d   (encoder role 0)
+// KIND 2: multiplier   u = d, emits e = d ^ P[0] in place of d   (encoder role 0, last 16 steps)
+template <int ROLE, int KIND>
+__device__ __forceinline__ void stream_step(uint32_t (&P)[16][8], uint32_t saddr /* plane 0 of the symbol, this lane */)
+{
+    uint32_t d[8], e[8];
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        d[t] = lds32(saddr + (uint32_t)(t * 128));
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        e[t] = d[t] ^ P[0][t];
+    if (KIND != 0) {
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            sts32(saddr + (uint32_t)(t * 128), e[t]);
+    }
+    if (KIND == 2)
+        lfsr_update<ROLE>(P, d);
+    else
+        lfsr_update<ROLE>(P, e);
+}
+
+template <int MODE, int ROLE>
+__device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
+{
+    constexpr int NB = MODE == MODE_ENCODE ? 3 : 2; // window buffers in rotation
     const int lane = threadIdx.x & 31;
-    const uint32_t ring_s = smem_u32(ring);
-    const uint32_t lane_s = ring_s + (uint32_t)lane * 16u;
-    const size_t ntiles = (A.n + kTile - 1) / kTile;
+    const uint32_t ring_s = smem_u32(smem);
+    const uint32_t lane_ring = ring_s + (uint32_t)lane * 16u;
+    const uint32_t lane_buf = ring_s + (uint32_t)kRingBytes2 + (uint32_t)lane * 4u;
+    const size_t ntiles = 4 * ((A.n + 4095) / 4096);
+    const int nW = (A.len + 3) >> 2;
 
     for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const size_t cw0 = tile * kTile + (size_t)lane;
-        const uint8_t *s0 = A.stream + cw0 * A.stride; // stream of (i = 0)
-        const uint32_t o = (uint32_t)((uintptr_t)s0 & 15u);
-        const uint8_t *a0 = s0 - o; // 16-byte aligned
-        const size_t istride = 32 * A.stride;
-        const int nchunks = (int)((o + (uint32_t)A.len + 15u) >> 4);
-        const int rounds = (A.len + 15) >> 4;
-        const uint32_t sel = 0x3210u + 0x1111u * (o & 3u); // PRMT selector re-aligning (lo, hi) words
-        const uint32_t wbase = o >> 2;
+        const size_t cw0 = tile_cw0(A, tile, lane);
+        const int wb = (int)((A.wbs >> (2u * (unsigned)(tile & 3))) & 3u);
+        const uint8_t *s0 = A.stream + cw0 * A.stride;
+        const uint32_t o = (uint32_t)((uintptr_t)s0 & 15u); // (o >> 2) == wb for every lane of the tile
+        const uint8_t *a0 = s0 - o;
+        const size_t istride = 16 * A.stride;
+        const int nchunks = (4 * wb + 3 + A.len + 15) >> 4;
+        const uint32_t sel = 0x3210u + 0x1111u * (o & 3u);
 
-        // this role fetches chunk `k` of its half of the codewords (i in [16*ROLE, 16*ROLE + 16))
-        auto fetch = [&](int k) {
-            if (k < nchunks) {
-                const uint32_t stage = (uint32_t)(k % 3);
+        // this role fetches chunk c of its half of the codewords (i in [16*ROLE, 16*ROLE + 16))
+        auto fetch = [&](int c) {
+            if (c < nchunks) {
+                const uint32_t dst = lane_ring + (uint32_t)((c & 1) * kRingStage);
 #pragma unroll
                 for (int ii = 0; ii < 16; ii++) {
                     const int i = 16 * ROLE + ii;
-                    const uint8_t *g = a0 + (size_t)i * istride + (size_t)k * 16;
+                    const uint8_t *g = a0 + (size_t)i * istride + (size_t)c * 16;
                     uint32_t nbytes = 0;
-                    if (cw0 + 32 * (size_t)i < A.n && g < A.gend) {
+                    if (cw0 + 16 * (size_t)i < A.n && g < A.gend) {
                         const size_t left = (size_t)(A.gend - g);
                         nbytes = left >= 16 ? 16u : (uint32_t)left;
                     }
-                    cp_async16(lane_s + (uint32_t)((i * 3 + stage) * 512), nbytes ? g : A.stream, nbytes);
+                    cp_async16(dst + (uint32_t)(i * 512), nbytes ? g : A.stream, nbytes);
                 }
             }
             cp_async_commit();
+        };
+
+        // bytes -> bit-planes of window W (symbols 4W .. 4W+3) into window buffer `slot`
+        auto transpose_window = [&](int W, int slot) {
+            const uint32_t jlo = (uint32_t)(wb + W), jhi = jlo + 1;
+            const uint32_t off_lo = ((jlo >> 2) & 1u) * (uint32_t)kRingStage + (jlo & 3u) * 4u;
+            const uint32_t off_hi = ((jhi >> 2) & 1u) * (uint32_t)kRingStage + (jhi & 3u) * 4u;
+            uint32_t X[32];
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+                const uint32_t lo = lds32(lane_ring + (uint32_t)(i * 512) + off_lo);
+                const uint32_t hi = lds32(lane_ring + (uint32_t)(i * 512) + off_hi);
+                X[i] = __byte_perm(lo, hi, sel);
+            }
+            transpose32(X); // X[8*y + t] = plane of bit t of symbol 4W + y
+            const uint32_t dst = lane_buf + (uint32_t)(slot * kWinBytes);
+#pragma unroll
+            for (int p = 0; p < 32; p++)
+                sts32(dst + (uint32_t)(p * 128), X[p]);
         };
 
         uint32_t P[16][8];
@@ -316,60 +392,90 @@ __device__ __forceinline__ void lfsr_role(const LfsrArgs &A, uint8_t *ring)
             for (int t = 0; t < 8; t++)
                 P[j][t] = 0;
 
-        __syncthreads(); // the previous tile's epilogue is done with the ring memory
+        __syncthreads(); // the previous tile's epilogue is done with the shared memory
         fetch(0);
         fetch(1);
-        for (int r = 0; r < rounds; r++) {
-            cp_async_wait_all();
-            __syncthreads(); // chunks <= r+1 of BOTH roles are visible; both roles are done with chunk r-1
-            fetch(r + 2);
+        cp_async_wait_all();
+        __syncthreads();
+        if (ROLE == 0)
+            transpose_window(0, 0);
+        __syncthreads();
+
+        // step w: the window-(w+1) transpose (roles alternate), then the register updates for window w
+        // (encoder role 1 runs one window behind role 0, on the quotient symbols role 0 left in place)
+        const int nsteps = MODE == MODE_ENCODE ? nW + 1 : nW;
+        int slot_cur = 0; // w % NB
 #pragma unroll 1
-            for (int win = 0; win < 4; win++) {
-                const int W = 4 * r + win;
-                if (4 * W >= A.len)
-                    break;
-                const uint32_t jlo = wbase + (uint32_t)W, jhi = jlo + 1;
-                const uint32_t off_lo = ((jlo >> 2) % 3u) * 512u + (jlo & 3u) * 4u;
-                const uint32_t off_hi = ((jhi >> 2) % 3u) * 512u + (jhi & 3u) * 4u;
-                uint32_t X[32];
-#pragma unroll
-                for (int i = 0; i < 32; i++) {
-                    const uint32_t lo = lds32(lane_s + (uint32_t)(i * 1536) + off_lo);
-                    const uint32_t hi = lds32(lane_s + (uint32_t)(i * 1536) + off_hi);
-                    X[i] = __byte_perm(lo, hi, sel);
+        for (int w = 0; w < nsteps; w++) {
+            const int slot_next = slot_cur + 1 == NB ? 0 : slot_cur + 1;
+            if (((w + wb) & 3) == 3)
+                fetch((w + wb + 5) >> 2);
+            if (w + 1 < nW && ((w + 1) & 1) == ROLE)
+                transpose_window(w + 1, slot_next);
+            if (MODE == MODE_ENCODE && ROLE == 1) {
+                if (w >= 1) {
+                    const int slot_prev = slot_cur == 0 ? NB - 1 : slot_cur - 1;
+                    const uint32_t src = lane_buf + (uint32_t)(slot_prev * kWinBytes);
+                    const int left = A.len - 4 * (w - 1);
+#pragma unroll 1
+                    for (int y = 0; y < 4; y++) {
+                        if (y < left)
+                            stream_step<ROLE, 0>(P, src + (uint32_t)(y * 1024));
+                    }
                 }
-                transpose32(X); // X[8*y + t] = plane of bit t of symbol 4W + y
-#pragma unroll
+            } else if (w < nW) {
+                const uint32_t src = lane_buf + (uint32_t)(slot_cur * kWinBytes);
+                const int left = A.len - 4 * w;
+#pragma unroll 1
                 for (int y = 0; y < 4; y++) {
-                    if (4 * W + y < A.len)
-                        lfsr_step<ROLE>(P, &X[8 * y]);
+                    if (y < left)
+                        stream_step<ROLE, MODE == MODE_ENCODE ? 1 : 0>(P, src + (uint32_t)(y * 1024));
                 }
             }
+            if (((w + wb) & 3) == 1)
+                cp_async_wait_all();
+            __syncthreads();
+            slot_cur = slot_next;
         }
         cp_async_wait_all();
-        __syncthreads(); // both roles finished reading the ring: it becomes epilogue scratch
-
-        // spill the state planes: [role][plane = 8j + t][lane]
-        const uint32_t st_s = ring_s + (uint32_t)(ROLE * 16384) + (uint32_t)lane * 4u;
-#pragma unroll
-        for (int j = 0; j < 16; j++)
-#pragma unroll
-            for (int t = 0; t < 8; t++)
-                sts32(st_s + (uint32_t)((8 * j + t) * 128), P[j][t]);
+        __syncthreads(); // every chunk has landed and been consumed: the ring becomes epilogue scratch
 
         uint32_t acc[16][8];
-#pragma unroll
-        for (int q = 0; q < 16; q++)
-#pragma unroll
-            for (int t = 0; t < 8; t++)
-                acc[q][t] = 0;
-
+        int out_half = ROLE; // which 16 bytes of the 32-byte output row this role writes
         if (MODE == MODE_ENCODE) {
-            __syncthreads(); // both states are in shared memory
-            // parity bytes [16*ROLE, 16*ROLE + 16) = (sA * FA + sB * FB) restricted to those coefficients
-            linmap_vec<CrtM<0>, 16 * ROLE>(acc, ring_s + (uint32_t)lane * 4u, std::make_integer_sequence<int, 16>{});
-            linmap_vec<CrtM<1>, 16 * ROLE>(acc, ring_s + 16384u + (uint32_t)lane * 4u,
-                                           std::make_integer_sequence<int, 16>{});
+            // parity = tB * gA + sA * x^16 (sA, tB: the final registers of roles 0 and 1).  Role 0 keeps going as
+            // a multiplier by gA, fed with tB's 16 symbols: the 16 symbols it emits are parity[0..15], the register
+            // it is left with is parity[16..31].
+            const uint32_t scr = ring_s + (uint32_t)lane * 4u;
+            if (ROLE == 1) {
+#pragma unroll
+                for (int j = 0; j < 16; j++)
+#pragma unroll
+                    for (int t = 0; t < 8; t++)
+                        sts32(scr + (uint32_t)((8 * j + t) * 128), P[j][t]);
+            }
+            __syncthreads();
+            if (ROLE == 0) {
+#pragma unroll 1
+                for (int k = 0; k < 16; k++)
+                    stream_step<0, 2>(P, scr + (uint32_t)(k * 1024));
+            }
+            __syncthreads();
+            if (ROLE == 0) {
+#pragma unroll
+                for (int j = 0; j < 16; j++)
+#pragma unroll
+                    for (int t = 0; t < 8; t++)
+                        acc[j][t] = P[j][t];
+                out_half = 1;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; j++)
+#pragma unroll
+                    for (int t = 0; t < 8; t++)
+                        acc[j][t] = lds32(scr + (uint32_t)((8 * j + t) * 128));
+                out_half = 0;
+            }
         } else {
             uint32_t nz = 0;
 #pragma unroll
@@ -380,6 +486,18 @@ __device__ __forceinline__ void lfsr_role(const LfsrArgs &A, uint8_t *ring)
             A.dmask[2 * (tile * 32 + (size_t)lane) + ROLE] = nz;
             if (!__any_sync(0xFFFFFFFFu, nz != 0))
                 continue; // every codeword of the tile is clean for this role: its 16 syndromes are zero
+            // spill the state planes: [role][plane = 8j + t][lane], then evaluate them at the role's 16 roots
+            const uint32_t st_s = ring_s + (uint32_t)(ROLE * 16384) + (uint32_t)lane * 4u;
+#pragma unroll
+            for (int j = 0; j < 16; j++)
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    sts32(st_s + (uint32_t)((8 * j + t) * 128), P[j][t]);
+#pragma unroll
+            for (int q = 0; q < 16; q++)
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    acc[q][t] = 0;
             __syncwarp();
             linmap_vec<SynMasks<ROLE>, 0>(acc, st_s, std::make_integer_sequence<int, 16>{});
         }
@@ -396,12 +514,12 @@ __device__ __forceinline__ void lfsr_role(const LfsrArgs &A, uint8_t *ring)
         }
 #pragma unroll
         for (int i = 0; i < 32; i++) {
-            const size_t cw = cw0 + 32 * (size_t)i;
+            const size_t cw = cw0 + 16 * (size_t)i;
             if (cw >= A.n)
                 continue;
             const uint4 v = make_uint4(B[0][i], B[1][i], B[2][i], B[3][i]);
             if (MODE == MODE_ENCODE) {
-                uint8_t *p = A.parity + cw * A.parity_stride + 16 * ROLE;
+                uint8_t *p = A.parity + cw * A.parity_stride + 16 * out_half;
                 if (((uintptr_t)p & 15u) == 0) {
                     *reinterpret_cast<uint4 *>(p) = v;
                 } else if (((uintptr_t)p & 3u) == 0) {
@@ -429,24 +547,27 @@ __global__ void __launch_bounds__(64, 4) rs255_lfsr_kernel(LfsrArgs A)
 {
     extern __shared__ __align__(16) uint8_t ring[];
     if ((threadIdx.x >> 5) == 0)
-        lfsr_role<MODE, 0>(A, ring);
+        stream_role<MODE, 0>(A, ring);
     else
-        lfsr_role<MODE, 1>(A, ring);
+        stream_role<MODE, 1>(A, ring);
 }
+
 
 // ---------------------------------------------------------------------------------------------------
 // compaction: clean codewords get their status here and cost nothing further; dirty ones are queued
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-rs255_compact_kernel(const uint32_t *__restrict__ dmask, size_t n, uint32_t *__restrict__ queue,
+rs255_compact_kernel(const uint32_t *__restrict__ dmask, size_t n, uint64_t invperm, uint32_t *__restrict__ queue,
                      uint32_t *__restrict__ counter, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
 {
     const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t flags = 0;
     if (cw < n) {
-        const size_t tile = cw / kTile;
-        const uint32_t within = (uint32_t)(cw % kTile);
-        const uint32_t i = within >> 5, l = within & 31;
+        // inverse of tile_cw0(): codeword -> (tile, lane, i)
+        const uint32_t within = (uint32_t)(cw & 4095u);
+        const uint32_t slot = (uint32_t)(invperm >> (4u * (within & 15u))) & 15u;
+        const uint32_t q = within >> 4, i = q & 31u, l = 4u * (q >> 5) + (slot & 3u);
+        const size_t tile = (cw >> 12) * 4 + (slot >> 2);
         const uint2 m = reinterpret_cast<const uint2 *>(dmask)[tile * 32 + l];
         flags = ((m.x >> i) & 1u) | (((m.y >> i) & 1u) << 1);
         if (!flags) {
@@ -649,7 +770,7 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
     ctx->d_rem = nullptr;
     ctx->d_counters = nullptr;
     ctx->queue_cap = 0;
-    const size_t tiles = (n + kTile - 1) / kTile;
+    const size_t tiles = 4 * ((n + 4095) / 4096);
     // queue [n rounded up to 4] | dmask [tiles * 64] | queue2 [n]
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64 + n) * sizeof(uint32_t)));
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32));
@@ -680,9 +801,9 @@ bool rs255_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size
 int rs255_init(poporon_cuda_rs *ctx)
 {
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_ENCODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kRingBytes));
+                                     kSmemEncode));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kRingBytes));
+                                     kSmemScreen));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
     (void)ctx;
     return 0;
@@ -690,9 +811,27 @@ int rs255_init(poporon_cuda_rs *ctx)
 
 static unsigned lfsr_grid(const poporon_cuda_rs *ctx, size_t n)
 {
-    const size_t tiles = (n + kTile - 1) / kTile;
+    const size_t tiles = 4 * ((n + 4095) / 4096);
     const size_t cap = (size_t)ctx->sm_count * 4; // 4 CTAs (8 warps) per SM, persistent over tiles
     return (unsigned)(tiles < cap ? tiles : cap);
+}
+
+// Tile geometry for a stream buffer (see LfsrArgs): sort the 16 residues r = codeword index mod 16 by the word
+// offset ((base + r*stride) mod 16) >> 2 of their streams and cut the sorted list into four groups.  Every
+// offset class has 4, 8 or 16 members whatever base and stride are, so a group never straddles two classes.
+static void tile_geometry(const uint8_t *stream, size_t stride, uint64_t *perm, uint64_t *invperm, uint32_t *wbs)
+{
+    unsigned slot = 0;
+    *perm = 0, *invperm = 0, *wbs = 0;
+    for (unsigned wb = 0; wb < 4; wb++)
+        for (unsigned r = 0; r < 16; r++)
+            if (((((uintptr_t)stream + r * stride) & 15u) >> 2) == wb) {
+                *perm |= (uint64_t)r << (4 * slot);
+                *invperm |= (uint64_t)slot << (4 * r);
+                if ((slot & 3u) == 0)
+                    *wbs |= wb << (2 * (slot >> 2));
+                slot++;
+            }
 }
 
 int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, size_t size, uint8_t *parity,
@@ -709,7 +848,9 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
     A.parity = parity;
     A.parity_stride = parity_stride;
     A.ok = ok;
-    rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64, kRingBytes, stream>>>(A);
+    uint64_t invperm;
+    tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
+    rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64, kSmemEncode, stream>>>(A);
     ctx->launches++;
     return check(cudaGetLastError(), "rs255 encode launch");
 }
@@ -723,7 +864,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     int rc = ensure_scratch(ctx, n);
     if (rc != 0)
         return rc;
-    const size_t tiles = (n + kTile - 1) / kTile;
+    const size_t tiles = 4 * ((n + 4095) / 4096);
     uint32_t *dmask = ctx->d_queue + ((n + 3) & ~(size_t)3);
     PP_CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 64, stream));
     LfsrArgs A{};
@@ -734,8 +875,10 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     A.gend = data + (n - 1) * data_stride + size + kPar;
     A.dmask = dmask;
     A.syn = ctx->d_rem;
-    rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64, kRingBytes, stream>>>(A);
-    rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(dmask, n, ctx->d_queue,
+    uint64_t invperm;
+    tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
+    rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64, kSmemScreen, stream>>>(A);
+    rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(dmask, n, invperm, ctx->d_queue,
                                                                                     ctx->d_counters, ok, corrected);
     const unsigned cblocks = (unsigned)ctx->sm_count * 8;
     const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
