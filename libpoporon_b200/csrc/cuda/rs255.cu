@@ -281,8 +281,8 @@ struct LfsrArgs {
 constexpr int kRingStage = 16384;          // [i = 32][lane = 32][16 B]
 constexpr int kRingBytes2 = 2 * kRingStage; // two stages
 constexpr int kWinBytes = 4096;            // one window of 4 symbols: [plane = 32][lane = 32] words
-constexpr int kSmemEncode = kRingBytes2 + 3 * kWinBytes;
-constexpr int kSmemScreen = kRingBytes2 + 2 * kWinBytes;
+constexpr int kSmemEncode = kRingBytes2 + 6 * kWinBytes;
+constexpr int kSmemScreen = kRingBytes2 + 4 * kWinBytes;
 
 __device__ __forceinline__ size_t tile_cw0(const LfsrArgs &A, size_t tile, int lane)
 {
@@ -305,13 +305,11 @@ __device__ __forceinline__ void lfsr_update(uint32_t (&P)[16][8], const uint32_t
 // KIND 0: divider      u = d ^ P[0]                       (screen roles, encoder role 1)
 // KIND 1: divider that also emits the quotient symbol e = d ^ P[0] in place of d   (encoder role 0)
 // KIND 2: multiplier   u = d, emits e = d ^ P[0] in place of d   (encoder role 0, last 16 steps)
+// d holds the 8 planes of the symbol at saddr (loaded by the caller, one symbol ahead of use).
 template <int ROLE, int KIND>
-__device__ __forceinline__ void stream_step(uint32_t (&P)[16][8], uint32_t saddr /* plane 0 of the symbol, this lane */)
+__device__ __forceinline__ void stream_step(uint32_t (&P)[16][8], const uint32_t (&d)[8], uint32_t saddr)
 {
-    uint32_t d[8], e[8];
-#pragma unroll
-    for (int t = 0; t < 8; t++)
-        d[t] = lds32(saddr + (uint32_t)(t * 128));
+    uint32_t e[8];
 #pragma unroll
     for (int t = 0; t < 8; t++)
         e[t] = d[t] ^ P[0][t];
@@ -326,60 +324,119 @@ __device__ __forceinline__ void stream_step(uint32_t (&P)[16][8], uint32_t saddr
         lfsr_update<ROLE>(P, e);
 }
 
+__device__ __forceinline__ void load_symbol(uint32_t (&d)[8], uint32_t saddr)
+{
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        d[t] = lds32(saddr + (uint32_t)(t * 128));
+}
+
+// `count` consecutive symbols starting at saddr (1 KB apart), the next symbol's planes loaded while the current
+// one is being processed
+template <int ROLE, int KIND>
+__device__ __forceinline__ void stream_run(uint32_t (&P)[16][8], uint32_t saddr, int count)
+{
+    if (count <= 0)
+        return;
+    uint32_t d0[8], d1[8];
+    load_symbol(d0, saddr);
+#pragma unroll 1
+    for (int y = 0; y < count; y += 2) {
+        if (y + 1 < count)
+            load_symbol(d1, saddr + 1024u);
+        stream_step<ROLE, KIND>(P, d0, saddr);
+        if (y + 1 < count) {
+            if (y + 2 < count)
+                load_symbol(d0, saddr + 2048u);
+            stream_step<ROLE, KIND>(P, d1, saddr + 1024u);
+        }
+        saddr += 2048u;
+    }
+}
+
+__device__ __forceinline__ uint2 lds64(uint32_t saddr)
+{
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];\n" : "=r"(v.x), "=r"(v.y) : "r"(saddr));
+    return v;
+}
+
 template <int MODE, int ROLE>
 __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
 {
-    constexpr int NB = MODE == MODE_ENCODE ? 3 : 2; // window buffers in rotation
+    // A step is two windows (8 symbols); window buffers come in sets of two, NB sets in rotation
+    constexpr int NB = MODE == MODE_ENCODE ? 3 : 2;
+    constexpr int kSetBytes = 2 * kWinBytes;
     const int lane = threadIdx.x & 31;
     const uint32_t ring_s = smem_u32(smem);
     const uint32_t lane_ring = ring_s + (uint32_t)lane * 16u;
     const uint32_t lane_buf = ring_s + (uint32_t)kRingBytes2 + (uint32_t)lane * 4u;
     const size_t ntiles = 4 * ((A.n + 4095) / 4096);
     const int nW = (A.len + 3) >> 2;
+    const int nS = (nW + 1) >> 1;
 
     for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const size_t cw0 = tile_cw0(A, tile, lane);
         const int wb = (int)((A.wbs >> (2u * (unsigned)(tile & 3))) & 3u);
         const uint8_t *s0 = A.stream + cw0 * A.stride;
         const uint32_t o = (uint32_t)((uintptr_t)s0 & 15u); // (o >> 2) == wb for every lane of the tile
-        const uint8_t *a0 = s0 - o;
         const size_t istride = 16 * A.stride;
+        const uint8_t *g0 = s0 - o + (size_t)(16 * ROLE) * istride; // chunk 0 of this role's first codeword
         const int nchunks = (4 * wb + 3 + A.len + 15) >> 4;
         const uint32_t sel = 0x3210u + 0x1111u * (o & 3u);
+        // whole tile inside the batch and every chunk inside the buffer: no per-copy checks (all but the last tiles)
+        const bool interior = ((tile >> 2) + 1) * 4096 <= A.n &&
+                              A.stream + (((tile >> 2) + 1) * 4096 - 1) * A.stride + (size_t)nchunks * 16 + 16 <= A.gend;
 
         // this role fetches chunk c of its half of the codewords (i in [16*ROLE, 16*ROLE + 16))
         auto fetch = [&](int c) {
             if (c < nchunks) {
-                const uint32_t dst = lane_ring + (uint32_t)((c & 1) * kRingStage);
+                const uint32_t dst = lane_ring + (uint32_t)((c & 1) * kRingStage + 16 * ROLE * 512);
+                const uint8_t *g = g0 + (size_t)c * 16;
+                if (interior) {
 #pragma unroll
-                for (int ii = 0; ii < 16; ii++) {
-                    const int i = 16 * ROLE + ii;
-                    const uint8_t *g = a0 + (size_t)i * istride + (size_t)c * 16;
-                    uint32_t nbytes = 0;
-                    if (cw0 + 16 * (size_t)i < A.n && g < A.gend) {
-                        const size_t left = (size_t)(A.gend - g);
-                        nbytes = left >= 16 ? 16u : (uint32_t)left;
+                    for (int ii = 0; ii < 16; ii++)
+                        cp_async16(dst + (uint32_t)(ii * 512), g + (size_t)ii * istride, 16u);
+                } else {
+#pragma unroll 1
+                    for (int ii = 0; ii < 16; ii++) {
+                        const uint8_t *gi = g + (size_t)ii * istride;
+                        uint32_t nbytes = 0;
+                        if (cw0 + 16 * (size_t)(16 * ROLE + ii) < A.n && gi < A.gend) {
+                            const size_t left = (size_t)(A.gend - gi);
+                            nbytes = left >= 16 ? 16u : (uint32_t)left;
+                        }
+                        cp_async16(dst + (uint32_t)(ii * 512), nbytes ? gi : A.stream, nbytes);
                     }
-                    cp_async16(dst + (uint32_t)(i * 512), nbytes ? g : A.stream, nbytes);
                 }
             }
             cp_async_commit();
         };
 
-        // bytes -> bit-planes of window W (symbols 4W .. 4W+3) into window buffer `slot`
-        auto transpose_window = [&](int W, int slot) {
-            const uint32_t jlo = (uint32_t)(wb + W), jhi = jlo + 1;
-            const uint32_t off_lo = ((jlo >> 2) & 1u) * (uint32_t)kRingStage + (jlo & 3u) * 4u;
-            const uint32_t off_hi = ((jhi >> 2) & 1u) * (uint32_t)kRingStage + (jhi & 3u) * 4u;
+        // bytes -> bit-planes of window W (symbols 4W .. 4W+3) into window buffer at dst (this lane's column).
+        // The window is words jlo, jlo+1 of every stream; jlo is the same for the whole tile.
+        auto transpose_window = [&](int W, uint32_t dst) {
+            const uint32_t jlo = (uint32_t)(wb + W);
             uint32_t X[32];
+            if ((jlo & 1u) == 0) { // one aligned 8-byte load per codeword
+                const uint32_t off = ((jlo >> 2) & 1u) * (uint32_t)kRingStage + (jlo & 3u) * 4u;
 #pragma unroll
-            for (int i = 0; i < 32; i++) {
-                const uint32_t lo = lds32(lane_ring + (uint32_t)(i * 512) + off_lo);
-                const uint32_t hi = lds32(lane_ring + (uint32_t)(i * 512) + off_hi);
-                X[i] = __byte_perm(lo, hi, sel);
+                for (int i = 0; i < 32; i++) {
+                    const uint2 v = lds64(lane_ring + (uint32_t)(i * 512) + off);
+                    X[i] = __byte_perm(v.x, v.y, sel);
+                }
+            } else { // the two words straddle an 8-byte boundary (possibly two ring stages)
+                const uint32_t jhi = jlo + 1;
+                const uint32_t off_lo = ((jlo >> 2) & 1u) * (uint32_t)kRingStage + (jlo & 3u) * 4u;
+                const uint32_t off_hi = ((jhi >> 2) & 1u) * (uint32_t)kRingStage + (jhi & 3u) * 4u;
+#pragma unroll
+                for (int i = 0; i < 32; i++) {
+                    const uint32_t lo = lds32(lane_ring + (uint32_t)(i * 512) + off_lo);
+                    const uint32_t hi = lds32(lane_ring + (uint32_t)(i * 512) + off_hi);
+                    X[i] = __byte_perm(lo, hi, sel);
+                }
             }
             transpose32(X); // X[8*y + t] = plane of bit t of symbol 4W + y
-            const uint32_t dst = lane_buf + (uint32_t)(slot * kWinBytes);
 #pragma unroll
             for (int p = 0; p < 32; p++)
                 sts32(dst + (uint32_t)(p * 128), X[p]);
@@ -397,49 +454,40 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
         fetch(1);
         cp_async_wait_all();
         __syncthreads();
-        if (ROLE == 0)
-            transpose_window(0, 0);
+        if (ROLE < nW)
+            transpose_window(ROLE, lane_buf + (uint32_t)(ROLE * kWinBytes)); // windows 0 and 1 -> set 0
         __syncthreads();
 
-        // step w: the window-(w+1) transpose (roles alternate), then the register updates for window w
-        // (encoder role 1 runs one window behind role 0, on the quotient symbols role 0 left in place)
-        const int nsteps = MODE == MODE_ENCODE ? nW + 1 : nW;
-        int slot_cur = 0; // w % NB
+        // step s: role r transposes window 2s+2+r into the next set, then both run the registers over windows
+        // 2s and 2s+1 (encoder role 1 runs one step behind role 0, on the quotient symbols role 0 left in place)
+        const int nsteps = MODE == MODE_ENCODE ? nS + 1 : nS;
+        int set_cur = 0, set_prev = NB - 1;
 #pragma unroll 1
-        for (int w = 0; w < nsteps; w++) {
-            const int slot_next = slot_cur + 1 == NB ? 0 : slot_cur + 1;
-            if (((w + wb) & 3) == 3)
-                fetch((w + wb + 5) >> 2);
-            if (w + 1 < nW && ((w + 1) & 1) == ROLE)
-                transpose_window(w + 1, slot_next);
+        for (int s = 0; s < nsteps; s++) {
+            const int set_next = set_cur + 1 == NB ? 0 : set_cur + 1;
+            const int v = 2 * s - 2 + wb;
+            if ((v & 2) == 0 && v >= 0)
+                fetch((v >> 2) + 2);
+            if (2 * s + 2 + ROLE < nW)
+                transpose_window(2 * s + 2 + ROLE, lane_buf + (uint32_t)(set_next * kSetBytes + ROLE * kWinBytes));
             if (MODE == MODE_ENCODE && ROLE == 1) {
-                if (w >= 1) {
-                    const int slot_prev = slot_cur == 0 ? NB - 1 : slot_cur - 1;
-                    const uint32_t src = lane_buf + (uint32_t)(slot_prev * kWinBytes);
-                    const int left = A.len - 4 * (w - 1);
-#pragma unroll 1
-                    for (int y = 0; y < 4; y++) {
-                        if (y < left)
-                            stream_step<ROLE, 0>(P, src + (uint32_t)(y * 1024));
-                    }
+                if (s >= 1) {
+                    const int left = A.len - 8 * (s - 1);
+                    stream_run<ROLE, 0>(P, lane_buf + (uint32_t)(set_prev * kSetBytes), left < 8 ? left : 8);
                 }
-            } else if (w < nW) {
-                const uint32_t src = lane_buf + (uint32_t)(slot_cur * kWinBytes);
-                const int left = A.len - 4 * w;
-#pragma unroll 1
-                for (int y = 0; y < 4; y++) {
-                    if (y < left)
-                        stream_step<ROLE, MODE == MODE_ENCODE ? 1 : 0>(P, src + (uint32_t)(y * 1024));
-                }
+            } else if (s < nS) {
+                const int left = A.len - 8 * s;
+                stream_run<ROLE, MODE == MODE_ENCODE ? 1 : 0>(P, lane_buf + (uint32_t)(set_cur * kSetBytes),
+                                                               left < 8 ? left : 8);
             }
-            if (((w + wb) & 3) == 1)
+            if ((v & 2) == 0 && v >= 0)
                 cp_async_wait_all();
             __syncthreads();
-            slot_cur = slot_next;
+            set_prev = set_cur;
+            set_cur = set_next;
         }
         cp_async_wait_all();
         __syncthreads(); // every chunk has landed and been consumed: the ring becomes epilogue scratch
-
         uint32_t acc[16][8];
         int out_half = ROLE; // which 16 bytes of the 32-byte output row this role writes
         if (MODE == MODE_ENCODE) {
@@ -456,9 +504,7 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
             }
             __syncthreads();
             if (ROLE == 0) {
-#pragma unroll 1
-                for (int k = 0; k < 16; k++)
-                    stream_step<0, 2>(P, scr + (uint32_t)(k * 1024));
+                stream_run<0, 2>(P, scr, 16);
             }
             __syncthreads();
             if (ROLE == 0) {
