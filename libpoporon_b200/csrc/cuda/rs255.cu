@@ -558,31 +558,47 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
                 B[w][c] = flat[32 * w + c];
             transpose32(B[w]);
         }
-#pragma unroll
-        for (int i = 0; i < 32; i++) {
-            const size_t cw = cw0 + 16 * (size_t)i;
-            if (cw >= A.n)
-                continue;
-            const uint4 v = make_uint4(B[0][i], B[1][i], B[2][i], B[3][i]);
-            if (MODE == MODE_ENCODE) {
-                uint8_t *p = A.parity + cw * A.parity_stride + 16 * out_half;
-                if (((uintptr_t)p & 15u) == 0) {
-                    *reinterpret_cast<uint4 *>(p) = v;
-                } else if (((uintptr_t)p & 3u) == 0) {
-                    reinterpret_cast<uint32_t *>(p)[0] = v.x;
-                    reinterpret_cast<uint32_t *>(p)[1] = v.y;
-                    reinterpret_cast<uint32_t *>(p)[2] = v.z;
-                    reinterpret_cast<uint32_t *>(p)[3] = v.w;
+        if (MODE == MODE_ENCODE) {
+            // 16 parity bytes per codeword at an arbitrary byte alignment `al` (the same for all 32 codewords of
+            // a lane: they are 16 strides apart): three whole words through a funnel shift, the first and last
+            // partial words as single bytes (or one more whole word when al == 0)
+            uint8_t *p0 = A.parity + cw0 * A.parity_stride + 16 * out_half;
+            const uint32_t al = (uint32_t)((uintptr_t)p0 & 3u), sh = 8u * al;
+            p0 -= al;
+            const size_t pstep = 16 * A.parity_stride;
+#pragma unroll 4
+            for (int i = 0; i < 32; i++) {
+                if (cw0 + 16 * (size_t)i >= A.n)
+                    break;
+                uint8_t *q = p0 + (size_t)i * pstep; // 4-byte aligned
+                const uint32_t w0 = B[0][i], w1 = B[1][i], w2 = B[2][i], w3 = B[3][i];
+                uint32_t *qw = reinterpret_cast<uint32_t *>(q);
+                qw[1] = __funnelshift_l(w0, w1, sh);
+                qw[2] = __funnelshift_l(w1, w2, sh);
+                qw[3] = __funnelshift_l(w2, w3, sh);
+                if (al == 0) {
+                    qw[0] = w0;
                 } else {
-                    const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                    for (int b = 0; b < 16; b++)
-                        p[b] = (uint8_t)(w4[b >> 2] >> (8 * (b & 3)));
+                    q[3] = (uint8_t)(w0 >> (24u - sh));
+                    if (al <= 2)
+                        q[2] = (uint8_t)(w0 >> (16u - sh));
+                    if (al <= 1)
+                        q[1] = (uint8_t)w0;
+                    const uint32_t tail = w3 >> (32u - sh);
+                    q[16] = (uint8_t)tail;
+                    if (al >= 2)
+                        q[17] = (uint8_t)(tail >> 8);
+                    if (al >= 3)
+                        q[18] = (uint8_t)(tail >> 16);
                 }
-                if (ROLE == 0 && A.ok)
-                    A.ok[cw] = 1;
-            } else {
-                *reinterpret_cast<uint4 *>(A.syn + cw * 32 + 16 * ROLE) = v;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+                const size_t cw = cw0 + 16 * (size_t)i;
+                if (cw >= A.n)
+                    continue;
+                *reinterpret_cast<uint4 *>(A.syn + cw * 32 + 16 * ROLE) = make_uint4(B[0][i], B[1][i], B[2][i], B[3][i]);
             }
         }
     }
@@ -896,6 +912,8 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
     A.ok = ok;
     uint64_t invperm;
     tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
+    if (ok)
+        PP_CUDA_TRY(cudaMemsetAsync(ok, 1, n, stream)); // the encoder cannot fail (src/encode.c:17-145 returns true)
     rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64, kSmemEncode, stream>>>(A);
     ctx->launches++;
     return check(cudaGetLastError(), "rs255 encode launch");
