@@ -494,7 +494,7 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
             // parity = tB * gA + sA * x^16 (sA, tB: the final registers of roles 0 and 1).  Role 0 keeps going as
             // a multiplier by gA, fed with tB's 16 symbols: the 16 symbols it emits are parity[0..15], the register
             // it is left with is parity[16..31].
-            const uint32_t scr = ring_s + (uint32_t)lane * 4u;
+            const uint32_t scr = lane_buf; // the window sets are free now (16 KB needed, 24 KB there)
             if (ROLE == 1) {
 #pragma unroll
                 for (int j = 0; j < 16; j++)
@@ -559,37 +559,77 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
             transpose32(B[w]);
         }
         if (MODE == MODE_ENCODE) {
-            // 16 parity bytes per codeword at an arbitrary byte alignment `al` (the same for all 32 codewords of
-            // a lane: they are 16 strides apart): three whole words through a funnel shift, the first and last
-            // partial words as single bytes (or one more whole word when al == 0)
-            uint8_t *p0 = A.parity + cw0 * A.parity_stride + 16 * out_half;
-            const uint32_t al = (uint32_t)((uintptr_t)p0 & 3u), sh = 8u * al;
-            p0 -= al;
-            const size_t pstep = 16 * A.parity_stride;
-#pragma unroll 4
-            for (int i = 0; i < 32; i++) {
-                if (cw0 + 16 * (size_t)i >= A.n)
-                    break;
-                uint8_t *q = p0 + (size_t)i * pstep; // 4-byte aligned
-                const uint32_t w0 = B[0][i], w1 = B[1][i], w2 = B[2][i], w3 = B[3][i];
-                uint32_t *qw = reinterpret_cast<uint32_t *>(q);
-                qw[1] = __funnelshift_l(w0, w1, sh);
-                qw[2] = __funnelshift_l(w1, w2, sh);
-                qw[3] = __funnelshift_l(w2, w3, sh);
-                if (al == 0) {
-                    qw[0] = w0;
-                } else {
-                    q[3] = (uint8_t)(w0 >> (24u - sh));
-                    if (al <= 2)
-                        q[2] = (uint8_t)(w0 >> (16u - sh));
-                    if (al <= 1)
-                        q[1] = (uint8_t)w0;
-                    const uint32_t tail = w3 >> (32u - sh);
-                    q[16] = (uint8_t)tail;
-                    if (al >= 2)
-                        q[17] = (uint8_t)(tail >> 8);
-                    if (al >= 3)
-                        q[18] = (uint8_t)(tail >> 16);
+            // Stage the 32-byte parity rows in the (idle) ring, row = 32*i + lane, then let 8 threads write one row:
+            // a store instruction then covers 8 whole rows (8-16 sectors) instead of 32 different ones.
+#pragma unroll
+            for (int i = 0; i < 32; i++)
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};\n" ::"r"(ring_s + (uint32_t)((32 * i + lane) * 32 + 16 * out_half)),
+                             "r"(B[0][i]), "r"(B[1][i]), "r"(B[2][i]), "r"(B[3][i])
+                             : "memory");
+            __syncthreads();
+            // pass 1, whole words: thread (t & 7) = s of a group of 8 writes aligned word s+1 of the row (s < 7;
+            // s = 7 writes aligned word 0 when the row happens to be 4-byte aligned).  Rows of this thread:
+            // 32*i + 8*k + (t >> 3), k = 0..3, i.e. codeword i of lane 8*k + (t >> 3).
+            {
+                const int t = (int)threadIdx.x, sub = t & 7;
+                uint8_t *gq[4];   // address of this thread's word in row i = 0
+                uint32_t shv[4];  // funnel shift (bits)
+                int cnt[4];       // rows (values of i) to write
+                const uint32_t wsel = sub < 7 ? (uint32_t)(4 * sub) : 0u; // row byte offset of the low source word
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const size_t c0 = tile_cw0(A, tile, 8 * k + (t >> 3));
+                    uint8_t *p = A.parity + c0 * A.parity_stride;
+                    const uint32_t al = (uint32_t)((uintptr_t)p & 3u);
+                    gq[k] = p - al + (sub < 7 ? 4 * (sub + 1) : 0);
+                    shv[k] = sub < 7 ? 8u * al : 32u; // s = 7: funnel(x, w0, 32 & 31 = 0) = w0
+                    const size_t rows = c0 < A.n ? (A.n - c0 + 15) / 16 : 0;
+                    cnt[k] = (sub == 7 && al != 0) ? 0 : (int)(rows < 32 ? rows : 32);
+                }
+                const size_t pstep = 16 * A.parity_stride;
+                uint32_t row_s = ring_s + (uint32_t)((t >> 3) * 32) + wsel;
+#pragma unroll 1
+                for (int i = 0; i < 32; i++) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (i < cnt[k]) {
+                            const uint32_t lo = lds32(row_s + (uint32_t)(k * 256));
+                            const uint32_t hi = sub < 7 ? lds32(row_s + (uint32_t)(k * 256 + 4)) : lo;
+                            *reinterpret_cast<uint32_t *>(gq[k]) = __funnelshift_l(lo, hi, shv[k]);
+                        }
+                        gq[k] += pstep;
+                    }
+                    row_s += 1024u;
+                }
+            }
+            // pass 2, the partial words at both ends of a row that is not 4-byte aligned: every thread takes rows of
+            // its own lane (i = 2*j + role)
+            {
+                uint8_t *p = A.parity + cw0 * A.parity_stride;
+                const uint32_t al = (uint32_t)((uintptr_t)p & 3u), sh = 8u * al;
+                if (al != 0) {
+                    const size_t pstep = 16 * A.parity_stride;
+                    uint8_t *q = p - al + (size_t)ROLE * pstep;
+                    uint32_t row_s = ring_s + (uint32_t)((32 * ROLE + lane) * 32);
+#pragma unroll 1
+                    for (int i = ROLE; i < 32; i += 2) {
+                        if (cw0 + 16 * (size_t)i < A.n) {
+                            const uint32_t w0 = lds32(row_s), w7 = lds32(row_s + 28u);
+                            q[3] = (uint8_t)(w0 >> (24u - sh));
+                            if (al <= 2)
+                                q[2] = (uint8_t)(w0 >> (16u - sh));
+                            if (al <= 1)
+                                q[1] = (uint8_t)w0;
+                            const uint32_t tail = w7 >> (32u - sh);
+                            q[32] = (uint8_t)tail;
+                            if (al >= 2)
+                                q[33] = (uint8_t)(tail >> 8);
+                            if (al >= 3)
+                                q[34] = (uint8_t)(tail >> 16);
+                        }
+                        q += 2 * pstep;
+                        row_s += 2048u;
+                    }
                 }
             }
         } else {
