@@ -758,8 +758,8 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 // Codewords the solver declines (register length > 16 or a vanishing leading coefficient - uncorrectable
 // words only) are appended to a second queue for the literal per-codeword stage.
 // ---------------------------------------------------------------------------------------------------
-constexpr int kSolveWords = bs::kWordsS + bs::kWordsB;
-constexpr int kSolveSmem = kSolveWords * 128;
+constexpr int kSolveWords = bs::kWordsS + bs::kWordsB + 32; // + the 32 queue entries of the lane
+constexpr int kSolveSmem = kSolveWords * 128 + 512;          // + exp / log tables (256 B each)
 
 template <int W>
 __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], const uint8_t *__restrict__ syn_raw,
@@ -794,14 +794,37 @@ __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], 
 
 __global__ void __launch_bounds__(32, 4)
 rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *parity, size_t parity_stride,
-                   const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
-                   const uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2,
-                   uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+                   uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter, uint8_t *__restrict__ syn_raw,
+                   uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2, uint8_t *__restrict__ ok,
+                   uint32_t *__restrict__ corrected)
 {
     extern __shared__ __align__(16) uint32_t solve_smem[];
     const int lane = threadIdx.x;
     const bs::Mem<32> S{solve_smem + lane};
     const bs::Mem<32> B{solve_smem + bs::kWordsS * 32 + lane};
+    const bs::Mem<32> E{solve_smem + (bs::kWordsS + bs::kWordsB) * 32 + lane};
+    uint8_t *exp_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWords * 32);
+    uint8_t *log_tab = exp_tab + 256;
+    {
+        // exp_tab[i] = alpha^i (i = 0..255), log_tab[alpha^i] = i mod 255: each lane fills 8 consecutive powers
+        uint32_t x = 1;
+        for (int i = 0; i < 8 * lane; i++) {
+            x <<= 1;
+            if (x & 0x100u)
+                x ^= gf256::kPoly;
+        }
+        for (int i = 8 * lane; i < 8 * lane + 8; i++) {
+            exp_tab[i] = (uint8_t)x;
+            if (i < 255)
+                log_tab[x] = (uint8_t)i;
+            x <<= 1;
+            if (x & 0x100u)
+                x ^= gf256::kPoly;
+        }
+        if (lane == 0)
+            log_tab[0] = 0;
+    }
+    __syncwarp();
     const uint32_t total = *counter;
     const int pad = kMsg - (int)size;
 
@@ -812,52 +835,133 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
             for (int c = 0; c < 32; c++) {
                 const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
                 ent[c] = q < total ? queue[q] : 0xFFFFFFFFu;
+                E.st(c, ent[c]);
             }
             solve_load_syndromes<0>(ent, syn_raw, S);
         }
+        uint32_t L[bs::kLS][8];
         bs::LaneOut out;
-        bs::solve_lane<32>(S, B, pad, out);
+        bs::solve_lane<32>(S, B, pad, exp_tab, L, out);
 
-        // Corrections are applied with word-wide atomic XORs (RED.XOR, no return value): nothing in this loop
-        // waits on memory, and bytes of neighbouring records that share a word cannot be lost.
-        uint32_t next_entry = g0 + (uint32_t)lane < total ? queue[g0 + (uint32_t)lane] : 0u;
+        // Outcome of every codeword of the lane.  What the solver declines goes to the literal stage.  A decodable
+        // codeword gets an error record in place of its (now dead) raw syndrome row: bytes 0..15 the roots
+        // x = alpha^(location + 1), bytes 16..31 the magnitudes; rs255_apply_kernel turns the records into
+        // corrections.  Queue entries of all other codewords are blanked so that the apply kernel skips them.
+        uint32_t okmask = 0;
+        int maxroots = 0;
 #pragma unroll 1
         for (int c = 0; c < 32; c++) {
-            const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
-            const uint32_t entry = next_entry;
-            if (c + 1 < 32 && q + 32u < total)
-                next_entry = queue[q + 32u];
-            if (q >= total)
+            const uint32_t entry = E.ld(c);
+            if (entry == 0xFFFFFFFFu)
                 continue;
-            const size_t cw = entry & 0x3FFFFFFFu;
+            const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
             int nroots = 0;
-            const int st = bs::classify<32>(B, out, c, nroots);
+            const int st = bs::classify<32>(S, out, c, nroots);
+            if (st == bs::kOk) {
+                okmask |= 1u << c;
+                maxroots = nroots > maxroots ? nroots : maxroots;
+                uint4 *row = reinterpret_cast<uint4 *>(syn_raw + (size_t)(entry & 0x3FFFFFFFu) * 32);
+                row[0] = make_uint4(S.ld(bs::kListBase + 4 * c), S.ld(bs::kListBase + 4 * c + 1),
+                                    S.ld(bs::kListBase + 4 * c + 2), S.ld(bs::kListBase + 4 * c + 3));
+                row[1] = make_uint4(0u, 0u, 0u, 0u);
+                continue;
+            }
+            queue[q] = 0xFFFFFFFFu;
             if (st == bs::kDeclined) {
                 queue2[atomicAdd(counter2, 1u)] = entry;
+            } else {
+                const size_t cw = entry & 0x3FFFFFFFu;
+                if (ok)
+                    ok[cw] = 0;
+                if (corrected)
+                    corrected[cw] = 0;
+            }
+        }
+
+        // Forney on four list slots at a time; the magnitude words go to the error records
+        uint32_t nzc[5] = {0u, 0u, 0u, 0u, 0u};
+#pragma unroll 1
+        for (int w = 0; w < 4; w++) {
+            if (!__any_sync(0xFFFFFFFFu, maxroots > 4 * w))
+                break;
+            bs::forney_slots<32>(L, B, S, w, nzc);
+            uint32_t X[32];
+            bs::magnitude_words<32>(S, X);
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+                if (((okmask >> c) & 1u) && X[c] != 0u)
+                    reinterpret_cast<uint32_t *>(syn_raw + (size_t)(E.ld(c) & 0x3FFFFFFFu) * 32 + 16)[w] = X[c];
+            }
+        }
+#pragma unroll 1
+        for (int c = 0; c < 32; c++) {
+            if (!((okmask >> c) & 1u))
                 continue;
-            }
+            const size_t cw = E.ld(c) & 0x3FFFFFFFu;
             uint32_t nnz = 0;
-            if (st == bs::kOk) {
-                uint8_t *d = data + cw * data_stride;
-                uint8_t *p = parity + cw * parity_stride;
-                for (int e = 0; e < nroots; e++) {
-                    const uint32_t v = (S.ld(8 * c + (e >> 1)) >> (16 * (e & 1))) & 0xFFFFu;
-                    const uint32_t mag = v >> 8;
-                    const int pos = (int)(v & 0xFFu) - pad; // >= 0: no root fell into the padding
-                    if (mag) {
-                        nnz++;
-                        uint8_t *a = pos < (int)size ? d + pos : p + (pos - (int)size);
-                        const uintptr_t ua = (uintptr_t)a;
-                        atomicXor(reinterpret_cast<unsigned int *>(ua & ~(uintptr_t)3), mag << (8u * (unsigned)(ua & 3u)));
-                    }
-                }
-            }
+#pragma unroll
+            for (int b = 0; b < 5; b++)
+                nnz |= ((nzc[b] >> c) & 1u) << b;
             if (ok)
-                ok[cw] = st == bs::kOk ? 1 : 0;
+                ok[cw] = 1;
             if (corrected)
                 corrected[cw] = nnz;
         }
         __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// corrections from the error records of the solver: one thread per queued codeword, at full occupancy, so
+// that the scattered read-modify-writes (about one 32-byte sector per corrected byte) are bound by memory
+// throughput and not by one warp's store queue.  Word-wide atomic XORs (RED.XOR, no return value): bytes of
+// neighbouring records that share a word cannot be lost.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+rs255_apply_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *parity, size_t parity_stride,
+                   const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+                   const uint8_t *__restrict__ records)
+{
+    __shared__ uint8_t log_tab[256];
+    {
+        // log_tab[alpha^i] = i, i = 0..254 (thread i computes alpha^i by square-and-multiply on the exponent bits)
+        const int i = (int)threadIdx.x;
+        if (i < 255) {
+            uint32_t x = 1, b = 2; // b = alpha^(2^j)
+            for (int j = 0; j < 8; j++) {
+                if ((i >> j) & 1)
+                    x = gf256::mul((uint8_t)x, (uint8_t)b);
+                b = gf256::mul((uint8_t)b, (uint8_t)b);
+            }
+            log_tab[x] = (uint8_t)i;
+        }
+        if (i == 255)
+            log_tab[0] = 0;
+    }
+    __syncthreads();
+    const uint32_t total = *counter;
+    const int pad = kMsg - (int)size;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
+        const uint32_t entry = queue[q];
+        if (entry == 0xFFFFFFFFu)
+            continue;
+        const size_t cw = entry & 0x3FFFFFFFu;
+        const uint4 *row = reinterpret_cast<const uint4 *>(records + cw * 32);
+        const uint4 xs4 = row[0], mg4 = row[1];
+        const uint32_t xs[4] = {xs4.x, xs4.y, xs4.z, xs4.w}, mg[4] = {mg4.x, mg4.y, mg4.z, mg4.w};
+        uint8_t *d = data + cw * data_stride;
+        uint8_t *p = parity + cw * parity_stride;
+#pragma unroll
+        for (int e = 0; e < 16; e++) {
+            const uint32_t mag = (mg[e >> 2] >> (8 * (e & 3))) & 0xFFu;
+            if (mag) {
+                const int lg = (int)log_tab[(xs[e >> 2] >> (8 * (e & 3))) & 0xFFu]; // x = alpha^(k+1)
+                const int pos = (lg == 0 ? 254 : lg - 1) - pad;                      // >= 0: no root in the padding
+                uint8_t *a = pos < (int)size ? d + pos : p + (pos - (int)size);
+                const uintptr_t ua = (uintptr_t)a;
+                atomicXor(reinterpret_cast<unsigned int *>(ua & ~(uintptr_t)3), mag << (8u * (unsigned)(ua & 3u)));
+            }
+        }
     }
 }
 
@@ -994,9 +1098,11 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         rs255_solve_kernel<<<(unsigned)(groups < cap ? groups : cap), 32, kSolveSmem, stream>>>(
             data, data_stride, size, parity, parity_stride, ctx->d_queue, ctx->d_counters, ctx->d_rem, queue2,
             ctx->d_counters + 1, ok, corrected);
+        rs255_apply_kernel<<<(unsigned)ctx->sm_count * 8, 256, 0, stream>>>(data, data_stride, size, parity, parity_stride,
+                                                                            ctx->d_queue, ctx->d_counters, ctx->d_rem);
         cq = queue2;
         cc = ctx->d_counters + 1;
-        ctx->launches++;
+        ctx->launches += 2;
     }
     rs255_correct_kernel<<<cblocks, 128, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride, size, parity,
                                                       parity_stride, cq, cc, ctx->d_rem, pos, pos_stride, cnt, ok,

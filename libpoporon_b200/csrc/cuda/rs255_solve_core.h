@@ -15,10 +15,11 @@
 //     non-zero scalar multiple of the reference's, so degree, roots, L and the Forney ratio are identical;
 //   * the length test runs on a bitsliced counter k = r - 1 - 2*el (k >= 0  <=>  2*el <= r - 1;
 //     length change: k <- -k - 1 = ~k; otherwise k <- k + 1);
-//   * Chien + Forney are one sweep over the 255 locations: per location the 16 locator terms and 16
-//     evaluator terms are advanced by constant multipliers and the locator value tested for zero; where it
-//     is zero (about one codeword per lane and location) x*Omega(x) and x*Lambda'(x) are gathered from the
-//     planes and divided with a 512-byte log/antilog table.
+//   * the Chien search advances the 16 locator terms by constant multipliers location by location and
+//     tests the sum for zero; the root masks are transposed in blocks of 32 locations and the roots
+//     x = alpha^(k+1) appended to a byte list per codeword (about one root per lane and location);
+//   * Forney's formula then runs bitsliced on the list slots (slot e of all 32 codewords at once):
+//     x*Omega(x) by Horner, x*Lambda'(x) from the odd terms, the quotient through a^254.
 //
 // Domain.  The solver keeps 17 locator coefficients: it is exact for every codeword whose final register
 // length L is <= 16 and whose locator has degree L.  Anything else (L > 16, or a vanishing leading
@@ -221,16 +222,50 @@ BS_FN uint32_t or8(const uint32_t (&a)[8])
     return (a[0] | a[1] | a[2]) | (a[3] | a[4] | a[5]) | (a[6] | a[7]);
 }
 
-// ---- inversion-free Berlekamp-Massey ---------------------------------------------------------------------
-// S: 32 syndromes, word (8*m + t) = plane t of S_{m+1}.  B: scratch of kNL*8 words.
-// On return L[i] is the locator (a non-zero multiple of the reference's lambda), K the counter planes after
-// the last iteration (k = 32 - 2*el, two's complement, 7 planes).
-template <int STRIDE>
-BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kNL][8], uint32_t (&K)[7])
+// (a & m) | (b & ~m): one LOP3 on the device (the optimiser would otherwise unfold the masked merge)
+BS_FN uint32_t merge_bits(uint32_t a, uint32_t b, uint32_t m)
 {
-    uint32_t gamma[8];
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(d) : "r"(a), "r"(b), "r"(m));
+    return d;
+#else
+    return (a & m) | (b & ~m);
+#endif
+}
+
+// ---- inversion-free Berlekamp-Massey ---------------------------------------------------------------------
+// S: 32 syndromes, word (8*m + t) = plane t of S_{m+1}.  B: scratch of kT*8 words.
+// On return L[0..16] is the locator (a non-zero multiple of the reference's lambda; L[17] is padding), K the
+// counter planes after the last iteration (k = 32 - 2*el, two's complement, 7 planes).
+//
+// One pass over the coefficients per iteration r: T_i = gamma*L_i + Delta_r*B_{i-1} replaces L_i, B_i becomes
+// L_i or B_{i-1}, and T_i * S_{r+1-i} is accumulated straight into the NEXT discrepancy Delta_{r+1}.
+// Instruction-cache shape: the 18 coefficient slots are three groups of six; the loop body is written for the
+// group held in L[0..5] and the groups are rotated through those registers (moves, which run on the FMA pipe),
+// so the body is 6 coefficient steps (~25 KB of SASS) instead of 17 (the straight-line version ran at a third
+// of the ALU rate, fetch-bound: tools/ubench_icache.cu).
+constexpr int kLS = 18; // coefficient slots (17 used)
+
+BS_FN void rotate_groups(uint32_t (&L)[kLS][8])
+{
 #pragma unroll
-    for (int i = 0; i < kNL; i++)
+    for (int j = 0; j < 6; j++)
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            const uint32_t tmp = L[j][t];
+            L[j][t] = L[j + 6][t];
+            L[j + 6][t] = L[j + 12][t];
+            L[j + 12][t] = tmp;
+        }
+}
+
+template <int STRIDE>
+BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uint32_t (&K)[7])
+{
+    uint32_t gamma[8], delta[8];
+#pragma unroll
+    for (int i = 0; i < kLS; i++)
 #pragma unroll
         for (int t = 0; t < 8; t++) {
             L[i][t] = (i == 0 && t == 0) ? 0xFFFFFFFFu : 0u;
@@ -243,107 +278,94 @@ BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kNL][8],
 #pragma unroll
     for (int b = 0; b < 7; b++)
         K[b] = 0;
+    ld8(S, 0, delta); // Delta_1 = L_0 * S_1 = S_1
 
 #pragma unroll 1
     for (int r = 1; r <= kNS; r++) {
-        // discrepancy: sum_{i < r, i <= 16} L_i * S_{r-i}     (S_{r-i} is word block r-1-i)
-        uint32_t acc[15], delta[8], s[8], sn[8];
-        clear15(acc);
-        ld8(S, r - 1, s);
-#pragma unroll
-        for (int i = 0; i < kNL; i++) {
-            if (i < r) {
-                if (i + 1 < kNL && i + 1 < r)
-                    ld8(S, r - 2 - i, sn);
-                BS_FENCE();
-                mac(acc, L[i], s);
-                cp8(s, sn);
-            }
-        }
-        reduce(acc, delta);
         const uint32_t chg = or8(delta) & ~K[6]; // delta != 0 and k >= 0
-
-        // T_i = gamma*L_i + delta*B_{i-1};  B_i <- chg ? L_i : B_{i-1}    (descending i: in place)
-        {
-            uint32_t bp[8], bn[8];
-            const int top = r < kNL - 1 ? r : kNL - 1; // highest coefficient that can be non-zero
-            if (top > 0)
-                ld8(B, top - 1, bp);
+        const int top = r < kT ? r : kT;         // highest coefficient that can be non-zero after this iteration
+        uint32_t acc[15], bcur[8];
+        clear15(acc);
 #pragma unroll
-            for (int i = kNL - 1; i >= 0; i--) {
-                if (i <= r) {
-                    uint32_t tacc[15];
-                    if (i == 0) {
+        for (int t = 0; t < 8; t++)
+            bcur[t] = 0u; // "B_{-1}"
+#pragma unroll 1
+        for (int g = 0; g < 3; g++) {
+            // Every coefficient of an active group is updated, without branches (so that the six steps can be
+            // scheduled into each other): beyond `top` both L_i and B_{i-1} are still zero and stay zero.
+            if (6 * g <= top) {
 #pragma unroll
-                        for (int t = 0; t < 8; t++)
-                            bp[t] = 0u;
+                for (int j = 0; j < 6; j++) {
+                    const int i = 6 * g + j;
+                    uint32_t bnext[8], s[8], tacc[15], T[8], nb[8];
+                    const int d = r - i; // S_{r+1-i}; clamped where T_i is zero (i > r) or the sum is not used any more (r = 32)
+                    const int sidx = d < 0 ? 0 : (d > kNS - 1 ? kNS - 1 : d);
+#pragma unroll
+                    for (int t = 0; t < 8; t++) {
+                        bnext[t] = i < kT ? B.ld(8 * i + t) : 0u; // old B_i, wanted by the next step ("B_16" = 0)
+                        s[t] = S.ld(8 * sidx + t);
                     }
-                    if (i >= 2)
-                        ld8(B, i - 2, bn);
-                    BS_FENCE();
                     clear15(tacc);
-                    mac(tacc, gamma, L[i]);
-                    if (i > 0)
-                        mac(tacc, delta, bp);
-                    if (i < kT) { // B_16 is never read again
-                        uint32_t nb[8];
+                    mac(tacc, gamma, L[j]);
+                    mac(tacc, delta, bcur);
 #pragma unroll
-                        for (int t = 0; t < 8; t++)
-                            nb[t] = (chg & L[i][t]) | (~chg & bp[t]);
+                    for (int t = 0; t < 8; t++)
+                        nb[t] = merge_bits(L[j][t], bcur[t], chg);
+                    if (i < kT)
                         st8(B, i, nb);
-                    }
-                    reduce(tacc, L[i]);
-                    cp8(bp, bn);
+                    reduce(tacc, T);
+                    cp8(L[j], T);
+                    mac(acc, T, s);
+                    cp8(bcur, bnext);
                 }
             }
+            rotate_groups(L);
         }
 #pragma unroll
         for (int t = 0; t < 8; t++)
-            gamma[t] = (chg & delta[t]) | (~chg & gamma[t]);
+            gamma[t] = merge_bits(delta[t], gamma[t], chg);
         uint32_t carry = 0xFFFFFFFFu;
 #pragma unroll
         for (int b = 0; b < 7; b++) {
             const uint32_t inc = K[b] ^ carry;
             carry &= K[b];
-            K[b] = (chg & ~K[b]) | (~chg & inc);
+            K[b] = merge_bits(~K[b], inc, chg);
         }
+        reduce(acc, delta);
     }
 }
 
 // ---- evaluator: Omega_i = sum_{j <= i} S_{i-j+1} * L_j, i = 0..15 (src/decode.c:147-158) -------------------
-// Stored to O as word block i, already advanced to "location 0" form is NOT done here (see sweep_init).
+// Rolled loops: L_0..L_15 are parked in the syndrome blocks 16..31 (dead once BM is done, and Omega only reads
+// S_1..S_16), Omega_i goes to word block i of O.
 template <int STRIDE>
-BS_FN void omega(const Mem<STRIDE> S, const uint32_t (&L)[kNL][8], const Mem<STRIDE> O)
+BS_FN void omega(const Mem<STRIDE> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE> O)
 {
 #pragma unroll
+    for (int j = 0; j < kT; j++)
+        st8(S, kT + j, L[j]);
+#pragma unroll 1
     for (int i = 0; i < kT; i++) {
-        uint32_t acc[15], o[8];
+        uint32_t acc[15], o[8], a[8], s[8];
         clear15(acc);
-#pragma unroll
+        ld8(S, kT, a);
+        ld8(S, i, s);
+#pragma unroll 1
         for (int j = 0; j <= i; j++) {
-            uint32_t s[8];
-#pragma unroll
-            for (int t = 0; t < 8; t++)
-                s[t] = S.ld(8 * (i - j) + t);
-            mac(acc, L[j], s);
+            uint32_t an[8], sn[8];
+            if (j < i) {
+                ld8(S, kT + j + 1, an);
+                ld8(S, i - j - 1, sn);
+            }
+            mac(acc, a, s);
+            if (j < i) {
+                cp8(a, an);
+                cp8(s, sn);
+            }
         }
         reduce(acc, o);
-#pragma unroll
-        for (int t = 0; t < 8; t++)
-            O.st(8 * i + t, o[t]);
+        st8(O, i, o);
     }
-}
-
-// (a & m) | (b & ~m): one LOP3 on the device (the optimiser would otherwise unfold the masked merge)
-BS_FN uint32_t merge_bits(uint32_t a, uint32_t b, uint32_t m)
-{
-#if defined(__CUDA_ARCH__)
-    uint32_t d;
-    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(d) : "r"(a), "r"(b), "r"(m));
-    return d;
-#else
-    return (a & m) | (b & ~m);
-#endif
 }
 
 // ---- 32x32 bit-matrix transpose: x[r] bit c <-> x[c] bit r (an involution) ---------------------------------
@@ -404,7 +426,7 @@ BS_FN void transpose32(uint32_t (&x)[32])
 // Before location k is examined every term is advanced once, L_j <- L_j * alpha^j (j = 1..16), so that L_j
 // holds lambda_j * alpha^(j*(k+1)).  After all 255 locations every term is back at lambda_j (alpha^255 = 1).
 template <int J>
-BS_FN void advance_L(uint32_t (&L)[kNL][8])
+BS_FN void advance_L(uint32_t (&L)[kLS][8])
 {
     if constexpr (J <= kT) {
         cmul<gf256::pow_alpha(J)>(L[J], L[J]);
@@ -413,7 +435,7 @@ BS_FN void advance_L(uint32_t (&L)[kNL][8])
 }
 
 // one location: returns the mask of codewords whose locator vanishes there
-BS_FN uint32_t chien_step(uint32_t (&L)[kNL][8])
+BS_FN uint32_t chien_step(uint32_t (&L)[kLS][8])
 {
     advance_L<1>(L);
     uint32_t nz = 0;
@@ -428,28 +450,118 @@ BS_FN uint32_t chien_step(uint32_t (&L)[kNL][8])
     return ~nz;
 }
 
+// ---- memory map of the S area (256 words per lane) once the evaluator has been computed -----------------------
+//   [0, 32)     scratch: root masks of 32 locations / x planes of four list slots / magnitude words
+//   [32, 160)   root lists: word 32 + 4c + (e >> 2), byte e & 3 = the e-th root x = alpha^(k+1) of codeword c
+//   [160, 168)  root counters, one byte per codeword
+constexpr int kWordsS = 8 * kNS;  // 256
+constexpr int kWordsB = 8 * kT;   // 128: BM scratch, then the evaluator coefficients
+constexpr int kListBase = 32;
+constexpr int kCntBase = 160;
+
+struct LaneOut {
+    uint32_t K[7];       // k = 32 - 2*L per codeword (bit-planes, two's complement)
+    uint32_t nzL[kNL];   // nzL[j] bit c: locator coefficient j of codeword c is non-zero
+    uint32_t padfail;    // bit c: a root fell into the zero padding (k < pad), src/decode.c:132-134
+};
+
+#if defined(__CUDA_ARCH__)
+#define BS_CTZ(x) (__ffs((int)(x)) - 1)
+#else
+#define BS_CTZ(x) __builtin_ctz(x)
+#endif
+
+// The sweep runs in blocks of 32 locations: the 32 root masks of a block are transposed into one word per
+// codeword (bit kk = "location 32*blk + kk is a root") and the set bits appended to the codeword's root list.
+// exp_tab[i] = alpha^i, i = 0..255.
+template <int STRIDE>
+BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, const uint8_t *exp_tab, LaneOut &out)
+{
+    for (int w = kListBase; w < kCntBase + 8; w++)
+        S.st(w, 0u);
+    uint32_t padfail = 0;
+    uint32_t cntreg[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}; // root counters, one byte per codeword (at most 255 roots)
+#pragma unroll 1
+    for (int blk = 0; blk < 8; blk++) {
+#pragma unroll 1
+        for (int kk = 0; kk < 32; kk++) {
+            const int k = 32 * blk + kk;
+            uint32_t m = 0;
+            if (k < 255) {
+                m = chien_step(L);
+                if (k < pad)
+                    padfail |= m;
+            }
+            S.st(kk, m);
+        }
+        {
+            uint32_t X[32];
+#pragma unroll
+            for (int c = 0; c < 32; c++)
+                X[c] = S.ld(c);
+            transpose32(X);
+            // Masks and counters stay in registers (c is a compile-time index).  A codeword has about one root per
+            // block: the first two are taken without branches, so that the 32 codewords' look-ups overlap; more than
+            // two roots in one block of 32 locations fall to the loop.
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+                uint32_t bits = X[c];
+                uint32_t n = (cntreg[c >> 2] >> (8 * (c & 3))) & 0xFFu;
+                const uint32_t n0 = n;
+#pragma unroll
+                for (int it = 0; it < 2; it++) {
+                    const bool live = bits != 0;
+                    const int kk = live ? BS_CTZ(bits) : 0;
+                    const uint32_t x = exp_tab[32 * blk + kk + 1];
+                    if (live && n < (uint32_t)kT)
+                        S.st_byte(kListBase + 4 * c + (int)(n >> 2), (int)(n & 3u), x);
+                    n += live ? 1u : 0u;
+                    bits &= bits - 1;
+                }
+                while (bits) {
+                    const int kk = BS_CTZ(bits);
+                    bits &= bits - 1;
+                    if (n < (uint32_t)kT)
+                        S.st_byte(kListBase + 4 * c + (int)(n >> 2), (int)(n & 3u), exp_tab[32 * blk + kk + 1]);
+                    n++;
+                }
+                cntreg[c >> 2] += (n - n0) << (8 * (c & 3));
+            }
+        }
+    }
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+        S.st(kCntBase + w, cntreg[w]);
+    out.padfail = padfail;
+    // every term is back at its coefficient (alpha^(255 j) = 1)
+#pragma unroll
+    for (int j = 0; j < kNL; j++)
+        out.nzL[j] = or8(L[j]);
+}
+
 // ---- Forney on one list slot ----------------------------------------------------------------------------------
 // x = the root alpha^(k+1) found for each of the 32 codewords (planes).  Magnitude (src/decode.c:159-191,
 // fcr = 1 so num2 = 1):  Omega(x) / Lambda'(x)  =  x*Omega(x) / (sum of the odd-degree locator terms at x).
-// A vanishing numerator gives magnitude 0 (the reference does not count such a root either).
+// A vanishing numerator gives magnitude 0 (the reference does not count such a root either); an empty slot
+// (x = 0) gives 0 as well.
 template <int STRIDE>
-BS_FN void forney_slot(const uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_t (&x)[8])
+BS_FN void forney_slot(const uint32_t (&L)[kLS][8], const Mem<STRIDE> O, uint32_t (&x)[8])
 {
-    uint32_t num[8], odd[8], x2[8], o[8], on[8];
+    uint32_t num[8], odd[8], x2[8], o[8];
     // Horner: Omega_15, then acc <- acc*x + Omega_j
     ld8(O, kT - 1, num);
     ld8(O, kT - 2, o);
-#pragma unroll
+#pragma unroll 1
     for (int j = kT - 2; j >= 0; j--) {
-        uint32_t acc[15];
+        uint32_t acc[15], on[8];
         if (j > 0)
             ld8(O, j - 1, on);
-        BS_FENCE();
         clear15(acc);
         cp8(*reinterpret_cast<uint32_t(*)[8]>(&acc[0]), o);
         mac(acc, num, x);
         reduce(acc, num);
-        cp8(o, on);
+        if (j > 0)
+            cp8(o, on);
     }
     mul(num, x, num);
     sqr(x, x2);
@@ -467,85 +579,52 @@ BS_FN void forney_slot(const uint32_t (&L)[kNL][8], const Mem<STRIDE> O, uint32_
     mul(num, odd, x);
 }
 
-// ---- one lane, start to finish ----------------------------------------------------------------------------
-#if defined(__CUDA_ARCH__)
-#define BS_CTZ(x) (__ffs((int)(x)) - 1)
-#else
-#define BS_CTZ(x) __builtin_ctz(x)
-#endif
-
-constexpr int kWordsS = 8 * kNS;      // 256: syndromes in, per-codeword root lists out
-constexpr int kWordsB = 8 * kNL;      // 136: BM scratch (128), then evaluator terms (128) + root counters (8)
-constexpr int kCntBase = 8 * kT;      // word offset of the root counters (one byte per codeword) in the B area
-
-struct LaneOut {
-    uint32_t K[7];       // k = 32 - 2*L per codeword (bit-planes, two's complement)
-    uint32_t nzL[kNL];   // nzL[j] bit c: locator coefficient j of codeword c is non-zero
-    uint32_t padfail;    // bit c: a root fell into the zero padding (k < pad), src/decode.c:132-134
-};
-
-// Root list of codeword c: up to 16 half-word entries in words [8c, 8c+8) of the S area.  The Chien sweep
-// writes (location | root << 8); the Forney pass turns the high byte into the error magnitude.
-// Root counter of codeword c: byte c of the 8 words at kCntBase of the B area.
+// List slots 4w .. 4w+3 of all 32 codewords: afterwards scratch words 8y .. 8y+7 of S hold the magnitude planes
+// of slot 4w + y, and cnt (5 bit-planes) has counted the non-zero magnitudes.  magnitude_words() then gives
+// one word per codeword (byte y = magnitude of slot 4w + y).
 template <int STRIDE>
-BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, LaneOut &out)
+BS_FN void forney_slots(const uint32_t (&L)[kLS][8], const Mem<STRIDE> O, const Mem<STRIDE> S, int w, uint32_t (&cnt)[5])
 {
-    uint32_t L[kNL][8];
-    ribm<STRIDE>(S, B, L, out.K);
-    omega<STRIDE>(S, L, B); // evaluator coefficients replace the BM scratch (words 0..127)
-    for (int w = 0; w < kWordsS; w++)
-        S.st(w, 0u);
-    for (int w = 0; w < 8; w++)
-        B.st(kCntBase + w, 0u);
-
-    uint32_t padfail = 0;
-    uint32_t xr = 1; // alpha^(k+1) after the update below
-#pragma unroll 1
-    for (int k = 0; k < 255; k++) {
-        xr <<= 1;
-        if (xr & 0x100u)
-            xr ^= gf256::kPoly;
-        uint32_t m = chien_step(L);
-        if (k < pad)
-            padfail |= m;
-        while (m) {
-            const int c = BS_CTZ(m);
-            m &= m - 1;
-            const uint32_t e = B.ld_byte(kCntBase + (c >> 2), c & 3);
-            B.st_byte(kCntBase + (c >> 2), c & 3, e + 1);
-            if (e < (uint32_t)kT)
-                S.st_half(8 * c + (int)(e >> 1), (int)(e & 1u), (uint32_t)k | (xr << 8));
-        }
-    }
-    out.padfail = padfail;
-    // every term is back at its coefficient (alpha^(255 j) = 1)
-#pragma unroll
-    for (int j = 0; j < kNL; j++)
-        out.nzL[j] = or8(L[j]);
-
-    // Forney, two list slots per pass: word w of every codeword's list holds slots 2w and 2w+1; a transpose
-    // turns the 32 codewords' words into planes (bytes 1 and 3 = the roots), and back afterwards
-#pragma unroll 1
-    for (int w = 0; w < 8; w++) {
+    {
         uint32_t X[32];
 #pragma unroll
         for (int c = 0; c < 32; c++)
-            X[c] = S.ld(8 * c + w);
-        transpose32(X);
-        forney_slot<STRIDE>(L, B, *reinterpret_cast<uint32_t(*)[8]>(&X[8]));
-        forney_slot<STRIDE>(L, B, *reinterpret_cast<uint32_t(*)[8]>(&X[24]));
-        transpose32(X);
+            X[c] = S.ld(kListBase + 4 * c + w);
+        transpose32(X); // X[8*y + t] = plane t of the roots in slot 4w + y
 #pragma unroll
-        for (int c = 0; c < 32; c++)
-            S.st(8 * c + w, X[c]);
+        for (int p = 0; p < 32; p++)
+            S.st(p, X[p]);
     }
+#pragma unroll 1
+    for (int y = 0; y < 4; y++) {
+        uint32_t x[8];
+        ld8(S, y, x);
+        forney_slot<STRIDE>(L, O, x);
+        st8(S, y, x);
+        uint32_t m = or8(x);
+#pragma unroll
+        for (int b = 0; b < 5; b++) {
+            const uint32_t t = cnt[b] & m;
+            cnt[b] ^= m;
+            m = t;
+        }
+    }
+}
+
+template <int STRIDE>
+BS_FN void magnitude_words(const Mem<STRIDE> S, uint32_t (&X)[32])
+{
+#pragma unroll
+    for (int p = 0; p < 32; p++)
+        X[p] = S.ld(p);
+    transpose32(X);
 }
 
 enum { kDeclined = 0, kFail = 1, kOk = 2 };
 
 // Outcome of codeword c of a lane (see the header comment for the rules).  nroots = roots found.
 template <int STRIDE>
-BS_FN int classify(const Mem<STRIDE> B, const LaneOut &o, int c, int &nroots)
+BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots)
 {
     int k = 0;
 #pragma unroll
@@ -561,10 +640,20 @@ BS_FN int classify(const Mem<STRIDE> B, const LaneOut &o, int c, int &nroots)
             lead = (o.nzL[j] >> c) & 1u;
     if (!lead || el == 0)
         return kDeclined; // degree below the register length: leave it to the literal stage
-    nroots = (int)B.ld_byte(kCntBase + (c >> 2), c & 3);
+    nroots = (int)S.ld_byte(kCntBase + (c >> 2), c & 3);
     if (nroots != el || ((o.padfail >> c) & 1u))
         return kFail;
     return kOk;
+}
+
+// key equation + root search for one lane: afterwards classify() and forney_pass() may be used
+template <int STRIDE>
+BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, const uint8_t *exp_tab, uint32_t (&L)[kLS][8],
+                      LaneOut &out)
+{
+    ribm<STRIDE>(S, B, L, out.K);
+    omega<STRIDE>(S, L, B); // evaluator coefficients replace the BM scratch
+    chien_collect<STRIDE>(L, S, pad, exp_tab, out);
 }
 
 } // namespace bs

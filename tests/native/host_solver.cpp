@@ -11,6 +11,11 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
                           int8_t *status /* [n] 0 declined, 1 fail, 2 ok */, uint8_t *nroots /* [n] */,
                           uint16_t *lists /* [n][16]: location | magnitude << 8 */)
 {
+    uint8_t exp_tab[256], log_tab[256];
+    for (int i = 0; i < 256; i++) {
+        exp_tab[i] = gf256::pow_alpha(i);
+        log_tab[exp_tab[i]] = (uint8_t)(i % 255);
+    }
     for (size_t g = 0; g < n; g += 32) {
         uint32_t S[bs::kWordsS], B[bs::kWordsB];
         memset(S, 0, sizeof S);
@@ -22,14 +27,30 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
                     if ((syn[(g + c) * 32 + m] >> t) & 1)
                         S[8 * m + t] |= 1u << c;
         bs::LaneOut out;
-        bs::solve_lane<1>(bs::Mem<1>{S}, bs::Mem<1>{B}, pad, out);
+        uint32_t L[bs::kLS][8];
+        const bs::Mem<1> Sm{S}, Bm{B};
+        bs::solve_lane<1>(Sm, Bm, pad, exp_tab, L, out);
         for (size_t c = 0; c < cnt; c++) {
             int nr = 0;
-            status[g + c] = (int8_t)bs::classify<1>(bs::Mem<1>{B}, out, (int)c, nr);
+            status[g + c] = (int8_t)bs::classify<1>(Sm, out, (int)c, nr);
             nroots[g + c] = (uint8_t)nr;
-            for (int e = 0; e < 16; e++)
-                lists[(g + c) * 16 + e] = (uint16_t)(S[8 * c + (e >> 1)] >> (16 * (e & 1)));
         }
+        uint32_t nzc[5] = {0, 0, 0, 0, 0};
+        for (int w = 0; w < 4; w++) {
+            bs::forney_slots<1>(L, Bm, Sm, w, nzc);
+            uint32_t X[32];
+            bs::magnitude_words<1>(Sm, X);
+            for (size_t c = 0; c < cnt; c++) {
+                const uint32_t mags = X[c], xs = S[bs::kListBase + 4 * c + w];
+                for (int y = 0; y < 4; y++) {
+                    const uint32_t x = (xs >> (8 * y)) & 0xFFu, mag = (mags >> (8 * y)) & 0xFFu;
+                    const uint32_t lg = log_tab[x]; // x = alpha^(k+1)
+                    const uint32_t loc = x ? (lg == 0 ? 254u : lg - 1u) : 0u;
+                    lists[(g + c) * 16 + 4 * w + y] = (uint16_t)(loc | (mag << 8));
+                }
+            }
+        }
+        (void)nzc;
     }
     return 0;
 }
