@@ -758,8 +758,9 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 // Codewords the solver declines (register length > 16 or a vanishing leading coefficient - uncorrectable
 // words only) are appended to a second queue for the literal per-codeword stage.
 // ---------------------------------------------------------------------------------------------------
-constexpr int kSolveWords = bs::kWordsS + bs::kWordsB + 32; // + the 32 queue entries of the lane
-constexpr int kSolveSmem = kSolveWords * 128 + 512;          // + exp / log tables (256 B each)
+constexpr int kSolveSmem = bs::kWordsW * 128 + 256;             // work area + the root table (256 B)
+constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO;  // per lane, in global memory (L2-resident)
+constexpr int kSolveWarpsPerSM = 8;
 
 template <int W>
 __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], const uint8_t *__restrict__ syn_raw,
@@ -792,21 +793,23 @@ __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], 
     }
 }
 
-__global__ void __launch_bounds__(32, 4)
-rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *parity, size_t parity_stride,
-                   uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter, uint8_t *__restrict__ syn_raw,
-                   uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2, uint8_t *__restrict__ ok,
-                   uint32_t *__restrict__ corrected)
+// One warp per CTA, eight CTAs per SM: a warp keeps only its 25 KB work area in shared memory; the syndrome planes
+// and the evaluator live in a per-warp scratch in global memory (48 KB, written and read by the same lane, so it
+// stays in L2).  With one warp per scheduler the ALU pipe idled ~45 % of the time behind fixed-latency waits.
+__global__ void __launch_bounds__(32, kSolveWarpsPerSM)
+rs255_solve_kernel(size_t size, uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+                   uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2,
+                   uint32_t *__restrict__ counter2, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
 {
     extern __shared__ __align__(16) uint32_t solve_smem[];
     const int lane = threadIdx.x;
-    const bs::Mem<32> S{solve_smem + lane};
-    const bs::Mem<32> B{solve_smem + bs::kWordsS * 32 + lane};
-    const bs::Mem<32> E{solve_smem + (bs::kWordsS + bs::kWordsB) * 32 + lane};
-    uint8_t *exp_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWords * 32);
-    uint8_t *log_tab = exp_tab + 256;
+    const bs::Mem<32> S{solve_smem + lane}; // the work area
+    uint32_t *gs = scratch + (size_t)blockIdx.x * (kSolveScratchWords * 32) + lane;
+    const bs::Mem<32> Syn{gs};
+    const bs::Mem<32> B{gs + bs::kWordsS * 32}; // the evaluator
+    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + bs::kWordsW * 32);
     {
-        // exp_tab[i] = alpha^i (i = 0..255), log_tab[alpha^i] = i mod 255: each lane fills 8 consecutive powers
+        // root_tab[0] = 0 (empty list slot), root_tab[v] = alpha^v for v = 1..255: each lane fills 8 consecutive powers
         uint32_t x = 1;
         for (int i = 0; i < 8 * lane; i++) {
             x <<= 1;
@@ -814,15 +817,11 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
                 x ^= gf256::kPoly;
         }
         for (int i = 8 * lane; i < 8 * lane + 8; i++) {
-            exp_tab[i] = (uint8_t)x;
-            if (i < 255)
-                log_tab[x] = (uint8_t)i;
+            root_tab[i] = i == 0 ? (uint8_t)0 : (uint8_t)x;
             x <<= 1;
             if (x & 0x100u)
                 x ^= gf256::kPoly;
         }
-        if (lane == 0)
-            log_tab[0] = 0;
     }
     __syncwarp();
     const uint32_t total = *counter;
@@ -835,26 +834,25 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
             for (int c = 0; c < 32; c++) {
                 const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
                 ent[c] = q < total ? queue[q] : 0xFFFFFFFFu;
-                E.st(c, ent[c]);
             }
-            solve_load_syndromes<0>(ent, syn_raw, S);
+            solve_load_syndromes<0>(ent, syn_raw, Syn);
         }
         uint32_t L[bs::kLS][8];
         bs::LaneOut out;
-        bs::solve_lane<32>(S, B, pad, exp_tab, L, out);
+        bs::solve_lane<32, 32>(Syn, B, S, pad, L, out);
 
         // Outcome of every codeword of the lane.  What the solver declines goes to the literal stage.  A decodable
-        // codeword gets an error record in place of its (now dead) raw syndrome row: bytes 0..15 the roots
-        // x = alpha^(location + 1), bytes 16..31 the magnitudes; rs255_apply_kernel turns the records into
+        // codeword gets an error record in place of its (now dead) raw syndrome row: bytes 0..15 the error locations
+        // + 1 (0 = none), bytes 16..31 the magnitudes; rs255_apply_kernel turns the records into
         // corrections.  Queue entries of all other codewords are blanked so that the apply kernel skips them.
         uint32_t okmask = 0;
         int maxroots = 0;
 #pragma unroll 1
         for (int c = 0; c < 32; c++) {
-            const uint32_t entry = E.ld(c);
-            if (entry == 0xFFFFFFFFu)
-                continue;
             const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
+            if (q >= total)
+                continue;
+            const uint32_t entry = queue[q];
             int nroots = 0;
             const int st = bs::classify<32>(S, out, c, nroots);
             if (st == bs::kOk) {
@@ -884,20 +882,22 @@ rs255_solve_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
         for (int w = 0; w < 4; w++) {
             if (!__any_sync(0xFFFFFFFFu, maxroots > 4 * w))
                 break;
-            bs::forney_slots<32>(L, B, S, w, nzc);
+            bs::forney_slots<32, 32>(L, B, S, w, root_tab, nzc);
             uint32_t X[32];
             bs::magnitude_words<32>(S, X);
 #pragma unroll
             for (int c = 0; c < 32; c++) {
-                if (((okmask >> c) & 1u) && X[c] != 0u)
-                    reinterpret_cast<uint32_t *>(syn_raw + (size_t)(E.ld(c) & 0x3FFFFFFFu) * 32 + 16)[w] = X[c];
+                if (((okmask >> c) & 1u) && X[c] != 0u) {
+                    const uint32_t entry = queue[g0 + 32u * (uint32_t)c + (uint32_t)lane];
+                    reinterpret_cast<uint32_t *>(syn_raw + (size_t)(entry & 0x3FFFFFFFu) * 32 + 16)[w] = X[c];
+                }
             }
         }
 #pragma unroll 1
         for (int c = 0; c < 32; c++) {
             if (!((okmask >> c) & 1u))
                 continue;
-            const size_t cw = E.ld(c) & 0x3FFFFFFFu;
+            const size_t cw = queue[g0 + 32u * (uint32_t)c + (uint32_t)lane] & 0x3FFFFFFFu;
             uint32_t nnz = 0;
 #pragma unroll
             for (int b = 0; b < 5; b++)
@@ -922,23 +922,6 @@ rs255_apply_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
                    const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
                    const uint8_t *__restrict__ records)
 {
-    __shared__ uint8_t log_tab[256];
-    {
-        // log_tab[alpha^i] = i, i = 0..254 (thread i computes alpha^i by square-and-multiply on the exponent bits)
-        const int i = (int)threadIdx.x;
-        if (i < 255) {
-            uint32_t x = 1, b = 2; // b = alpha^(2^j)
-            for (int j = 0; j < 8; j++) {
-                if ((i >> j) & 1)
-                    x = gf256::mul((uint8_t)x, (uint8_t)b);
-                b = gf256::mul((uint8_t)b, (uint8_t)b);
-            }
-            log_tab[x] = (uint8_t)i;
-        }
-        if (i == 255)
-            log_tab[0] = 0;
-    }
-    __syncthreads();
     const uint32_t total = *counter;
     const int pad = kMsg - (int)size;
     for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
@@ -955,8 +938,7 @@ rs255_apply_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *pari
         for (int e = 0; e < 16; e++) {
             const uint32_t mag = (mg[e >> 2] >> (8 * (e & 3))) & 0xFFu;
             if (mag) {
-                const int lg = (int)log_tab[(xs[e >> 2] >> (8 * (e & 3))) & 0xFFu]; // x = alpha^(k+1)
-                const int pos = (lg == 0 ? 254 : lg - 1) - pad;                      // >= 0: no root in the padding
+                const int pos = (int)((xs[e >> 2] >> (8 * (e & 3))) & 0xFFu) - 1 - pad; // >= 0: no root in the padding
                 uint8_t *a = pos < (int)size ? d + pos : p + (pos - (int)size);
                 const uintptr_t ua = (uintptr_t)a;
                 atomicXor(reinterpret_cast<unsigned int *>(ua & ~(uintptr_t)3), mag << (8u * (unsigned)(ua & 3u)));
@@ -979,7 +961,9 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
     const size_t tiles = 4 * ((n + 4095) / 4096);
     // queue [n rounded up to 4] | dmask [tiles * 64] | queue2 [n]
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64 + n) * sizeof(uint32_t)));
-    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32));
+    // raw syndrome rows / error records [tiles * 1024][32 B] | solver scratch, one slab per resident solver warp
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32 + (size_t)ctx->sm_count * kSolveWarpsPerSM *
+                                                                          kSolveScratchWords * 128));
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, 64));
     ctx->queue_cap = n;
     return 0;
@@ -1094,10 +1078,10 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         // bitsliced solver first; what it declines lands in queue2 for the literal stage below
         uint32_t *queue2 = dmask + tiles * 64;
         const size_t groups = (n + 1023) / 1024;
-        const size_t cap = (size_t)ctx->sm_count * 4;
+        const size_t cap = (size_t)ctx->sm_count * kSolveWarpsPerSM;
+        uint32_t *scratch = reinterpret_cast<uint32_t *>(ctx->d_rem + tiles * kTile * 32);
         rs255_solve_kernel<<<(unsigned)(groups < cap ? groups : cap), 32, kSolveSmem, stream>>>(
-            data, data_stride, size, parity, parity_stride, ctx->d_queue, ctx->d_counters, ctx->d_rem, queue2,
-            ctx->d_counters + 1, ok, corrected);
+            size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected);
         rs255_apply_kernel<<<(unsigned)ctx->sm_count * 8, 256, 0, stream>>>(data, data_stride, size, parity, parity_stride,
                                                                             ctx->d_queue, ctx->d_counters, ctx->d_rem);
         cq = queue2;

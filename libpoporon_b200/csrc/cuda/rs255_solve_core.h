@@ -260,8 +260,8 @@ BS_FN void rotate_groups(uint32_t (&L)[kLS][8])
         }
 }
 
-template <int STRIDE>
-BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uint32_t (&K)[7])
+template <int STRIDE, int SO>
+BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uint32_t (&K)[7])
 {
     uint32_t gamma[8], delta[8];
 #pragma unroll
@@ -336,25 +336,25 @@ BS_FN void ribm(const Mem<STRIDE> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8],
 }
 
 // ---- evaluator: Omega_i = sum_{j <= i} S_{i-j+1} * L_j, i = 0..15 (src/decode.c:147-158) -------------------
-// Rolled loops: L_0..L_15 are parked in the syndrome blocks 16..31 (dead once BM is done, and Omega only reads
-// S_1..S_16), Omega_i goes to word block i of O.
-template <int STRIDE>
-BS_FN void omega(const Mem<STRIDE> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE> O)
+// Rolled loops: L_0..L_15 are parked in P (16 blocks; the BM scratch, dead by now), Omega_i goes to word block i
+// of O.
+template <int STRIDE, int SO>
+BS_FN void omega(const Mem<SO> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE> P, const Mem<SO> O)
 {
 #pragma unroll
     for (int j = 0; j < kT; j++)
-        st8(S, kT + j, L[j]);
+        st8(P, j, L[j]);
 #pragma unroll 1
     for (int i = 0; i < kT; i++) {
         uint32_t acc[15], o[8], a[8], s[8];
         clear15(acc);
-        ld8(S, kT, a);
+        ld8(P, 0, a);
         ld8(S, i, s);
 #pragma unroll 1
         for (int j = 0; j <= i; j++) {
             uint32_t an[8], sn[8];
             if (j < i) {
-                ld8(S, kT + j + 1, an);
+                ld8(P, j + 1, an);
                 ld8(S, i - j - 1, sn);
             }
             mac(acc, a, s);
@@ -450,12 +450,14 @@ BS_FN uint32_t chien_step(uint32_t (&L)[kLS][8])
     return ~nz;
 }
 
-// ---- memory map of the S area (256 words per lane) once the evaluator has been computed -----------------------
+// ---- memory map of the work area W (200 words per lane) ---------------------------------------------------------
 //   [0, 32)     scratch: root masks of 32 locations / x planes of four list slots / magnitude words
-//   [32, 160)   root lists: word 32 + 4c + (e >> 2), byte e & 3 = the e-th root x = alpha^(k+1) of codeword c
+//   [32, 160)   root lists: word 32 + 4c + (e >> 2), byte e & 3 = location + 1 of the e-th root of codeword c (0 = none)
 //   [160, 168)  root counters, one byte per codeword
-constexpr int kWordsS = 8 * kNS;  // 256
-constexpr int kWordsB = 8 * kT;   // 128: BM scratch, then the evaluator coefficients
+//   [168, 200)  parked root masks of the previous block of 32 locations
+constexpr int kWordsS = 8 * kNS;  // 256: the syndromes
+constexpr int kWordsO = 8 * kT;   // 128: the evaluator coefficients
+constexpr int kWordsW = 200;      // the work area
 constexpr int kListBase = 32;
 constexpr int kCntBase = 160;
 
@@ -472,20 +474,53 @@ struct LaneOut {
 #endif
 
 // The sweep runs in blocks of 32 locations: the 32 root masks of a block are transposed into one word per
-// codeword (bit kk = "location 32*blk + kk is a root") and the set bits appended to the codeword's root list.
-// exp_tab[i] = alpha^i, i = 0..255.
+// codeword (bit kk = "location 32*blk + kk is a root") and parked in the S area; while the NEXT block is being
+// swept, each location step also appends the roots of one codeword of the parked block to that codeword's list
+// (the list work is all latency - find-first-set, table look-up, byte store - and hides behind the XOR networks
+// of the sweep).  exp_tab[i] = alpha^i, i = 0..255.
+constexpr int kParkBase = 168; // 32 parked mask words
+
+// bits: the parked mask word of codeword c, n: its root counter (both loaded by the caller, ahead of use).
+// List entries are location + 1 (1..255; 0 = empty slot).
 template <int STRIDE>
-BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, const uint8_t *exp_tab, LaneOut &out)
+BS_FN void append_roots(const Mem<STRIDE> S, int c, int blk, uint32_t bits, uint32_t n)
 {
-    for (int w = kListBase; w < kCntBase + 8; w++)
+    const uint32_t n0 = n;
+    // a codeword has about one root per block: the first two are taken without branches
+#pragma unroll
+    for (int it = 0; it < 2; it++) {
+        const bool live = bits != 0;
+        const int kk = live ? BS_CTZ(bits) : 0;
+        if (live && n < (uint32_t)kT)
+            S.st_byte(kListBase + 4 * c + (int)(n >> 2), (int)(n & 3u), (uint32_t)(32 * blk + kk + 1));
+        n += live ? 1u : 0u;
+        bits &= bits - 1;
+    }
+    while (bits) {
+        const int kk = BS_CTZ(bits);
+        bits &= bits - 1;
+        if (n < (uint32_t)kT)
+            S.st_byte(kListBase + 4 * c + (int)(n >> 2), (int)(n & 3u), (uint32_t)(32 * blk + kk + 1));
+        n++;
+    }
+    if (n != n0)
+        S.st_byte(kCntBase + (c >> 2), c & 3, n);
+}
+
+template <int STRIDE>
+BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, LaneOut &out)
+{
+    for (int w = kListBase; w < kParkBase + 32; w++)
         S.st(w, 0u);
     uint32_t padfail = 0;
-    uint32_t cntreg[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}; // root counters, one byte per codeword (at most 255 roots)
 #pragma unroll 1
     for (int blk = 0; blk < 8; blk++) {
 #pragma unroll 1
         for (int kk = 0; kk < 32; kk++) {
             const int k = 32 * blk + kk;
+            // parked block (all-zero masks while blk == 0): operands fetched before the sweep step, used after it
+            const uint32_t bits = S.ld(kParkBase + kk);
+            const uint32_t n = S.ld_byte(kCntBase + (kk >> 2), kk & 3);
             uint32_t m = 0;
             if (k < 255) {
                 m = chien_step(L);
@@ -493,45 +528,20 @@ BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, co
                     padfail |= m;
             }
             S.st(kk, m);
+            append_roots<STRIDE>(S, kk, blk - 1, bits, n);
         }
-        {
-            uint32_t X[32];
+        uint32_t X[32];
 #pragma unroll
-            for (int c = 0; c < 32; c++)
-                X[c] = S.ld(c);
-            transpose32(X);
-            // Masks and counters stay in registers (c is a compile-time index).  A codeword has about one root per
-            // block: the first two are taken without branches, so that the 32 codewords' look-ups overlap; more than
-            // two roots in one block of 32 locations fall to the loop.
+        for (int c = 0; c < 32; c++)
+            X[c] = S.ld(c);
+        transpose32(X);
 #pragma unroll
-            for (int c = 0; c < 32; c++) {
-                uint32_t bits = X[c];
-                uint32_t n = (cntreg[c >> 2] >> (8 * (c & 3))) & 0xFFu;
-                const uint32_t n0 = n;
-#pragma unroll
-                for (int it = 0; it < 2; it++) {
-                    const bool live = bits != 0;
-                    const int kk = live ? BS_CTZ(bits) : 0;
-                    const uint32_t x = exp_tab[32 * blk + kk + 1];
-                    if (live && n < (uint32_t)kT)
-                        S.st_byte(kListBase + 4 * c + (int)(n >> 2), (int)(n & 3u), x);
-                    n += live ? 1u : 0u;
-                    bits &= bits - 1;
-                }
-                while (bits) {
-                    const int kk = BS_CTZ(bits);
-                    bits &= bits - 1;
-                    if (n < (uint32_t)kT)
-                        S.st_byte(kListBase + 4 * c + (int)(n >> 2), (int)(n & 3u), exp_tab[32 * blk + kk + 1]);
-                    n++;
-                }
-                cntreg[c >> 2] += (n - n0) << (8 * (c & 3));
-            }
-        }
+        for (int c = 0; c < 32; c++)
+            S.st(kParkBase + c, X[c]);
     }
-#pragma unroll
-    for (int w = 0; w < 8; w++)
-        S.st(kCntBase + w, cntreg[w]);
+#pragma unroll 1
+    for (int c = 0; c < 32; c++)
+        append_roots<STRIDE>(S, c, 7, S.ld(kParkBase + c), S.ld_byte(kCntBase + (c >> 2), c & 3));
     out.padfail = padfail;
     // every term is back at its coefficient (alpha^(255 j) = 1)
 #pragma unroll
@@ -544,8 +554,8 @@ BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, co
 // fcr = 1 so num2 = 1):  Omega(x) / Lambda'(x)  =  x*Omega(x) / (sum of the odd-degree locator terms at x).
 // A vanishing numerator gives magnitude 0 (the reference does not count such a root either); an empty slot
 // (x = 0) gives 0 as well.
-template <int STRIDE>
-BS_FN void forney_slot(const uint32_t (&L)[kLS][8], const Mem<STRIDE> O, uint32_t (&x)[8])
+template <int SO>
+BS_FN void forney_slot(const uint32_t (&L)[kLS][8], const Mem<SO> O, uint32_t (&x)[8])
 {
     uint32_t num[8], odd[8], x2[8], o[8];
     // Horner: Omega_15, then acc <- acc*x + Omega_j
@@ -582,14 +592,18 @@ BS_FN void forney_slot(const uint32_t (&L)[kLS][8], const Mem<STRIDE> O, uint32_
 // List slots 4w .. 4w+3 of all 32 codewords: afterwards scratch words 8y .. 8y+7 of S hold the magnitude planes
 // of slot 4w + y, and cnt (5 bit-planes) has counted the non-zero magnitudes.  magnitude_words() then gives
 // one word per codeword (byte y = magnitude of slot 4w + y).
-template <int STRIDE>
-BS_FN void forney_slots(const uint32_t (&L)[kLS][8], const Mem<STRIDE> O, const Mem<STRIDE> S, int w, uint32_t (&cnt)[5])
+template <int STRIDE, int SO>
+BS_FN void forney_slots(const uint32_t (&L)[kLS][8], const Mem<SO> O, const Mem<STRIDE> S, int w,
+                        const uint8_t *root_tab /* [0] = 0, [v] = alpha^v */, uint32_t (&cnt)[5])
 {
     {
         uint32_t X[32];
 #pragma unroll
-        for (int c = 0; c < 32; c++)
-            X[c] = S.ld(kListBase + 4 * c + w);
+        for (int c = 0; c < 32; c++) {
+            const uint32_t v = S.ld(kListBase + 4 * c + w); // four list entries (location + 1, 0 = empty)
+            X[c] = (uint32_t)root_tab[v & 0xFFu] | ((uint32_t)root_tab[(v >> 8) & 0xFFu] << 8) |
+                   ((uint32_t)root_tab[(v >> 16) & 0xFFu] << 16) | ((uint32_t)root_tab[v >> 24] << 24);
+        }
         transpose32(X); // X[8*y + t] = plane t of the roots in slot 4w + y
 #pragma unroll
         for (int p = 0; p < 32; p++)
@@ -599,7 +613,7 @@ BS_FN void forney_slots(const uint32_t (&L)[kLS][8], const Mem<STRIDE> O, const 
     for (int y = 0; y < 4; y++) {
         uint32_t x[8];
         ld8(S, y, x);
-        forney_slot<STRIDE>(L, O, x);
+        forney_slot<SO>(L, O, x);
         st8(S, y, x);
         uint32_t m = or8(x);
 #pragma unroll
@@ -646,14 +660,19 @@ BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots)
     return kOk;
 }
 
-// key equation + root search for one lane: afterwards classify() and forney_pass() may be used
-template <int STRIDE>
-BS_FN void solve_lane(const Mem<STRIDE> S, const Mem<STRIDE> B, int pad, const uint8_t *exp_tab, uint32_t (&L)[kLS][8],
-                      LaneOut &out)
+// key equation + root search for one lane: afterwards classify() and forney_slots() may be used.
+//   Syn: the 32 syndromes (256 words), read-only.   Om: receives the evaluator (128 words).
+//   W: work area of kWordsW words: scratch / root lists / counters / parked masks (map above); its words
+//      [kListBase, kListBase + 128) double as the BM scratch and as the parking space of the evaluator loop.
+// Syn and Om may live in slower memory than W (on the device: an L2-resident scratch in global memory, so that
+// a warp needs 25 KB of shared memory and eight warps fit one SM).
+template <int STRIDE, int SO>
+BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<STRIDE> W, int pad, uint32_t (&L)[kLS][8], LaneOut &out)
 {
-    ribm<STRIDE>(S, B, L, out.K);
-    omega<STRIDE>(S, L, B); // evaluator coefficients replace the BM scratch
-    chien_collect<STRIDE>(L, S, pad, exp_tab, out);
+    const Mem<STRIDE> B{W.base + kListBase * STRIDE};
+    ribm<STRIDE, SO>(Syn, B, L, out.K);
+    omega<STRIDE, SO>(Syn, L, B, Om);
+    chien_collect<STRIDE>(L, W, pad, out);
 }
 
 } // namespace bs

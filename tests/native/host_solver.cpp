@@ -11,25 +11,25 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
                           int8_t *status /* [n] 0 declined, 1 fail, 2 ok */, uint8_t *nroots /* [n] */,
                           uint16_t *lists /* [n][16]: location | magnitude << 8 */)
 {
-    uint8_t exp_tab[256], log_tab[256];
-    for (int i = 0; i < 256; i++) {
-        exp_tab[i] = gf256::pow_alpha(i);
-        log_tab[exp_tab[i]] = (uint8_t)(i % 255);
-    }
+    uint8_t root_tab[256];
+    root_tab[0] = 0;
+    for (int i = 1; i < 256; i++)
+        root_tab[i] = gf256::pow_alpha(i);
     for (size_t g = 0; g < n; g += 32) {
-        uint32_t S[bs::kWordsS], B[bs::kWordsB];
-        memset(S, 0, sizeof S);
+        uint32_t Syn[bs::kWordsS], B[bs::kWordsO], S[bs::kWordsW];
+        memset(Syn, 0, sizeof Syn);
         memset(B, 0, sizeof B);
+        memset(S, 0, sizeof S);
         const size_t cnt = n - g < 32 ? n - g : 32;
         for (size_t c = 0; c < cnt; c++)
             for (int m = 0; m < 32; m++)
                 for (int t = 0; t < 8; t++)
                     if ((syn[(g + c) * 32 + m] >> t) & 1)
-                        S[8 * m + t] |= 1u << c;
+                        Syn[8 * m + t] |= 1u << c;
         bs::LaneOut out;
         uint32_t L[bs::kLS][8];
-        const bs::Mem<1> Sm{S}, Bm{B};
-        bs::solve_lane<1>(Sm, Bm, pad, exp_tab, L, out);
+        const bs::Mem<1> Sm{S}, Bm{B}, Synm{Syn};
+        bs::solve_lane<1, 1>(Synm, Bm, Sm, pad, L, out);
         for (size_t c = 0; c < cnt; c++) {
             int nr = 0;
             status[g + c] = (int8_t)bs::classify<1>(Sm, out, (int)c, nr);
@@ -37,15 +37,14 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
         }
         uint32_t nzc[5] = {0, 0, 0, 0, 0};
         for (int w = 0; w < 4; w++) {
-            bs::forney_slots<1>(L, Bm, Sm, w, nzc);
+            bs::forney_slots<1, 1>(L, Bm, Sm, w, root_tab, nzc);
             uint32_t X[32];
             bs::magnitude_words<1>(Sm, X);
             for (size_t c = 0; c < cnt; c++) {
                 const uint32_t mags = X[c], xs = S[bs::kListBase + 4 * c + w];
                 for (int y = 0; y < 4; y++) {
-                    const uint32_t x = (xs >> (8 * y)) & 0xFFu, mag = (mags >> (8 * y)) & 0xFFu;
-                    const uint32_t lg = log_tab[x]; // x = alpha^(k+1)
-                    const uint32_t loc = x ? (lg == 0 ? 254u : lg - 1u) : 0u;
+                    const uint32_t v = (xs >> (8 * y)) & 0xFFu, mag = (mags >> (8 * y)) & 0xFFu;
+                    const uint32_t loc = v ? v - 1u : 0u; // list entries are location + 1
                     lists[(g + c) * 16 + 4 * w + y] = (uint16_t)(loc | (mag << 8));
                 }
             }
