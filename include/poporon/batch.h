@@ -78,6 +78,11 @@ bool poporon_decode_batch_async(struct _poporon_t *pprn, uint8_t *data, size_t d
 
 /* kernels launched on behalf of this handle so far (all devices) */
 uint64_t poporon_kernel_launches(const struct _poporon_t *pprn);
+/* Opt-in per-kernel timing (RS handles; CUDA events around every kernel launched for this handle).
+ * profile(h, true) starts/restarts accumulation on the devices the handle has touched so far;
+ * profile_read returns the kernel's name (NULL past the last id), its launches and summed milliseconds. */
+bool poporon_kernel_profile(struct _poporon_t *pprn, bool on);
+const char *poporon_kernel_profile_read(struct _poporon_t *pprn, int kernel, uint64_t *launches, double *total_ms);
 /* text of the last device-layer failure on this thread ("" if none) */
 const char *poporon_last_error(void);
 

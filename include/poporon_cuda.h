@@ -144,6 +144,14 @@ int poporon_cuda_rs_decode_dev(poporon_cuda_rs_t *ctx, int mode, uint8_t *data, 
 /* Number of kernels this context has launched since creation (bench.py's gpu_launches). */
 uint64_t poporon_cuda_rs_launch_count(const poporon_cuda_rs_t *ctx);
 
+/* Opt-in per-kernel timing of the RS(255,223) fast path: CUDA event pairs recorded around every kernel the
+ * context launches, on the stream it launches on.  profile(ctx, 1) starts/restarts accumulation,
+ * profile(ctx, 0) stops it; profile_read synchronises on the recorded events and returns launches and the
+ * summed duration of kernel id `kernel` (0 .. 6, names from profile_name).  bench.py's roofline leg. */
+int poporon_cuda_rs_profile(poporon_cuda_rs_t *ctx, int on);
+int poporon_cuda_rs_profile_read(poporon_cuda_rs_t *ctx, int kernel, uint64_t *launches, double *total_ms);
+const char *poporon_cuda_rs_profile_name(int kernel);
+
 /* ---- binary BCH ---------------------------------------------------------------------------- */
 int poporon_cuda_bch_create(const poporon_cuda_bch_desc_t *desc, int device, poporon_cuda_bch_t **out);
 void poporon_cuda_bch_destroy(poporon_cuda_bch_t *ctx);

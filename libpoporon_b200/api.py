@@ -112,6 +112,8 @@ _sig(host, "poporon_encode_batch_async", C.c_bool, C.c_void_p, C.c_void_p, C.c_s
 _sig(host, "poporon_decode_batch_async", C.c_bool, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p,
      C.c_size_t, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p)
 _sig(host, "poporon_kernel_launches", C.c_uint64, C.c_void_p)
+_sig(host, "poporon_kernel_profile", C.c_bool, C.c_void_p, C.c_bool)
+_sig(host, "poporon_kernel_profile_read", C.c_char_p, C.c_void_p, C.c_int, _P(C.c_uint64), _P(C.c_double))
 _sig(host, "poporon_last_error", C.c_char_p)
 # ---- include/poporon_cuda.h (the part tests/bench bind directly) ----------------------------------
 _sig(cuda, "poporon_cuda_device_count", C.c_int)
@@ -231,6 +233,22 @@ class Poporon:
     @property
     def launches(self):
         return host.poporon_kernel_launches(self.ptr)
+
+    def profile(self, on=True) -> bool:
+        """start / stop per-kernel CUDA-event timing on the devices this handle has used so far"""
+        return bool(host.poporon_kernel_profile(self.ptr, bool(on)))
+
+    def profile_read(self):
+        """{kernel name: (launches, total ms)} accumulated since profile(True)"""
+        out, k = {}, 0
+        while True:
+            n, ms = C.c_uint64(0), C.c_double(0.0)
+            name = host.poporon_kernel_profile_read(self.ptr, k, C.byref(n), C.byref(ms))
+            if name is None:
+                return out
+            if n.value:
+                out[name.decode()] = (int(n.value), float(ms.value))
+            k += 1
 
     def use_devices(self, devices=None) -> bool:
         if not devices:

@@ -50,6 +50,10 @@ struct RsCode {
     uint16_t fcr, prim, iprim;
 };
 
+// kernel ids of the per-kernel profile (poporon_cuda_rs_profile_read)
+enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_APPLY, PROF_GENERAL, PROF_GENERIC, PROF_KINDS };
+constexpr int kProfCap = 8192;
+
 static inline int sm_count_of(int device)
 {
     int n = 0;
@@ -58,6 +62,18 @@ static inline int sm_count_of(int device)
     return n;
 }
 
+} // namespace ppcu
+
+struct poporon_cuda_rs;
+namespace ppcu {
+// RAII event pair around one kernel launch; a no-op unless profiling is on for the context
+struct ProfScope {
+    poporon_cuda_rs *ctx;
+    cudaStream_t stream;
+    int slot;
+    ProfScope(poporon_cuda_rs *c, int id, cudaStream_t s);
+    ~ProfScope();
+};
 } // namespace ppcu
 
 // Context layouts (opaque to C callers).
@@ -74,6 +90,13 @@ struct poporon_cuda_rs {
     uint8_t *d_rem;           // per-dirty-codeword remainder / syndromes
     uint32_t *d_counters;     // [0] = dirty count
     size_t queue_cap;
+    // opt-in per-kernel timing (poporon_cuda_rs_profile): CUDA event pairs around each launch
+    bool prof_on;
+    int prof_used;
+    cudaEvent_t *prof_ev;     // [2 * kProfCap]
+    uint8_t *prof_id;         // [kProfCap]
+    double prof_ms[8];
+    uint64_t prof_n[8];
 };
 
 struct poporon_cuda_bch {

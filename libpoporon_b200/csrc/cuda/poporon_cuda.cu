@@ -31,6 +31,47 @@ int check(cudaError_t e, const char *what)
     return POPORON_CUDA_ERR_DEVICE;
 }
 
+ProfScope::ProfScope(poporon_cuda_rs *c, int id, cudaStream_t s) : ctx(c), stream(s), slot(-1)
+{
+    if (!c || !c->prof_on || !c->prof_ev || c->prof_used >= kProfCap)
+        return;
+    slot = c->prof_used++;
+    c->prof_id[slot] = (uint8_t)id;
+    cudaEventRecord(c->prof_ev[2 * slot], s);
+}
+
+ProfScope::~ProfScope()
+{
+    if (slot >= 0)
+        cudaEventRecord(ctx->prof_ev[2 * slot + 1], stream);
+}
+
+static void prof_drain(poporon_cuda_rs *ctx)
+{
+    for (int i = 0; i < ctx->prof_used; i++) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(ctx->prof_ev[2 * i + 1]) == cudaSuccess &&
+            cudaEventElapsedTime(&ms, ctx->prof_ev[2 * i], ctx->prof_ev[2 * i + 1]) == cudaSuccess) {
+            ctx->prof_ms[ctx->prof_id[i]] += ms;
+            ctx->prof_n[ctx->prof_id[i]]++;
+        }
+    }
+    ctx->prof_used = 0;
+}
+
+static void prof_release(poporon_cuda_rs *ctx)
+{
+    if (ctx->prof_ev)
+        for (int i = 0; i < 2 * kProfCap; i++)
+            if (ctx->prof_ev[i])
+                cudaEventDestroy(ctx->prof_ev[i]);
+    free(ctx->prof_ev);
+    free(ctx->prof_id);
+    ctx->prof_ev = nullptr;
+    ctx->prof_id = nullptr;
+    ctx->prof_used = 0;
+}
+
 } // namespace ppcu
 
 using namespace ppcu;
@@ -265,6 +306,7 @@ void poporon_cuda_rs_destroy(poporon_cuda_rs_t *ctx)
     if (!ctx)
         return;
     DeviceGuard g(ctx->device);
+    prof_release(ctx);
     cudaFree(ctx->d_tables);
     cudaFree(ctx->d_queue);
     cudaFree(ctx->d_rem);
@@ -286,6 +328,55 @@ void poporon_cuda_rs_force_generic(poporon_cuda_rs_t *ctx, int on)
 uint64_t poporon_cuda_rs_launch_count(const poporon_cuda_rs_t *ctx)
 {
     return ctx ? ctx->launches : 0;
+}
+
+int poporon_cuda_rs_profile(poporon_cuda_rs_t *ctx, int on)
+{
+    if (!ctx)
+        return POPORON_CUDA_ERR_ARG;
+    GUARD(ctx->device);
+    if (on && !ctx->prof_ev) {
+        ctx->prof_ev = (cudaEvent_t *)calloc(2 * kProfCap, sizeof(cudaEvent_t));
+        ctx->prof_id = (uint8_t *)calloc(kProfCap, 1);
+        if (!ctx->prof_ev || !ctx->prof_id) {
+            prof_release(ctx);
+            return POPORON_CUDA_ERR_NOMEM;
+        }
+        for (int i = 0; i < 2 * kProfCap; i++)
+            if (cudaEventCreate(&ctx->prof_ev[i]) != cudaSuccess) {
+                prof_release(ctx);
+                return check(cudaGetLastError(), "cudaEventCreate (profile)");
+            }
+    }
+    if (on) { /* (re)start: forget what was accumulated */
+        prof_drain(ctx);
+        memset(ctx->prof_ms, 0, sizeof ctx->prof_ms);
+        memset(ctx->prof_n, 0, sizeof ctx->prof_n);
+    }
+    ctx->prof_on = on != 0;
+    return 0;
+}
+
+int poporon_cuda_rs_profile_read(poporon_cuda_rs_t *ctx, int kernel, uint64_t *launches, double *total_ms)
+{
+    if (!ctx || kernel < 0 || kernel >= PROF_KINDS)
+        return POPORON_CUDA_ERR_ARG;
+    GUARD(ctx->device);
+    prof_drain(ctx);
+    if (launches)
+        *launches = ctx->prof_n[kernel];
+    if (total_ms)
+        *total_ms = ctx->prof_ms[kernel];
+    return 0;
+}
+
+const char *poporon_cuda_rs_profile_name(int kernel)
+{
+    static const char *names[PROF_KINDS] = {"rs255_lfsr_kernel<ENCODE>", "rs255_lfsr_kernel<SCREEN>",
+                                            "rs255_compact_kernel",      "rs255_solve_kernel",
+                                            "rs255_apply_kernel",        "rs255_correct_kernel",
+                                            "rs_generic kernels"};
+    return kernel >= 0 && kernel < PROF_KINDS ? names[kernel] : NULL;
 }
 
 int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, int op, const uint8_t *data, size_t data_stride, size_t size,

@@ -1042,7 +1042,10 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
     tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
     if (ok)
         PP_CUDA_TRY(cudaMemsetAsync(ok, 1, n, stream)); // the encoder cannot fail (src/encode.c:17-145 returns true)
-    rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64, kSmemEncode, stream>>>(A);
+    {
+        ProfScope prof(ctx, PROF_ENCODE, stream);
+        rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64, kSmemEncode, stream>>>(A);
+    }
     ctx->launches++;
     return check(cudaGetLastError(), "rs255 encode launch");
 }
@@ -1069,9 +1072,15 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     A.syn = ctx->d_rem;
     uint64_t invperm;
     tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
-    rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64, kSmemScreen, stream>>>(A);
-    rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(dmask, n, invperm, ctx->d_queue,
-                                                                                    ctx->d_counters, ok, corrected);
+    {
+        ProfScope prof(ctx, PROF_SCREEN, stream);
+        rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64, kSmemScreen, stream>>>(A);
+    }
+    {
+        ProfScope prof(ctx, PROF_COMPACT, stream);
+        rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(
+            dmask, n, invperm, ctx->d_queue, ctx->d_counters, ok, corrected);
+    }
     const unsigned cblocks = (unsigned)ctx->sm_count * 8;
     const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
     if (mode == POPORON_CUDA_MODE_PLAIN) {
@@ -1080,17 +1089,26 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         const size_t groups = (n + 1023) / 1024;
         const size_t cap = (size_t)ctx->sm_count * kSolveWarpsPerSM;
         uint32_t *scratch = reinterpret_cast<uint32_t *>(ctx->d_rem + tiles * kTile * 32);
-        rs255_solve_kernel<<<(unsigned)(groups < cap ? groups : cap), 32, kSolveSmem, stream>>>(
-            size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected);
-        rs255_apply_kernel<<<(unsigned)ctx->sm_count * 8, 256, 0, stream>>>(data, data_stride, size, parity, parity_stride,
-                                                                            ctx->d_queue, ctx->d_counters, ctx->d_rem);
+        {
+            ProfScope prof(ctx, PROF_SOLVE, stream);
+            rs255_solve_kernel<<<(unsigned)(groups < cap ? groups : cap), 32, kSolveSmem, stream>>>(
+                size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected);
+        }
+        {
+            ProfScope prof(ctx, PROF_APPLY, stream);
+            rs255_apply_kernel<<<(unsigned)ctx->sm_count * 8, 256, 0, stream>>>(
+                data, data_stride, size, parity, parity_stride, ctx->d_queue, ctx->d_counters, ctx->d_rem);
+        }
         cq = queue2;
         cc = ctx->d_counters + 1;
         ctx->launches += 2;
     }
-    rs255_correct_kernel<<<cblocks, 128, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride, size, parity,
-                                                      parity_stride, cq, cc, ctx->d_rem, pos, pos_stride, cnt, ok,
-                                                      corrected);
+    {
+        ProfScope prof(ctx, PROF_GENERAL, stream);
+        rs255_correct_kernel<<<cblocks, 128, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride, size,
+                                                          parity, parity_stride, cq, cc, ctx->d_rem, pos, pos_stride,
+                                                          cnt, ok, corrected);
+    }
     ctx->launches += 3;
     return check(cudaGetLastError(), "rs255 decode launch");
 }

@@ -150,6 +150,37 @@ uint64_t poporon_kernel_launches(const poporon_t *h)
     return total;
 }
 
+bool poporon_kernel_profile(poporon_t *h, bool on)
+{
+    size_t l;
+    bool any = false;
+    if (!h)
+        return false;
+    for (l = 0; l < PP_MAX_DEVICES; l++)
+        if (h->lane[l].rs && poporon_cuda_rs_profile(h->lane[l].rs, on ? 1 : 0) == 0)
+            any = true;
+    return any;
+}
+
+const char *poporon_kernel_profile_read(poporon_t *h, int kernel, uint64_t *launches, double *total_ms)
+{
+    size_t l;
+    uint64_t n = 0, ln;
+    double ms = 0.0, lms;
+    if (!h || !poporon_cuda_rs_profile_name(kernel))
+        return NULL;
+    for (l = 0; l < PP_MAX_DEVICES; l++)
+        if (h->lane[l].rs && poporon_cuda_rs_profile_read(h->lane[l].rs, kernel, &ln, &lms) == 0) {
+            n += ln;
+            ms += lms;
+        }
+    if (launches)
+        *launches = n;
+    if (total_ms)
+        *total_ms = ms;
+    return poporon_cuda_rs_profile_name(kernel);
+}
+
 /* ------------------------------------------------------------------------------------------------
  * kernel dispatch on device-resident buffers
  * ---------------------------------------------------------------------------------------------- */
