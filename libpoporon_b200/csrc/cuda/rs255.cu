@@ -793,13 +793,105 @@ __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], 
     }
 }
 
+// Corrections of the PREVIOUS tile, issued in 256 small portions from inside the Chien sweep of the current one
+// (bs::chien_collect calls before()/after() around every location step): portion k = list slots 2*(k & 7) and
+// 2*(k & 7) + 1 of codeword c = k >> 3 of this lane.  The loads of a portion (queue entry eight steps ahead, two
+// bytes of locations and two of magnitudes one step ahead) are in flight while the XOR networks of the step run,
+// and the corrections leave as word-wide RED.XORs (no return value, so nothing waits for them; bytes of
+// neighbouring records that share a word cannot be lost).  This replaces a separate apply kernel (2.4 ms per
+// 16 Mi codewords): the scattered sector read-modify-writes now overlap the ALU-bound solver.
+// Records: the solver leaves, in place of a decodable codeword's raw syndrome row, bytes 0..15 = error
+// locations + 1 (0 = none) and bytes 16..31 = magnitudes; queue entries of all other codewords are blanked.
+struct ApplyHook {
+    uint32_t g0p;          // first queue index of the previous tile (0xFFFFFFFF: nothing pending) - the only state
+                           // that stays live between sweeps
+    const uint32_t *queue;
+    uint32_t total, lane;
+    const uint32_t *qprev; // queue + g0p + lane
+    uint32_t nvalid;       // codewords c < nvalid of the previous tile exist for this lane
+    const uint8_t *records;
+    uint8_t *data;
+    uint32_t stride32;
+    int pad;
+    uint32_t entry_cur, entry_nxt, entry_app;
+    uint32_t p2, m2; // raw 16-bit loads of a portion, zero-extended by the load itself: nothing touches them before
+                     // after(), so nothing waits for them early
+
+    __device__ __forceinline__ uint32_t entry_of(uint32_t c) const
+    {
+        return c < nvalid ? qprev[32u * c] : 0xFFFFFFFFu;
+    }
+    __device__ __forceinline__ void begin()
+    {
+        const uint32_t first = g0p + lane;
+        nvalid = 0;
+        if (g0p != 0xFFFFFFFFu && first < total) {
+            const uint32_t left = (total - first + 31u) / 32u;
+            nvalid = left < 32u ? left : 32u;
+        }
+        qprev = queue + first;
+        entry_cur = entry_of(0);
+        entry_nxt = 0xFFFFFFFFu;
+        p2 = 0;
+        m2 = 0;
+    }
+    // XORs of the portion whose loads were issued one step ago.  Records are packed (parity = data + size, one
+    // stride: rs255_shape_ok), so symbol `loc` of the codeword lives at data + cw*stride + loc - pad.
+    __device__ __forceinline__ void flush()
+    {
+        if (m2 != 0u) {
+            const uintptr_t base = (uintptr_t)data + (size_t)(entry_app & 0x3FFFFFFFu) * (size_t)stride32 - (size_t)(1 + pad);
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const uint32_t mag = (m2 >> (8 * e)) & 0xFFu;
+                if (mag) {
+                    const uintptr_t ua = base + ((p2 >> (8 * e)) & 0xFFu); // list entry = location + 1 > pad
+                    asm volatile("red.relaxed.gpu.global.xor.b32 [%0], %1;" ::"l"(ua & ~(uintptr_t)3),
+                                 "r"(mag << (8u * (unsigned)(ua & 3u)))
+                                 : "memory");
+                }
+            }
+        }
+        m2 = 0;
+    }
+    // The consumer of a portion's loads sits at the top of the NEXT step (the assembler otherwise hoists the
+    // first use - a compare - right behind the loads and the warp waits an L2 round trip per step).
+    __device__ __forceinline__ void before(int k)
+    {
+        flush();
+        const uint32_t sp = (uint32_t)k & 7u;
+        if (sp == 0)
+            entry_nxt = entry_of(((uint32_t)k >> 3) + 1u);
+        entry_app = entry_cur;
+        if (entry_cur != 0xFFFFFFFFu) {
+            const uint8_t *row = records + (size_t)(entry_cur & 0x3FFFFFFFu) * 32 + 2u * sp;
+            asm volatile("ld.global.u16 %0, [%1];" : "=r"(p2) : "l"(row));
+            asm volatile("ld.global.u16 %0, [%1+16];" : "=r"(m2) : "l"(row));
+        }
+        if (sp == 7u)
+            entry_cur = entry_nxt;
+    }
+    __device__ __forceinline__ void after(int) {}
+    __device__ __forceinline__ void end() { flush(); }
+    // everything still pending (after a warp's last tile)
+    __device__ __forceinline__ void drain()
+    {
+        begin();
+#pragma unroll 1
+        for (int k = 0; k < 256; k++)
+            before(k);
+        flush();
+        g0p = 0xFFFFFFFFu;
+    }
+};
+
 // One warp per CTA, eight CTAs per SM: a warp keeps only its 25 KB work area in shared memory; the syndrome planes
 // and the evaluator live in a per-warp scratch in global memory (48 KB, written and read by the same lane, so it
 // stays in L2).  With one warp per scheduler the ALU pipe idled ~45 % of the time behind fixed-latency waits.
 __global__ void __launch_bounds__(32, kSolveWarpsPerSM)
-rs255_solve_kernel(size_t size, uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
-                   uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2,
-                   uint32_t *__restrict__ counter2, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ counter, uint8_t *syn_raw,
+                   uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2,
+                   uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data, size_t data_stride)
 {
     extern __shared__ __align__(16) uint32_t solve_smem[];
     const int lane = threadIdx.x;
@@ -826,6 +918,15 @@ rs255_solve_kernel(size_t size, uint32_t *__restrict__ queue, const uint32_t *__
     __syncwarp();
     const uint32_t total = *counter;
     const int pad = kMsg - (int)size;
+    ApplyHook hook;
+    hook.records = syn_raw;
+    hook.data = data;
+    hook.stride32 = (uint32_t)data_stride;
+    hook.pad = pad;
+    hook.queue = queue;
+    hook.total = total;
+    hook.lane = (uint32_t)lane;
+    hook.g0p = 0xFFFFFFFFu;
 
     for (uint32_t g0 = blockIdx.x * 1024u; g0 < total; g0 += gridDim.x * 1024u) {
         {
@@ -839,7 +940,7 @@ rs255_solve_kernel(size_t size, uint32_t *__restrict__ queue, const uint32_t *__
         }
         uint32_t L[bs::kLS][8];
         bs::LaneOut out;
-        bs::solve_lane<32, 32>(Syn, B, S, pad, L, out);
+        bs::solve_lane<32, 32>(Syn, B, S, pad, L, out, hook); // also drains the previous tile's corrections
 
         // Outcome of every codeword of the lane.  What the solver declines goes to the literal stage.  A decodable
         // codeword gets an error record in place of its (now dead) raw syndrome row: bytes 0..15 the error locations
@@ -907,44 +1008,10 @@ rs255_solve_kernel(size_t size, uint32_t *__restrict__ queue, const uint32_t *__
             if (corrected)
                 corrected[cw] = nnz;
         }
+        hook.g0p = g0; // this tile's records are final: applied during the next sweep (or by the drain below)
         __syncwarp();
     }
-}
-
-// ---------------------------------------------------------------------------------------------------
-// corrections from the error records of the solver: one thread per queued codeword, at full occupancy, so
-// that the scattered read-modify-writes (about one 32-byte sector per corrected byte) are bound by memory
-// throughput and not by one warp's store queue.  Word-wide atomic XORs (RED.XOR, no return value): bytes of
-// neighbouring records that share a word cannot be lost.
-// ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-rs255_apply_kernel(uint8_t *data, size_t data_stride, size_t size, uint8_t *parity, size_t parity_stride,
-                   const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
-                   const uint8_t *__restrict__ records)
-{
-    const uint32_t total = *counter;
-    const int pad = kMsg - (int)size;
-    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
-        const uint32_t entry = queue[q];
-        if (entry == 0xFFFFFFFFu)
-            continue;
-        const size_t cw = entry & 0x3FFFFFFFu;
-        const uint4 *row = reinterpret_cast<const uint4 *>(records + cw * 32);
-        const uint4 xs4 = row[0], mg4 = row[1];
-        const uint32_t xs[4] = {xs4.x, xs4.y, xs4.z, xs4.w}, mg[4] = {mg4.x, mg4.y, mg4.z, mg4.w};
-        uint8_t *d = data + cw * data_stride;
-        uint8_t *p = parity + cw * parity_stride;
-#pragma unroll
-        for (int e = 0; e < 16; e++) {
-            const uint32_t mag = (mg[e >> 2] >> (8 * (e & 3))) & 0xFFu;
-            if (mag) {
-                const int pos = (int)((xs[e >> 2] >> (8 * (e & 3))) & 0xFFu) - 1 - pad; // >= 0: no root in the padding
-                uint8_t *a = pos < (int)size ? d + pos : p + (pos - (int)size);
-                const uintptr_t ua = (uintptr_t)a;
-                atomicXor(reinterpret_cast<unsigned int *>(ua & ~(uintptr_t)3), mag << (8u * (unsigned)(ua & 3u)));
-            }
-        }
-    }
+    hook.drain();
 }
 
 int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
@@ -984,7 +1051,7 @@ bool rs255_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size
     if (size < 1 || size > (size_t)kMsg || data_stride < size || ((uintptr_t)data & 15u) != 0)
         return false;
     if (op == 1) // the screen kernel reads ONE contiguous stream per codeword: packed records only
-        return parity == data + size && parity_stride == data_stride;
+        return parity == data + size && parity_stride == data_stride && data_stride <= 0xFFFFFFFFull; // 32-bit stride math
     return true;
 }
 
@@ -1092,16 +1159,12 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         {
             ProfScope prof(ctx, PROF_SOLVE, stream);
             rs255_solve_kernel<<<(unsigned)(groups < cap ? groups : cap), 32, kSolveSmem, stream>>>(
-                size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected);
-        }
-        {
-            ProfScope prof(ctx, PROF_APPLY, stream);
-            rs255_apply_kernel<<<(unsigned)ctx->sm_count * 8, 256, 0, stream>>>(
-                data, data_stride, size, parity, parity_stride, ctx->d_queue, ctx->d_counters, ctx->d_rem);
+                size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected,
+                data, data_stride);
         }
         cq = queue2;
         cc = ctx->d_counters + 1;
-        ctx->launches += 2;
+        ctx->launches += 1;
     }
     {
         ProfScope prof(ctx, PROF_GENERAL, stream);

@@ -507,11 +507,21 @@ BS_FN void append_roots(const Mem<STRIDE> S, int c, int blk, uint32_t bits, uint
         S.st_byte(kCntBase + (c >> 2), c & 3, n);
 }
 
-template <int STRIDE>
-BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, LaneOut &out)
+// A hook that does nothing (host tests).  The device passes one that issues the PREVIOUS tile's corrections in
+// small portions: before(step) starts the loads of one portion, after(step) consumes them, 256 steps per sweep.
+struct NoHook {
+    BS_FN void begin() {}
+    BS_FN void before(int) {}
+    BS_FN void after(int) {}
+    BS_FN void end() {}
+};
+
+template <int STRIDE, class Hook>
+BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, LaneOut &out, Hook &hook)
 {
     for (int w = kListBase; w < kParkBase + 32; w++)
         S.st(w, 0u);
+    hook.begin();
     uint32_t padfail = 0;
 #pragma unroll 1
     for (int blk = 0; blk < 8; blk++) {
@@ -521,12 +531,14 @@ BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, La
             // parked block (all-zero masks while blk == 0): operands fetched before the sweep step, used after it
             const uint32_t bits = S.ld(kParkBase + kk);
             const uint32_t n = S.ld_byte(kCntBase + (kk >> 2), kk & 3);
+            hook.before(k);
             uint32_t m = 0;
             if (k < 255) {
                 m = chien_step(L);
                 if (k < pad)
                     padfail |= m;
             }
+            hook.after(k);
             S.st(kk, m);
             append_roots<STRIDE>(S, kk, blk - 1, bits, n);
         }
@@ -542,6 +554,7 @@ BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, La
 #pragma unroll 1
     for (int c = 0; c < 32; c++)
         append_roots<STRIDE>(S, c, 7, S.ld(kParkBase + c), S.ld_byte(kCntBase + (c >> 2), c & 3));
+    hook.end();
     out.padfail = padfail;
     // every term is back at its coefficient (alpha^(255 j) = 1)
 #pragma unroll
@@ -666,13 +679,14 @@ BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots)
 //      [kListBase, kListBase + 128) double as the BM scratch and as the parking space of the evaluator loop.
 // Syn and Om may live in slower memory than W (on the device: an L2-resident scratch in global memory, so that
 // a warp needs 25 KB of shared memory and eight warps fit one SM).
-template <int STRIDE, int SO>
-BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<STRIDE> W, int pad, uint32_t (&L)[kLS][8], LaneOut &out)
+template <int STRIDE, int SO, class Hook>
+BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<STRIDE> W, int pad, uint32_t (&L)[kLS][8], LaneOut &out,
+                      Hook &hook)
 {
     const Mem<STRIDE> B{W.base + kListBase * STRIDE};
     ribm<STRIDE, SO>(Syn, B, L, out.K);
     omega<STRIDE, SO>(Syn, L, B, Om);
-    chien_collect<STRIDE>(L, W, pad, out);
+    chien_collect<STRIDE, Hook>(L, W, pad, out, hook);
 }
 
 } // namespace bs

@@ -29,7 +29,8 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
         bs::LaneOut out;
         uint32_t L[bs::kLS][8];
         const bs::Mem<1> Sm{S}, Bm{B}, Synm{Syn};
-        bs::solve_lane<1, 1>(Synm, Bm, Sm, pad, L, out);
+        bs::NoHook hook;
+        bs::solve_lane<1, 1>(Synm, Bm, Sm, pad, L, out, hook);
         for (size_t c = 0; c < cnt; c++) {
             int nr = 0;
             status[g + c] = (int8_t)bs::classify<1>(Sm, out, (int)c, nr);
