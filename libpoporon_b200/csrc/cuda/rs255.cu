@@ -813,7 +813,7 @@ struct ApplyHook {
     uint8_t *data;
     uint32_t stride32;
     int pad;
-    uint32_t entry_cur, entry_nxt, entry_app;
+    uint32_t entry_cur, entry_app;
     uint32_t p2, m2; // raw 16-bit loads of a portion, zero-extended by the load itself: nothing touches them before
                      // after(), so nothing waits for them early
 
@@ -831,7 +831,6 @@ struct ApplyHook {
         }
         qprev = queue + first;
         entry_cur = entry_of(0);
-        entry_nxt = 0xFFFFFFFFu;
         p2 = 0;
         m2 = 0;
     }
@@ -860,27 +859,53 @@ struct ApplyHook {
     {
         flush();
         const uint32_t sp = (uint32_t)k & 7u;
-        if (sp == 0)
-            entry_nxt = entry_of(((uint32_t)k >> 3) + 1u);
         entry_app = entry_cur;
         if (entry_cur != 0xFFFFFFFFu) {
             const uint8_t *row = records + (size_t)(entry_cur & 0x3FFFFFFFu) * 32 + 2u * sp;
             asm volatile("ld.global.u16 %0, [%1];" : "=r"(p2) : "l"(row));
             asm volatile("ld.global.u16 %0, [%1+16];" : "=r"(m2) : "l"(row));
         }
+        // the next codeword's queue entry is fetched straight into entry_cur one step before its first use (a
+        // separate "next" register merged by a select would be read - and waited for - every step)
         if (sp == 7u)
-            entry_cur = entry_nxt;
+            entry_cur = entry_of(((uint32_t)k >> 3) + 1u);
     }
     __device__ __forceinline__ void after(int) {}
     __device__ __forceinline__ void end() { flush(); }
-    // everything still pending (after a warp's last tile)
+    // everything still pending (after a warp's last tile): whole records, four codewords per round so that the
+    // exposed round trips (entry -> record -> XORs) are few
     __device__ __forceinline__ void drain()
     {
         begin();
 #pragma unroll 1
-        for (int k = 0; k < 256; k++)
-            before(k);
-        flush();
+        for (uint32_t c0 = 0; c0 < 32u; c0 += 4u) {
+            uint32_t ent[4];
+            uint4 xs[4], mg[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                ent[u] = entry_of(c0 + (uint32_t)u);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                xs[u] = make_uint4(0u, 0u, 0u, 0u);
+                mg[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (ent[u] != 0xFFFFFFFFu) {
+                    const uint4 *row = reinterpret_cast<const uint4 *>(records + (size_t)(ent[u] & 0x3FFFFFFFu) * 32);
+                    xs[u] = row[0];
+                    mg[u] = row[1];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t xw[4] = {xs[u].x, xs[u].y, xs[u].z, xs[u].w}, mw[4] = {mg[u].x, mg[u].y, mg[u].z, mg[u].w};
+                entry_app = ent[u];
+#pragma unroll
+                for (int h = 0; h < 8; h++) {
+                    p2 = (xw[h >> 1] >> (16 * (h & 1))) & 0xFFFFu;
+                    m2 = (mw[h >> 1] >> (16 * (h & 1))) & 0xFFFFu;
+                    flush();
+                }
+            }
+        }
         g0p = 0xFFFFFFFFu;
     }
 };
@@ -938,9 +963,8 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
             }
             solve_load_syndromes<0>(ent, syn_raw, Syn);
         }
-        uint32_t L[bs::kLS][8];
         bs::LaneOut out;
-        bs::solve_lane<32, 32>(Syn, B, S, pad, L, out, hook); // also drains the previous tile's corrections
+        bs::solve_lane<32, 32>(Syn, B, S, pad, out, hook); // also drains the previous tile's corrections
 
         // Outcome of every codeword of the lane.  What the solver declines goes to the literal stage.  A decodable
         // codeword gets an error record in place of its (now dead) raw syndrome row: bytes 0..15 the error locations
@@ -983,7 +1007,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
         for (int w = 0; w < 4; w++) {
             if (!__any_sync(0xFFFFFFFFu, maxroots > 4 * w))
                 break;
-            bs::forney_slots<32, 32>(L, B, S, w, root_tab, nzc);
+            bs::forney_slots<32, 32>(Syn, B, S, w, root_tab, nzc);
             uint32_t X[32];
             bs::magnitude_words<32>(S, X);
 #pragma unroll

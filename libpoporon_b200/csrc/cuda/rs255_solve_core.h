@@ -34,6 +34,8 @@
 #pragma once
 #include <stdint.h>
 
+#include <utility>
+
 #include "gf256_consts.cuh"
 
 #if defined(__CUDACC__)
@@ -346,22 +348,22 @@ BS_FN void omega(const Mem<SO> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE>
         st8(P, j, L[j]);
 #pragma unroll 1
     for (int i = 0; i < kT; i++) {
-        uint32_t acc[15], o[8], a[8], s[8];
+        // the syndromes come from the slower memory: fetched two terms ahead (s, s1, s2 = S_{i-j}, S_{i-j-1}, S_{i-j-2})
+        uint32_t acc[15], o[8], a[8], s[8], s1[8], s2[8];
         clear15(acc);
         ld8(P, 0, a);
         ld8(S, i, s);
+        ld8(S, i >= 1 ? i - 1 : 0, s1);
 #pragma unroll 1
         for (int j = 0; j <= i; j++) {
-            uint32_t an[8], sn[8];
-            if (j < i) {
-                ld8(P, j + 1, an);
-                ld8(S, i - j - 1, sn);
-            }
+            // unconditional loads with clamped indices (values past the end are never used)
+            uint32_t an[8];
+            ld8(S, j + 2 <= i ? i - j - 2 : 0, s2);
+            ld8(P, j < i ? j + 1 : 0, an);
             mac(acc, a, s);
-            if (j < i) {
-                cp8(a, an);
-                cp8(s, sn);
-            }
+            cp8(a, an);
+            cp8(s, s1);
+            cp8(s1, s2);
         }
         reduce(acc, o);
         st8(O, i, o);
@@ -421,33 +423,145 @@ BS_FN void transpose32(uint32_t (&x)[32])
     }
 }
 
-// ---- Chien search -------------------------------------------------------------------------------------------
-// Location k = 0..254 corresponds to the root alpha^(k+1) (src/decode.c:117-141 with prim = 1: k = i - 1).
-// Before location k is examined every term is advanced once, L_j <- L_j * alpha^j (j = 1..16), so that L_j
-// holds lambda_j * alpha^(j*(k+1)).  After all 255 locations every term is back at lambda_j (alpha^255 = 1).
-template <int J>
-BS_FN void advance_L(uint32_t (&L)[kLS][8])
+// ---- Chien search as a linear recurring sequence ---------------------------------------------------------------
+// Location k = 0..254 corresponds to the root alpha^(k+1) (src/decode.c:117-141 with prim = 1: k = i - 1), and the
+// value examined there is  v_k = sum_{j=0..16} L_j * alpha^(j*(k+1)).  As a sequence in k this is a sum of 17
+// geometric progressions, so its generating function is rational with a CONSTANT denominator:
+//     V(z) = sum_k v_k z^k = sum_j A_j / (1 - b_j z) = N(z) / D(z),   A_j = L_j alpha^j,  b_j = alpha^j,
+//     D(z) = prod_{j=0..16} (1 - alpha^j z)  (degree 17, D_0 = 1),   N(z) = sum_j A_j prod_{i != j} (1 - alpha^i z).
+// Power-series division of N by D is the classic shift-register circuit: keep r (17 coefficients, r = N at the
+// start); each step emits v = r_0 and replaces r by (r + v*D)/z, i.e. r_i <- r_{i+1} + v*D_{i+1} (r_17 = 0).
+// One location therefore costs two 16-entry subset tables of the 8 planes of v (22 XOR) and ONE three-input XOR
+// per state plane (136) - the same shape as the encoder's LFSR step - instead of 16 in-place constant multipliers
+// plus a 17-term sum (~260 LOP3 + ~115 moves).  N is a constant linear map of the locator (17 x 17 field
+// constants M[i][j] = alpha^j * [z^i] prod_{i' != j} (1 - alpha^i' z)), applied once per sweep.
+struct ChienConsts {
+    uint8_t d[18];     // D_0 .. D_17
+    uint8_t m[17][17]; // N_i = sum_j m[i][j] * L_j
+};
+
+constexpr ChienConsts make_chien_consts()
 {
-    if constexpr (J <= kT) {
-        cmul<gf256::pow_alpha(J)>(L[J], L[J]);
-        advance_L<J + 1>(L);
+    ChienConsts c{};
+    const gf256::Poly all = gf256::roots_poly(0, 17); // prod (x - alpha^j), degree 17: D_i = all_{17-i}
+    for (int i = 0; i <= 17; i++)
+        c.d[i] = all.c[17 - i];
+    for (int j = 0; j <= 16; j++) {
+        gf256::Poly q = gf256::zero_poly(); // prod_{i != j} (x - alpha^i), degree 16; [z^i] of the reversed = q_{16-i}
+        q.c[0] = 1;
+        int deg = 0;
+        for (int i = 0; i <= 16; i++) {
+            if (i == j)
+                continue;
+            const uint8_t r = gf256::pow_alpha(i);
+            for (int k = deg + 1; k > 0; k--)
+                q.c[k] = q.c[k - 1] ^ gf256::mul(q.c[k], r);
+            q.c[0] = gf256::mul(q.c[0], r);
+            deg++;
+        }
+        for (int i = 0; i <= 16; i++)
+            c.m[i][j] = gf256::mul(gf256::pow_alpha(j), q.c[16 - i]);
     }
+    return c;
+}
+constexpr ChienConsts kChien = make_chien_consts();
+static_assert(kChien.d[0] == 1, "D(0) = 1");
+
+// a ^ b ^ c in one LOP3 (spelled out on the device: ptxas otherwise re-associates the table look-ups away)
+BS_FN uint32_t xor3(uint32_t a, uint32_t b, uint32_t c)
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#else
+    return a ^ b ^ c;
+#endif
 }
 
-// one location: returns the mask of codewords whose locator vanishes there
-BS_FN uint32_t chien_step(uint32_t (&L)[kLS][8])
+// all 16 subset-XORs of four planes (11 XORs)
+BS_FN void subset_table(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3, uint32_t (&T)[16])
 {
-    advance_L<1>(L);
-    uint32_t nz = 0;
-#pragma unroll
-    for (int t = 0; t < 8; t++) {
-        uint32_t v = L[0][t];
-#pragma unroll
-        for (int j = 1; j <= kT; j++)
-            v ^= L[j][t];
-        nz |= v;
-    }
+    T[0] = 0;
+    T[1] = b0;
+    T[2] = b1;
+    T[3] = b0 ^ b1;
+    T[4] = b2;
+    T[5] = b2 ^ b0;
+    T[6] = b2 ^ b1;
+    T[7] = b2 ^ T[3];
+    T[8] = b3;
+    T[9] = b3 ^ b0;
+    T[10] = b3 ^ b1;
+    T[11] = b3 ^ T[3];
+    T[12] = b3 ^ b2;
+    T[13] = T[12] ^ b0;
+    T[14] = T[12] ^ b1;
+    T[15] = T[12] ^ T[3];
+}
+
+constexpr int kNR = 17; // state bytes of the sequence generator
+
+template <int IT>
+BS_FN void chien_update_one(uint32_t (&R)[kNR][8], const uint32_t (&T1)[16], const uint32_t (&T2)[16])
+{
+    constexpr int I = IT >> 3, T = IT & 7;
+    constexpr unsigned m = gf256::rowmask(kChien.d[I + 1], T);
+    if constexpr (I < kNR - 1)
+        R[I][T] = xor3(R[I + 1][T], T1[m & 15], T2[m >> 4]);
+    else
+        R[I][T] = T1[m & 15] ^ T2[m >> 4];
+}
+template <int... IT>
+BS_FN void chien_update_all(uint32_t (&R)[kNR][8], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
+                            std::integer_sequence<int, IT...>)
+{
+    (chien_update_one<IT>(R, T1, T2), ...);
+}
+
+// one location: returns the mask of codewords whose locator vanishes there, and advances the generator
+BS_FN uint32_t chien_step(uint32_t (&R)[kNR][8])
+{
+    const uint32_t nz = or8(R[0]);
+    uint32_t T1[16], T2[16];
+    subset_table(R[0][0], R[0][1], R[0][2], R[0][3], T1);
+    subset_table(R[0][4], R[0][5], R[0][6], R[0][7], T2);
+    chien_update_all(R, T1, T2, std::make_integer_sequence<int, 8 * kNR>{});
     return ~nz;
+}
+
+// R += M[.][J] * L_J for one locator coefficient (8 planes in l)
+template <int J, int IT>
+BS_FN void chien_init_one(uint32_t (&R)[kNR][8], const uint32_t (&T1)[16], const uint32_t (&T2)[16])
+{
+    constexpr int I = IT >> 3, T = IT & 7;
+    constexpr unsigned m = gf256::rowmask(kChien.m[I][J], T);
+    if constexpr (J == 0)
+        R[I][T] = T1[m & 15] ^ T2[m >> 4];
+    else
+        R[I][T] = xor3(R[I][T], T1[m & 15], T2[m >> 4]);
+}
+template <int J, int... IT>
+BS_FN void chien_init_all(uint32_t (&R)[kNR][8], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
+                          std::integer_sequence<int, IT...>)
+{
+    (chien_init_one<J, IT>(R, T1, T2), ...);
+}
+// LM: the locator, word block j = L_j (17 blocks).  The next coefficient is loaded while the current one is used.
+template <int J, int SL>
+BS_FN void chien_init_from(const Mem<SL> LM, uint32_t (&R)[kNR][8], const uint32_t (&l)[8])
+{
+    if constexpr (J < kNR) {
+        uint32_t ln[8], T1[16], T2[16];
+        if constexpr (J + 1 < kNR)
+            ld8(LM, J + 1, ln);
+        BS_FENCE();
+        subset_table(l[0], l[1], l[2], l[3], T1);
+        subset_table(l[4], l[5], l[6], l[7], T2);
+        chien_init_all<J>(R, T1, T2, std::make_integer_sequence<int, 8 * kNR>{});
+        if constexpr (J + 1 < kNR)
+            chien_init_from<J + 1, SL>(LM, R, ln);
+    }
 }
 
 // ---- memory map of the work area W (200 words per lane) ---------------------------------------------------------
@@ -516,9 +630,15 @@ struct NoHook {
     BS_FN void end() {}
 };
 
-template <int STRIDE, class Hook>
-BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, LaneOut &out, Hook &hook)
+template <int STRIDE, int SL, class Hook>
+BS_FN void chien_collect(const Mem<SL> LM, const Mem<STRIDE> S, int pad, LaneOut &out, Hook &hook)
 {
+    uint32_t R[kNR][8];
+    {
+        uint32_t l0[8];
+        ld8(LM, 0, l0);
+        chien_init_from<0, SL>(LM, R, l0);
+    }
     for (int w = kListBase; w < kParkBase + 32; w++)
         S.st(w, 0u);
     hook.begin();
@@ -534,7 +654,7 @@ BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, La
             hook.before(k);
             uint32_t m = 0;
             if (k < 255) {
-                m = chien_step(L);
+                m = chien_step(R);
                 if (k < pad)
                     padfail |= m;
             }
@@ -556,57 +676,22 @@ BS_FN void chien_collect(uint32_t (&L)[kLS][8], const Mem<STRIDE> S, int pad, La
         append_roots<STRIDE>(S, c, 7, S.ld(kParkBase + c), S.ld_byte(kCntBase + (c >> 2), c & 3));
     hook.end();
     out.padfail = padfail;
-    // every term is back at its coefficient (alpha^(255 j) = 1)
-#pragma unroll
-    for (int j = 0; j < kNL; j++)
-        out.nzL[j] = or8(L[j]);
 }
 
-// ---- Forney on one list slot ----------------------------------------------------------------------------------
+// ---- Forney on four list slots at a time -----------------------------------------------------------------------
 // x = the root alpha^(k+1) found for each of the 32 codewords (planes).  Magnitude (src/decode.c:159-191,
 // fcr = 1 so num2 = 1):  Omega(x) / Lambda'(x)  =  x*Omega(x) / (sum of the odd-degree locator terms at x).
 // A vanishing numerator gives magnitude 0 (the reference does not count such a root either); an empty slot
 // (x = 0) gives 0 as well.
-template <int SO>
-BS_FN void forney_slot(const uint32_t (&L)[kLS][8], const Mem<SO> O, uint32_t (&x)[8])
-{
-    uint32_t num[8], odd[8], x2[8], o[8];
-    // Horner: Omega_15, then acc <- acc*x + Omega_j
-    ld8(O, kT - 1, num);
-    ld8(O, kT - 2, o);
-#pragma unroll 1
-    for (int j = kT - 2; j >= 0; j--) {
-        uint32_t acc[15], on[8];
-        if (j > 0)
-            ld8(O, j - 1, on);
-        clear15(acc);
-        cp8(*reinterpret_cast<uint32_t(*)[8]>(&acc[0]), o);
-        mac(acc, num, x);
-        reduce(acc, num);
-        if (j > 0)
-            cp8(o, on);
-    }
-    mul(num, x, num);
-    sqr(x, x2);
-    cp8(odd, L[kT - 1]);
-#pragma unroll
-    for (int j = kT - 3; j >= 1; j -= 2) {
-        uint32_t acc[15];
-        clear15(acc);
-        cp8(*reinterpret_cast<uint32_t(*)[8]>(&acc[0]), L[j]);
-        mac(acc, odd, x2);
-        reduce(acc, odd);
-    }
-    mul(odd, x, odd);
-    inv(odd, odd);
-    mul(num, odd, x);
-}
-
+//
 // List slots 4w .. 4w+3 of all 32 codewords: afterwards scratch words 8y .. 8y+7 of S hold the magnitude planes
 // of slot 4w + y, and cnt (5 bit-planes) has counted the non-zero magnitudes.  magnitude_words() then gives
 // one word per codeword (byte y = magnitude of slot 4w + y).
+// The two Horner recurrences run over the four slots in lock step: one coefficient (fetched from the L2-resident
+// scratch one step ahead) feeds four independent multiply-reduce chains, so its latency hides behind ~340
+// instructions and the chains overlap each other's dependent steps.
 template <int STRIDE, int SO>
-BS_FN void forney_slots(const uint32_t (&L)[kLS][8], const Mem<SO> O, const Mem<STRIDE> S, int w,
+BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, int w,
                         const uint8_t *root_tab /* [0] = 0, [v] = alpha^v */, uint32_t (&cnt)[5])
 {
     {
@@ -622,13 +707,79 @@ BS_FN void forney_slots(const uint32_t (&L)[kLS][8], const Mem<SO> O, const Mem<
         for (int p = 0; p < 32; p++)
             S.st(p, X[p]);
     }
+    {
+        uint32_t x[4][8], num[4][8], o[8];
+        ld8(O, kT - 1, o);
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            ld8(S, y, x[y]);
+            cp8(num[y], o);
+        }
+        // x * Omega(x): Horner from Omega_15 down, then one more factor x
+        ld8(O, kT - 2, o);
+#pragma unroll 1
+        for (int j = kT - 2; j >= 0; j--) {
+            // (unconditional, index clamped: a conditionally loaded array is demoted to local memory and its
+            // spill store then waits for the load)
+            uint32_t on[8];
+            ld8(O, j > 0 ? j - 1 : 0, on);
+#pragma unroll
+            for (int y = 0; y < 4; y++) {
+                uint32_t acc[15];
+                clear15(acc);
+                cp8(*reinterpret_cast<uint32_t(*)[8]>(&acc[0]), o);
+                mac(acc, num[y], x[y]);
+                reduce(acc, num[y]);
+            }
+            cp8(o, on);
+        }
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            mul(num[y], x[y], num[y]);
+            for (int t = 0; t < 8; t++) // parked in the (idle) parked-mask words until the division
+                S.st(kParkBase + 8 * y + t, num[y][t]);
+        }
+        // x * Lambda'(x) = x * sum over odd j of L_j x^(j-1): Horner in x^2 from L_15 down
+        uint32_t x2[4][8], odd[4][8];
+        ld8(LM, kT - 1, o);
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            sqr(x[y], x2[y]);
+            cp8(odd[y], o);
+        }
+        ld8(LM, kT - 3, o);
+#pragma unroll 1
+        for (int j = kT - 3; j >= 1; j -= 2) {
+            uint32_t on[8];
+            ld8(LM, j > 1 ? j - 2 : 1, on);
+#pragma unroll
+            for (int y = 0; y < 4; y++) {
+                uint32_t acc[15];
+                clear15(acc);
+                cp8(*reinterpret_cast<uint32_t(*)[8]>(&acc[0]), o);
+                mac(acc, odd[y], x2[y]);
+                reduce(acc, odd[y]);
+            }
+            cp8(o, on);
+        }
+        // denominators over the x planes
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            mul(odd[y], x[y], odd[y]);
+            st8(S, y, odd[y]);
+        }
+    }
 #pragma unroll 1
     for (int y = 0; y < 4; y++) {
-        uint32_t x[8];
-        ld8(S, y, x);
-        forney_slot<SO>(L, O, x);
-        st8(S, y, x);
-        uint32_t m = or8(x);
+        uint32_t num[8], den[8], mag[8];
+        ld8(S, y, den);
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            num[t] = S.ld(kParkBase + 8 * y + t);
+        inv(den, den);
+        mul(num, den, mag);
+        st8(S, y, mag);
+        uint32_t m = or8(mag);
 #pragma unroll
         for (int b = 0; b < 5; b++) {
             const uint32_t t = cnt[b] & m;
@@ -680,13 +831,22 @@ BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots)
 // Syn and Om may live in slower memory than W (on the device: an L2-resident scratch in global memory, so that
 // a warp needs 25 KB of shared memory and eight warps fit one SM).
 template <int STRIDE, int SO, class Hook>
-BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<STRIDE> W, int pad, uint32_t (&L)[kLS][8], LaneOut &out,
-                      Hook &hook)
+BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<STRIDE> W, int pad, LaneOut &out, Hook &hook)
 {
     const Mem<STRIDE> B{W.base + kListBase * STRIDE};
-    ribm<STRIDE, SO>(Syn, B, L, out.K);
-    omega<STRIDE, SO>(Syn, L, B, Om);
-    chien_collect<STRIDE, Hook>(L, W, pad, out, hook);
+    {
+        uint32_t L[kLS][8];
+        ribm<STRIDE, SO>(Syn, B, L, out.K);
+        omega<STRIDE, SO>(Syn, L, B, Om);
+        // the syndromes are dead now: their first 17 word blocks receive the locator (read by the sweep set-up
+        // and by Forney)
+#pragma unroll
+        for (int j = 0; j < kNL; j++) {
+            out.nzL[j] = or8(L[j]);
+            st8(Syn, j, L[j]);
+        }
+    }
+    chien_collect<STRIDE, SO, Hook>(Syn, W, pad, out, hook);
 }
 
 } // namespace bs

@@ -27,10 +27,9 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
                     if ((syn[(g + c) * 32 + m] >> t) & 1)
                         Syn[8 * m + t] |= 1u << c;
         bs::LaneOut out;
-        uint32_t L[bs::kLS][8];
         const bs::Mem<1> Sm{S}, Bm{B}, Synm{Syn};
         bs::NoHook hook;
-        bs::solve_lane<1, 1>(Synm, Bm, Sm, pad, L, out, hook);
+        bs::solve_lane<1, 1>(Synm, Bm, Sm, pad, out, hook);
         for (size_t c = 0; c < cnt; c++) {
             int nr = 0;
             status[g + c] = (int8_t)bs::classify<1>(Sm, out, (int)c, nr);
@@ -38,7 +37,7 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
         }
         uint32_t nzc[5] = {0, 0, 0, 0, 0};
         for (int w = 0; w < 4; w++) {
-            bs::forney_slots<1, 1>(L, Bm, Sm, w, root_tab, nzc);
+            bs::forney_slots<1, 1>(Synm, Bm, Sm, w, root_tab, nzc);
             uint32_t X[32];
             bs::magnitude_words<1>(Sm, X);
             for (size_t c = 0; c < cnt; c++) {
