@@ -202,6 +202,58 @@ bch_decode_kernel(BchParams P, const uint8_t *__restrict__ gtab, uint8_t *data, 
         corrected[cw] = nc;
 }
 
+// ---- complete decode map for short codes (n <= 15) ------------------------------------------------------------
+// The outcome of poporon_bch_decode (src/bch.c:382-435) is a pure function of the n received bits, so for n <= 15
+// the exact step-by-step decoder above is run ONCE over all 2^n words when the context is created and batches are
+// decoded by look-up: word = fixed codeword | num_errors << 24 | ok << 31.  The 128 KB table stays in L1/L2, the
+// batch kernel is then bound by its 9 bytes per codeword of HBM traffic instead of ~900 table-driven field
+// operations per codeword.  Bit-exact by construction (every entry IS the reference-shaped decoder's answer).
+constexpr int kMapMaxN = 15;
+
+__global__ void __launch_bounds__(128)
+bch_build_map_kernel(BchParams P, const uint8_t *__restrict__ gtab, uint32_t *__restrict__ map)
+{
+    __shared__ BchSmem T;
+    bch_load_tables(T, gtab);
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= (1u << P.n))
+        return;
+    uint32_t fixed;
+    int ne;
+    const bool good = bch_decode_word(P, T, w, fixed, ne);
+    map[w] = good ? (fixed | ((uint32_t)(ne > 0 ? ne : 0) << 24) | 0x80000000u) : 0u;
+}
+
+__global__ void __launch_bounds__(256)
+bch_decode_map_kernel(BchParams P, const uint32_t *__restrict__ map, uint8_t *data, size_t data_stride, size_t size,
+                      const uint8_t *__restrict__ parity, size_t parity_stride, size_t n, uint8_t *__restrict__ ok,
+                      uint32_t *__restrict__ corrected)
+{
+    const int db = (P.k + 7) / 8, pb = (P.parity_bits + 7) / 8;
+    const bool sized = size != 0 && size >= (size_t)db;
+    for (size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x; cw < n; cw += (size_t)gridDim.x * blockDim.x) {
+        bool good = false;
+        uint32_t nc = 0;
+        if (sized) {
+            uint8_t *d = data + cw * data_stride;
+            const uint32_t dv = pack_be(d, db) & low_mask(P.k);
+            const uint32_t pv = pack_be(parity + cw * parity_stride, pb) & low_mask(P.parity_bits);
+            const uint32_t e = __ldg(map + ((dv << P.parity_bits) | pv));
+            if (e & 0x80000000u) {
+                const uint32_t out = ((e & 0xFFFFu) >> P.parity_bits) & low_mask(P.k);
+                for (int i = 0; i < db && i < 4; i++)
+                    d[db - 1 - i] = (uint8_t)(out >> (8 * i));
+                nc = (e >> 24) & 0x7Fu;
+                good = true;
+            }
+        }
+        if (ok)
+            ok[cw] = good ? 1 : 0;
+        if (corrected)
+            corrected[cw] = nc;
+    }
+}
+
 BchParams params_of(const poporon_cuda_bch *ctx)
 {
     BchParams P;
@@ -230,11 +282,31 @@ int launch_bch_encode(poporon_cuda_bch *ctx, const uint8_t *data, size_t data_st
     return check(cudaGetLastError(), "bch_encode launch");
 }
 
+int bch_build_decode_map(poporon_cuda_bch *ctx)
+{
+    if (ctx->n > kMapMaxN)
+        return 0;
+    const uint32_t words = 1u << ctx->n;
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_map, words * sizeof(uint32_t)));
+    bch_build_map_kernel<<<(words + 127) / 128, 128>>>(params_of(ctx), ctx->d_tables, ctx->d_map);
+    ctx->launches++;
+    PP_CUDA_TRY(cudaGetLastError());
+    return check(cudaDeviceSynchronize(), "bch decode map");
+}
+
 int launch_bch_decode(poporon_cuda_bch *ctx, uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
                       size_t parity_stride, size_t n, uint8_t *ok, uint32_t *corrected, cudaStream_t stream)
 {
     if (n == 0)
         return 0;
+    if (ctx->d_map) {
+        size_t blocks = (n + 255) / 256;
+        const size_t cap = (size_t)ctx->sm_count * 32;
+        bch_decode_map_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(
+            params_of(ctx), ctx->d_map, data, data_stride, size, parity, parity_stride, n, ok, corrected);
+        ctx->launches++;
+        return check(cudaGetLastError(), "bch_decode (map) launch");
+    }
     const int threads = 128;
     bch_decode_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, stream>>>(
         params_of(ctx), ctx->d_tables, data, data_stride, size, parity, parity_stride, n, ok, corrected);

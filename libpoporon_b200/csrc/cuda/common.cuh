@@ -105,5 +105,6 @@ struct poporon_cuda_bch {
     int m, nn, n, k, parity_bits, t;
     uint32_t gen;
     uint8_t *d_tables; // alpha_to[256] | index_of[256]
+    uint32_t *d_map;   // n <= 15: the complete decode map, one word per received word (bch.cu), else NULL
     uint64_t launches;
 };

@@ -458,6 +458,8 @@ int poporon_cuda_bch_create(const poporon_cuda_bch_desc_t *d, int device, poporo
     int rc = check(cudaMalloc((void **)&ctx->d_tables, sizeof h), "cudaMalloc bch tables");
     if (rc == 0)
         rc = check(cudaMemcpy(ctx->d_tables, h, sizeof h, cudaMemcpyHostToDevice), "upload bch tables");
+    if (rc == 0)
+        rc = bch_build_decode_map(ctx);
     if (rc != 0) {
         poporon_cuda_bch_destroy(ctx);
         return rc;
@@ -472,6 +474,7 @@ void poporon_cuda_bch_destroy(poporon_cuda_bch_t *ctx)
         return;
     DeviceGuard g(ctx->device);
     cudaFree(ctx->d_tables);
+    cudaFree(ctx->d_map);
     free(ctx);
 }
 
