@@ -111,6 +111,7 @@ int poporon_cuda_event_create(int device, void **event);
 int poporon_cuda_event_destroy(int device, void *event);
 int poporon_cuda_event_record(int device, void *event, void *stream);
 int poporon_cuda_event_elapsed_ms(int device, void *start, void *stop, float *ms); /* synchronises on stop */
+int poporon_cuda_stream_wait_event(int device, void *stream, void *event);          /* cudaStreamWaitEvent */
 
 /* ---- Reed-Solomon -------------------------------------------------------------------------- */
 int poporon_cuda_rs_create(const poporon_cuda_rs_desc_t *desc, int device, poporon_cuda_rs_t **out);

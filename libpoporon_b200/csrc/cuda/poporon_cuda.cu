@@ -254,6 +254,12 @@ int poporon_cuda_event_elapsed_ms(int device, void *start, void *stop, float *ms
     return check(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop), "cudaEventElapsedTime");
 }
 
+int poporon_cuda_stream_wait_event(int device, void *stream, void *event)
+{
+    GUARD(device);
+    return check(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0), "cudaStreamWaitEvent");
+}
+
 /* ------------------------------------------------------------------------------------------ RS */
 
 int poporon_cuda_rs_create(const poporon_cuda_rs_desc_t *d, int device, poporon_cuda_rs_t **out)

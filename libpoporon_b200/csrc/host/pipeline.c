@@ -57,8 +57,10 @@ bool pp_lane_prepare(poporon_t *h, pp_lane_t *lane)
     if (rc != 0)
         return false;
     for (s = 0; s < PP_SLOTS; s++) {
-        if (poporon_cuda_stream_create(lane->device, &lane->slot[s].stream) != 0)
+        if (poporon_cuda_stream_create(lane->device, &lane->slot[s].stream) != 0 ||
+            poporon_cuda_event_create(lane->device, &lane->slot[s].kdone) != 0)
             return false;
+        lane->slot[s].kdone_set = false;
     }
     lane->ready = true;
     return true;
@@ -76,6 +78,8 @@ void pp_handle_release_lanes(poporon_t *h)
                 poporon_cuda_stream_sync(lane->device, sl->stream);
                 poporon_cuda_stream_destroy(lane->device, sl->stream);
             }
+            if (sl->kdone)
+                poporon_cuda_event_destroy(lane->device, sl->kdone);
             poporon_cuda_free(lane->device, sl->d_span);
             poporon_cuda_free(lane->device, sl->d_pspan);
             poporon_cuda_free(lane->device, sl->d_aux);
@@ -362,8 +366,23 @@ static void run_lane(lane_task_t *t)
         dj.syn = (const uint16_t *)d_syn;
         dj.ok = d_ok;
         dj.corrected = (uint32_t *)d_cor;
+        /* The device context owns ONE set of decode scratch (dirty queue, syndrome rows, counters), so the kernel
+         * sections of consecutive chunks must not overlap even though they sit on different streams: wait for the
+         * other slot's kernels; copies on either side still overlap them. */
+        {
+            int o;
+            for (o = 0; o < PP_SLOTS; o++) {
+                pp_slot_t *other = &lane->slot[o];
+                if (other != sl && other->kdone_set &&
+                    poporon_cuda_stream_wait_event(dev, sl->stream, other->kdone) != 0)
+                    return;
+            }
+        }
         if (launch(h, lane, &dj, sl->stream) != 0)
             return;
+        if (poporon_cuda_event_record(dev, sl->kdone, sl->stream) != 0)
+            return;
+        sl->kdone_set = true;
 
         /* ---- device -> host ---- */
         if (j->op == 0) {

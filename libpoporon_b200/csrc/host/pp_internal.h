@@ -63,6 +63,8 @@ struct _poporon_config_t {
 /* one staging slot: a stream plus grow-only device buffers */
 typedef struct {
     void *stream;
+    void *kdone;       /* event: this slot's kernels have finished (the decode context's scratch is free again) */
+    bool kdone_set;
     uint8_t *d_span;   /* data (and, for merged layouts, parity) bytes */
     size_t span_cap;
     uint8_t *d_pspan;  /* parity bytes when not merged */

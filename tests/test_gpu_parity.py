@@ -538,3 +538,29 @@ def test_rs_default_solver_heavy_loads(gpu_device, orc, size, elo, ehi, n):
     with api.Poporon.rs_default() as h:
         got = _gpu_decode(h, cw[:, :size], cw[:, size:])
     _assert_same(got, orc.rs_decode(cw[:, :size], cw[:, size:], threads=8), f"heavy {size} {elo}-{ehi}")
+
+
+def test_host_batch_many_chunks_on_two_streams(gpu_device):
+    """Packed 255-byte records on the host, 5 staging chunks, every codeword dirty (0-16 errors): consecutive
+    chunks sit on different CUDA streams but share the device context's decode scratch, so their kernel sections
+    must be ordered (pipeline.c).  Round-trip property at a size the oracle would not finish quickly."""
+    rng = np.random.default_rng(77)
+    n = (1 << 18) * 4 + 12345
+    rec = np.zeros((n, 255), np.uint8)
+    rec[:, :223] = rng.integers(0, 256, (n, 223), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        flat = rec.reshape(-1)
+        assert h.encode_batch(flat.ctypes.data, 255, 223, flat.ctypes.data + 223, 255, n)
+        clean = rec.copy()
+        e = rng.integers(0, 17, n)
+        for k in range(16):
+            rows = np.nonzero(e > k)[0]
+            # distinct positions per row: position = (start + 16 * k + small offset) mod 255 never repeats for k < 16
+            pos = (rows * 7 + 16 * k) % 255
+            rec[rows, pos] ^= rng.integers(1, 256, len(rows), dtype=np.uint8)
+        ok = np.zeros(n, np.uint8)
+        cor = np.zeros(n, np.uint32)
+        assert h.decode_batch(flat.ctypes.data, 255, 223, flat.ctypes.data + 223, 255, n, ok, cor)
+        assert ok.all()
+        assert (cor == e).all()
+        assert (rec == clean).all()
