@@ -226,7 +226,18 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout at the first collective: keep stdout for the ONE JSON line
+        sys.stdout.flush()
+        keep = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(keep, 1)
+            os.close(keep)
 
     n = args.ncw
     i0 = rank * n  # this rank's slice of the global codeword index space
@@ -406,7 +417,7 @@ def run_ours(args):
             dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         e2e_s = float(tmax.item())
         e2e = {"value": payload_step / e2e_s / 1e9, "unit": UNIT,
-               "h2d_bytes_per_step": n * (K_MSG + K_CW), "d2h_bytes_per_step": n * (K_PAR + K_CW + 5),
+               "h2d_bytes_per_step": world * n * (K_MSG + K_CW), "d2h_bytes_per_step": world * n * (K_PAR + K_CW + 5),
                "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
                "api": "poporon_encode_batch + poporon_decode_batch on page-locked host buffers"}
 
