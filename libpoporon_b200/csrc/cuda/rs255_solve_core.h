@@ -236,6 +236,35 @@ BS_FN uint32_t merge_bits(uint32_t a, uint32_t b, uint32_t m)
 #endif
 }
 
+// smallest of the 32 seven-bit two's-complement counters held in the planes K (bit-plane b = bit b)
+BS_FN int min_counter(const uint32_t (&K)[7])
+{
+    uint32_t cand = 0xFFFFFFFFu;
+    int v = 0;
+    {
+        const uint32_t neg = cand & K[6]; // any negative value is smaller than every non-negative one
+        if (neg) {
+            cand = neg;
+            v = -64;
+        }
+    }
+#pragma unroll
+    for (int b = 5; b >= 0; b--) {
+        const uint32_t zero = cand & ~K[b];
+        if (zero)
+            cand = zero;
+        else
+            v += 1 << b;
+    }
+    return v;
+}
+
+#if defined(__CUDA_ARCH__)
+#define BS_WARP_MIN(x) __reduce_min_sync(0xFFFFFFFFu, (x))
+#else
+#define BS_WARP_MIN(x) (x)
+#endif
+
 // ---- inversion-free Berlekamp-Massey ---------------------------------------------------------------------
 // S: 32 syndromes, word (8*m + t) = plane t of S_{m+1}.  B: scratch of kT*8 words.
 // On return L[0..16] is the locator (a non-zero multiple of the reference's lambda; L[17] is padding), K the
@@ -286,7 +315,21 @@ BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uin
     for (int r = 1; r <= kNS; r++) {
         const uint32_t chg = or8(delta) & ~K[6]; // delta != 0 and k >= 0
         const int top = r < kT ? r : kT;         // highest coefficient that can be non-zero after this iteration
+        // the counters first (they depend on chg only): afterwards k = r - 2*el with el the NEW register length
+        {
+            uint32_t carry = 0xFFFFFFFFu;
+#pragma unroll
+            for (int b = 0; b < 7; b++) {
+                const uint32_t inc = K[b] ^ carry;
+                carry &= K[b];
+                K[b] = merge_bits(~K[b], inc, chg);
+            }
+        }
+        // Largest new register length among the warp's 1024 codewords: T_i = 0 beyond it for every one of them
+        // (deg T <= el), so coefficient groups past it only shift B and skip the three products.
+        const int elmax = (r - BS_WARP_MIN(min_counter(K))) >> 1;
         uint32_t acc[15], bcur[8];
+        int full = 0; // coefficients 0 .. full-1 went through the complete update
         clear15(acc);
 #pragma unroll
         for (int t = 0; t < 8; t++)
@@ -295,7 +338,7 @@ BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uin
         for (int g = 0; g < 3; g++) {
             // Every coefficient of an active group is updated, without branches (so that the six steps can be
             // scheduled into each other): beyond `top` both L_i and B_{i-1} are still zero and stay zero.
-            if (6 * g <= top) {
+            if (6 * g <= top && 6 * g <= elmax) {
 #pragma unroll
                 for (int j = 0; j < 6; j++) {
                     const int i = 6 * g + j;
@@ -320,19 +363,30 @@ BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uin
                     mac(acc, T, s);
                     cp8(bcur, bnext);
                 }
+                full = 6 * g + 6;
             }
             rotate_groups(L);
+        }
+        // Coefficients full .. top were skipped: L_i = T_i = 0 there for all codewords, only B moves,
+        // B_i <- (length change ? L_i = 0 : B_{i-1}).  A small rolled loop, highest index first (the loop body of the
+        // groups above must stay inside the 32 KB instruction cache), bcur = old B_{full-1}.
+        {
+            const int hi = top < kT - 1 ? top : kT - 1;
+#pragma unroll 1
+            for (int i = hi; i > full; i--) {
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    B.st(8 * i + t, B.ld(8 * (i - 1) + t) & ~chg);
+            }
+            if (full <= hi) {
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    B.st(8 * full + t, bcur[t] & ~chg);
+            }
         }
 #pragma unroll
         for (int t = 0; t < 8; t++)
             gamma[t] = merge_bits(delta[t], gamma[t], chg);
-        uint32_t carry = 0xFFFFFFFFu;
-#pragma unroll
-        for (int b = 0; b < 7; b++) {
-            const uint32_t inc = K[b] ^ carry;
-            carry &= K[b];
-            K[b] = merge_bits(~K[b], inc, chg);
-        }
         reduce(acc, delta);
     }
 }
