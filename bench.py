@@ -351,8 +351,9 @@ def run_ours(args):
         "rs255_lfsr_kernel<ENCODE>": n * (K_MSG + K_PAR),
         "rs255_lfsr_kernel<SCREEN>": n * (K_CW + 0.25 + 32 * dirty_frac),
         "rs255_compact_kernel": n * (0.25 + 5 + 4 * dirty_frac),
-        "rs255_solve_kernel": n * dirty_frac * (4 + 32 + 5 + 2 * mean_err / max(dirty_frac, 1e-9)),
-        "rs255_apply_kernel": n * dirty_frac * (4 + 2 * mean_err / max(dirty_frac, 1e-9)) + 2 * n * mean_err,
+        # queue entry + syndrome row + status per dirty codeword; error record (2 B) + read-modify-write of the
+        # corrected byte (2 B) per correction (the solver applies its own corrections)
+        "rs255_solve_kernel": n * dirty_frac * (4 + 32 + 5) + n * mean_err * (2 + 2),
         "rs255_correct_kernel": 8,
     }
     kernels = {}
