@@ -702,13 +702,15 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
                      uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
 {
     __shared__ SmemTables T;
+    __shared__ uint8_t work[SmemWork<32>::kBytes]; // [array][index][thread]: no local-memory arrays
     load_tables(T, gtab);
+    SmemWork<32> wk{work + threadIdx.x};
+    const auto syn = wk.arr(7);
     const uint32_t total = *counter;
     for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
         const uint32_t entry = queue[q];
         const size_t cw = entry & 0x3FFFFFFFu;
         const uint32_t flags = entry >> 30;
-        uint8_t syn[33];
         // raw[q'] = state(alpha^j) = c(alpha^j) * alpha^(16 j)  ->  S_j in index form
         const uint4 *raw4 = reinterpret_cast<const uint4 *>(syn_raw + cw * 32);
 #pragma unroll
@@ -737,10 +739,10 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
         bool success;
         if (mode == POPORON_CUDA_MODE_ERASURE) {
             const uint32_t ec = cnt[cw];
-            success = ec <= 32u && rs_correct<32>(c, T, d, size, p, syn, ec, pos + cw * pos_stride, pos_stride, true,
+            success = ec <= 32u && rs_correct<32>(c, T, d, size, p, wk, syn, ec, pos + cw * pos_stride, pos_stride, true,
                                                   pad, ncorr);
         } else {
-            success = rs_correct<32>(c, T, d, size, p, syn, 0, nullptr, 0, false, pad, ncorr);
+            success = rs_correct<32>(c, T, d, size, p, wk, syn, 0, nullptr, 0, false, pad, ncorr);
         }
         if (ok)
             ok[cw] = success ? 1 : 0;

@@ -29,23 +29,63 @@ __device__ __forceinline__ void load_tables(SmemTables &s, const RsTables *g)
     __syncthreads();
 }
 
-// v mod nn for a 16-bit v (what the reference's fold loop computes, src/internal/common.h:102-110)
+// v mod nn for a 16-bit v (what the reference's fold loop computes, src/internal/common.h:102-110).
+// nn = 255 (the common field) folds bytes instead of dividing by a run-time value: 2^8 = 1 (mod 255).
 __device__ __forceinline__ uint32_t redc(uint32_t v16, int nn)
 {
-    return (v16 & 0xFFFFu) % (uint32_t)nn;
+    v16 &= 0xFFFFu;
+    if (nn == 255) {
+        v16 = (v16 & 0xFFu) + (v16 >> 8); // <= 510
+        v16 = (v16 & 0xFFu) + (v16 >> 8); // <= 255
+        return v16 == 255u ? 0u : v16;
+    }
+    return v16 % (uint32_t)nn;
 }
+
+// the same for a sum of two logarithms (each < nn, so the sum is < 2*nn): one conditional subtraction
+__device__ __forceinline__ uint32_t redc2(uint32_t v, int nn)
+{
+    return v >= (uint32_t)nn ? v - (uint32_t)nn : v;
+}
+
+// Work arrays of the correction stage (7 arrays of MAXR + 1 bytes, indexed at run time).
+// LocalWork: per-thread arrays (local memory) - any MAXR.  SmemWork: one column per thread of a shared-memory
+// block laid out [array][index][thread] (consecutive threads = consecutive bytes: conflict-free, and no
+// local-memory round trips), for CTAs of exactly kWorkThreads threads and small MAXR.
+constexpr int kWorkThreads = 128;
+
+template <int MAXR>
+struct LocalWork {
+    uint8_t a[7][MAXR + 1];
+    struct Ref {
+        uint8_t *p;
+        __device__ __forceinline__ uint8_t &operator[](int i) const { return p[i]; }
+    };
+    __device__ __forceinline__ Ref arr(int k) { return Ref{a[k]}; }
+};
+
+template <int MAXR>
+struct SmemWork {
+    uint8_t *base; // this thread's column: smem block + threadIdx.x
+    struct Ref {
+        uint8_t *p;
+        __device__ __forceinline__ uint8_t &operator[](int i) const { return p[i * kWorkThreads]; }
+    };
+    __device__ __forceinline__ Ref arr(int k) { return Ref{base + k * (MAXR + 1) * kWorkThreads}; }
+    static constexpr int kBytes = 8 * (MAXR + 1) * kWorkThreads; // 7 arrays + the syndromes (array 7)
+};
 
 // The correction stage, shared by all three decode modes.  Returns the reference's bool and sets
 // ncorr when the reference would have set *errors_corrected.
-template <int MAXR>
+template <int MAXR, class WORK, class SYN>
 __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, size_t size, uint8_t *parity,
-                           const uint8_t *syn /* index form */, uint32_t ecount, const uint32_t *epos,
+                           WORK &wk, const SYN syn /* index form, [i] */, uint32_t ecount, const uint32_t *epos,
                            size_t pos_stride, bool erasure_apply, int16_t pad, uint32_t &ncorr)
 {
     const int nr = c.nroots, nn = c.nn;
     const uint8_t A0 = (uint8_t)nn;
-    uint8_t lambda[MAXR + 1], b[MAXR + 1], t[MAXR + 1], omega[MAXR + 1];
-    uint8_t root[MAXR + 1], loc[MAXR + 1], reg[MAXR + 1];
+    const auto lambda = wk.arr(0), b = wk.arr(1), t = wk.arr(2), omega = wk.arr(3);
+    const auto root = wk.arr(4), loc = wk.arr(5), reg = wk.arr(6);
 
     for (int i = 0; i <= nr; i++)
         lambda[i] = 0;
@@ -58,7 +98,7 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
             for (int j = i + 1; j > 0; j--) {
                 const uint8_t lg = T.index_of[lambda[j - 1]];
                 if (lg != A0)
-                    lambda[j] ^= T.alpha_to[redc(term + lg, nn)];
+                    lambda[j] ^= T.alpha_to[redc2(term + lg, nn)];
             }
         }
     }
@@ -71,7 +111,7 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         for (uint32_t i = 0; i < r; i++) {
             const uint8_t s = syn[r - i - 1];
             if (lambda[i] != 0 && s != A0)
-                disc ^= T.alpha_to[redc((uint32_t)T.index_of[lambda[i]] + s, nn)];
+                disc ^= T.alpha_to[redc2((uint32_t)T.index_of[lambda[i]] + s, nn)];
         }
         disc = T.index_of[disc];
         if (disc == A0) {
@@ -81,7 +121,7 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         } else {
             t[0] = lambda[0];
             for (int i = 0; i < nr; i++)
-                t[i + 1] = (b[i] != A0) ? (uint8_t)(lambda[i + 1] ^ T.alpha_to[redc((uint32_t)disc + b[i], nn)])
+                t[i + 1] = (b[i] != A0) ? (uint8_t)(lambda[i + 1] ^ T.alpha_to[redc2((uint32_t)disc + b[i], nn)])
                                         : lambda[i + 1];
             if (2 * el <= r + ecount - 1) {
                 el = r + ecount - el;
@@ -116,7 +156,7 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
             uint8_t q = 1;
             for (int j = deg; j > 0; j--) {
                 if (reg[j] != A0) {
-                    reg[j] = (uint8_t)redc((uint32_t)reg[j] + j, nn);
+                    reg[j] = (uint8_t)redc2((uint32_t)reg[j] + j, nn);
                     q ^= T.alpha_to[reg[j]];
                 }
             }
@@ -137,7 +177,7 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         uint8_t acc = 0;
         for (int j = i; j >= 0; j--) {
             if (syn[i - j] != A0 && lambda[j] != A0)
-                acc ^= T.alpha_to[redc((uint32_t)syn[i - j] + lambda[j], nn)];
+                acc ^= T.alpha_to[redc2((uint32_t)syn[i - j] + lambda[j], nn)];
         }
         omega[i] = T.index_of[acc];
     }

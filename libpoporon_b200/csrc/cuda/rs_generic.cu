@@ -87,6 +87,7 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
     uint8_t *d = data + cw * data_stride;
     uint8_t *p = parity + cw * parity_stride;
     uint8_t syn[MAXR + 1];
+    LocalWork<MAXR> wk;
     uint32_t ncorr = 0;
     bool success = false;
 
@@ -101,7 +102,7 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
                 syn[i] = (uint8_t)(s > (uint16_t)nn ? nn : s);
                 dirty |= (s != (uint16_t)nn);
             }
-            success = !dirty || rs_correct<MAXR>(c, T, d, size, p, syn, 0, nullptr, 0, false, pad, ncorr);
+            success = !dirty || rs_correct<MAXR>(c, T, d, size, p, wk, (const uint8_t *)syn, 0, nullptr, 0, false, pad, ncorr);
         } else {
             // Horner over data || parity at the generator roots
             const uint32_t first = d[0] & nn;
@@ -128,10 +129,10 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
             } else if (mode == POPORON_CUDA_MODE_ERASURE) {
                 const uint32_t ec = cnt[cw];
                 if (ec <= (uint32_t)nr) // > nroots erasures overrun the reference's scratch: report failure
-                    success = rs_correct<MAXR>(c, T, d, size, p, syn, ec, pos + cw * pos_stride, pos_stride, true,
+                    success = rs_correct<MAXR>(c, T, d, size, p, wk, (const uint8_t *)syn, ec, pos + cw * pos_stride, pos_stride, true,
                                                pad, ncorr);
             } else {
-                success = rs_correct<MAXR>(c, T, d, size, p, syn, 0, nullptr, 0, false, pad, ncorr);
+                success = rs_correct<MAXR>(c, T, d, size, p, wk, (const uint8_t *)syn, 0, nullptr, 0, false, pad, ncorr);
             }
         }
     }
