@@ -11,7 +11,7 @@
 
 #define PP_VERSION_ID  20000000u /* reference src/internal/common.h:29 */
 #define PP_MAX_DEVICES 16
-#define PP_SLOTS       2         /* staging slots (CUDA streams) per device */
+#define PP_SLOTS       4         /* staging slots (CUDA streams + buffers) per device: H2D of chunk i+2.. runs while chunk i drains */
 
 #ifndef POPORON_BUILDTIME
 #define POPORON_BUILDTIME 1
