@@ -254,6 +254,76 @@ bch_decode_map_kernel(BchParams P, const uint32_t *__restrict__ map, uint8_t *da
     }
 }
 
+// Packed BCH(15,k) batches (1 data byte and 2 parity bytes per codeword, both arrays dense): four codewords per
+// thread with 4-, 8- and 16-byte accesses, so that the kernel runs at memory speed (9 B of traffic per codeword).
+__global__ void __launch_bounds__(256)
+bch_decode_map4_kernel(BchParams P, const uint32_t *__restrict__ map, uint8_t *data, const uint8_t *__restrict__ parity,
+                       size_t n4 /* groups of four */, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+{
+    const uint32_t kmask = low_mask(P.k), pmask = low_mask(P.parity_bits);
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t dw = reinterpret_cast<const uint32_t *>(data)[g];
+        const uint2 pw = reinterpret_cast<const uint2 *>(parity)[g];
+        uint32_t out = 0, okw = 0;
+        uint32_t nc[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t dv = (dw >> (8 * u)) & 0xFFu & kmask;
+            const uint32_t ph = u < 2 ? pw.x : pw.y; // two bytes per codeword, big endian
+            const uint32_t pb2 = (ph >> (16 * (u & 1))) & 0xFFFFu;
+            const uint32_t pv = (((pb2 & 0xFFu) << 8) | (pb2 >> 8)) & pmask;
+            const uint32_t e = __ldg(map + ((dv << P.parity_bits) | pv));
+            const bool good = (e & 0x80000000u) != 0;
+            const uint32_t fixed = ((e & 0xFFFFu) >> P.parity_bits) & kmask;
+            out |= (good ? fixed : ((dw >> (8 * u)) & 0xFFu)) << (8 * u); // failure leaves the data byte alone
+            okw |= (good ? 1u : 0u) << (8 * u);
+            nc[u] = good ? ((e >> 24) & 0x7Fu) : 0u;
+        }
+        reinterpret_cast<uint32_t *>(data)[g] = out;
+        if (ok)
+            reinterpret_cast<uint32_t *>(ok)[g] = okw;
+        if (corrected)
+            reinterpret_cast<uint4 *>(corrected)[g] = make_uint4(nc[0], nc[1], nc[2], nc[3]);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+bch_encode4_kernel(BchParams P, const uint8_t *__restrict__ data, uint8_t *__restrict__ parity, size_t n4,
+                   uint8_t *__restrict__ ok)
+{
+    // k <= 8 here: the 2^k parity words (already byte-swapped to big endian) are tabulated per CTA by the
+    // reference-shaped division (src/bch.c:352-380), the batch is then one shared-memory look-up per codeword
+    __shared__ uint16_t tab[256];
+    const uint32_t kmask = low_mask(P.k), pmask = low_mask(P.parity_bits);
+    if (threadIdx.x <= kmask) {
+        const uint32_t shifted = (uint32_t)threadIdx.x << P.parity_bits;
+        uint32_t rem = shifted;
+        for (int i = P.n - 1; i >= P.gen_deg; i--)
+            if (rem & (1u << i))
+                rem ^= P.gen << (i - P.gen_deg);
+        const uint32_t pv = (shifted ^ rem) & pmask;
+        tab[threadIdx.x] = (uint16_t)(((pv & 0xFFu) << 8) | (pv >> 8));
+    }
+    __syncthreads();
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t dw = reinterpret_cast<const uint32_t *>(data)[g];
+        const uint32_t p0 = tab[dw & kmask], p1 = tab[(dw >> 8) & kmask], p2 = tab[(dw >> 16) & kmask],
+                       p3 = tab[(dw >> 24) & kmask];
+        reinterpret_cast<uint2 *>(parity)[g] = make_uint2(p0 | (p1 << 16), p2 | (p3 << 16));
+        if (ok)
+            reinterpret_cast<uint32_t *>(ok)[g] = 0x01010101u;
+    }
+}
+
+// one data byte + two parity bytes per codeword, dense arrays, vector-aligned pointers
+static bool packed_1_2(const poporon_cuda_bch *ctx, const void *data, size_t data_stride, size_t size, const void *parity,
+                       size_t parity_stride, const void *ok, const void *corrected)
+{
+    const int db = (ctx->k + 7) / 8, pb = (ctx->parity_bits + 7) / 8;
+    return db == 1 && pb == 2 && size >= 1 && data_stride == 1 && parity_stride == 2 && ((uintptr_t)data & 3u) == 0 &&
+           ((uintptr_t)parity & 7u) == 0 && ((uintptr_t)ok & 3u) == 0 && ((uintptr_t)corrected & 15u) == 0;
+}
+
 BchParams params_of(const poporon_cuda_bch *ctx)
 {
     BchParams P;
@@ -276,6 +346,17 @@ int launch_bch_encode(poporon_cuda_bch *ctx, const uint8_t *data, size_t data_st
     if (n == 0)
         return 0;
     const int threads = 256;
+    if (packed_1_2(ctx, data, data_stride, size, parity, parity_stride, ok, nullptr) && n >= 4) {
+        const size_t n4 = n / 4, cap = (size_t)ctx->sm_count * 16;
+        const size_t blocks = (n4 + threads - 1) / threads;
+        bch_encode4_kernel<<<(unsigned)(blocks < cap ? blocks : cap), threads, 0, stream>>>(params_of(ctx), data, parity,
+                                                                                      n4, ok);
+        ctx->launches++;
+        const size_t done = n4 * 4;
+        if (done == n)
+            return check(cudaGetLastError(), "bch_encode4 launch");
+        data += done, parity += done * 2, ok = ok ? ok + done : ok, n -= done;
+    }
     bch_encode_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, stream>>>(
         params_of(ctx), data, data_stride, size, parity, parity_stride, n, ok);
     ctx->launches++;
@@ -299,6 +380,18 @@ int launch_bch_decode(poporon_cuda_bch *ctx, uint8_t *data, size_t data_stride, 
 {
     if (n == 0)
         return 0;
+    if (ctx->d_map && packed_1_2(ctx, data, data_stride, size, parity, parity_stride, ok, corrected) && n >= 4) {
+        const size_t n4 = n / 4, cap = (size_t)ctx->sm_count * 16;
+        const size_t blocks = (n4 + 255) / 256;
+        bch_decode_map4_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(params_of(ctx), ctx->d_map,
+                                                                                      data, parity, n4, ok, corrected);
+        ctx->launches++;
+        const size_t done = n4 * 4;
+        if (done == n)
+            return check(cudaGetLastError(), "bch_decode (map4) launch");
+        data += done, parity += done * 2, ok = ok ? ok + done : ok, corrected = corrected ? corrected + done : corrected;
+        n -= done;
+    }
     if (ctx->d_map) {
         size_t blocks = (n + 255) / 256;
         const size_t cap = (size_t)ctx->sm_count * 32;
