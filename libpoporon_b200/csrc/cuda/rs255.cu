@@ -1174,7 +1174,16 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(
             dmask, n, invperm, ctx->d_queue, ctx->d_counters, ok, corrected);
     }
-    const unsigned cblocks = (unsigned)ctx->sm_count * 8;
+    // one resident wave of the general stage (its shared-memory work arrays limit it to a few CTAs per SM); a grid
+    // larger than one wave would leave a thin second wave behind the grid-stride loop
+    static int correct_ctas_per_sm = 0;
+    if (correct_ctas_per_sm == 0) {
+        int v = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, rs255_correct_kernel, 128, 0) != cudaSuccess || v < 1)
+            v = 4;
+        correct_ctas_per_sm = v;
+    }
+    const unsigned cblocks = (unsigned)(ctx->sm_count * correct_ctas_per_sm);
     const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
     if (mode == POPORON_CUDA_MODE_PLAIN) {
         // bitsliced solver first; what it declines lands in queue2 for the literal stage below

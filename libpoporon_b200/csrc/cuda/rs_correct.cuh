@@ -147,10 +147,36 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
     if (deg == 0)
         return false;
 
-    for (int i = 1; i <= nr; i++)
-        reg[i] = lambda[i];
     int count = 0;
-    {
+    if constexpr (MAXR <= 32) {
+        // the running terms stay in registers (fully unrolled over the at most 32 coefficients): one table look-up
+        // per live term and location instead of three shared-memory accesses
+        uint32_t rg[MAXR + 1];
+#pragma unroll
+        for (int j = 1; j <= MAXR; j++)
+            rg[j] = (j <= deg) ? (uint32_t)lambda[j] : (uint32_t)A0;
+        int16_t k = (int16_t)(c.iprim - 1);
+        for (int i = 1; i <= nn; i++, k = (int16_t)redc((uint32_t)(int32_t)(k + c.iprim), nn)) {
+            uint32_t q = 1;
+#pragma unroll
+            for (int j = MAXR; j > 0; j--) {
+                if (rg[j] != (uint32_t)A0) {
+                    rg[j] = redc2(rg[j] + (uint32_t)j, nn);
+                    q ^= T.alpha_to[rg[j]];
+                }
+            }
+            if (q != 0)
+                continue;
+            if (k < pad)
+                return false;
+            root[count] = (uint8_t)i;
+            loc[count] = (uint8_t)k;
+            if (++count == deg)
+                break;
+        }
+    } else {
+        for (int i = 1; i <= nr; i++)
+            reg[i] = lambda[i];
         int16_t k = (int16_t)(c.iprim - 1);
         for (int i = 1; i <= nn; i++, k = (int16_t)redc((uint32_t)(int32_t)(k + c.iprim), nn)) {
             uint8_t q = 1;
