@@ -55,7 +55,9 @@ struct CrtM {
     static constexpr gf256::CrtMasks<SRC> v = gf256::make_crt_masks<SRC>();
 };
 
-// syndrome map of a role: V_q = s(alpha^(1 + 16*ROLE + q)) = sum_k s[k] * alpha^(j*(15-k))
+// syndrome map of a role: the role's register holds s = c(x) * x^16 mod g_role (coefficient k of s = x^(15-k)), so
+// for a root alpha^j of g_role, j = 1 + 16*ROLE + q:  S_j = c(alpha^j) = s(alpha^j) * alpha^(-16 j)
+//                                                          = sum_k s[k] * alpha^(j*(15-k) - 16 j) = sum_k s[k] * alpha^(-j*(k+1))
 template <int ROLE>
 struct SynM {
     uint8_t m[16][16][8];
@@ -67,7 +69,7 @@ constexpr SynM<ROLE> make_synm()
     for (int k = 0; k < 16; k++)
         for (int q = 0; q < 16; q++)
             for (int t = 0; t < 8; t++)
-                r.m[k][q][t] = gf256::rowmask(gf256::pow_alpha((1 + 16 * ROLE + q) * (15 - k)), t);
+                r.m[k][q][t] = gf256::rowmask(gf256::pow_alpha(-(1 + 16 * ROLE + q) * (k + 1)), t);
     return r;
 }
 template <int ROLE>
@@ -275,7 +277,7 @@ struct LfsrArgs {
     uint8_t *ok;
     // SCREEN outputs
     uint32_t *dmask; // [2 * groups]: per (tile, lane, role) 32-bit "state != 0" mask over i
-    uint8_t *syn;    // [n][32]: raw evaluations V_q of the role's final state at its 16 roots
+    uint8_t *syn;    // [n][32]: the syndromes S_1 .. S_32 (field elements), 16 per role
 };
 
 constexpr int kRingStage = 16384;          // [i = 32][lane = 32][16 B]
@@ -711,7 +713,7 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
         const uint32_t entry = queue[q];
         const size_t cw = entry & 0x3FFFFFFFu;
         const uint32_t flags = entry >> 30;
-        // raw[q'] = state(alpha^j) = c(alpha^j) * alpha^(16 j)  ->  S_j in index form
+        // row = S_1 .. S_32 as field elements (screen kernel) -> index form
         const uint4 *raw4 = reinterpret_cast<const uint4 *>(syn_raw + cw * 32);
 #pragma unroll
         for (int half = 0; half < 2; half++) {
@@ -721,16 +723,8 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
                 w[0] = v.x, w[1] = v.y, w[2] = v.z, w[3] = v.w;
             }
 #pragma unroll
-            for (int b = 0; b < 16; b++) {
-                const int j = 1 + 16 * half + b;
-                const uint32_t val = (w[b >> 2] >> (8 * (b & 3))) & 0xFFu;
-                uint32_t lg = T.index_of[val];
-                if (val != 0) {
-                    lg += 255u - (uint32_t)((16 * j) % 255);
-                    lg = lg >= 255u ? lg - 255u : lg;
-                }
-                syn[j - 1] = (uint8_t)lg;
-            }
+            for (int b = 0; b < 16; b++)
+                syn[16 * half + b] = T.index_of[(w[b >> 2] >> (8 * (b & 3))) & 0xFFu];
         }
         uint8_t *d = data + cw * data_stride;
         uint8_t *p = parity + cw * parity_stride;
@@ -764,11 +758,14 @@ constexpr int kSolveSmem = bs::kWordsW * 128 + 256;             // work area + t
 constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO;  // per lane, in global memory (L2-resident)
 constexpr int kSolveWarpsPerSM = 8;
 
-template <int W>
+// Syndrome rows (32 bytes per queued codeword: S_1 .. S_32 as field elements, written by the screen kernel) ->
+// bit-planes: word W of the 32 rows of a lane is transposed into the planes of S_{4W+1} .. S_{4W+4}.  A rolled loop
+// (the solver's straight-line code competes with its loop bodies for the instruction cache).
 __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], const uint8_t *__restrict__ syn_raw,
                                                      const bs::Mem<32> S)
 {
-    if constexpr (W < 8) {
+#pragma unroll 1
+    for (int W = 0; W < 8; W++) {
         uint32_t X[32];
 #pragma unroll
         for (int c = 0; c < 32; c++) {
@@ -777,21 +774,10 @@ __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], 
             const bool live = e != 0xFFFFFFFFu && ((e >> (30 + (W >> 2))) & 1u);
             X[c] = live ? __ldg(reinterpret_cast<const uint32_t *>(syn_raw) + (size_t)(e & 0x3FFFFFFFu) * 8 + W) : 0u;
         }
-        transpose32(X); // X[8*y + t] = plane t of raw byte 4W + y = state(alpha^j), j = 1 + 4W + y
+        bs::transpose32(X); // X[8*y + t] = plane t of S_{4W + y + 1}
 #pragma unroll
-        for (int y = 0; y < 4; y++) {
-            // S_j = state(alpha^j) * alpha^(-16 j)
-            uint32_t(&in)[8] = *reinterpret_cast<uint32_t(*)[8]>(&X[8 * y]);
-            uint32_t s[8];
-            if (y == 0) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 0))>(in, s);
-            if (y == 1) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 1))>(in, s);
-            if (y == 2) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 2))>(in, s);
-            if (y == 3) bs::cmul<gf256::pow_alpha(-16 * (1 + 4 * W + 3))>(in, s);
-#pragma unroll
-            for (int t = 0; t < 8; t++)
-                S.st(8 * (4 * W + y) + t, s[t]);
-        }
-        solve_load_syndromes<W + 1>(ent, syn_raw, S);
+        for (int p = 0; p < 32; p++)
+            S.st(32 * W + p, X[p]);
     }
 }
 
@@ -963,7 +949,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
                 const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
                 ent[c] = q < total ? queue[q] : 0xFFFFFFFFu;
             }
-            solve_load_syndromes<0>(ent, syn_raw, Syn);
+            solve_load_syndromes(ent, syn_raw, Syn);
         }
         bs::LaneOut out;
         bs::solve_lane<32, 32>(Syn, B, S, pad, out, hook); // also drains the previous tile's corrections
