@@ -754,7 +754,11 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 // Codewords the solver declines (register length > 16 or a vanishing leading coefficient - uncorrectable
 // words only) are appended to a second queue for the literal per-codeword stage.
 // ---------------------------------------------------------------------------------------------------
-constexpr int kSolveSmem = bs::kWordsW * 128 + 256;             // work area + the root table (256 B)
+#ifndef PP_SOLVE_WARPS_PER_CTA
+#define PP_SOLVE_WARPS_PER_CTA 8
+#endif
+constexpr int kSolveWarpsPerCTA = PP_SOLVE_WARPS_PER_CTA; // warps of a CTA move from tile to tile together (see the kernel)
+constexpr int kSolveSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 256; // work areas + the root table (256 B)
 constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO;  // per lane, in global memory (L2-resident)
 constexpr int kSolveWarpsPerSM = 8;
 
@@ -901,18 +905,21 @@ struct ApplyHook {
 // One warp per CTA, eight CTAs per SM: a warp keeps only its 25 KB work area in shared memory; the syndrome planes
 // and the evaluator live in a per-warp scratch in global memory (48 KB, written and read by the same lane, so it
 // stays in L2).  With one warp per scheduler the ALU pipe idled ~45 % of the time behind fixed-latency waits.
-__global__ void __launch_bounds__(32, kSolveWarpsPerSM)
+// The warps of a CTA meet at a barrier after every tile: they then run the same phase (BM, sweep, Forney) at the
+// same time and share its code in the 32 KB instruction cache, which eight warps drifting apart do not.
+__global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, kSolveWarpsPerSM / kSolveWarpsPerCTA)
 rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ counter, uint8_t *syn_raw,
                    uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2,
                    uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data, size_t data_stride)
 {
     extern __shared__ __align__(16) uint32_t solve_smem[];
-    const int lane = threadIdx.x;
-    const bs::Mem<32> S{solve_smem + lane}; // the work area
-    uint32_t *gs = scratch + (size_t)blockIdx.x * (kSolveScratchWords * 32) + lane;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t gw = blockIdx.x * kSolveWarpsPerCTA + (uint32_t)warp, nw = gridDim.x * kSolveWarpsPerCTA;
+    const bs::Mem<32> S{solve_smem + warp * (bs::kWordsW * 32) + lane}; // the work area
+    uint32_t *gs = scratch + (size_t)gw * (kSolveScratchWords * 32) + lane;
     const bs::Mem<32> Syn{gs};
     const bs::Mem<32> B{gs + bs::kWordsS * 32}; // the evaluator
-    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + bs::kWordsW * 32);
+    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWarpsPerCTA * bs::kWordsW * 32);
     {
         // root_tab[0] = 0 (empty list slot), root_tab[v] = alpha^v for v = 1..255: each lane fills 8 consecutive powers
         uint32_t x = 1;
@@ -928,7 +935,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
                 x ^= gf256::kPoly;
         }
     }
-    __syncwarp();
+    __syncthreads(); // (every warp wrote the same table)
     const uint32_t total = *counter;
     const int pad = kMsg - (int)size;
     ApplyHook hook;
@@ -941,7 +948,10 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
     hook.lane = (uint32_t)lane;
     hook.g0p = 0xFFFFFFFFu;
 
-    for (uint32_t g0 = blockIdx.x * 1024u; g0 < total; g0 += gridDim.x * 1024u) {
+    const uint32_t rounds = (total + nw * 1024u - 1u) / (nw * 1024u); // the same for every warp of the CTA
+    for (uint32_t it = 0; it < rounds; it++) {
+        const uint32_t g0 = (it * nw + gw) * 1024u;
+        if (g0 < total) {
         {
             uint32_t ent[32];
 #pragma unroll
@@ -1021,7 +1031,8 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
                 corrected[cw] = nnz;
         }
         hook.g0p = g0; // this tile's records are final: applied during the next sweep (or by the drain below)
-        __syncwarp();
+        }
+        __syncthreads();
     }
     hook.drain();
 }
@@ -1179,7 +1190,9 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         uint32_t *scratch = reinterpret_cast<uint32_t *>(ctx->d_rem + tiles * kTile * 32);
         {
             ProfScope prof(ctx, PROF_SOLVE, stream);
-            rs255_solve_kernel<<<(unsigned)(groups < cap ? groups : cap), 32, kSolveSmem, stream>>>(
+            const size_t warps = groups < cap ? groups : cap;
+            rs255_solve_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
+                                 kSolveSmem, stream>>>(
                 size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected,
                 data, data_stride);
         }
