@@ -257,6 +257,17 @@ __device__ __forceinline__ void linmap_vec(uint32_t (&acc)[16][8], uint32_t sbas
 // ---------------------------------------------------------------------------------------------------
 // the stream kernel: one CTA = two warps (roles) x one tile of 1024 codewords at a time
 // ---------------------------------------------------------------------------------------------------
+#ifndef PP_LFSR_PAIRS
+#define PP_LFSR_PAIRS 4
+#endif
+constexpr int kPairs = PP_LFSR_PAIRS; // role pairs (64 threads each) per CTA: 4, 2 or 1
+
+// barrier of one role pair (64 threads); barrier 0 is the CTA-wide __syncthreads()
+__device__ __forceinline__ void pair_sync(int pair)
+{
+    asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+}
+
 // Tile geometry.  Codewords are taken in blocks of 4096; a block is four tiles ("groups" G = 0..3).  Lane l of
 // the tile owns the 32 codewords  cw = 4096*block + 512*(l >> 2) + 16*i + r,  i = 0..31, where r is one of the
 // four residues (mod 16) of the group.  Consecutive i are 16 codewords apart, so all 32 streams of a lane
@@ -370,6 +381,7 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
     constexpr int NB = MODE == MODE_ENCODE ? 3 : 2;
     constexpr int kSetBytes = 2 * kWinBytes;
     const int lane = threadIdx.x & 31;
+    const int pair = (int)(threadIdx.x >> 6); // which of the CTA's role pairs (each works on its own tile)
     const uint32_t ring_s = smem_u32(smem);
     const uint32_t lane_ring = ring_s + (uint32_t)lane * 16u;
     const uint32_t lane_buf = ring_s + (uint32_t)kRingBytes2 + (uint32_t)lane * 4u;
@@ -377,7 +389,16 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
     const int nW = (A.len + 3) >> 2;
     const int nS = (nW + 1) >> 1;
 
-    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    // The four pairs of a CTA take the four tiles of one 4096-codeword block and meet at a CTA-wide barrier after
+    // every round: all eight warps of the SM then run the same phase (main loop, epilogue) at the same time and
+    // share its code in the instruction cache (the straight-line epilogue of a pair drifting on its own evicted the
+    // main loops of the three others).
+    const size_t vstride = (size_t)gridDim.x * kPairs;
+    const size_t rounds = (ntiles + vstride - 1) / vstride;
+    for (size_t it = 0; it < rounds; it++, __syncthreads()) {
+        const size_t tile = it * vstride + (size_t)blockIdx.x * kPairs + (size_t)pair;
+        if (tile >= ntiles)
+            continue;
         const size_t cw0 = tile_cw0(A, tile, lane);
         const int wb = (int)((A.wbs >> (2u * (unsigned)(tile & 3))) & 3u);
         const uint8_t *s0 = A.stream + cw0 * A.stride;
@@ -451,14 +472,14 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
             for (int t = 0; t < 8; t++)
                 P[j][t] = 0;
 
-        __syncthreads(); // the previous tile's epilogue is done with the shared memory
+        pair_sync(pair); // the previous tile's epilogue is done with the shared memory
         fetch(0);
         fetch(1);
         cp_async_wait_all();
-        __syncthreads();
+        pair_sync(pair);
         if (ROLE < nW)
             transpose_window(ROLE, lane_buf + (uint32_t)(ROLE * kWinBytes)); // windows 0 and 1 -> set 0
-        __syncthreads();
+        pair_sync(pair);
 
         // step s: role r transposes window 2s+2+r into the next set, then both run the registers over windows
         // 2s and 2s+1 (encoder role 1 runs one step behind role 0, on the quotient symbols role 0 left in place)
@@ -484,12 +505,12 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
             }
             if ((v & 2) == 0 && v >= 0)
                 cp_async_wait_all();
-            __syncthreads();
+            pair_sync(pair);
             set_prev = set_cur;
             set_cur = set_next;
         }
         cp_async_wait_all();
-        __syncthreads(); // every chunk has landed and been consumed: the ring becomes epilogue scratch
+        pair_sync(pair); // every chunk has landed and been consumed: the ring becomes epilogue scratch
         uint32_t acc[16][8];
         int out_half = ROLE; // which 16 bytes of the 32-byte output row this role writes
         if (MODE == MODE_ENCODE) {
@@ -504,11 +525,11 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
                     for (int t = 0; t < 8; t++)
                         sts32(scr + (uint32_t)((8 * j + t) * 128), P[j][t]);
             }
-            __syncthreads();
+            pair_sync(pair);
             if (ROLE == 0) {
                 stream_run<0, 2>(P, scr, 16);
             }
-            __syncthreads();
+            pair_sync(pair);
             if (ROLE == 0) {
 #pragma unroll
                 for (int j = 0; j < 16; j++)
@@ -568,12 +589,12 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
                 asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};\n" ::"r"(ring_s + (uint32_t)((32 * i + lane) * 32 + 16 * out_half)),
                              "r"(B[0][i]), "r"(B[1][i]), "r"(B[2][i]), "r"(B[3][i])
                              : "memory");
-            __syncthreads();
+            pair_sync(pair);
             // pass 1, whole words: thread (t & 7) = s of a group of 8 writes aligned word s+1 of the row (s < 7;
             // s = 7 writes aligned word 0 when the row happens to be 4-byte aligned).  Rows of this thread:
             // 32*i + 8*k + (t >> 3), k = 0..3, i.e. codeword i of lane 8*k + (t >> 3).
             {
-                const int t = (int)threadIdx.x, sub = t & 7;
+                const int t = (int)(threadIdx.x & 63u), sub = t & 7;
                 uint8_t *gq[4];   // address of this thread's word in row i = 0
                 uint32_t shv[4];  // funnel shift (bits)
                 int cnt[4];       // rows (values of i) to write
@@ -647,13 +668,14 @@ __device__ __forceinline__ void stream_role(const LfsrArgs &A, uint8_t *smem)
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(64, 4) rs255_lfsr_kernel(LfsrArgs A)
+__global__ void __launch_bounds__(64 * kPairs, 4 / kPairs) rs255_lfsr_kernel(LfsrArgs A)
 {
     extern __shared__ __align__(16) uint8_t ring[];
-    if ((threadIdx.x >> 5) == 0)
-        stream_role<MODE, 0>(A, ring);
+    uint8_t *mine = ring + (threadIdx.x >> 6) * (MODE == MODE_ENCODE ? kSmemEncode : kSmemScreen);
+    if (((threadIdx.x >> 5) & 1u) == 0)
+        stream_role<MODE, 0>(A, mine);
     else
-        stream_role<MODE, 1>(A, ring);
+        stream_role<MODE, 1>(A, mine);
 }
 
 
@@ -1081,9 +1103,9 @@ bool rs255_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size
 int rs255_init(poporon_cuda_rs *ctx)
 {
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_ENCODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kSmemEncode));
+                                     kPairs * kSmemEncode));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kSmemScreen));
+                                     kPairs * kSmemScreen));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
     (void)ctx;
     return 0;
@@ -1091,9 +1113,9 @@ int rs255_init(poporon_cuda_rs *ctx)
 
 static unsigned lfsr_grid(const poporon_cuda_rs *ctx, size_t n)
 {
-    const size_t tiles = 4 * ((n + 4095) / 4096);
-    const size_t cap = (size_t)ctx->sm_count * 4; // 4 CTAs (8 warps) per SM, persistent over tiles
-    return (unsigned)(tiles < cap ? tiles : cap);
+    const size_t ctas = (4 * ((n + 4095) / 4096) + kPairs - 1) / kPairs; // kPairs tiles per CTA and round
+    const size_t cap = (size_t)ctx->sm_count * (4 / kPairs);             // 8 warps per SM, persistent over tiles
+    return (unsigned)(ctas < cap ? ctas : cap);
 }
 
 // Tile geometry for a stream buffer (see LfsrArgs): sort the 16 residues r = codeword index mod 16 by the word
@@ -1134,7 +1156,7 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
         PP_CUDA_TRY(cudaMemsetAsync(ok, 1, n, stream)); // the encoder cannot fail (src/encode.c:17-145 returns true)
     {
         ProfScope prof(ctx, PROF_ENCODE, stream);
-        rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64, kSmemEncode, stream>>>(A);
+        rs255_lfsr_kernel<MODE_ENCODE><<<lfsr_grid(ctx, n), 64 * kPairs, kPairs * kSmemEncode, stream>>>(A);
     }
     ctx->launches++;
     return check(cudaGetLastError(), "rs255 encode launch");
@@ -1164,7 +1186,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
     {
         ProfScope prof(ctx, PROF_SCREEN, stream);
-        rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64, kSmemScreen, stream>>>(A);
+        rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64 * kPairs, kPairs * kSmemScreen, stream>>>(A);
     }
     {
         ProfScope prof(ctx, PROF_COMPACT, stream);
