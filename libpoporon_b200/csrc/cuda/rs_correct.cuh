@@ -48,6 +48,14 @@ __device__ __forceinline__ uint32_t redc2(uint32_t v, int nn)
     return v >= (uint32_t)nn ? v - (uint32_t)nn : v;
 }
 
+// Branch-free forms for the register-resident paths (MAXR <= 32).  wrapn: t mod nn for t < 2*nn, and a huge value
+// stays huge: a dead term (zero factor) is coded as kDead and clamps to alpha_to[A0] = 0 at the look-up.
+constexpr uint32_t kDead = 0xFFFF0000u;
+__device__ __forceinline__ uint32_t wrapn(uint32_t t, int nn)
+{
+    return min(t, t - (uint32_t)nn);
+}
+
 // Work arrays of the correction stage (7 arrays of MAXR + 1 bytes, indexed at run time).
 // LocalWork: per-thread arrays (local memory) - any MAXR.  SmemWork: one column per thread of a shared-memory
 // block laid out [array][index][thread] (consecutive threads = consecutive bytes: conflict-free, and no
@@ -151,19 +159,19 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
     if constexpr (MAXR <= 32) {
         // the running terms stay in registers (fully unrolled over the at most 32 coefficients): one table look-up
         // per live term and location instead of three shared-memory accesses
+        // A term that is zero (or past the degree) is coded as kDead: it stays huge under the update and looks up
+        // alpha_to[A0] = 0, so a term is five integer instructions and one look-up, without a branch.
         uint32_t rg[MAXR + 1];
 #pragma unroll
         for (int j = 1; j <= MAXR; j++)
-            rg[j] = (j <= deg) ? (uint32_t)lambda[j] : (uint32_t)A0;
+            rg[j] = (j <= deg && lambda[j] != A0) ? (uint32_t)lambda[j] : kDead;
         int16_t k = (int16_t)(c.iprim - 1);
         for (int i = 1; i <= nn; i++, k = (int16_t)redc((uint32_t)(int32_t)(k + c.iprim), nn)) {
             uint32_t q = 1;
 #pragma unroll
             for (int j = MAXR; j > 0; j--) {
-                if (rg[j] != (uint32_t)A0) {
-                    rg[j] = redc2(rg[j] + (uint32_t)j, nn);
-                    q ^= T.alpha_to[rg[j]];
-                }
+                rg[j] = wrapn(rg[j] + (uint32_t)j, nn);
+                q ^= T.alpha_to[min(rg[j], (uint32_t)A0)];
             }
             if (q != 0)
                 continue;
@@ -209,6 +217,36 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
     }
 
     ncorr = 0;
+    if constexpr (MAXR <= 32) {
+        // evaluator and odd locator coefficients in registers, dead-coded; i * root (mod nn) kept as a running sum
+        // (i * root <= 31 * 255 never reaches the 16-bit truncation of the reference's gf_mod argument)
+        uint32_t og[MAXR], ld[MAXR / 2];
+#pragma unroll
+        for (int i = 0; i < MAXR; i++)
+            og[i] = (i < deg && omega[i] != A0) ? (uint32_t)omega[i] : kDead;
+#pragma unroll
+        for (int i = 0; i < MAXR; i += 2)
+            ld[i / 2] = (i <= ((deg < nr - 1 ? deg : nr - 1) & ~1) && lambda[i + 1] != A0) ? (uint32_t)lambda[i + 1] : kDead;
+        for (int j = count - 1; j >= 0; j--) {
+            const uint32_t rt = root[j];
+            const uint32_t rtn = rt == (uint32_t)nn ? 0u : rt; // root mod nn
+            uint32_t m = 0, num1 = 0, den = 0;
+#pragma unroll
+            for (int i = 0; i < MAXR; i++) {
+                num1 ^= T.alpha_to[min(wrapn(og[i] + m, nn), (uint32_t)A0)];
+                if ((i & 1) == 0)
+                    den ^= T.alpha_to[min(wrapn(ld[i / 2] + m, nn), (uint32_t)A0)];
+                m = wrapn(m + rtn, nn);
+            }
+            if (num1 == 0) {
+                b[j] = 0;
+                continue;
+            }
+            const uint8_t num2 = T.alpha_to[redc(rt * ((uint32_t)c.fcr - 1u) + (uint32_t)nn, nn)];
+            b[j] = T.alpha_to[redc((uint32_t)T.index_of[num1] + T.index_of[num2] + nn - T.index_of[den], nn)];
+            ncorr++;
+        }
+    } else
     for (int j = count - 1; j >= 0; j--) {
         uint8_t num1 = 0, den = 0;
         for (int i = deg - 1; i >= 0; i--) {
@@ -228,6 +266,34 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         ncorr++;
     }
 
+    // Re-syndrome check.  When no exponent can reach 2^16 (the reference truncates its gf_mod argument to 16 bits)
+    // the exponent of correction j at syndrome i is ib_j + (fcr + i) * step_j (mod nn): one running sum per j.
+    const bool plain_exponents = (uint32_t)(c.fcr + nr) * (uint32_t)c.prim * (uint32_t)(nn - 1) + (uint32_t)nn < 65536u;
+    if (MAXR <= 32 && plain_exponents) {
+        uint32_t acc[MAXR <= 32 ? MAXR : 1];
+#pragma unroll
+        for (int i = 0; i < (MAXR <= 32 ? MAXR : 1); i++)
+            acc[i] = 0;
+        for (int j = 0; j < count; j++) {
+            const uint32_t bj = b[j];
+            if (bj == 0)
+                continue;
+            const uint32_t step = redc((uint32_t)c.prim * (uint32_t)(nn - loc[j] - 1), nn);
+            uint32_t e = redc((uint32_t)T.index_of[bj] + (uint32_t)c.fcr * (uint32_t)c.prim * (uint32_t)(nn - loc[j] - 1), nn);
+#pragma unroll
+            for (int i = 0; i < (MAXR <= 32 ? MAXR : 1); i++) {
+                acc[i] ^= T.alpha_to[e];
+                e = wrapn(e + step, nn);
+            }
+        }
+        bool same = true;
+#pragma unroll
+        for (int i = 0; i < (MAXR <= 32 ? MAXR : 1); i++)
+            if (i < nr && acc[i] != T.alpha_to[syn[i]])
+                same = false;
+        if (!same)
+            return false;
+    } else
     for (int i = 0; i < nr; i++) {
         uint8_t acc = 0;
         for (int j = 0; j < count; j++) {
