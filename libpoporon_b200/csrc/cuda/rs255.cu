@@ -783,7 +783,16 @@ rs255_compact_kernel(const uint32_t *__restrict__ dmask, size_t n, uint64_t invp
 // ---------------------------------------------------------------------------------------------------
 // correction of the queued codewords: one thread per dirty codeword (rs_correct.cuh)
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
+#ifndef PP_CORRECT_SYNC
+#define PP_CORRECT_SYNC 1
+#endif
+constexpr int kCorrectSmem = SmemWork<32>::kBytes;
+#if PP_CORRECT_SYNC
+using PhaseSync = CtaPhaseSync;
+#else
+using PhaseSync = NoPhaseSync;
+#endif
+__global__ void __launch_bounds__(kWorkThreads)
 rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint8_t *data, size_t data_stride,
                      size_t size, uint8_t *parity, size_t parity_stride, const uint32_t *__restrict__ queue,
                      const uint32_t *__restrict__ counter, const uint8_t *__restrict__ syn_raw,
@@ -791,15 +800,21 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
                      uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
 {
     __shared__ SmemTables T;
-    __shared__ uint8_t work[SmemWork<32>::kBytes]; // [array][index][thread]: no local-memory arrays
+    extern __shared__ __align__(16) uint8_t work[]; // [array][index][thread]: no local-memory arrays
     load_tables(T, gtab);
     SmemWork<32> wk{work + threadIdx.x};
     const auto syn = wk.arr(7);
     const uint32_t total = *counter;
-    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
-        const uint32_t entry = queue[q];
+    // The warps of a CTA start every codeword together (one barrier per trip): the stage is ~100 KB of code and
+    // warps that drift apart evict each other's loops from the instruction cache.
+    for (uint32_t q0 = blockIdx.x * blockDim.x; q0 < total; q0 += gridDim.x * blockDim.x) {
+        if (PP_CORRECT_SYNC)
+            __syncthreads();
+        const uint32_t q = q0 + threadIdx.x;
+        const bool live = q < total; // threads past the end of the queue still walk through the phase barriers
+        const uint32_t entry = live ? queue[q] : 0u;
         const size_t cw = entry & 0x3FFFFFFFu;
-        const uint32_t flags = entry >> 30;
+        const uint32_t flags = live ? entry >> 30 : 0u;
         // row = S_1 .. S_32 as field elements (screen kernel) -> index form
         const uint4 *raw4 = reinterpret_cast<const uint4 *>(syn_raw + cw * 32);
 #pragma unroll
@@ -819,12 +834,14 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
         uint32_t ncorr = 0;
         bool success;
         if (mode == POPORON_CUDA_MODE_ERASURE) {
-            const uint32_t ec = cnt[cw];
-            success = ec <= 32u && rs_correct<32>(c, T, d, size, p, wk, syn, ec, pos + cw * pos_stride, pos_stride, true,
-                                                  pad, ncorr);
+            const uint32_t ec = live ? cnt[cw] : 0u;
+            success = rs_correct<32, PhaseSync>(c, T, d, size, p, wk, syn, ec <= 32u ? ec : 0u, pos + cw * pos_stride,
+                                                pos_stride, true, pad, ncorr, live && ec <= 32u);
         } else {
-            success = rs_correct<32>(c, T, d, size, p, wk, syn, 0, nullptr, 0, false, pad, ncorr);
+            success = rs_correct<32, PhaseSync>(c, T, d, size, p, wk, syn, 0, nullptr, 0, false, pad, ncorr, live);
         }
+        if (!live)
+            continue;
         if (ok)
             ok[cw] = success ? 1 : 0;
         if (corrected)
@@ -1175,6 +1192,7 @@ int rs255_init(poporon_cuda_rs *ctx)
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      kPairs * kSmemScreen));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_correct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCorrectSmem));
     (void)ctx;
     return 0;
 }
@@ -1266,7 +1284,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     static int correct_ctas_per_sm = 0;
     if (correct_ctas_per_sm == 0) {
         int v = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, rs255_correct_kernel, 128, 0) != cudaSuccess || v < 1)
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, rs255_correct_kernel, kWorkThreads, kCorrectSmem) != cudaSuccess || v < 1)
             v = 4;
         correct_ctas_per_sm = v;
     }
@@ -1292,7 +1310,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     }
     {
         ProfScope prof(ctx, PROF_GENERAL, stream);
-        rs255_correct_kernel<<<cblocks, 128, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride, size,
+        rs255_correct_kernel<<<cblocks, kWorkThreads, kCorrectSmem, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride, size,
                                                           parity, parity_stride, cq, cc, ctx->d_rem, pos, pos_stride,
                                                           cnt, ok, corrected);
     }

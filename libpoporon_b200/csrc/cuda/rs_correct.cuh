@@ -60,7 +60,10 @@ __device__ __forceinline__ uint32_t wrapn(uint32_t t, int nn)
 // LocalWork: per-thread arrays (local memory) - any MAXR.  SmemWork: one column per thread of a shared-memory
 // block laid out [array][index][thread] (consecutive threads = consecutive bytes: conflict-free, and no
 // local-memory round trips), for CTAs of exactly kWorkThreads threads and small MAXR.
-constexpr int kWorkThreads = 128;
+#ifndef PP_CORRECT_THREADS
+#define PP_CORRECT_THREADS 128
+#endif
+constexpr int kWorkThreads = PP_CORRECT_THREADS;
 
 template <int MAXR>
 struct LocalWork {
@@ -85,16 +88,31 @@ struct SmemWork {
 
 // The correction stage, shared by all three decode modes.  Returns the reference's bool and sets
 // ncorr when the reference would have set *errors_corrected.
-template <int MAXR, class WORK, class SYN>
+//
+// PSYNC is called between the phases (locator, root search, evaluator, magnitudes, check + apply) by EVERY thread of
+// the CTA, also by those that have already failed or were not given a codeword (live = false): with CtaPhaseSync the
+// warps of a CTA run the same phase at the same time and share its code in the instruction cache.
+struct NoPhaseSync {
+    __device__ __forceinline__ void operator()() const {}
+};
+struct CtaPhaseSync {
+    __device__ __forceinline__ void operator()() const { __syncthreads(); }
+};
+
+template <int MAXR, class PSYNC = NoPhaseSync, class WORK, class SYN>
 __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, size_t size, uint8_t *parity,
                            WORK &wk, const SYN syn /* index form, [i] */, uint32_t ecount, const uint32_t *epos,
-                           size_t pos_stride, bool erasure_apply, int16_t pad, uint32_t &ncorr)
+                           size_t pos_stride, bool erasure_apply, int16_t pad, uint32_t &ncorr, bool live = true)
 {
+    const PSYNC phase_sync;
+    bool failed = !live;
     const int nr = c.nroots, nn = c.nn;
     const uint8_t A0 = (uint8_t)nn;
     const auto lambda = wk.arr(0), b = wk.arr(1), t = wk.arr(2), omega = wk.arr(3);
     const auto root = wk.arr(4), loc = wk.arr(5), reg = wk.arr(6);
 
+    int deg = 0;
+    if (!failed) {
     for (int i = 0; i <= nr; i++)
         lambda[i] = 0;
     lambda[0] = 1;
@@ -146,17 +164,20 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         }
     }
 
-    int deg = 0;
     for (int i = 0; i <= nr; i++) {
         lambda[i] = T.index_of[lambda[i]];
         if (lambda[i] != A0)
             deg = i;
     }
     if (deg == 0)
-        return false;
+        failed = true;
+    }
+    phase_sync();
 
+    // a failed thread walks through the remaining phases with deg = count = 0 (empty loops) and returns before the check
     int count = 0;
-    if constexpr (MAXR <= 32) {
+    if (failed) {
+    } else if constexpr (MAXR <= 32) {
         // the running terms stay in registers (fully unrolled over the at most 32 coefficients): one table look-up
         // per live term and location instead of three shared-memory accesses
         // A term that is zero (or past the degree) is coded as kDead: it stays huge under the update and looks up
@@ -175,8 +196,10 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
             }
             if (q != 0)
                 continue;
-            if (k < pad)
-                return false;
+            if (k < pad) {
+                failed = true;
+                break;
+            }
             root[count] = (uint8_t)i;
             loc[count] = (uint8_t)k;
             if (++count == deg)
@@ -196,8 +219,10 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
             }
             if (q != 0)
                 continue;
-            if (k < pad)
-                return false;
+            if (k < pad) {
+                failed = true;
+                break;
+            }
             root[count] = (uint8_t)i;
             loc[count] = (uint8_t)k;
             if (++count == deg)
@@ -205,8 +230,35 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         }
     }
     if (deg != count)
-        return false;
+        failed = true;
+    if (failed)
+        deg = count = 0;
+    phase_sync();
 
+    if constexpr (MAXR <= 32) {
+        // omega = S * lambda mod x^deg as lambda_j times the syndromes shifted up by j places: all 32 product terms of a
+        // step in registers with static indices, dead-coded, no branch (the triangular loop nest ran at 7 of 32 lanes)
+        uint32_t sh[MAXR], oacc[MAXR];
+#pragma unroll
+        for (int i = 0; i < MAXR; i++) {
+            sh[i] = (i < nr && syn[i] != A0) ? (uint32_t)syn[i] : kDead;
+            oacc[i] = 0;
+        }
+        for (int j = 0; j < deg; j++) {
+            const uint32_t lj = lambda[j] != A0 ? (uint32_t)lambda[j] : kDead;
+#pragma unroll
+            for (int i = 0; i < MAXR; i++)
+                oacc[i] ^= T.alpha_to[min(wrapn(sh[i] + lj, nn), (uint32_t)A0)];
+#pragma unroll
+            for (int i = MAXR - 1; i > 0; i--)
+                sh[i] = sh[i - 1];
+            sh[0] = kDead;
+        }
+#pragma unroll
+        for (int i = 0; i < MAXR; i++)
+            if (i < deg)
+                omega[i] = T.index_of[oacc[i]];
+    } else
     for (int i = 0; i < deg; i++) {
         uint8_t acc = 0;
         for (int j = i; j >= 0; j--) {
@@ -216,7 +268,9 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         omega[i] = T.index_of[acc];
     }
 
-    ncorr = 0;
+    phase_sync();
+    if (!failed)
+        ncorr = 0;
     if constexpr (MAXR <= 32) {
         // evaluator and odd locator coefficients in registers, dead-coded; i * root (mod nn) kept as a running sum
         // (i * root <= 31 * 255 never reaches the 16-bit truncation of the reference's gf_mod argument)
@@ -265,6 +319,10 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
         b[j] = T.alpha_to[redc((uint32_t)T.index_of[num1] + T.index_of[num2] + nn - T.index_of[den], nn)];
         ncorr++;
     }
+
+    phase_sync();
+    if (failed)
+        return false;
 
     // Re-syndrome check.  When no exponent can reach 2^16 (the reference truncates its gf_mod argument to 16 bits)
     // the exponent of correction j at syndrome i is ib_j + (fcr + i) * step_j (mod nn): one running sum per j.
