@@ -131,24 +131,30 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
     for (int i = 0; i <= nr; i++)
         b[i] = T.index_of[lambda[i]];
 
-    uint32_t r = ecount, el = ecount;
-    while (++r <= (uint32_t)nr) {
-        uint8_t disc = 0;
+    // r runs over 1 .. nr for every thread and a thread joins at r = ecount + 1 (src/decode.c:49: r = no_eras; while
+    // (++r <= nroots)): the threads of a warp are then at the same r, so the inner loops have one trip count.
+    uint32_t el = ecount;
+    for (uint32_t r = 1; r <= (uint32_t)nr; r++) {
+        if (r <= ecount)
+            continue;
+        uint32_t dsum = 0;
         for (uint32_t i = 0; i < r; i++) {
-            const uint8_t s = syn[r - i - 1];
-            if (lambda[i] != 0 && s != A0)
-                disc ^= T.alpha_to[redc2((uint32_t)T.index_of[lambda[i]] + s, nn)];
+            const uint32_t s = syn[r - i - 1], il = T.index_of[lambda[i]];
+            const uint32_t v = T.alpha_to[wrapn(il + s, nn)];
+            dsum ^= (il != A0 && s != A0) ? v : 0u;
         }
-        disc = T.index_of[disc];
+        const uint8_t disc = T.index_of[dsum];
         if (disc == A0) {
             for (int i = nr; i > 0; i--)
                 b[i] = b[i - 1];
             b[0] = A0;
         } else {
             t[0] = lambda[0];
-            for (int i = 0; i < nr; i++)
-                t[i + 1] = (b[i] != A0) ? (uint8_t)(lambda[i + 1] ^ T.alpha_to[redc2((uint32_t)disc + b[i], nn)])
-                                        : lambda[i + 1];
+            for (int i = 0; i < nr; i++) {
+                const uint32_t bi = b[i], li = lambda[i + 1];
+                const uint32_t v = T.alpha_to[wrapn((uint32_t)disc + bi, nn)];
+                t[i + 1] = (uint8_t)(li ^ (bi != A0 ? v : 0u));
+            }
             if (2 * el <= r + ecount - 1) {
                 el = r + ecount - el;
                 for (int i = 0; i <= nr; i++)
