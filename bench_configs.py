@@ -174,6 +174,54 @@ def run_bch(args, torch, api, dev):
     h.close()
 
 
+def run_bch31(args, torch, api, dev):
+    """BCH(31,16) t=3 ("also BCH(31,k)"): n > 15, so the exact per-thread decoder runs (no map)."""
+    n = args.ncw or 64 * 1024 * 1024
+    stream = torch.cuda.current_stream().cuda_stream
+    h = api.Poporon.bch(5, 0x25, 3)
+    g = torch.Generator(device=dev)
+    g.manual_seed(0x5EED0431)
+    data = torch.randint(0, 256, (n, 2), dtype=torch.uint8, device=dev, generator=g)  # 16 data bits, big-endian
+    par = torch.zeros((n, 2), dtype=torch.uint8, device=dev)
+    reps = args.reps
+    enc_ms = timed(torch, lambda i: h.encode_batch_async(data.data_ptr(), 2, 2, par.data_ptr(), 2, n, stream), reps + 1)
+    d32 = (data[:, 0].to(torch.int64) << 8) | data[:, 1].to(torch.int64)
+    p32 = ((par[:, 0].to(torch.int64) << 8) | par[:, 1].to(torch.int64)) & 0x7FFF
+    cw = (d32 << 15) | p32
+    nb = torch.randint(0, 4, (n,), dtype=torch.int64, device=dev, generator=g)
+    flips = torch.zeros(n, dtype=torch.int64, device=dev)
+    for k in range(3):  # bits may coincide (then fewer than nb errors): the count below is the true weight
+        b = torch.randint(0, 31, (n,), dtype=torch.int64, device=dev, generator=g)
+        flips ^= torch.where(nb > k, torch.ones_like(b) << b, torch.zeros_like(b))
+    pop = torch.zeros(n, dtype=torch.int64, device=dev)
+    for b in range(31):
+        pop += (flips >> b) & 1
+    rx = cw ^ flips
+    rd = torch.stack([((rx >> 23) & 255).to(torch.uint8), ((rx >> 15) & 255).to(torch.uint8)], 1).contiguous()
+    rp = torch.stack([((rx >> 8) & 127).to(torch.uint8), (rx & 255).to(torch.uint8)], 1).contiguous()
+    ok = torch.empty(n, dtype=torch.uint8, device=dev)
+    cor = torch.empty(n, dtype=torch.int32, device=dev)
+    rds = [rd.clone() for _ in range(reps + 1)]
+    torch.cuda.synchronize()
+
+    def dec(i):
+        assert h.decode_batch_async(rds[i].data_ptr(), 2, 2, rp.data_ptr(), 2, n, ok.data_ptr(), cor.data_ptr(),
+                                    stream=stream)
+
+    dec(reps)
+    torch.cuda.synchronize()
+    dec_ms = timed(torch, dec, reps)
+    assert bool(ok.bool().all().item()), "a BCH(31,16) word with <= 3 bit errors failed"
+    assert bool((cor.to(torch.int64) == pop).all().item()), "corrected_num differs from the injected bit count"
+    assert bool((rds[0] == data).all().item()), "data bytes not restored"
+    te, td = sum(enc_ms[1:]) / reps, sum(dec_ms) / reps
+    emit(args, {"workload": "BCH(31,16) t=3, 0-3 flipped bits per codeword (exact per-thread decoder)", "codewords": n,
+                "encode_ms": te, "decode_ms": td, "encode_Gcw_per_s": n / te / 1e6, "decode_Gcw_per_s": n / td / 1e6,
+                "encode_alg_GBps": n * 4 / te / 1e6, "decode_alg_GBps": n * (4 + 2 + 5) / td / 1e6,
+                "mean_bit_errors": float(pop.float().mean().item())})
+    h.close()
+
+
 def run_load(args, torch, api, dev):
     n = args.ncw or 128 * 1024 * 1024
     stream = torch.cuda.current_stream().cuda_stream
@@ -248,7 +296,7 @@ def main():
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
     for w in args.which:
-        {"erasure": run_erasure, "bch": run_bch, "load": run_load}[w](args, torch, api, dev)
+        {"erasure": run_erasure, "bch": run_bch, "bch31": run_bch31, "load": run_load}[w](args, torch, api, dev)
         torch.cuda.empty_cache()
 
 

@@ -106,5 +106,6 @@ struct poporon_cuda_bch {
     uint32_t gen;
     uint8_t *d_tables; // alpha_to[256] | index_of[256]
     uint32_t *d_map;   // n <= 15: the complete decode map, one word per received word (bch.cu), else NULL
+    uint32_t *d_smap;  // n > 15, parity_bits <= 20: decode map indexed by the remainder mod g (bch.cu), else NULL
     uint64_t launches;
 };

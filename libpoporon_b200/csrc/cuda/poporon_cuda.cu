@@ -481,6 +481,7 @@ void poporon_cuda_bch_destroy(poporon_cuda_bch_t *ctx)
     DeviceGuard g(ctx->device);
     cudaFree(ctx->d_tables);
     cudaFree(ctx->d_map);
+    cudaFree(ctx->d_smap);
     free(ctx);
 }
 

@@ -465,6 +465,39 @@ def test_bch_default_single_api(gpu_device):
         assert not ok and c is None and d[0] == 21 ^ 0x1F  # failure: data and corrected_num untouched
 
 
+@pytest.mark.parametrize("t", [1, 2, 3, 5, 7])
+def test_bch31_batches_vs_oracle(gpu_device, orc, t):
+    """BCH(31,k): the remainder-indexed decode map (parity bits <= 20: t = 1, 2, 3, 5) and the exact per-thread
+    decoder (t = 7) against the oracle, 0 .. t + 3 flipped bits anywhere in the 31, garbage above the k data bits."""
+    info = orc.bch_info(5, 0x25, t)
+    k, pbits = info["k"], info["parity_bits"]
+    db, pb = (k + 7) // 8, (pbits + 7) // 8
+    rng = np.random.default_rng(3100 + t)
+    n = 20000
+    with api.Poporon.bch(5, 0x25, t) as h:
+        msg = rng.integers(0, 256, (n, db), dtype=np.uint8)
+        par = np.full((n, pb), 0xEE, np.uint8)
+        assert h.encode_batch(msg, db, db, par, pb, n)
+        wpar, wok = orc.bch_encode(msg, pb, 5, 0x25, t)
+        assert wok.all() and (par == wpar).all()
+        d = msg.copy()
+        pp = par.copy()
+        for i in range(n):
+            for bit in rng.choice(31, int(rng.integers(0, t + 4)), replace=False):
+                if bit < pbits:
+                    pp[i, pb - 1 - bit // 8] ^= 1 << (bit % 8)
+                else:
+                    b = bit - pbits
+                    d[i, db - 1 - b // 8] ^= 1 << (b % 8)
+        rx_d, rx_p = d.copy(), pp.copy()
+        ok = np.full(n, 7, np.uint8)
+        cor = np.full(n, 0xFFFFFFFF, np.uint32)
+        assert h.decode_batch(d, db, db, pp, pb, n, ok, cor)
+        wd, wok, wcor = orc.bch_decode(rx_d, rx_p, 5, 0x25, t)
+        assert (ok == wok).all() and (cor == wcor).all() and (d == wd).all() and (pp == rx_p).all()
+        assert int(wok.sum()) > 0 and (t == 1 or int(wok.sum()) < n)  # both outcomes (t = 1 is a perfect code)
+
+
 def test_bch_word_level_api(gpu_device, orc):
     """poporon_bch_encode/decode/extract_data as used by reference tests/test_bch.c:61-187,251-305"""
     host = api.host
