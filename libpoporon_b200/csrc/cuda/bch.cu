@@ -51,33 +51,51 @@ __device__ __forceinline__ uint32_t low_mask(int bits)
     return bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
 }
 
+// rem[b][v] = (v * x^(8b + p)) mod g for data byte b (b = 0 the least significant byte of the k data bits): the
+// remainder of d * x^p by g is the XOR of four look-ups (division by g is linear over GF(2)), src/bch.c:352-380
+__device__ __forceinline__ void bch_build_rem_tables(const BchParams &P, uint32_t (*rem)[256])
+{
+    for (int e = threadIdx.x; e < 1024; e += blockDim.x) {
+        const int b = e >> 8;
+        uint32_t r = 0;
+        if (8 * b < P.k) {
+            uint64_t w = ((uint64_t)(((uint32_t)(e & 255) << (8 * b)) & low_mask(P.k))) << P.parity_bits;
+            for (int i = P.k + P.parity_bits - 1; i >= P.gen_deg; i--)
+                if (w & (1ull << i))
+                    w ^= (uint64_t)P.gen << (i - P.gen_deg);
+            r = (uint32_t)w;
+        }
+        rem[b][e & 255] = r;
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ uint32_t bch_rem(const uint32_t (*rem)[256], uint32_t dv)
+{
+    return rem[0][dv & 255] ^ rem[1][(dv >> 8) & 255] ^ rem[2][(dv >> 16) & 255] ^ rem[3][dv >> 24];
+}
+
 __global__ void __launch_bounds__(256)
 bch_encode_kernel(BchParams P, const uint8_t *__restrict__ data, size_t data_stride, size_t size,
                   uint8_t *__restrict__ parity, size_t parity_stride, size_t n, uint8_t *__restrict__ ok)
 {
-    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (cw >= n)
-        return;
+    __shared__ uint32_t rem[4][256];
+    bch_build_rem_tables(P, rem);
     const int db = (P.k + 7) / 8, pb = (P.parity_bits + 7) / 8;
-    bool good = false;
-    if (size >= (size_t)db) {
-        uint32_t d = pack_be(data + cw * data_stride, db) & low_mask(P.k);
-        // systematic encoding: remainder of d * x^p by g (src/bch.c:352-380)
-        const uint32_t shifted = d << P.parity_bits;
-        uint32_t rem = shifted;
-        for (int i = P.n - 1; i >= P.gen_deg; i--)
-            if (rem & (1u << i))
-                rem ^= P.gen << (i - P.gen_deg);
-        const uint32_t pv = (shifted ^ rem) & low_mask(P.parity_bits);
-        uint8_t *p = parity + cw * parity_stride;
-        for (int i = 0; i < pb; i++)
-            p[i] = 0;
-        for (int i = 0; i < pb && i < 4; i++)
-            p[pb - 1 - i] = (uint8_t)(pv >> (8 * i));
-        good = true;
+    for (size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x; cw < n; cw += (size_t)gridDim.x * blockDim.x) {
+        bool good = false;
+        if (size >= (size_t)db) {
+            const uint32_t d = pack_be(data + cw * data_stride, db) & low_mask(P.k);
+            const uint32_t pv = bch_rem(rem, d); // systematic encoding: remainder of d * x^p by g
+            uint8_t *p = parity + cw * parity_stride;
+            for (int i = 0; i < pb; i++)
+                p[i] = 0;
+            for (int i = 0; i < pb && i < 4; i++)
+                p[pb - 1 - i] = (uint8_t)(pv >> (8 * i));
+            good = true;
+        }
+        if (ok)
+            ok[cw] = good ? 1 : 0;
     }
-    if (ok)
-        ok[cw] = good ? 1 : 0;
 }
 
 __device__ bool bch_syndromes(const BchParams &P, const BchSmem &T, uint32_t w, uint8_t *s)
@@ -284,22 +302,8 @@ bch_decode_smap_kernel(BchParams P, const uint32_t *__restrict__ smap, uint8_t *
                        const uint8_t *__restrict__ parity, size_t parity_stride, size_t n, uint8_t *__restrict__ ok,
                        uint32_t *__restrict__ corrected)
 {
-    // rem[b][v] = (v * x^(8b + p)) mod g: the remainder of data byte b (b = 0 the least significant)
     __shared__ uint32_t rem[4][256];
-    for (int e = threadIdx.x; e < 1024; e += blockDim.x) {
-        const int b = e >> 8;
-        uint32_t r = 0;
-        if (8 * b < P.k) {
-            // (v << 8b) masked to k bits, times x^p, reduced bit by bit from the top
-            uint64_t w = ((uint64_t)(((uint32_t)(e & 255) << (8 * b)) & low_mask(P.k))) << P.parity_bits;
-            for (int i = P.k + P.parity_bits - 1; i >= P.gen_deg; i--)
-                if (w & (1ull << i))
-                    w ^= (uint64_t)P.gen << (i - P.gen_deg);
-            r = (uint32_t)w;
-        }
-        rem[b][e & 255] = r;
-    }
-    __syncthreads();
+    bch_build_rem_tables(P, rem);
     const int db = (P.k + 7) / 8, pb = (P.parity_bits + 7) / 8;
     const bool sized = size != 0 && size >= (size_t)db;
     for (size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x; cw < n; cw += (size_t)gridDim.x * blockDim.x) {
@@ -309,7 +313,7 @@ bch_decode_smap_kernel(BchParams P, const uint32_t *__restrict__ smap, uint8_t *
             uint8_t *d = data + cw * data_stride;
             const uint32_t dv = pack_be(d, db) & low_mask(P.k);
             const uint32_t pv = pack_be(parity + cw * parity_stride, pb) & low_mask(P.parity_bits);
-            const uint32_t s = rem[0][dv & 255] ^ rem[1][(dv >> 8) & 255] ^ rem[2][(dv >> 16) & 255] ^ rem[3][dv >> 24] ^ pv;
+            const uint32_t s = bch_rem(rem, dv) ^ pv;
             const uint32_t e = __ldg(smap + s);
             if (e & 0x80000000u) {
                 const uint32_t out = dv ^ (e & low_mask(P.k));
@@ -429,7 +433,8 @@ int launch_bch_encode(poporon_cuda_bch *ctx, const uint8_t *data, size_t data_st
             return check(cudaGetLastError(), "bch_encode4 launch");
         data += done, parity += done * 2, ok = ok ? ok + done : ok, n -= done;
     }
-    bch_encode_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, stream>>>(
+    const size_t eblocks = (n + threads - 1) / threads, ecap = (size_t)ctx->sm_count * 8;
+    bch_encode_kernel<<<(unsigned)(eblocks < ecap ? eblocks : ecap), threads, 0, stream>>>(
         params_of(ctx), data, data_stride, size, parity, parity_stride, n, ok);
     ctx->launches++;
     return check(cudaGetLastError(), "bch_encode launch");
