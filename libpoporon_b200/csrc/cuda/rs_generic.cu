@@ -31,11 +31,45 @@ rs_encode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, const uint
                          size_t n, uint8_t *__restrict__ ok)
 {
     __shared__ SmemTables T;
+    __shared__ uint8_t mtab[MAXR <= 32 ? 32 * 256 : 4]; // mtab[k][v] = v * g_k (src/encode.c:120-144 arithmetic)
     load_tables(T, gtab);
+    if constexpr (MAXR <= 32) {
+        for (int e = threadIdx.x; e < c.nroots * 256; e += blockDim.x) {
+            const uint32_t lg = T.index_of[e & 255];
+            uint32_t x = lg + T.genpoly[e >> 8];
+            x = x >= (uint32_t)c.nn ? x - c.nn : x;
+            mtab[e] = lg == (uint32_t)c.nn ? 0 : T.alpha_to[x];
+        }
+        __syncthreads();
+    }
     const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (cw >= n)
         return;
     const int nr = c.nroots, nn = c.nn;
+    if constexpr (MAXR <= 32) {
+        // parity register in registers (static indices, rows past nroots stay zero); fb * g_k by one look-up in a
+        // per-CTA product table built with the reference's own log arithmetic
+        uint32_t par[MAXR + 1];
+#pragma unroll
+        for (int j = 0; j <= MAXR; j++)
+            par[j] = 0;
+        const uint8_t *d = data + cw * data_stride;
+        const uint8_t *row0 = mtab + (nr - 1) * 256; // row of g_{nroots-1-q} for q = 0
+        for (size_t i = 0; i < size; i++) {
+            const uint32_t fb = (uint32_t)(d[i] & nn) ^ par[0];
+#pragma unroll
+            for (int q = 0; q < MAXR; q++)
+                par[q] = q < nr ? par[q + 1] ^ (uint32_t)row0[(int)fb - q * 256] : 0u;
+        }
+        uint8_t *p = parity + cw * parity_stride;
+#pragma unroll
+        for (int j = 0; j < MAXR; j++)
+            if (j < nr)
+                p[j] = (uint8_t)par[j];
+        if (ok)
+            ok[cw] = 1;
+        return;
+    }
     uint8_t ring[MAXR]; // circular LFSR state: logical p[j] = ring[(head + j) mod nr]
     for (int j = 0; j < nr; j++)
         ring[j] = 0;
@@ -78,7 +112,19 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
                          uint32_t *__restrict__ corrected)
 {
     __shared__ SmemTables T;
+    __shared__ uint8_t mtab[MAXR <= 32 ? 32 * 256 : 4]; // mtab[i][v] = v * alpha^((fcr + i) * prim), src/decode.c:375-415
     load_tables(T, gtab);
+    if constexpr (MAXR <= 32) {
+        if (mode != POPORON_CUDA_MODE_EXTSYN) {
+            for (int e = threadIdx.x; e < c.nroots * 256; e += blockDim.x) {
+                const uint32_t v = e & 255;
+                mtab[e] = v == 0 ? 0
+                                 : T.alpha_to[redc((uint32_t)T.index_of[v] + (uint32_t)(c.fcr + (e >> 8)) * (uint32_t)c.prim,
+                                                   c.nn)];
+            }
+        }
+        __syncthreads();
+    }
     const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (cw >= n)
         return;
@@ -106,9 +152,27 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
         } else {
             // Horner over data || parity at the generator roots
             const uint32_t first = d[0] & nn;
+            const size_t total = size + (size_t)nr;
+            if constexpr (MAXR <= 32) {
+                // the 32 running sums in registers, one product look-up per root and symbol
+                uint32_t sr[MAXR];
+#pragma unroll
+                for (int i = 0; i < MAXR; i++)
+                    sr[i] = first;
+                for (size_t j = 1; j < total; j++) {
+                    const uint32_t sym = (j < size ? d[j] : p[j - size]) & nn;
+#pragma unroll
+                    for (int i = 0; i < MAXR; i++)
+                        if (i < nr)
+                            sr[i] = sym ^ (uint32_t)mtab[i * 256 + sr[i]];
+                }
+#pragma unroll
+                for (int i = 0; i < MAXR; i++)
+                    if (i < nr)
+                        syn[i] = (uint8_t)sr[i];
+            } else {
             for (int i = 0; i < nr; i++)
                 syn[i] = (uint8_t)first;
-            const size_t total = size + (size_t)nr;
             for (size_t j = 1; j < total; j++) {
                 const uint32_t sym = (j < size ? d[j] : p[j - size]) & nn;
                 for (int i = 0; i < nr; i++) {
@@ -118,6 +182,7 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
                                                                             (uint32_t)(c.fcr + i) * (uint32_t)c.prim,
                                                                         nn)]);
                 }
+            }
             }
             uint32_t any = 0;
             for (int i = 0; i < nr; i++) {
