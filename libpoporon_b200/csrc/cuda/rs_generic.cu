@@ -126,19 +126,24 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
         __syncthreads();
     }
     const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (cw >= n)
-        return;
+    const bool present = cw < n; // threads past the batch still walk through the phase barriers of rs_correct
     const int nr = c.nroots, nn = c.nn;
     const uint8_t A0 = (uint8_t)nn;
     uint8_t *d = data + cw * data_stride;
     uint8_t *p = parity + cw * parity_stride;
-    uint8_t syn[MAXR + 1];
-    LocalWork<MAXR> wk;
     uint32_t ncorr = 0;
     bool success = false;
+    // nroots <= 32: work arrays in shared memory ([array][index][thread]) and the warps of the CTA phase-locked,
+    // as in rs255_correct_kernel; otherwise thread-local arrays
+    extern __shared__ __align__(16) uint8_t gwork[];
+    [[maybe_unused]] uint8_t syn_local[MAXR <= 32 ? 1 : MAXR + 1];
+    [[maybe_unused]] LocalWork<MAXR <= 32 ? 0 : MAXR> wk_local;
+    auto run = [&](auto &wk, auto syn) {
+    bool need = false, erasure = false; // rs_correct is called by every thread, need = this one has work for it
+    uint32_t ec = 0;
 
     const int16_t pad = (int16_t)(uint16_t)((size_t)nn - (size_t)nr - size); // src/decode.c:418-429
-    if (size != 0 && !(pad < 0 || pad >= (int16_t)(nn - nr))) {
+    if (present && size != 0 && !(pad < 0 || pad >= (int16_t)(nn - nr))) {
         if (mode == POPORON_CUDA_MODE_EXTSYN) {
             bool dirty = false;
             for (int i = 0; i < nr; i++) {
@@ -148,7 +153,8 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
                 syn[i] = (uint8_t)(s > (uint16_t)nn ? nn : s);
                 dirty |= (s != (uint16_t)nn);
             }
-            success = !dirty || rs_correct<MAXR>(c, T, d, size, p, wk, (const uint8_t *)syn, 0, nullptr, 0, false, pad, ncorr);
+            success = !dirty;
+            need = dirty;
         } else {
             // Horner over data || parity at the generator roots
             const uint32_t first = d[0] & nn;
@@ -192,16 +198,33 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
             if (!any) {
                 success = true;
             } else if (mode == POPORON_CUDA_MODE_ERASURE) {
-                const uint32_t ec = cnt[cw];
-                if (ec <= (uint32_t)nr) // > nroots erasures overrun the reference's scratch: report failure
-                    success = rs_correct<MAXR>(c, T, d, size, p, wk, (const uint8_t *)syn, ec, pos + cw * pos_stride, pos_stride, true,
-                                               pad, ncorr);
+                ec = cnt[cw];
+                need = erasure = ec <= (uint32_t)nr; // > nroots erasures overrun the reference's scratch: failure
             } else {
-                success = rs_correct<MAXR>(c, T, d, size, p, wk, (const uint8_t *)syn, 0, nullptr, 0, false, pad, ncorr);
+                need = true;
             }
         }
     }
+    if constexpr (MAXR <= 32) {
+        const bool r = rs_correct<MAXR, CtaPhaseSync>(c, T, d, size, p, wk, syn, erasure ? ec : 0u,
+                                                      erasure ? pos + cw * pos_stride : nullptr, pos_stride, erasure, pad,
+                                                      ncorr, need);
+        if (need)
+            success = r;
+    } else if (need) {
+        success = rs_correct<MAXR>(c, T, d, size, p, wk, syn, erasure ? ec : 0u,
+                                   erasure ? pos + cw * pos_stride : nullptr, pos_stride, erasure, pad, ncorr);
+    }
+    };
+    if constexpr (MAXR <= 32) {
+        SmemWork<32> wk{gwork + threadIdx.x};
+        run(wk, wk.arr(7));
+    } else {
+        run(wk_local, (uint8_t *)syn_local);
+    }
     (void)A0;
+    if (!present)
+        return;
     if (ok)
         ok[cw] = success ? 1 : 0;
     if (corrected)
@@ -237,7 +260,7 @@ int launch_rs_decode_generic(poporon_cuda_rs *ctx, int mode, uint8_t *data, size
     const int threads = 128;
     const unsigned blocks = (unsigned)((n + threads - 1) / threads);
     if (ctx->code.nroots <= 32)
-        rs_decode_generic_kernel<32><<<blocks, threads, 0, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride,
+        rs_decode_generic_kernel<32><<<blocks, threads, SmemWork<32>::kBytes, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride,
                                                                      size, parity, parity_stride, n, pos, pos_stride,
                                                                      cnt, syn, ok, corrected);
     else
