@@ -90,6 +90,8 @@ struct poporon_cuda_rs {
     uint8_t *d_rem;           // per-dirty-codeword remainder / syndromes
     uint32_t *d_counters;     // [0] = dirty count
     size_t queue_cap;
+    uint8_t *d_slab;          // rs255_fft: one 255 KB bit-plane slab per SM (allocated on first use)
+    int use_lfsr;             // PP_RS255_LFSR=1: the round-1 LFSR kernels instead of the transform kernels (A/B runs)
     // opt-in per-kernel timing (poporon_cuda_rs_profile): CUDA event pairs around each launch
     bool prof_on;
     int prof_used;

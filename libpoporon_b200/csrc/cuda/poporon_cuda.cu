@@ -316,6 +316,7 @@ void poporon_cuda_rs_destroy(poporon_cuda_rs_t *ctx)
     cudaFree(ctx->d_tables);
     cudaFree(ctx->d_queue);
     cudaFree(ctx->d_rem);
+    cudaFree(ctx->d_slab);
     cudaFree(ctx->d_counters);
     free(ctx);
 }

@@ -34,6 +34,8 @@
 #include "gf256_consts.cuh"
 #include "rs_correct.cuh"
 #include "rs255_solve_core.h"
+#include "rs255_fft.cuh"
+#include <stdlib.h>
 
 namespace ppcu {
 
@@ -909,8 +911,9 @@ struct ApplyHook {
     const uint32_t *qprev; // queue + g0p + lane
     uint32_t nvalid;       // codewords c < nvalid of the previous tile exist for this lane
     const uint8_t *records;
-    uint8_t *data;
-    uint32_t stride32;
+    uint8_t *data, *parity; // message rows and parity rows (one span when the records are packed)
+    uint32_t stride32, pstride32;
+    uint32_t size;          // message bytes per codeword
     int pad;
     uint32_t entry_cur, entry_app;
     uint32_t p2, m2; // raw 16-bit loads of a portion, zero-extended by the load itself: nothing touches them before
@@ -933,17 +936,22 @@ struct ApplyHook {
         p2 = 0;
         m2 = 0;
     }
-    // XORs of the portion whose loads were issued one step ago.  Records are packed (parity = data + size, one
-    // stride: rs255_shape_ok), so symbol `loc` of the codeword lives at data + cw*stride + loc - pad.
+    // XORs of the portion whose loads were issued one step ago.  Symbol `loc` of the codeword is byte loc - pad of
+    // its message row when that is < size, else byte loc - pad - size of its parity row (the two-pointer shape of
+    // reference include/poporon.h:90-91; for packed records both expressions name the same address).
     __device__ __forceinline__ void flush()
     {
         if (m2 != 0u) {
-            const uintptr_t base = (uintptr_t)data + (size_t)(entry_app & 0x3FFFFFFFu) * (size_t)stride32 - (size_t)(1 + pad);
+            const size_t cw = entry_app & 0x3FFFFFFFu;
+            const uintptr_t dbase = (uintptr_t)data + cw * (size_t)stride32 - (size_t)(1 + pad);
+            const uintptr_t pbase = (uintptr_t)parity + cw * (size_t)pstride32 - (size_t)(1 + pad) - (size_t)size;
+            const uint32_t split = size + 1u + (uint32_t)pad; // list entries >= split are parity symbols
 #pragma unroll
             for (int e = 0; e < 2; e++) {
                 const uint32_t mag = (m2 >> (8 * e)) & 0xFFu;
                 if (mag) {
-                    const uintptr_t ua = base + ((p2 >> (8 * e)) & 0xFFu); // list entry = location + 1 > pad
+                    const uint32_t le = (p2 >> (8 * e)) & 0xFFu; // list entry = location + 1 > pad
+                    const uintptr_t ua = (le >= split ? pbase : dbase) + le;
                     asm volatile("red.relaxed.gpu.global.xor.b32 [%0], %1;" ::"l"(ua & ~(uintptr_t)3),
                                  "r"(mag << (8u * (unsigned)(ua & 3u)))
                                  : "memory");
@@ -1017,7 +1025,8 @@ struct ApplyHook {
 __global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, kSolveWarpsPerSM / kSolveWarpsPerCTA)
 rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ counter, uint8_t *syn_raw,
                    uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2,
-                   uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data, size_t data_stride)
+                   uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data, size_t data_stride,
+                   uint8_t *parity, size_t parity_stride)
 {
     extern __shared__ __align__(16) uint32_t solve_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1049,6 +1058,9 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
     hook.records = syn_raw;
     hook.data = data;
     hook.stride32 = (uint32_t)data_stride;
+    hook.parity = parity;
+    hook.pstride32 = (uint32_t)parity_stride;
+    hook.size = (uint32_t)size;
     hook.pad = pad;
     hook.queue = queue;
     hook.total = total;
@@ -1193,7 +1205,16 @@ int rs255_init(poporon_cuda_rs *ctx)
                                      kPairs * kSmemScreen));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_correct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCorrectSmem));
-    (void)ctx;
+    const char *env = getenv("PP_RS255_LFSR");
+    ctx->use_lfsr = env && env[0] == '1';
+    return rs255_fft_init(ctx);
+}
+
+static int ensure_slab(poporon_cuda_rs *ctx)
+{
+    if (ctx->d_slab)
+        return 0;
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_slab, rs255_fft_slab_bytes(ctx->sm_count)));
     return 0;
 }
 
@@ -1227,6 +1248,20 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
 {
     if (n == 0)
         return 0;
+    FftShape shape;
+    if (!ctx->use_lfsr && rs255_fft_shape_ok(0, data, data_stride, size, parity, parity_stride, &shape)) {
+        int rc = ensure_slab(ctx);
+        if (rc != 0)
+            return rc;
+        if (ok)
+            PP_CUDA_TRY(cudaMemsetAsync(ok, 1, n, stream));
+        {
+            ProfScope prof(ctx, PROF_ENCODE, stream);
+            rc = rs255_fft_encode(ctx, shape, data, data_stride, size, parity, parity_stride, n, ctx->d_slab, stream);
+        }
+        ctx->launches++;
+        return rc;
+    }
     LfsrArgs A{};
     A.stream = data;
     A.stride = data_stride;
@@ -1268,16 +1303,36 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     A.gend = data + (n - 1) * data_stride + size + kPar;
     A.dmask = dmask;
     A.syn = ctx->d_rem;
-    uint64_t invperm;
-    tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
-    {
-        ProfScope prof(ctx, PROF_SCREEN, stream);
-        rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64 * kPairs, kPairs * kSmemScreen, stream>>>(A);
-    }
-    {
-        ProfScope prof(ctx, PROF_COMPACT, stream);
-        rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(
-            dmask, n, invperm, ctx->d_queue, ctx->d_counters, ok, corrected);
+    FftShape shape;
+    if (!ctx->use_lfsr && rs255_fft_shape_ok(1, data, data_stride, size, parity, parity_stride, &shape)) {
+        rc = ensure_slab(ctx);
+        if (rc != 0)
+            return rc;
+        {
+            ProfScope prof(ctx, PROF_SCREEN, stream);
+            rc = rs255_fft_screen(ctx, shape, data, data_stride, size, parity, parity_stride, n, ctx->d_slab, dmask,
+                                  ctx->d_rem, stream);
+        }
+        if (rc != 0)
+            return rc;
+        {
+            ProfScope prof(ctx, PROF_COMPACT, stream);
+            rc = rs255_fft_compact(ctx, dmask, n, ctx->d_queue, ctx->d_counters, ok, corrected, stream);
+        }
+        if (rc != 0)
+            return rc;
+    } else {
+        uint64_t invperm;
+        tile_geometry(data, data_stride, &A.perm, &invperm, &A.wbs);
+        {
+            ProfScope prof(ctx, PROF_SCREEN, stream);
+            rs255_lfsr_kernel<MODE_SCREEN><<<lfsr_grid(ctx, n), 64 * kPairs, kPairs * kSmemScreen, stream>>>(A);
+        }
+        {
+            ProfScope prof(ctx, PROF_COMPACT, stream);
+            rs255_compact_kernel<<<(unsigned)((tiles * kTile + 255) / 256), 256, 0, stream>>>(
+                dmask, n, invperm, ctx->d_queue, ctx->d_counters, ok, corrected);
+        }
     }
     // one resident wave of the general stage (its shared-memory work arrays limit it to a few CTAs per SM); a grid
     // larger than one wave would leave a thin second wave behind the grid-stride loop
@@ -1302,7 +1357,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
             rs255_solve_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
                                  kSolveSmem, stream>>>(
                 size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected,
-                data, data_stride);
+                data, data_stride, parity, parity_stride);
         }
         cq = queue2;
         cc = ctx->d_counters + 1;

@@ -1,0 +1,809 @@
+// rs255_fft.cu — syndromes (and through them the parity) of RS(255,223) as a 15 x 17 Cooley-Tukey transform on
+// bit-planes.  sm_100a only.
+//
+// What replaces what (reference tree):
+//   calculate_syndrome_u8 (src/decode.c:232-416) ... rs255_fft_kernel<SCREEN>: "is the codeword clean" + S_1..S_32
+//   rs_encode (src/encode.c:17-145) ................ rs255_fft_kernel<ENCODE>: parity = V^-1 * syndromes(message * x^32)
+//
+// The arithmetic (tools/gen_rs255_fft.py derives, checks and writes the XOR networks, rs255_fft_gen.cuh):
+//   e = 17 d + c,  R_c[k] = sum_d r_(17d+c) beta^(dk)  (15-point DFT, twiddles in GF(16), 488 lane-ops per class)
+//   S_j = sum_c alpha^(jc) R_c[j mod 15]               (Horner in c, 486 lane-ops per class)
+// = 18.6 K lane-ops per 32 codewords against 80.6 K for 32 Horner / LFSR recurrences over 255 symbols.
+//
+// A transform needs a whole codeword at once, and 1024 codewords in bit-plane form (one plane word = 32
+// codewords, 32 lanes) are 255 KB: more than a CTA's shared memory.  So a CTA works on a tile of 1024 consecutive
+// codewords in two phases, with the planes parked in a CTA-private 255 KB slab of global memory that is written
+// and read back by the same SM and therefore lives in L2:
+//   phase A  every warp takes sub-tiles of 32 consecutive codewords (one lane-slot of the tile).  The rows arrive
+//            by ONE bulk copy (cp.async.bulk + mbarrier: the 32 rows are contiguous in memory), double-buffered per
+//            warp.  Lane x transposes word-column x of the 32 rows (4 symbols x 32 codewords) into bit-planes,
+//            changes basis and stores each symbol's 8 planes (32 bytes) to slab[slot(e)][lane-slot].
+//   phase B  warps 0-3 ("S1") run the 15-point DFTs class by class (class c = 15 slab slots = 15 KB contiguous) and
+//            hand R_c to warps 4-7 ("S2") through a 4-slot shared-memory ring (mbarrier full/empty); S2 warp u owns
+//            the eight syndromes of four residues j mod 15 and runs their Horner recurrences in registers.
+//   output   SCREEN: a dirty bit per codeword + the 32 syndrome bytes of dirty codewords; ENCODE: the solve and the
+//            parity rows.
+#include "rs255_fft.cuh"
+
+#include <utility>
+
+#include "rs255_fft_gen.cuh"
+
+namespace ppcu {
+
+namespace {
+
+constexpr int kTile = 1024;  // codewords per CTA tile
+constexpr int kWarps = 8;
+constexpr int kSubPerWarp = 32 / kWarps;
+constexpr int kSlotBytes = 1024;                    // one symbol of the tile: [lane-slot 32][8 planes]
+constexpr size_t kSlabBytes = 255 * kSlotBytes;     // per CTA
+constexpr int kRingSlots = 4;
+constexpr int kRingSlotBytes = 15 * 1024;           // R_c: [k 15][half 2][lane 32][4 planes]
+constexpr int kRingBytes = kRingSlots * kRingSlotBytes;
+constexpr int kMaxBuf = 8448;                       // bytes of one sub-tile buffer (rows of 32 codewords)
+constexpr int kBarBytes = 1024;                      // mbarriers [0, 192) + the S2 warps' dirty words [256, 768)
+
+enum { MODE_SCREEN = 0, MODE_ENCODE = 1 };
+
+struct FftArgs {
+    const uint8_t *data;   // message rows
+    size_t dstride;
+    int size;              // message bytes per codeword, 1..223
+    const uint8_t *parity; // SCREEN: parity rows (32 bytes each)
+    size_t pstride;
+    int packed;            // SCREEN: parity == data + size with the same stride (one span per sub-tile)
+    size_t n;
+    uint8_t *slab;         // gridDim.x slabs
+    int bufbytes;          // bytes of one sub-tile buffer
+    int poff;              // offset of the parity span inside a buffer (split layout)
+    // SCREEN outputs
+    uint32_t *dirty;       // bitmap, bit (cw & 31) of word cw >> 5
+    uint8_t *syn;          // [n][32]
+    // ENCODE outputs
+    uint8_t *out_parity;
+    size_t out_pstride;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// small device helpers
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void lds128(uint32_t a, uint32_t (&v)[4])
+{
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(a));
+}
+__device__ __forceinline__ void sts128(uint32_t a, const uint32_t (&v)[4])
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+}
+__device__ __forceinline__ void ldg256(const void *p, uint32_t (&lo)[4], uint32_t (&hi)[4])
+{
+    asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(lo[0]), "=r"(lo[1]), "=r"(lo[2]), "=r"(lo[3]), "=r"(hi[0]), "=r"(hi[1]), "=r"(hi[2]), "=r"(hi[3])
+                 : "l"(p)
+                 : "memory");
+}
+__device__ __forceinline__ void stg256(void *p, const uint32_t (&v)[8])
+{
+    asm volatile("st.global.v8.b32 [%8], {%0, %1, %2, %3, %4, %5, %6, %7};" ::"r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]),
+                 "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "l"(p)
+                 : "memory");
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        " .reg .pred p;\n"
+        "WAIT_%=:\n"
+        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra DONE_%=;\n"
+        " bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+// one contiguous span global -> shared memory (both 16-byte aligned, bytes a multiple of 16), completion on an mbarrier
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+// (a & m) | (b & ~m) in one LOP3
+__device__ __forceinline__ uint32_t merge_bits(uint32_t a, uint32_t b, uint32_t m)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(d) : "r"(a), "r"(b), "r"(m));
+    return d;
+}
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// 32x32 bit-matrix transpose in registers: x[r] bit c <-> x[c] bit r (an involution)
+__device__ __forceinline__ void transpose32(uint32_t (&x)[32])
+{
+#pragma unroll
+    for (int r = 0; r < 16; r++) {
+        const uint32_t a = x[r], b = x[r + 16];
+        x[r] = __byte_perm(a, b, 0x5410);
+        x[r + 16] = __byte_perm(a, b, 0x7632);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 8)
+            continue;
+        const uint32_t a = x[r], b = x[r + 8];
+        x[r] = __byte_perm(a, b, 0x6240);
+        x[r + 8] = __byte_perm(a, b, 0x7351);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 4)
+            continue;
+        const uint32_t a = x[r], b = x[r + 4];
+        x[r] = merge_bits(a, b << 4, 0x0F0F0F0Fu);
+        x[r + 4] = merge_bits(a >> 4, b, 0x0F0F0F0Fu);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 2)
+            continue;
+        const uint32_t a = x[r], b = x[r + 2];
+        x[r] = merge_bits(a, b << 2, 0x33333333u);
+        x[r + 2] = merge_bits(a >> 2, b, 0x33333333u);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        if (r & 1)
+            continue;
+        const uint32_t a = x[r], b = x[r + 1];
+        x[r] = merge_bits(a, b << 1, 0x55555555u);
+        x[r + 1] = merge_bits(a >> 1, b, 0x55555555u);
+    }
+}
+
+// slab slot of the symbol with exponent e (< 255): class-major, slot = (e mod 17) * 15 + e / 17
+__device__ __forceinline__ uint32_t slot_of(uint32_t e)
+{
+    const uint32_t d = (e * 241u) >> 12; // e / 17 for e < 255
+    return (e - 17u * d) * 15u + d;
+}
+
+// all 16 subset-XORs of four planes
+__device__ __forceinline__ void subset_table(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3, uint32_t (&T)[16])
+{
+    T[0] = 0;
+    T[1] = b0;
+    T[2] = b1;
+    T[3] = b0 ^ b1;
+    T[4] = b2;
+    T[5] = b2 ^ b0;
+    T[6] = b2 ^ b1;
+    T[7] = b2 ^ T[3];
+    T[8] = b3;
+    T[9] = b3 ^ b0;
+    T[10] = b3 ^ b1;
+    T[11] = b3 ^ T[3];
+    T[12] = b3 ^ b2;
+    T[13] = T[12] ^ b0;
+    T[14] = T[12] ^ b1;
+    T[15] = T[12] ^ T[3];
+}
+
+// ---------------------------------------------------------------------------------------------------
+// shared memory map
+//   [0, kBarBytes)                       mbarriers: buffer-full [kWarps][2], ring full [4], ring empty [4]; nz words
+//   [kBarBytes, +kRingBytes)             S1 -> S2 ring
+//   [.., + kWarps * 2 * bufbytes)        sub-tile buffers: warp w, buffer b at (2w + b) * bufbytes
+// The output stage (256 planes x 128 B = 32 KB) reuses buffer 1 of warps 0..3 (free during phase B and the output).
+// ---------------------------------------------------------------------------------------------------
+struct Smem {
+    uint32_t base, bars, ring, bufs;
+    int bufbytes;
+    __device__ __forceinline__ uint32_t bar_buf(int w, int b) const { return bars + 8u * (uint32_t)(2 * w + b); }
+    __device__ __forceinline__ uint32_t bar_full(int s) const { return bars + 128u + 8u * (uint32_t)s; }
+    __device__ __forceinline__ uint32_t bar_empty(int s) const { return bars + 160u + 8u * (uint32_t)s; }
+    __device__ __forceinline__ uint32_t nzword(int u, int lane) const { return bars + 256u + 4u * (uint32_t)(32 * u + lane); }
+    __device__ __forceinline__ uint32_t buf(int w, int b) const { return bufs + (uint32_t)((2 * w + b) * bufbytes); }
+    // plane p (0..255) of the output stage, this lane
+    __device__ __forceinline__ uint32_t outplane(int p, int lane) const
+    {
+        return buf(p >> 6, 1) + (uint32_t)((p & 63) * 128 + lane * 4);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// phase A
+// ---------------------------------------------------------------------------------------------------
+// Issue the copy of the sub-tile that starts at codeword cwb (rows <= 32 of them exist) into buffer `bufaddr`.
+// The data span starts (g & 15) bytes into the buffer.  Called by the whole warp (lane 0 issues the bulk copies,
+// the other lanes move the few bytes that are not a multiple of 16).
+template <int MODE>
+__device__ __forceinline__ void issue_subtile(const FftArgs &A, uint32_t bufaddr, uint32_t bar, size_t cwb, int rows, int lane)
+{
+    __syncwarp(); // every lane is done reading the buffer's previous contents
+    uint32_t tx = 0;
+    const int rowlen = (MODE == MODE_SCREEN && A.packed) ? A.size + 32 : A.size;
+    const uint8_t *g = A.data + cwb * A.dstride;
+    const uint32_t a = (uint32_t)((uintptr_t)g & 15u);
+    const uint32_t total = rows > 0 ? a + (uint32_t)(rows - 1) * (uint32_t)A.dstride + (uint32_t)rowlen : 0u;
+    const uint32_t bulk = total & ~15u;
+    tx += bulk;
+    uint32_t bulk_p = 0, total_p = 0, ap = 0;
+    const uint8_t *gp = nullptr;
+    if (MODE == MODE_SCREEN && !A.packed) {
+        gp = A.parity + cwb * A.pstride;
+        ap = (uint32_t)((uintptr_t)gp & 15u);
+        total_p = rows > 0 ? ap + (uint32_t)(rows - 1) * (uint32_t)A.pstride + 32u : 0u;
+        bulk_p = total_p & ~15u;
+        tx += bulk_p;
+    }
+    if (lane == 0) {
+        mbar_expect_tx(bar, tx);
+        if (bulk)
+            bulk_load(bufaddr, g - a, bulk, bar);
+        if (bulk_p)
+            bulk_load(bufaddr + (uint32_t)A.poff, gp - ap, bulk_p, bar);
+    }
+    // tails: plain byte copies (a bulk copy moves multiples of 16 bytes and must not read past the batch)
+    if ((uint32_t)lane < (total & 15u)) {
+        const uint8_t v = (g - a)[bulk + (uint32_t)lane];
+        asm volatile("st.shared.u8 [%0], %1;" ::"r"(bufaddr + bulk + (uint32_t)lane), "r"((uint32_t)v) : "memory");
+    }
+    if (MODE == MODE_SCREEN && !A.packed && (uint32_t)lane < (total_p & 15u)) {
+        const uint8_t v = (gp - ap)[bulk_p + (uint32_t)lane];
+        asm volatile("st.shared.u8 [%0], %1;" ::"r"(bufaddr + (uint32_t)A.poff + bulk_p + (uint32_t)lane), "r"((uint32_t)v) : "memory");
+    }
+}
+
+// Transpose the sub-tile in `bufaddr` (lane-slot `ls` of the tile) into the slab.
+template <int MODE>
+__device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t bufaddr, size_t cwb, int ls, uint8_t *slab, int lane)
+{
+    const int L = A.size + 32;
+    const int ncd = (A.size + 3) >> 2;                        // word-columns of the message
+    const int ncols = MODE == MODE_SCREEN ? ncd + 8 : ncd;    // + 8 of the parity
+    const uint32_t ad = (uint32_t)((uintptr_t)(A.data + cwb * A.dstride) & 15u);
+    uint32_t pbase, pstr;
+    if (MODE == MODE_SCREEN) {
+        if (A.packed) {
+            pbase = bufaddr + ad + (uint32_t)A.size;
+            pstr = (uint32_t)A.dstride;
+        } else {
+            pbase = bufaddr + (uint32_t)A.poff + (uint32_t)((uintptr_t)(A.parity + cwb * A.pstride) & 15u);
+            pstr = (uint32_t)A.pstride;
+        }
+    } else {
+        pbase = bufaddr;
+        pstr = 0;
+    }
+#pragma unroll 1
+    for (int col0 = 0; col0 < ncols; col0 += 32) {
+        const int col = col0 + lane;
+        uint32_t base, stride;
+        int nvalid, e0;
+        if (col < ncd) {
+            base = bufaddr + ad + 4u * (uint32_t)col;
+            stride = (uint32_t)A.dstride;
+            nvalid = A.size - 4 * col;
+            e0 = L - 1 - 4 * col;
+        } else {
+            const int pc = col - ncd;
+            base = pbase + 4u * (uint32_t)(pc & 7);
+            stride = pstr;
+            nvalid = col < ncols ? 4 : 0;
+            e0 = 31 - 4 * (pc & 7);
+        }
+        // rows i and i + 4 are 4 * stride bytes apart: same byte offset inside their words.  Four aligned row bases
+        // and four PRMT selectors serve all 32 rows.
+        uint32_t rb[4], sel[4];
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+            const uint32_t addr = base + (uint32_t)v * stride;
+            rb[v] = addr & ~3u;
+            sel[v] = 0x3210u + 0x1111u * (addr & 3u);
+        }
+        const uint32_t s4 = 4u * stride;
+        uint32_t X[32];
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+            const uint32_t addr = rb[i & 3] + (uint32_t)(i >> 2) * s4;
+            const uint32_t lo = lds32(addr), hi = lds32(addr + 4u);
+            X[i] = __byte_perm(lo, hi, sel[i & 3]);
+        }
+        transpose32(X); // X[8 y + t] = plane t of byte y of the column
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            if (y < nvalid) {
+                uint32_t s[8], t[8];
+#pragma unroll
+                for (int q = 0; q < 8; q++)
+                    s[q] = X[8 * y + q];
+                rsfft::conv_in(s, t);
+                stg256(slab + (size_t)slot_of((uint32_t)(e0 - y)) * kSlotBytes + (size_t)ls * 32, t);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// phase B
+// ---------------------------------------------------------------------------------------------------
+// S1: the class tasks t = warp, warp + 4, ... (class c = 16 - t, so that S2 meets the classes in Horner order)
+__device__ __forceinline__ void s1_run(const Smem &sm, const uint8_t *slab, int warp, int lane, uint32_t &gtask)
+{
+    uint32_t lo[15][4], hi[15][4];
+#pragma unroll 1
+    for (int t = warp; t < 17; t += 4) {
+        const int c = 16 - t;
+        const uint8_t *src = slab + (size_t)(c * 15) * kSlotBytes + (size_t)lane * 32;
+#pragma unroll
+        for (int d = 0; d < 15; d++)
+            ldg256(src + (size_t)d * kSlotBytes, lo[d], hi[d]);
+        rsfft::dft15(lo);
+        rsfft::dft15(hi);
+        const uint32_t g = gtask + (uint32_t)t;
+        const int slot = (int)(g & (kRingSlots - 1));
+        mbar_wait(sm.bar_empty(slot), ((g / kRingSlots) & 1u) ^ 1u);
+        const uint32_t dst = sm.ring + (uint32_t)(slot * kRingSlotBytes + lane * 16);
+#pragma unroll
+        for (int k = 0; k < 15; k++) {
+            sts128(dst + (uint32_t)(k * 1024), lo[k]);
+            sts128(dst + (uint32_t)(k * 1024 + 512), hi[k]);
+        }
+        __syncwarp();
+        if (lane == 0)
+            mbar_arrive(sm.bar_full(slot));
+    }
+    gtask += 17;
+}
+
+// the syndromes of S2 warp U: residues k = j mod 15 and their j's (U = 0 has three residues with 3 + 3 + 2 syndromes,
+// the others four residues with two each)
+__host__ __device__ constexpr int s2_nk(int u) { return u == 0 ? 3 : 4; }
+__host__ __device__ constexpr int s2_k(int u, int i)
+{
+    return u == 0 ? (i < 3 ? i + 1 : 3) : u == 3 ? (i < 3 ? 12 + i : 0) : 4 * u + i;
+}
+__host__ __device__ constexpr int s2_kj(int u, int q) // which of the warp's residues feeds syndrome slot q
+{
+    return u == 0 ? (q < 3 ? 0 : q < 6 ? 1 : 2) : q >> 1;
+}
+__host__ __device__ constexpr int s2_j(int u, int q) // syndrome number of slot q
+{
+    return u == 0 ? (q < 6 ? (q / 3 + 1) + 15 * (q % 3) : 3 + 15 * (q - 6))
+                  : (s2_k(u, q >> 1) == 0 ? 15 : s2_k(u, q >> 1)) + 15 * (q & 1);
+}
+static_assert(s2_j(0, 0) == 1 && s2_j(0, 1) == 16 && s2_j(0, 2) == 31 && s2_j(0, 3) == 2 && s2_j(0, 5) == 32 &&
+              s2_j(0, 6) == 3 && s2_j(0, 7) == 18 && s2_j(1, 0) == 4 && s2_j(1, 1) == 19 && s2_j(3, 6) == 15 &&
+              s2_j(3, 7) == 30 && s2_j(2, 7) == 26, "syndrome assignment");
+
+template <int U, int... Q>
+__device__ __forceinline__ void s2_step(uint32_t (&acc)[8][8], const uint32_t (&r)[4][8], std::integer_sequence<int, Q...>)
+{
+    (rsfft::hstep<s2_j(U, Q)>(acc[Q], r[s2_kj(U, Q)]), ...);
+}
+
+// S2: Horner over the 17 classes for this warp's eight syndromes; leaves them (tower planes) in acc
+template <int U>
+__device__ __forceinline__ void s2_run(const Smem &sm, int lane, uint32_t &gtask, uint32_t (&acc)[8][8])
+{
+#pragma unroll
+    for (int q = 0; q < 8; q++)
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            acc[q][t] = 0;
+#pragma unroll 1
+    for (int t = 0; t < 17; t++) {
+        const uint32_t g = gtask + (uint32_t)t;
+        const int slot = (int)(g & (kRingSlots - 1));
+        mbar_wait(sm.bar_full(slot), (g / kRingSlots) & 1u);
+        const uint32_t src = sm.ring + (uint32_t)(slot * kRingSlotBytes + lane * 16);
+        uint32_t r[4][8];
+#pragma unroll
+        for (int i = 0; i < s2_nk(U); i++) {
+            uint32_t a[4], b[4];
+            lds128(src + (uint32_t)(s2_k(U, i) * 1024), a);
+            lds128(src + (uint32_t)(s2_k(U, i) * 1024 + 512), b);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                r[i][q] = a[q];
+                r[i][4 + q] = b[q];
+            }
+        }
+        if (s2_nk(U) < 4) {
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                r[3][q] = 0;
+        }
+        s2_step<U>(acc, r, std::make_integer_sequence<int, 8>{});
+        __syncwarp(); // every lane has its operands in registers (and used them)
+        if (lane == 0)
+            mbar_arrive(sm.bar_empty(slot));
+    }
+    gtask += 17;
+}
+
+// S2 epilogue: dirty mask of the warp's syndromes + planes to the output stage (standard basis for SCREEN, tower
+// planes for ENCODE, whose mask table expects them)
+template <int MODE, int U>
+__device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t (&acc)[8][8])
+{
+    uint32_t nz = 0;
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        uint32_t s[8];
+        if (MODE == MODE_SCREEN) {
+            rsfft::conv_out(acc[q], s);
+        } else {
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                s[t] = acc[q][t];
+        }
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            nz |= s[t];
+            sts32(sm.outplane(8 * (s2_j(U, q) - 1) + t, lane), s[t]);
+        }
+    }
+    return nz;
+}
+
+// ENCODE: parity bytes 4w .. 4w+3 (32 planes) from the 32 syndromes in the output stage
+template <int W, int J, int... QU>
+__device__ __forceinline__ void enc_acc(uint32_t (&acc)[32], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
+                                        std::integer_sequence<int, QU...>)
+{
+    ((acc[QU] = xor3(acc[QU], T1[rsfft::EncM::v.m[J][4 * W + (QU >> 3)][QU & 7] & 15],
+                     T2[rsfft::EncM::v.m[J][4 * W + (QU >> 3)][QU & 7] >> 4])),
+     ...);
+}
+template <int W, int J>
+__device__ __forceinline__ void enc_j(const Smem &sm, int lane, uint32_t (&acc)[32])
+{
+    uint32_t in[8], T1[16], T2[16];
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        in[t] = lds32(sm.outplane(8 * J + t, lane));
+    subset_table(in[0], in[1], in[2], in[3], T1);
+    subset_table(in[4], in[5], in[6], in[7], T2);
+    enc_acc<W, J>(acc, T1, T2, std::make_integer_sequence<int, 32>{});
+}
+template <int W, int... J>
+__device__ __forceinline__ void enc_all(const Smem &sm, int lane, uint32_t (&acc)[32], std::integer_sequence<int, J...>)
+{
+    (enc_j<W, J>(sm, lane, acc), ...);
+}
+
+// a 4-byte piece of an output row at an arbitrary address
+__device__ __forceinline__ void store_bytes4(uint8_t *p, uint32_t v)
+{
+    if (((uintptr_t)p & 3u) == 0) {
+        *reinterpret_cast<uint32_t *>(p) = v;
+    } else {
+        p[0] = (uint8_t)v;
+        p[1] = (uint8_t)(v >> 8);
+        p[2] = (uint8_t)(v >> 16);
+        p[3] = (uint8_t)(v >> 24);
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
+{
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    Smem sm;
+    sm.base = smem_u32(smem_raw);
+    sm.bars = sm.base;
+    sm.ring = sm.base + kBarBytes;
+    sm.bufs = sm.ring + kRingBytes;
+    sm.bufbytes = A.bufbytes;
+    uint8_t *slab = A.slab + (size_t)blockIdx.x * kSlabBytes;
+    const size_t ntiles = (A.n + kTile - 1) / kTile;
+
+    if (threadIdx.x == 0) {
+        for (int w = 0; w < kWarps; w++) {
+            mbar_init(sm.bar_buf(w, 0), 1);
+            mbar_init(sm.bar_buf(w, 1), 1);
+        }
+        for (int s = 0; s < kRingSlots; s++) {
+            mbar_init(sm.bar_full(s), 1);
+            mbar_init(sm.bar_empty(s), 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // symbols nobody writes are zero: exponents >= size + 32 (shortened code) and, for the encoder, the parity
+    // positions e < 32
+    {
+        const int L = A.size + 32;
+        const uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int e = warp; e < 255; e += kWarps)
+            if (e >= L || (MODE == MODE_ENCODE && e < 32))
+                stg256(slab + (size_t)slot_of((uint32_t)e) * kSlotBytes + (size_t)lane * 32, z);
+    }
+    __syncthreads();
+
+    // sub-tile s of a tile is lane-slot ls = kWarps * s + warp; its buffer is s & 1
+    uint32_t use[2] = {0, 0};     // completed uses of this warp's two buffers (mbarrier phase)
+    uint32_t gtask = 0;           // class tasks handed through the ring so far (ring phase)
+    auto rows_of = [&](size_t tile, int ls) -> int {
+        const size_t cwb = tile * kTile + (size_t)ls * 32;
+        if (cwb >= A.n)
+            return 0;
+        const size_t left = A.n - cwb;
+        return left < 32 ? (int)left : 32;
+    };
+    size_t tile = blockIdx.x;
+    if (tile < ntiles)
+        issue_subtile<MODE>(A, sm.buf(warp, 0), sm.bar_buf(warp, 0), tile * kTile + (size_t)warp * 32, rows_of(tile, warp), lane);
+
+    for (; tile < ntiles; tile += gridDim.x) {
+        // ---------------- phase A ----------------
+#pragma unroll 1
+        for (int s = 0; s < kSubPerWarp; s++) {
+            const int ls = kWarps * s + warp;
+            // next sub-tile (of this tile, or the first one of this CTA's next tile) into the other buffer
+            if (s + 1 < kSubPerWarp) {
+                const int nls = ls + kWarps;
+                issue_subtile<MODE>(A, sm.buf(warp, (s + 1) & 1), sm.bar_buf(warp, (s + 1) & 1), tile * kTile + (size_t)nls * 32,
+                                    rows_of(tile, nls), lane);
+            } else if (tile + gridDim.x < ntiles) {
+                const size_t nt = tile + gridDim.x;
+                issue_subtile<MODE>(A, sm.buf(warp, 0), sm.bar_buf(warp, 0), nt * kTile + (size_t)warp * 32, rows_of(nt, warp), lane);
+            }
+            const int b = s & 1;
+            mbar_wait(sm.bar_buf(warp, b), use[b] & 1u);
+            use[b]++;
+            __syncwarp();
+            transpose_subtile<MODE>(A, sm.buf(warp, b), tile * kTile + (size_t)ls * 32, ls, slab, lane);
+        }
+        __syncthreads(); // the slab is complete
+
+        // ---------------- phase B ----------------
+        uint32_t nz = 0;
+        if (warp < 4) {
+            s1_run(sm, slab, warp, lane, gtask);
+        } else {
+            uint32_t acc[8][8];
+            switch (warp) {
+            case 4:
+                s2_run<0>(sm, lane, gtask, acc);
+                nz = s2_store<MODE, 0>(sm, lane, acc);
+                break;
+            case 5:
+                s2_run<1>(sm, lane, gtask, acc);
+                nz = s2_store<MODE, 1>(sm, lane, acc);
+                break;
+            case 6:
+                s2_run<2>(sm, lane, gtask, acc);
+                nz = s2_store<MODE, 2>(sm, lane, acc);
+                break;
+            default:
+                s2_run<3>(sm, lane, gtask, acc);
+                nz = s2_store<MODE, 3>(sm, lane, acc);
+                break;
+            }
+            if (MODE == MODE_SCREEN)
+                sts32(sm.nzword(warp - 4, lane), nz);
+        }
+        __syncthreads(); // all 256 syndrome planes are in the output stage
+
+        // ---------------- output ----------------
+        const size_t cw0 = tile * kTile + (size_t)lane * 32; // this lane-slot's first codeword
+        uint32_t valid = 0;                                  // bit i: codeword cw0 + i exists
+        if (cw0 < A.n) {
+            const size_t left = A.n - cw0;
+            valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (unsigned)left) - 1u);
+        }
+        if (MODE == MODE_SCREEN) {
+            uint32_t dirty = 0;
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                dirty |= lds32(sm.nzword(u, lane));
+            dirty &= valid;
+            if (warp == 0 && cw0 < A.n)
+                A.dirty[cw0 >> 5] = dirty;
+            if (__any_sync(0xFFFFFFFFu, dirty != 0)) {
+                // syndrome word-column `warp`: S_{4w+1} .. S_{4w+4} of the lane-slot's 32 codewords
+                uint32_t X[32];
+#pragma unroll
+                for (int p = 0; p < 32; p++)
+                    X[p] = lds32(sm.outplane(32 * warp + p, lane));
+                transpose32(X);
+#pragma unroll
+                for (int i = 0; i < 32; i++)
+                    if ((dirty >> i) & 1u)
+                        *reinterpret_cast<uint32_t *>(A.syn + (cw0 + (size_t)i) * 32 + 4 * warp) = X[i];
+            }
+        } else {
+            uint32_t acc[32];
+#pragma unroll
+            for (int p = 0; p < 32; p++)
+                acc[p] = 0;
+            switch (warp) {
+            case 0: enc_all<0>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            case 1: enc_all<1>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            case 2: enc_all<2>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            case 3: enc_all<3>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            case 4: enc_all<4>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            case 5: enc_all<5>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            case 6: enc_all<6>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            default: enc_all<7>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
+            }
+            transpose32(acc); // acc[i] = parity bytes 4w .. 4w+3 of codeword cw0 + i
+#pragma unroll
+            for (int i = 0; i < 32; i++)
+                if ((valid >> i) & 1u)
+                    store_bytes4(A.out_parity + (cw0 + (size_t)i) * A.out_pstride + 4 * warp, acc[i]);
+        }
+        __syncthreads(); // the output stage (buffer 1 of warps 0..3) is free again
+    }
+}
+
+__global__ void __launch_bounds__(256)
+rs255_fft_compact_kernel(const uint32_t *__restrict__ dirty, size_t n, uint32_t *__restrict__ queue,
+                         uint32_t *__restrict__ counter, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+{
+    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t flag = 0;
+    if (cw < n) {
+        flag = (dirty[cw >> 5] >> (cw & 31u)) & 1u;
+        if (!flag) {
+            if (ok)
+                ok[cw] = 1;
+            if (corrected)
+                corrected[cw] = 0;
+        }
+    }
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, flag != 0);
+    if (ballot) {
+        const int lane = threadIdx.x & 31;
+        uint32_t base = 0;
+        if (lane == 0)
+            base = atomicAdd(counter, (uint32_t)__popc(ballot));
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (flag)
+            queue[base + __popc(ballot & ((1u << lane) - 1u))] = (uint32_t)cw | (3u << 30); // both syndrome halves are live
+    }
+}
+
+int smem_bytes(int bufbytes)
+{
+    return kBarBytes + kRingBytes + 2 * kWarps * bufbytes + 64;
+}
+
+} // namespace
+
+bool rs255_fft_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
+                        size_t parity_stride, FftShape *shape)
+{
+    if (size < 1 || size > 223 || data_stride < size)
+        return false;
+    const bool packed = op == 1 && parity == data + size && parity_stride == data_stride;
+    if (packed && data_stride < size + 32)
+        return false;
+    const size_t rowlen = packed ? size + 32 : size;
+    size_t dspan = 31 * data_stride + rowlen + 15 + 8; // + alignment of the span + the funnel's second word
+    dspan = (dspan + 15) & ~(size_t)15;
+    size_t total = dspan, poff = 0;
+    if (op == 1 && !packed) {
+        if (parity_stride < 32)
+            return false;
+        poff = dspan;
+        size_t pspan = 31 * parity_stride + 32 + 15 + 8;
+        pspan = (pspan + 15) & ~(size_t)15;
+        total += pspan;
+    }
+    if (total > (size_t)kMaxBuf)
+        return false;
+    if (shape) {
+        shape->packed = packed ? 1 : 0;
+        shape->bufbytes = (int)(total < 8192 ? 8192 : total); // the output stage borrows buffers: 64 planes x 128 B each
+        shape->poff = (int)poff;
+    }
+    return true;
+}
+
+size_t rs255_fft_slab_bytes(int sm_count)
+{
+    return (size_t)sm_count * kSlabBytes;
+}
+
+int rs255_fft_init(poporon_cuda_rs *ctx)
+{
+    (void)ctx;
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_fft_kernel<MODE_SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     smem_bytes(kMaxBuf)));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_fft_kernel<MODE_ENCODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     smem_bytes(kMaxBuf)));
+    return 0;
+}
+
+static unsigned fft_grid(const poporon_cuda_rs *ctx, size_t n)
+{
+    const size_t tiles = (n + kTile - 1) / kTile;
+    return (unsigned)(tiles < (size_t)ctx->sm_count ? tiles : (size_t)ctx->sm_count);
+}
+
+int rs255_fft_screen(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t *data, size_t data_stride, size_t size,
+                     const uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, uint32_t *dirty,
+                     uint8_t *syn, cudaStream_t stream)
+{
+    FftArgs A{};
+    A.data = data;
+    A.dstride = data_stride;
+    A.size = (int)size;
+    A.parity = parity;
+    A.pstride = parity_stride;
+    A.packed = shape.packed;
+    A.n = n;
+    A.slab = slab;
+    A.bufbytes = shape.bufbytes;
+    A.poff = shape.poff;
+    A.dirty = dirty;
+    A.syn = syn;
+    rs255_fft_kernel<MODE_SCREEN><<<fft_grid(ctx, n), 32 * kWarps, smem_bytes(shape.bufbytes), stream>>>(A);
+    return check(cudaGetLastError(), "rs255 fft screen launch");
+}
+
+int rs255_fft_compact(poporon_cuda_rs *ctx, const uint32_t *dirty, size_t n, uint32_t *queue, uint32_t *counter,
+                      uint8_t *ok, uint32_t *corrected, cudaStream_t stream)
+{
+    (void)ctx;
+    rs255_fft_compact_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(dirty, n, queue, counter, ok, corrected);
+    return check(cudaGetLastError(), "rs255 fft compact launch");
+}
+
+int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t *data, size_t data_stride, size_t size,
+                     uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, cudaStream_t stream)
+{
+    FftArgs A{};
+    A.data = data;
+    A.dstride = data_stride;
+    A.size = (int)size;
+    A.packed = 0;
+    A.n = n;
+    A.slab = slab;
+    A.bufbytes = shape.bufbytes;
+    A.poff = shape.poff;
+    A.out_parity = parity;
+    A.out_pstride = parity_stride;
+    rs255_fft_kernel<MODE_ENCODE><<<fft_grid(ctx, n), 32 * kWarps, smem_bytes(shape.bufbytes), stream>>>(A);
+    return check(cudaGetLastError(), "rs255 fft encode launch");
+}
+
+} // namespace ppcu
