@@ -51,7 +51,7 @@ struct RsCode {
 };
 
 // kernel ids of the per-kernel profile (poporon_cuda_rs_profile_read)
-enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_APPLY, PROF_GENERAL, PROF_GENERIC, PROF_KINDS };
+enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_PARITY, PROF_GENERAL, PROF_GENERIC, PROF_KINDS };
 constexpr int kProfCap = 8192;
 
 static inline int sm_count_of(int device)
@@ -91,6 +91,8 @@ struct poporon_cuda_rs {
     uint32_t *d_counters;     // [0] = dirty count
     size_t queue_cap;
     uint8_t *d_slab;          // rs255_fft: one 255 KB bit-plane slab per SM (allocated on first use)
+    uint32_t *d_synplanes;    // rs255_fft encoder: syndrome planes of the chunk in flight (grow-only)
+    size_t synplane_cap;      // codewords it holds
     int use_lfsr;             // PP_RS255_LFSR=1: the round-1 LFSR kernels instead of the transform kernels (A/B runs)
     // opt-in per-kernel timing (poporon_cuda_rs_profile): CUDA event pairs around each launch
     bool prof_on;

@@ -317,6 +317,7 @@ void poporon_cuda_rs_destroy(poporon_cuda_rs_t *ctx)
     cudaFree(ctx->d_queue);
     cudaFree(ctx->d_rem);
     cudaFree(ctx->d_slab);
+    cudaFree(ctx->d_synplanes);
     cudaFree(ctx->d_counters);
     free(ctx);
 }
@@ -379,9 +380,9 @@ int poporon_cuda_rs_profile_read(poporon_cuda_rs_t *ctx, int kernel, uint64_t *l
 
 const char *poporon_cuda_rs_profile_name(int kernel)
 {
-    static const char *names[PROF_KINDS] = {"rs255_lfsr_kernel<ENCODE>", "rs255_lfsr_kernel<SCREEN>",
-                                            "rs255_compact_kernel",      "rs255_solve_kernel",
-                                            "rs255_apply_kernel",        "rs255_correct_kernel",
+    static const char *names[PROF_KINDS] = {"rs255_fft_kernel<ENCODE>", "rs255_fft_kernel<SCREEN>",
+                                            "rs255_compact_kernel",     "rs255_solve_kernel",
+                                            "rs255_parity_kernel",      "rs255_correct_kernel",
                                             "rs_generic kernels"};
     return kernel >= 0 && kernel < PROF_KINDS ? names[kernel] : NULL;
 }
@@ -391,7 +392,7 @@ int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, int op, const uint8_t *da
 {
     if (!ctx)
         return POPORON_CUDA_ERR_ARG;
-    return (ctx->fast255 && !ctx->force_generic && rs255_shape_ok(op, data, data_stride, size, parity, parity_stride))
+    return (ctx->fast255 && !ctx->force_generic && rs255_shape_ok(ctx, op, data, data_stride, size, parity, parity_stride))
                ? 1
                : 0;
 }

@@ -1185,16 +1185,29 @@ bool rs255_matches(const poporon_cuda_rs_desc_t *d)
     return d->symbol_size == 8 && d->gfpoly == 0x11D && d->fcr == 1 && d->prim == 1 && d->nroots == 32;
 }
 
-bool rs255_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
-                    size_t parity_stride)
+// round-1 LFSR kernels: any message size 1..223; a lane's 32 codewords must be equally aligned inside their 16-byte
+// chunks, which 32 * stride = 0 (mod 16) guarantees for every stride once the base is 16-byte aligned.
+static bool lfsr_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
+                          size_t parity_stride)
 {
-    // Any message size 1..223.  A lane's 32 codewords must be equally aligned inside their 16-byte chunks,
-    // which 32 * stride = 0 (mod 16) guarantees for every stride once the base is 16-byte aligned.
     if (size < 1 || size > (size_t)kMsg || data_stride < size || ((uintptr_t)data & 15u) != 0)
         return false;
     if (op == 1) // the screen kernel reads ONE contiguous stream per codeword: packed records only
         return parity == data + size && parity_stride == data_stride && data_stride <= 0xFFFFFFFFull; // 32-bit stride math
     return true;
+}
+
+// Which batches the bitsliced kernels take.  The transform kernels (rs255_fft.cu) accept any base alignment and
+// the two-pointer shape of the reference API (message rows and parity rows as separate arrays, reference
+// include/poporon.h:90-91) as long as 32 consecutive rows fit a sub-tile buffer; longer strides fall back to the
+// LFSR kernels where those apply (16-byte aligned base, packed records for decode).
+bool rs255_shape_ok(const poporon_cuda_rs *ctx, int op, const uint8_t *data, size_t data_stride, size_t size,
+                    const uint8_t *parity, size_t parity_stride)
+{
+    if (!ctx->use_lfsr && data_stride <= 0xFFFFFFFFull && parity_stride <= 0xFFFFFFFFull &&
+        rs255_fft_shape_ok(op, data, data_stride, size, parity, parity_stride, nullptr))
+        return true;
+    return lfsr_shape_ok(op, data, data_stride, size, parity, parity_stride);
 }
 
 int rs255_init(poporon_cuda_rs *ctx)
@@ -1209,6 +1222,8 @@ int rs255_init(poporon_cuda_rs *ctx)
     ctx->use_lfsr = env && env[0] == '1';
     return rs255_fft_init(ctx);
 }
+
+constexpr size_t kEncChunk = (size_t)16 << 20; // codewords per encoder pass (512 MB of syndrome planes)
 
 static int ensure_slab(poporon_cuda_rs *ctx)
 {
@@ -1253,13 +1268,23 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
         int rc = ensure_slab(ctx);
         if (rc != 0)
             return rc;
+        // the syndrome planes between the two kernels: 32 bytes per codeword, at most kEncChunk codewords at a time
+        const size_t chunk = n < kEncChunk ? n : kEncChunk;
+        if (chunk > ctx->synplane_cap) {
+            cudaFree(ctx->d_synplanes);
+            ctx->d_synplanes = nullptr;
+            ctx->synplane_cap = 0;
+            PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_synplanes, rs255_fft_synplane_bytes(chunk)));
+            ctx->synplane_cap = chunk;
+        }
         if (ok)
             PP_CUDA_TRY(cudaMemsetAsync(ok, 1, n, stream));
-        {
-            ProfScope prof(ctx, PROF_ENCODE, stream);
-            rc = rs255_fft_encode(ctx, shape, data, data_stride, size, parity, parity_stride, n, ctx->d_slab, stream);
+        for (size_t c0 = 0; c0 < n && rc == 0; c0 += chunk) {
+            const size_t m = n - c0 < chunk ? n - c0 : chunk;
+            rc = rs255_fft_encode(ctx, shape, data + c0 * data_stride, data_stride, size, parity + c0 * parity_stride,
+                                  parity_stride, m, ctx->d_slab, ctx->d_synplanes, stream);
+            ctx->launches += 2;
         }
-        ctx->launches++;
         return rc;
     }
     LfsrArgs A{};

@@ -6,8 +6,8 @@ namespace ppcu {
 // true when the described code is exactly the reference's default RS config (src/poporon.c:281-284)
 bool rs255_matches(const poporon_cuda_rs_desc_t *d);
 // shapes the fast path accepts (everything else falls to the generic kernels)
-bool rs255_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
-                    size_t parity_stride);
+bool rs255_shape_ok(const poporon_cuda_rs *ctx, int op, const uint8_t *data, size_t data_stride, size_t size,
+                    const uint8_t *parity, size_t parity_stride);
 int rs255_init(poporon_cuda_rs *ctx);
 int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, size_t size, uint8_t *parity,
                  size_t parity_stride, size_t n, uint8_t *ok, cudaStream_t stream);

@@ -52,7 +52,8 @@ struct FftArgs {
     int size;              // message bytes per codeword, 1..223
     const uint8_t *parity; // SCREEN: parity rows (32 bytes each)
     size_t pstride;
-    int packed;            // SCREEN: parity == data + size with the same stride (one span per sub-tile)
+    int packed;            // SCREEN: parity rows interleaved with the message rows (one stride, one span per sub-tile)
+    int prow_off;          // packed: parity - data (>= size; == size for packed records)
     size_t n;
     uint8_t *slab;         // gridDim.x slabs
     int bufbytes;          // bytes of one sub-tile buffer
@@ -60,9 +61,9 @@ struct FftArgs {
     // SCREEN outputs
     uint32_t *dirty;       // bitmap, bit (cw & 31) of word cw >> 5
     uint8_t *syn;          // [n][32]
-    // ENCODE outputs
-    uint8_t *out_parity;
-    size_t out_pstride;
+    // ENCODE output: the syndromes of message * x^32 as tower planes, [tile][j - 1][lane-slot][8 planes] words
+    // (rs255_parity_kernel turns them into parity rows)
+    uint32_t *synplanes;
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -256,7 +257,7 @@ __device__ __forceinline__ void issue_subtile(const FftArgs &A, uint32_t bufaddr
 {
     __syncwarp(); // every lane is done reading the buffer's previous contents
     uint32_t tx = 0;
-    const int rowlen = (MODE == MODE_SCREEN && A.packed) ? A.size + 32 : A.size;
+    const int rowlen = (MODE == MODE_SCREEN && A.packed) ? A.prow_off + 32 : A.size;
     const uint8_t *g = A.data + cwb * A.dstride;
     const uint32_t a = (uint32_t)((uintptr_t)g & 15u);
     const uint32_t total = rows > 0 ? a + (uint32_t)(rows - 1) * (uint32_t)A.dstride + (uint32_t)rowlen : 0u;
@@ -300,7 +301,7 @@ __device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t buf
     uint32_t pbase, pstr;
     if (MODE == MODE_SCREEN) {
         if (A.packed) {
-            pbase = bufaddr + ad + (uint32_t)A.size;
+            pbase = bufaddr + ad + (uint32_t)A.prow_off;
             pstr = (uint32_t)A.dstride;
         } else {
             pbase = bufaddr + (uint32_t)A.poff + (uint32_t)((uintptr_t)(A.parity + cwb * A.pstride) & 15u);
@@ -457,68 +458,27 @@ __device__ __forceinline__ void s2_run(const Smem &sm, int lane, uint32_t &gtask
     gtask += 17;
 }
 
-// S2 epilogue: dirty mask of the warp's syndromes + planes to the output stage (standard basis for SCREEN, tower
-// planes for ENCODE, whose mask table expects them)
+// S2 epilogue.  SCREEN: dirty mask of the warp's syndromes + their standard-basis planes to the output stage.
+// ENCODE: the tower planes go to the global syndrome-plane array of the tile (32 bytes per lane and syndrome).
 template <int MODE, int U>
-__device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t (&acc)[8][8])
+__device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t (&acc)[8][8], uint32_t *tileplanes)
 {
     uint32_t nz = 0;
 #pragma unroll
     for (int q = 0; q < 8; q++) {
-        uint32_t s[8];
         if (MODE == MODE_SCREEN) {
+            uint32_t s[8];
             rsfft::conv_out(acc[q], s);
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                nz |= s[t];
+                sts32(sm.outplane(8 * (s2_j(U, q) - 1) + t, lane), s[t]);
+            }
         } else {
-#pragma unroll
-            for (int t = 0; t < 8; t++)
-                s[t] = acc[q][t];
-        }
-#pragma unroll
-        for (int t = 0; t < 8; t++) {
-            nz |= s[t];
-            sts32(sm.outplane(8 * (s2_j(U, q) - 1) + t, lane), s[t]);
+            stg256(tileplanes + ((size_t)(s2_j(U, q) - 1) * 32 + (size_t)lane) * 8, acc[q]);
         }
     }
     return nz;
-}
-
-// ENCODE: parity bytes 4w .. 4w+3 (32 planes) from the 32 syndromes in the output stage
-template <int W, int J, int... QU>
-__device__ __forceinline__ void enc_acc(uint32_t (&acc)[32], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
-                                        std::integer_sequence<int, QU...>)
-{
-    ((acc[QU] = xor3(acc[QU], T1[rsfft::EncM::v.m[J][4 * W + (QU >> 3)][QU & 7] & 15],
-                     T2[rsfft::EncM::v.m[J][4 * W + (QU >> 3)][QU & 7] >> 4])),
-     ...);
-}
-template <int W, int J>
-__device__ __forceinline__ void enc_j(const Smem &sm, int lane, uint32_t (&acc)[32])
-{
-    uint32_t in[8], T1[16], T2[16];
-#pragma unroll
-    for (int t = 0; t < 8; t++)
-        in[t] = lds32(sm.outplane(8 * J + t, lane));
-    subset_table(in[0], in[1], in[2], in[3], T1);
-    subset_table(in[4], in[5], in[6], in[7], T2);
-    enc_acc<W, J>(acc, T1, T2, std::make_integer_sequence<int, 32>{});
-}
-template <int W, int... J>
-__device__ __forceinline__ void enc_all(const Smem &sm, int lane, uint32_t (&acc)[32], std::integer_sequence<int, J...>)
-{
-    (enc_j<W, J>(sm, lane, acc), ...);
-}
-
-// a 4-byte piece of an output row at an arbitrary address
-__device__ __forceinline__ void store_bytes4(uint8_t *p, uint32_t v)
-{
-    if (((uintptr_t)p & 3u) == 0) {
-        *reinterpret_cast<uint32_t *>(p) = v;
-    } else {
-        p[0] = (uint8_t)v;
-        p[1] = (uint8_t)(v >> 8);
-        p[2] = (uint8_t)(v >> 16);
-        p[3] = (uint8_t)(v >> 24);
-    }
 }
 
 template <int MODE>
@@ -595,6 +555,7 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
 
         // ---------------- phase B ----------------
         uint32_t nz = 0;
+        uint32_t *tileplanes = MODE == MODE_ENCODE ? A.synplanes + tile * (size_t)(32 * 32 * 8) : nullptr;
         if (warp < 4) {
             s1_run(sm, slab, warp, lane, gtask);
         } else {
@@ -602,34 +563,34 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
             switch (warp) {
             case 4:
                 s2_run<0>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 0>(sm, lane, acc);
+                nz = s2_store<MODE, 0>(sm, lane, acc, tileplanes);
                 break;
             case 5:
                 s2_run<1>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 1>(sm, lane, acc);
+                nz = s2_store<MODE, 1>(sm, lane, acc, tileplanes);
                 break;
             case 6:
                 s2_run<2>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 2>(sm, lane, acc);
+                nz = s2_store<MODE, 2>(sm, lane, acc, tileplanes);
                 break;
             default:
                 s2_run<3>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 3>(sm, lane, acc);
+                nz = s2_store<MODE, 3>(sm, lane, acc, tileplanes);
                 break;
             }
             if (MODE == MODE_SCREEN)
                 sts32(sm.nzword(warp - 4, lane), nz);
         }
-        __syncthreads(); // all 256 syndrome planes are in the output stage
+        __syncthreads(); // S1 is done with the slab; SCREEN: all 256 syndrome planes are in the output stage
 
-        // ---------------- output ----------------
-        const size_t cw0 = tile * kTile + (size_t)lane * 32; // this lane-slot's first codeword
-        uint32_t valid = 0;                                  // bit i: codeword cw0 + i exists
-        if (cw0 < A.n) {
-            const size_t left = A.n - cw0;
-            valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (unsigned)left) - 1u);
-        }
+        // ---------------- output (SCREEN; the encoder's syndromes went to global memory) ----------------
         if (MODE == MODE_SCREEN) {
+            const size_t cw0 = tile * kTile + (size_t)lane * 32; // this lane-slot's first codeword
+            uint32_t valid = 0;                                  // bit i: codeword cw0 + i exists
+            if (cw0 < A.n) {
+                const size_t left = A.n - cw0;
+                valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (unsigned)left) - 1u);
+            }
             uint32_t dirty = 0;
 #pragma unroll
             for (int u = 0; u < 4; u++)
@@ -649,28 +610,141 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
                     if ((dirty >> i) & 1u)
                         *reinterpret_cast<uint32_t *>(A.syn + (cw0 + (size_t)i) * 32 + 4 * warp) = X[i];
             }
-        } else {
-            uint32_t acc[32];
-#pragma unroll
-            for (int p = 0; p < 32; p++)
-                acc[p] = 0;
-            switch (warp) {
-            case 0: enc_all<0>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            case 1: enc_all<1>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            case 2: enc_all<2>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            case 3: enc_all<3>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            case 4: enc_all<4>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            case 5: enc_all<5>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            case 6: enc_all<6>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            default: enc_all<7>(sm, lane, acc, std::make_integer_sequence<int, 32>{}); break;
-            }
-            transpose32(acc); // acc[i] = parity bytes 4w .. 4w+3 of codeword cw0 + i
-#pragma unroll
-            for (int i = 0; i < 32; i++)
-                if ((valid >> i) & 1u)
-                    store_bytes4(A.out_parity + (cw0 + (size_t)i) * A.out_pstride + 4 * warp, acc[i]);
+            __syncthreads(); // the output stage (buffer 1 of warps 0..3) is free again
         }
-        __syncthreads(); // the output stage (buffer 1 of warps 0..3) is free again
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// rs255_parity_kernel: parity rows from the syndrome planes of message * x^32 (replaces the tail of rs_encode,
+// src/encode.c:17-145: the reference divides by g(x); here parity = V^-1 S with V[j][t] = alpha^(j t), a dense
+// 256 x 256 bit matrix applied by four-Russians tables with compile-time masks, rsfft::EncM).
+// The product is ~10 K straight-line instructions (160 KB of code), far beyond the instruction cache, so every
+// instruction should serve as many warps as possible: a warp owns one tile (its 32 lanes = the tile's 32 lane-slots),
+// the eight warps of a CTA run the same stream on eight tiles and meet at a barrier every four syndromes.
+// Two passes of 128 output planes (16 parity bytes); the bytes of a pass are staged in shared memory and leave as
+// contiguous 16-byte pieces (parity rows sit at arbitrary alignment inside packed records).
+// ---------------------------------------------------------------------------------------------------
+constexpr int kParWarps = 8;
+constexpr int kParStageBytes = kTile * 16;             // one pass of one tile
+constexpr int kParSmem = kParWarps * kParStageBytes;
+
+struct ParArgs {
+    const uint32_t *synplanes; // [tile][32][32][8]
+    size_t n, ntiles;
+    uint8_t *parity;
+    size_t pstride;
+};
+
+template <int H, int J, int... QU>
+__device__ __forceinline__ void par_acc(uint32_t (&acc)[128], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
+                                        std::integer_sequence<int, QU...>)
+{
+    ((acc[QU] = xor3(acc[QU], T1[rsfft::EncM::v.m[J][16 * H + (QU >> 3)][QU & 7] & 15],
+                     T2[rsfft::EncM::v.m[J][16 * H + (QU >> 3)][QU & 7] >> 4])),
+     ...);
+}
+template <int H, int J>
+__device__ __forceinline__ void par_j(const uint32_t *tp, int lane, uint32_t (&in)[8], uint32_t (&acc)[128])
+{
+    if constexpr (J < 32) {
+        uint32_t nx[8], T1[16], T2[16];
+        if constexpr (J + 1 < 32) {
+            uint32_t lo[4], hi[4];
+            ldg256(tp + ((size_t)(J + 1) * 32 + (size_t)lane) * 8, lo, hi);
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                nx[t] = lo[t];
+                nx[4 + t] = hi[t];
+            }
+        }
+        subset_table(in[0], in[1], in[2], in[3], T1);
+        subset_table(in[4], in[5], in[6], in[7], T2);
+        par_acc<H, J>(acc, T1, T2, std::make_integer_sequence<int, 128>{});
+        if constexpr ((J & 3) == 3)
+            __syncthreads(); // keeps the CTA's warps on the same stretch of code
+        if constexpr (J + 1 < 32) {
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                in[t] = nx[t];
+            par_j<H, J + 1>(tp, lane, in, acc);
+        }
+    }
+}
+
+// stage slot of codeword (lane-slot ls, index i): 16 bytes; word w of the slot is stored at word w ^ (ls & 3).
+// For a fixed (i, w) the 32 lanes of a store hit 32 different banks.
+__device__ __forceinline__ uint32_t par_slot(uint32_t ls, uint32_t i)
+{
+    return ls * 32u + ((i + (ls >> 2)) & 31u);
+}
+
+template <int H>
+__device__ __forceinline__ void parity_pass(const ParArgs &A, const uint32_t *tp, uint32_t stage, size_t tile, bool active,
+                                            int lane)
+{
+    uint32_t acc[128];
+#pragma unroll
+    for (int p = 0; p < 128; p++)
+        acc[p] = 0;
+    {
+        uint32_t in[8], lo[4], hi[4];
+        ldg256(tp + (size_t)lane * 8, lo, hi);
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            in[t] = lo[t];
+            in[4 + t] = hi[t];
+        }
+        par_j<H, 0>(tp, lane, in, acc);
+    }
+    // planes -> bytes: word-column w of the pass = parity bytes 16 H + 4 w .. + 3 of the lane-slot's 32 codewords
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+        uint32_t X[32];
+#pragma unroll
+        for (int p = 0; p < 32; p++)
+            X[p] = acc[32 * w + p];
+        transpose32(X);
+#pragma unroll
+        for (int i = 0; i < 32; i++)
+            sts32(stage + par_slot((uint32_t)lane, (uint32_t)i) * 16u + (uint32_t)((w ^ (lane & 3)) * 4), X[i]);
+    }
+    __syncwarp();
+    // rows out: two codewords per step, one byte per lane (contiguous 16-byte pieces, coalesced by the LSU)
+    if (active) {
+        const size_t cwt = tile * kTile;
+        const uint32_t left = A.n - cwt >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt);
+        const uint32_t b = (uint32_t)lane & 15u, half = (uint32_t)lane >> 4;
+#pragma unroll 4
+        for (uint32_t r0 = 0; r0 < (uint32_t)kTile; r0 += 2) {
+            const uint32_t r = r0 + half;
+            const uint32_t ls = r >> 5, i = r & 31u;
+            uint32_t v;
+            asm volatile("ld.shared.u8 %0, [%1];"
+                         : "=r"(v)
+                         : "r"(stage + par_slot(ls, i) * 16u + ((((b >> 2) ^ (ls & 3u)) << 2) | (b & 3u))));
+            if (r < left)
+                A.parity[(cwt + r) * A.pstride + 16 * H + b] = (uint8_t)v;
+        }
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(32 * kParWarps, 1) rs255_parity_kernel(ParArgs A)
+{
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t stage = smem_u32(smem_raw) + (uint32_t)(warp * kParStageBytes);
+    const size_t per_round = (size_t)gridDim.x * kParWarps;
+    const size_t rounds = (A.ntiles + per_round - 1) / per_round;
+    for (size_t it = 0; it < rounds; it++) {
+        size_t tile = it * per_round + (size_t)blockIdx.x * kParWarps + (size_t)warp;
+        const bool active = tile < A.ntiles;
+        if (!active)
+            tile = A.ntiles - 1; // walks through the barriers on a tile that exists, stores nothing
+        const uint32_t *tp = A.synplanes + tile * (size_t)(32 * 32 * 8);
+        parity_pass<0>(A, tp, stage, tile, active, lane);
+        parity_pass<1>(A, tp, stage, tile, active, lane);
     }
 }
 
@@ -713,10 +787,11 @@ bool rs255_fft_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t 
 {
     if (size < 1 || size > 223 || data_stride < size)
         return false;
-    const bool packed = op == 1 && parity == data + size && parity_stride == data_stride;
-    if (packed && data_stride < size + 32)
-        return false;
-    const size_t rowlen = packed ? size + 32 : size;
+    // "packed": every parity row sits between its message row and the next one (packed 255-byte records are the
+    // case parity == data + size); the sub-tile is then one span
+    const bool packed = op == 1 && parity_stride == data_stride && parity >= data + size &&
+                        (size_t)(parity - data) + 32 <= data_stride;
+    const size_t rowlen = packed ? (size_t)(parity - data) + 32 : size;
     size_t dspan = 31 * data_stride + rowlen + 15 + 8; // + alignment of the span + the funnel's second word
     dspan = (dspan + 15) & ~(size_t)15;
     size_t total = dspan, poff = 0;
@@ -732,6 +807,7 @@ bool rs255_fft_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t 
         return false;
     if (shape) {
         shape->packed = packed ? 1 : 0;
+        shape->prow_off = packed ? (int)(parity - data) : 0;
         shape->bufbytes = (int)(total < 8192 ? 8192 : total); // the output stage borrows buffers: 64 planes x 128 B each
         shape->poff = (int)poff;
     }
@@ -750,6 +826,7 @@ int rs255_fft_init(poporon_cuda_rs *ctx)
                                      smem_bytes(kMaxBuf)));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_fft_kernel<MODE_ENCODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      smem_bytes(kMaxBuf)));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_parity_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kParSmem));
     return 0;
 }
 
@@ -770,6 +847,7 @@ int rs255_fft_screen(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     A.parity = parity;
     A.pstride = parity_stride;
     A.packed = shape.packed;
+    A.prow_off = shape.prow_off;
     A.n = n;
     A.slab = slab;
     A.bufbytes = shape.bufbytes;
@@ -788,8 +866,14 @@ int rs255_fft_compact(poporon_cuda_rs *ctx, const uint32_t *dirty, size_t n, uin
     return check(cudaGetLastError(), "rs255 fft compact launch");
 }
 
+size_t rs255_fft_synplane_bytes(size_t n)
+{
+    return ((n + kTile - 1) / kTile) * (size_t)(32 * 32 * 8 * 4);
+}
+
 int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t *data, size_t data_stride, size_t size,
-                     uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, cudaStream_t stream)
+                     uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, uint32_t *synplanes,
+                     cudaStream_t stream)
 {
     FftArgs A{};
     A.data = data;
@@ -800,10 +884,26 @@ int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     A.slab = slab;
     A.bufbytes = shape.bufbytes;
     A.poff = shape.poff;
-    A.out_parity = parity;
-    A.out_pstride = parity_stride;
-    rs255_fft_kernel<MODE_ENCODE><<<fft_grid(ctx, n), 32 * kWarps, smem_bytes(shape.bufbytes), stream>>>(A);
-    return check(cudaGetLastError(), "rs255 fft encode launch");
+    A.synplanes = synplanes;
+    int rc;
+    {
+        ProfScope prof(ctx, PROF_ENCODE, stream);
+        rs255_fft_kernel<MODE_ENCODE><<<fft_grid(ctx, n), 32 * kWarps, smem_bytes(shape.bufbytes), stream>>>(A);
+        rc = check(cudaGetLastError(), "rs255 fft encode launch");
+    }
+    if (rc != 0)
+        return rc;
+    ParArgs P{};
+    P.synplanes = synplanes;
+    P.n = n;
+    P.ntiles = (n + kTile - 1) / kTile;
+    P.parity = parity;
+    P.pstride = parity_stride;
+    const size_t ctas = (P.ntiles + kParWarps - 1) / kParWarps;
+    ProfScope prof(ctx, PROF_PARITY, stream);
+    rs255_parity_kernel<<<(unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count), 32 * kParWarps, kParSmem,
+                          stream>>>(P);
+    return check(cudaGetLastError(), "rs255 parity launch");
 }
 
 } // namespace ppcu

@@ -4,7 +4,8 @@
 
 namespace ppcu {
 struct FftShape {
-    int packed;   // SCREEN: parity rows follow the message rows in one span (parity == data + size, one stride)
+    int packed;   // SCREEN: parity rows interleaved with the message rows (one stride): one span per sub-tile
+    int prow_off; // packed: parity - data
     int bufbytes; // shared-memory bytes of one 32-codeword sub-tile
     int poff;     // offset of the parity span in a sub-tile buffer (split layout)
 };
@@ -20,6 +21,9 @@ int rs255_fft_screen(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
                      uint8_t *syn, cudaStream_t stream);
 int rs255_fft_compact(poporon_cuda_rs *ctx, const uint32_t *dirty, size_t n, uint32_t *queue, uint32_t *counter,
                       uint8_t *ok, uint32_t *corrected, cudaStream_t stream);
+// synplanes: scratch of rs255_fft_synplane_bytes(n) bytes (the syndromes of message * x^32, tower planes)
+size_t rs255_fft_synplane_bytes(size_t n);
 int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t *data, size_t data_stride, size_t size,
-                     uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, cudaStream_t stream);
+                     uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, uint32_t *synplanes,
+                     cudaStream_t stream);
 } // namespace ppcu
