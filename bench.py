@@ -352,6 +352,7 @@ def run_ours(args):
         # the 32 B per codeword of planes between them are implementation traffic, not algorithmic bytes
         "rs255_fft_kernel<ENCODE>": n * K_MSG,
         "rs255_parity_kernel": n * K_PAR,
+        "rs255_rows_kernel": n * K_PAR,
         "rs255_fft_kernel<SCREEN>": n * (K_CW + 0.25 + 32 * dirty_frac),
         "rs255_compact_kernel": n * (0.25 + 5 + 4 * dirty_frac),
         # queue entry + syndrome row + status per dirty codeword; error record (2 B) + read-modify-write of the

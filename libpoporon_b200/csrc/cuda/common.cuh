@@ -51,7 +51,7 @@ struct RsCode {
 };
 
 // kernel ids of the per-kernel profile (poporon_cuda_rs_profile_read)
-enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_PARITY, PROF_GENERAL, PROF_GENERIC, PROF_KINDS };
+enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_PARITY, PROF_GENERAL, PROF_GENERIC, PROF_ROWS, PROF_KINDS };
 constexpr int kProfCap = 8192;
 
 static inline int sm_count_of(int device)
@@ -99,8 +99,8 @@ struct poporon_cuda_rs {
     int prof_used;
     cudaEvent_t *prof_ev;     // [2 * kProfCap]
     uint8_t *prof_id;         // [kProfCap]
-    double prof_ms[8];
-    uint64_t prof_n[8];
+    double prof_ms[ppcu::PROF_KINDS];
+    uint64_t prof_n[ppcu::PROF_KINDS];
 };
 
 struct poporon_cuda_bch {

@@ -1223,7 +1223,7 @@ int rs255_init(poporon_cuda_rs *ctx)
     return rs255_fft_init(ctx);
 }
 
-constexpr size_t kEncChunk = (size_t)16 << 20; // codewords per encoder pass (512 MB of syndrome planes)
+constexpr size_t kEncChunk = (size_t)16 << 20; // codewords per encoder pass (2 x 512 MB of syndrome / parity planes)
 
 static int ensure_slab(poporon_cuda_rs *ctx)
 {
@@ -1283,7 +1283,7 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
             const size_t m = n - c0 < chunk ? n - c0 : chunk;
             rc = rs255_fft_encode(ctx, shape, data + c0 * data_stride, data_stride, size, parity + c0 * parity_stride,
                                   parity_stride, m, ctx->d_slab, ctx->d_synplanes, stream);
-            ctx->launches += 2;
+            ctx->launches += 3;
         }
         return rc;
     }

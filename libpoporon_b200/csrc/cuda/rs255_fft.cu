@@ -555,7 +555,7 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
 
         // ---------------- phase B ----------------
         uint32_t nz = 0;
-        uint32_t *tileplanes = MODE == MODE_ENCODE ? A.synplanes + tile * (size_t)(32 * 32 * 8) : nullptr;
+        uint32_t *tileplanes = MODE == MODE_ENCODE ? A.synplanes + tile * (size_t)(32 * 32 * 8) : nullptr; // kTilePlaneWords
         if (warp < 4) {
             s1_run(sm, slab, warp, lane, gtask);
         } else {
@@ -616,36 +616,46 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
 }
 
 // ---------------------------------------------------------------------------------------------------
-// rs255_parity_kernel: parity rows from the syndrome planes of message * x^32 (replaces the tail of rs_encode,
-// src/encode.c:17-145: the reference divides by g(x); here parity = V^-1 S with V[j][t] = alpha^(j t), a dense
-// 256 x 256 bit matrix applied by four-Russians tables with compile-time masks, rsfft::EncM).
-// The product is ~10 K straight-line instructions (160 KB of code), far beyond the instruction cache, so every
-// instruction should serve as many warps as possible: a warp owns one tile (its 32 lanes = the tile's 32 lane-slots),
-// the eight warps of a CTA run the same stream on eight tiles and meet at a barrier every four syndromes.
-// Two passes of 128 output planes (16 parity bytes); the bytes of a pass are staged in shared memory and leave as
-// contiguous 16-byte pieces (parity rows sit at arbitrary alignment inside packed records).
+// The tail of the encoder (replaces the rest of rs_encode, src/encode.c:17-145: the reference divides by g(x);
+// here parity = V^-1 S with V[j][t] = alpha^(j t)) in two kernels:
+//
+// rs255_parity_kernel   the dense 256 x 256 bit matrix V^-1 applied to the syndrome planes by four-Russians tables
+//     with compile-time masks (rsfft::EncM).  The product is ~12 K straight-line instructions (190 KB of code), far
+//     beyond the instruction cache, and cold code is fetched at about one 128-byte line per 150 cycles whatever
+//     the number of warps (measured: 0.43 warp-instructions per clock and SM with 8 warps, profiles/r02_*): every
+//     fetched instruction must serve as many warps as possible.  So a warp owns one tile (its 32 lanes = the tile's
+//     32 lane-slots), the SIXTEEN warps of a CTA run the same stream on sixteen tiles (128 registers each: four
+//     passes of 64 output planes) and meet at a barrier every four syndromes.  Output: parity bit-planes,
+//     [tile][plane / 4][lane-slot][plane % 4] words, plane = 8 * byte + bit (byte in memory order).
+// rs255_rows_kernel     planes -> bytes (32 x 32 bit transposes), staged per tile in shared memory as 32-byte rows
+//     and written to the parity rows, which sit at arbitrary alignment inside packed records: four rows of the same
+//     alignment class per step, one aligned 32-bit word per lane (head and tail of a misaligned row as bytes).
 // ---------------------------------------------------------------------------------------------------
-constexpr int kParWarps = 8;
-constexpr int kParStageBytes = kTile * 16;             // one pass of one tile
-constexpr int kParSmem = kParWarps * kParStageBytes;
+constexpr int kParWarps = 16;
+constexpr int kParPlanes = 64;                         // output planes per pass
+constexpr int kParPasses = 256 / kParPlanes;
+constexpr size_t kTilePlaneWords = 32 * 32 * 8;        // one tile of syndrome planes / parity planes
 
 struct ParArgs {
     const uint32_t *synplanes; // [tile][32][32][8]
-    size_t n, ntiles;
-    uint8_t *parity;
-    size_t pstride;
+    uint32_t *parplanes;       // [tile][64][32][4]
+    size_t ntiles;
 };
 
+template <int H, int J, int QU>
+__device__ __forceinline__ void par_one(uint32_t (&acc)[kParPlanes], const uint32_t (&T1)[16], const uint32_t (&T2)[16])
+{
+    constexpr unsigned m = rsfft::EncM::v.m[J][(kParPlanes / 8) * H + (QU >> 3)][QU & 7];
+    acc[QU] = xor3(acc[QU], T1[m & 15], T2[m >> 4]);
+}
 template <int H, int J, int... QU>
-__device__ __forceinline__ void par_acc(uint32_t (&acc)[128], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
+__device__ __forceinline__ void par_acc(uint32_t (&acc)[kParPlanes], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
                                         std::integer_sequence<int, QU...>)
 {
-    ((acc[QU] = xor3(acc[QU], T1[rsfft::EncM::v.m[J][16 * H + (QU >> 3)][QU & 7] & 15],
-                     T2[rsfft::EncM::v.m[J][16 * H + (QU >> 3)][QU & 7] >> 4])),
-     ...);
+    (par_one<H, J, QU>(acc, T1, T2), ...);
 }
 template <int H, int J>
-__device__ __forceinline__ void par_j(const uint32_t *tp, int lane, uint32_t (&in)[8], uint32_t (&acc)[128])
+__device__ __forceinline__ void par_j(const uint32_t *tp, int lane, uint32_t (&in)[8], uint32_t (&acc)[kParPlanes])
 {
     if constexpr (J < 32) {
         uint32_t nx[8], T1[16], T2[16];
@@ -660,7 +670,7 @@ __device__ __forceinline__ void par_j(const uint32_t *tp, int lane, uint32_t (&i
         }
         subset_table(in[0], in[1], in[2], in[3], T1);
         subset_table(in[4], in[5], in[6], in[7], T2);
-        par_acc<H, J>(acc, T1, T2, std::make_integer_sequence<int, 128>{});
+        par_acc<H, J>(acc, T1, T2, std::make_integer_sequence<int, kParPlanes>{});
         if constexpr ((J & 3) == 3)
             __syncthreads(); // keeps the CTA's warps on the same stretch of code
         if constexpr (J + 1 < 32) {
@@ -672,20 +682,12 @@ __device__ __forceinline__ void par_j(const uint32_t *tp, int lane, uint32_t (&i
     }
 }
 
-// stage slot of codeword (lane-slot ls, index i): 16 bytes; word w of the slot is stored at word w ^ (ls & 3).
-// For a fixed (i, w) the 32 lanes of a store hit 32 different banks.
-__device__ __forceinline__ uint32_t par_slot(uint32_t ls, uint32_t i)
-{
-    return ls * 32u + ((i + (ls >> 2)) & 31u);
-}
-
 template <int H>
-__device__ __forceinline__ void parity_pass(const ParArgs &A, const uint32_t *tp, uint32_t stage, size_t tile, bool active,
-                                            int lane)
+__device__ __forceinline__ void parity_pass(const uint32_t *tp, uint32_t *op, bool active, int lane)
 {
-    uint32_t acc[128];
+    uint32_t acc[kParPlanes];
 #pragma unroll
-    for (int p = 0; p < 128; p++)
+    for (int p = 0; p < kParPlanes; p++)
         acc[p] = 0;
     {
         uint32_t in[8], lo[4], hi[4];
@@ -697,44 +699,23 @@ __device__ __forceinline__ void parity_pass(const ParArgs &A, const uint32_t *tp
         }
         par_j<H, 0>(tp, lane, in, acc);
     }
-    // planes -> bytes: word-column w of the pass = parity bytes 16 H + 4 w .. + 3 of the lane-slot's 32 codewords
-#pragma unroll
-    for (int w = 0; w < 4; w++) {
-        uint32_t X[32];
-#pragma unroll
-        for (int p = 0; p < 32; p++)
-            X[p] = acc[32 * w + p];
-        transpose32(X);
-#pragma unroll
-        for (int i = 0; i < 32; i++)
-            sts32(stage + par_slot((uint32_t)lane, (uint32_t)i) * 16u + (uint32_t)((w ^ (lane & 3)) * 4), X[i]);
-    }
-    __syncwarp();
-    // rows out: two codewords per step, one byte per lane (contiguous 16-byte pieces, coalesced by the LSU)
     if (active) {
-        const size_t cwt = tile * kTile;
-        const uint32_t left = A.n - cwt >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt);
-        const uint32_t b = (uint32_t)lane & 15u, half = (uint32_t)lane >> 4;
-#pragma unroll 4
-        for (uint32_t r0 = 0; r0 < (uint32_t)kTile; r0 += 2) {
-            const uint32_t r = r0 + half;
-            const uint32_t ls = r >> 5, i = r & 31u;
-            uint32_t v;
-            asm volatile("ld.shared.u8 %0, [%1];"
-                         : "=r"(v)
-                         : "r"(stage + par_slot(ls, i) * 16u + ((((b >> 2) ^ (ls & 3u)) << 2) | (b & 3u))));
-            if (r < left)
-                A.parity[(cwt + r) * A.pstride + 16 * H + b] = (uint8_t)v;
-        }
+#pragma unroll
+        for (int q = 0; q < kParPlanes / 4; q++)
+            *reinterpret_cast<uint4 *>(op + ((size_t)((kParPlanes / 4) * H + q) * 32 + (size_t)lane) * 4) =
+                make_uint4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
     }
-    __syncwarp();
+}
+template <int... H>
+__device__ __forceinline__ void parity_passes(const uint32_t *tp, uint32_t *op, bool active, int lane,
+                                              std::integer_sequence<int, H...>)
+{
+    (parity_pass<H>(tp, op, active, lane), ...);
 }
 
 __global__ void __launch_bounds__(32 * kParWarps, 1) rs255_parity_kernel(ParArgs A)
 {
-    extern __shared__ __align__(128) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t stage = smem_u32(smem_raw) + (uint32_t)(warp * kParStageBytes);
     const size_t per_round = (size_t)gridDim.x * kParWarps;
     const size_t rounds = (A.ntiles + per_round - 1) / per_round;
     for (size_t it = 0; it < rounds; it++) {
@@ -742,9 +723,105 @@ __global__ void __launch_bounds__(32 * kParWarps, 1) rs255_parity_kernel(ParArgs
         const bool active = tile < A.ntiles;
         if (!active)
             tile = A.ntiles - 1; // walks through the barriers on a tile that exists, stores nothing
-        const uint32_t *tp = A.synplanes + tile * (size_t)(32 * 32 * 8);
-        parity_pass<0>(A, tp, stage, tile, active, lane);
-        parity_pass<1>(A, tp, stage, tile, active, lane);
+        parity_passes(A.synplanes + tile * kTilePlaneWords, A.parplanes + tile * kTilePlaneWords, active, lane,
+                      std::make_integer_sequence<int, kParPasses>{});
+    }
+}
+
+constexpr int kRowWarps = 6;
+constexpr int kRowStageBytes = kTile * 32; // the 32-byte parity rows of one tile
+constexpr int kRowSmem = kRowWarps * kRowStageBytes;
+
+struct RowArgs {
+    const uint32_t *parplanes;
+    size_t n, ntiles;
+    uint8_t *parity;
+    size_t pstride;
+};
+
+// stage word of (lane-slot ls, codeword i of the slot, word w of its row): rows of 8 words, the row of (ls, i) in
+// slot ls * 32 + ((i + (ls >> 3)) & 31), word w at position (w ^ ls) & 7: for a fixed (i, w) the 32 lanes of a
+// store hit 32 different banks (bank = 8 * (slot mod 4) + position).
+__device__ __forceinline__ uint32_t row_word(uint32_t ls, uint32_t i, uint32_t w)
+{
+    return ((ls * 32u + ((i + (ls >> 3)) & 31u)) * 8u + ((w ^ ls) & 7u)) * 4u;
+}
+
+__global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A)
+{
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t stage = smem_u32(smem_raw) + (uint32_t)(warp * kRowStageBytes);
+    for (size_t tile = (size_t)blockIdx.x * kRowWarps + (size_t)warp; tile < A.ntiles; tile += (size_t)gridDim.x * kRowWarps) {
+        const uint32_t *pp = A.parplanes + tile * kTilePlaneWords;
+        // planes -> bytes: word-column w = parity bytes 4 w .. 4 w + 3 of the lane-slot's 32 codewords
+#pragma unroll 1
+        for (int w = 0; w < 8; w++) {
+            uint32_t X[32];
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * w + q) * 32 + (size_t)lane) * 4);
+                X[4 * q] = v.x;
+                X[4 * q + 1] = v.y;
+                X[4 * q + 2] = v.z;
+                X[4 * q + 3] = v.w;
+            }
+            transpose32(X);
+#pragma unroll
+            for (int i = 0; i < 32; i++)
+                sts32(stage + row_word((uint32_t)lane, (uint32_t)i, (uint32_t)w), X[i]);
+        }
+        __syncwarp();
+        // rows out.  Lane = (row rr of four, word k of eight); the four rows of a step are r = 4 (4 it + rr) + c for a
+        // class c = r mod 4, so that their alignment a = address mod 4 is the same (r * pstride mod 4 depends on
+        // r mod 4 only) and every branch below is uniform.
+        const size_t cwt = tile * kTile;
+        const uint32_t left = A.n - cwt >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt);
+        const uint32_t rr = (uint32_t)lane >> 3, k = (uint32_t)lane & 7u;
+#pragma unroll 1
+        for (uint32_t c = 0; c < 4; c++) {
+            const uint32_t a = (uint32_t)(((uintptr_t)A.parity + (cwt + c) * A.pstride) & 3u);
+            const uint32_t sel = 0x3210u + 0x1111u * (4u - a); // bytes 4 - a .. 7 - a of (previous word, this word)
+#pragma unroll 2
+            for (uint32_t it = 0; it < 64; it++) {
+                const uint32_t r = 4u * (4u * it + rr) + c;
+                const uint32_t ls = r >> 5, i = r & 31u;
+                const uint32_t cur = lds32(stage + row_word(ls, i, k));
+                const uint32_t prv = lds32(stage + row_word(ls, i, (k + 7u) & 7u)); // k = 0: unused bytes
+                if (r < left) {
+                    uint8_t *row = A.parity + (cwt + r) * A.pstride;
+                    if (a == 0) {
+                        *reinterpret_cast<uint32_t *>(row + 4 * k) = cur;
+                    } else {
+                        uint8_t *g = row - a + 4 * k; // aligned word k of the row's span: row bytes 4 k - a .. 4 k - a + 3
+                        if (k != 0) {
+                            *reinterpret_cast<uint32_t *>(g) = __byte_perm(prv, cur, sel);
+                        } else { // head: row bytes 0 .. 3 - a
+                            if (a == 1) {
+                                g[1] = (uint8_t)cur;
+                                *reinterpret_cast<uint16_t *>(g + 2) = (uint16_t)(cur >> 8);
+                            } else if (a == 2) {
+                                *reinterpret_cast<uint16_t *>(g + 2) = (uint16_t)cur;
+                            } else {
+                                g[3] = (uint8_t)cur;
+                            }
+                        }
+                        if (k == 7) { // tail: row bytes 32 - a .. 31 = the top a bytes of word 7
+                            uint8_t *t = row - a + 32;
+                            if (a == 1) {
+                                t[0] = (uint8_t)(cur >> 24);
+                            } else if (a == 2) {
+                                *reinterpret_cast<uint16_t *>(t) = (uint16_t)(cur >> 16);
+                            } else {
+                                *reinterpret_cast<uint16_t *>(t) = (uint16_t)(cur >> 8);
+                                t[2] = (uint8_t)(cur >> 24);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -826,7 +903,7 @@ int rs255_fft_init(poporon_cuda_rs *ctx)
                                      smem_bytes(kMaxBuf)));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_fft_kernel<MODE_ENCODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      smem_bytes(kMaxBuf)));
-    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_parity_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kParSmem));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRowSmem));
     return 0;
 }
 
@@ -868,7 +945,7 @@ int rs255_fft_compact(poporon_cuda_rs *ctx, const uint32_t *dirty, size_t n, uin
 
 size_t rs255_fft_synplane_bytes(size_t n)
 {
-    return ((n + kTile - 1) / kTile) * (size_t)(32 * 32 * 8 * 4);
+    return 2 * ((n + kTile - 1) / kTile) * kTilePlaneWords * 4; // syndrome planes + parity planes
 }
 
 int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t *data, size_t data_stride, size_t size,
@@ -893,17 +970,32 @@ int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     }
     if (rc != 0)
         return rc;
-    ParArgs P{};
-    P.synplanes = synplanes;
-    P.n = n;
-    P.ntiles = (n + kTile - 1) / kTile;
-    P.parity = parity;
-    P.pstride = parity_stride;
-    const size_t ctas = (P.ntiles + kParWarps - 1) / kParWarps;
-    ProfScope prof(ctx, PROF_PARITY, stream);
-    rs255_parity_kernel<<<(unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count), 32 * kParWarps, kParSmem,
-                          stream>>>(P);
-    return check(cudaGetLastError(), "rs255 parity launch");
+    const size_t ntiles = (n + kTile - 1) / kTile;
+    uint32_t *parplanes = synplanes + ntiles * kTilePlaneWords;
+    {
+        ParArgs P{};
+        P.synplanes = synplanes;
+        P.parplanes = parplanes;
+        P.ntiles = ntiles;
+        const size_t ctas = (ntiles + kParWarps - 1) / kParWarps;
+        ProfScope prof(ctx, PROF_PARITY, stream);
+        rs255_parity_kernel<<<(unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count), 32 * kParWarps, 0,
+                              stream>>>(P);
+        rc = check(cudaGetLastError(), "rs255 parity launch");
+    }
+    if (rc != 0)
+        return rc;
+    RowArgs R{};
+    R.parplanes = parplanes;
+    R.n = n;
+    R.ntiles = ntiles;
+    R.parity = parity;
+    R.pstride = parity_stride;
+    const size_t ctas = (ntiles + kRowWarps - 1) / kRowWarps;
+    ProfScope prof(ctx, PROF_ROWS, stream);
+    rs255_rows_kernel<<<(unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count), 32 * kRowWarps, kRowSmem,
+                        stream>>>(R);
+    return check(cudaGetLastError(), "rs255 rows launch");
 }
 
 } // namespace ppcu
