@@ -25,6 +25,8 @@
 //            parity rows.
 #include "rs255_fft.cuh"
 
+#include <stdlib.h>
+
 #include <utility>
 
 #include "rs255_fft_gen.cuh"
@@ -728,7 +730,7 @@ __global__ void __launch_bounds__(32 * kParWarps, 1) rs255_parity_kernel(ParArgs
     }
 }
 
-constexpr int kRowWarps = 6;
+constexpr int kRowWarps = 7;
 constexpr int kRowStageBytes = kTile * 32; // the 32-byte parity rows of one tile
 constexpr int kRowSmem = kRowWarps * kRowStageBytes;
 
@@ -739,12 +741,14 @@ struct RowArgs {
     size_t pstride;
 };
 
-// stage word of (lane-slot ls, codeword i of the slot, word w of its row): rows of 8 words, the row of (ls, i) in
-// slot ls * 32 + ((i + (ls >> 3)) & 31), word w at position (w ^ ls) & 7: for a fixed (i, w) the 32 lanes of a
-// store hit 32 different banks (bank = 8 * (slot mod 4) + position).
+// stage word of (lane-slot ls, codeword i of the slot, word w of its row): rows of 8 words; the row of (ls, i) in
+// slot ls * 32 + sigma with sigma mod 4 = ((i >> 2) + (ls >> 3)) mod 4, word w at position (w ^ ls) & 7.  Bank =
+// 8 * (sigma mod 4) + position: the 32 lanes of a store (fixed i, w) hit 32 different banks, and so do the loads of
+// the rows i, i + 4, i + 8, i + 12 of one lane-slot (the four rows of a copy-out step).
 __device__ __forceinline__ uint32_t row_word(uint32_t ls, uint32_t i, uint32_t w)
 {
-    return ((ls * 32u + ((i + (ls >> 3)) & 31u)) * 8u + ((w ^ ls) & 7u)) * 4u;
+    const uint32_t sigma = (((i >> 2) + (ls >> 3)) & 3u) | ((i & 3u) << 2) | (i & 16u);
+    return ((ls * 32u + sigma) * 8u + ((w ^ ls) & 7u)) * 4u;
 }
 
 __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A)
@@ -754,17 +758,31 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
     const uint32_t stage = smem_u32(smem_raw) + (uint32_t)(warp * kRowStageBytes);
     for (size_t tile = (size_t)blockIdx.x * kRowWarps + (size_t)warp; tile < A.ntiles; tile += (size_t)gridDim.x * kRowWarps) {
         const uint32_t *pp = A.parplanes + tile * kTilePlaneWords;
-        // planes -> bytes: word-column w = parity bytes 4 w .. 4 w + 3 of the lane-slot's 32 codewords
+        // planes -> bytes: word-column w = parity bytes 4 w .. 4 w + 3 of the lane-slot's 32 codewords.  The planes of
+        // columns w + 1 .. w + 3 are in flight while column w is transposed (one transpose is ~0.5 us, a DRAM read
+        // under load more than 1 us, and a CTA has only six warps to hide it behind).
+        uint4 nx[3][8];
+#pragma unroll
+        for (int d = 0; d < 3; d++)
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                nx[d][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * d + q) * 32 + (size_t)lane) * 4);
 #pragma unroll 1
         for (int w = 0; w < 8; w++) {
             uint32_t X[32];
 #pragma unroll
             for (int q = 0; q < 8; q++) {
-                const uint4 v = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * w + q) * 32 + (size_t)lane) * 4);
-                X[4 * q] = v.x;
-                X[4 * q + 1] = v.y;
-                X[4 * q + 2] = v.z;
-                X[4 * q + 3] = v.w;
+                X[4 * q] = nx[0][q].x;
+                X[4 * q + 1] = nx[0][q].y;
+                X[4 * q + 2] = nx[0][q].z;
+                X[4 * q + 3] = nx[0][q].w;
+            }
+            const int wn = w + 3 < 8 ? w + 3 : 7;
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                nx[0][q] = nx[1][q];
+                nx[1][q] = nx[2][q];
+                nx[2][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * wn + q) * 32 + (size_t)lane) * 4);
             }
             transpose32(X);
 #pragma unroll
@@ -772,9 +790,15 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
                 sts32(stage + row_word((uint32_t)lane, (uint32_t)i, (uint32_t)w), X[i]);
         }
         __syncwarp();
-        // rows out.  Lane = (row rr of four, word k of eight); the four rows of a step are r = 4 (4 it + rr) + c for a
-        // class c = r mod 4, so that their alignment a = address mod 4 is the same (r * pstride mod 4 depends on
-        // r mod 4 only) and every branch below is uniform.
+        // rows out.  A parity row inside a packed record covers two 32-byte sectors partially; the L2 merges partial
+        // writes (a fill from DRAM per sector), which costs 3.4x the time of aligned contiguous rows (0.34 against
+        // 0.10 ms per 4 Mi rows, tools/enc_probe.py).  Tried and slower: merging in the SM by read-modify-write of
+        // the two-sector window (0.59 ms), prefetching the sectors into the L2 first (0.40 ms), head/tail bytes in a
+        // loop of their own (0.33 -> 0.34 ms: the partial writes of a sector should follow each other closely).
+        // Rows of a class c = r mod 4 have the same alignment a = address mod 4 (r * pstride mod 4 depends on r mod 4
+        // only), so a is uniform over a step.  Lane = (row rr of four consecutive rows of the class, word k of eight):
+        // one aligned 32-bit word per lane, its bytes picked from (previous word, this word) by one PRMT; the head
+        // of a misaligned row leaves from lane k = 0, its tail from lane k = 7, as bytes.
         const size_t cwt = tile * kTile;
         const uint32_t left = A.n - cwt >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt);
         const uint32_t rr = (uint32_t)lane >> 3, k = (uint32_t)lane & 7u;
@@ -782,40 +806,42 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
         for (uint32_t c = 0; c < 4; c++) {
             const uint32_t a = (uint32_t)(((uintptr_t)A.parity + (cwt + c) * A.pstride) & 3u);
             const uint32_t sel = 0x3210u + 0x1111u * (4u - a); // bytes 4 - a .. 7 - a of (previous word, this word)
-#pragma unroll 2
-            for (uint32_t it = 0; it < 64; it++) {
-                const uint32_t r = 4u * (4u * it + rr) + c;
-                const uint32_t ls = r >> 5, i = r & 31u;
-                const uint32_t cur = lds32(stage + row_word(ls, i, k));
-                const uint32_t prv = lds32(stage + row_word(ls, i, (k + 7u) & 7u)); // k = 0: unused bytes
-                if (r < left) {
+            const bool inner = a == 0 || k != 0;
+#pragma unroll 1
+            for (uint32_t it0 = 0; it0 < 64; it0 += 8) {
+                uint32_t cur[8], prv[8];
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++) { // all sixteen loads first, then the stores
+                    const uint32_t r = 4u * (4u * (it0 + u) + rr) + c;
+                    cur[u] = lds32(stage + row_word(r >> 5, r & 31u, k));
+                    prv[u] = lds32(stage + row_word(r >> 5, r & 31u, (k + 7u) & 7u));
+                }
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++) {
+                    const uint32_t r = 4u * (4u * (it0 + u) + rr) + c;
+                    if (r >= left)
+                        continue;
                     uint8_t *row = A.parity + (cwt + r) * A.pstride;
-                    if (a == 0) {
-                        *reinterpret_cast<uint32_t *>(row + 4 * k) = cur;
-                    } else {
-                        uint8_t *g = row - a + 4 * k; // aligned word k of the row's span: row bytes 4 k - a .. 4 k - a + 3
-                        if (k != 0) {
-                            *reinterpret_cast<uint32_t *>(g) = __byte_perm(prv, cur, sel);
-                        } else { // head: row bytes 0 .. 3 - a
-                            if (a == 1) {
-                                g[1] = (uint8_t)cur;
-                                *reinterpret_cast<uint16_t *>(g + 2) = (uint16_t)(cur >> 8);
-                            } else if (a == 2) {
-                                *reinterpret_cast<uint16_t *>(g + 2) = (uint16_t)cur;
-                            } else {
-                                g[3] = (uint8_t)cur;
-                            }
+                    if (inner)
+                        *reinterpret_cast<uint32_t *>(row - a + 4 * k) = __byte_perm(prv[u], cur[u], sel);
+                    if (a != 0 && k == 0) { // head: row bytes 0 .. 3 - a
+                        if (a == 1) {
+                            row[0] = (uint8_t)cur[u];
+                            *reinterpret_cast<uint16_t *>(row + 1) = (uint16_t)(cur[u] >> 8);
+                        } else if (a == 2) {
+                            *reinterpret_cast<uint16_t *>(row) = (uint16_t)cur[u];
+                        } else {
+                            row[0] = (uint8_t)cur[u];
                         }
-                        if (k == 7) { // tail: row bytes 32 - a .. 31 = the top a bytes of word 7
-                            uint8_t *t = row - a + 32;
-                            if (a == 1) {
-                                t[0] = (uint8_t)(cur >> 24);
-                            } else if (a == 2) {
-                                *reinterpret_cast<uint16_t *>(t) = (uint16_t)(cur >> 16);
-                            } else {
-                                *reinterpret_cast<uint16_t *>(t) = (uint16_t)(cur >> 8);
-                                t[2] = (uint8_t)(cur >> 24);
-                            }
+                    }
+                    if (a != 0 && k == 7) { // tail: row bytes 32 - a .. 31, the top a bytes of word 7
+                        if (a == 1) {
+                            row[31] = (uint8_t)(cur[u] >> 24);
+                        } else if (a == 2) {
+                            *reinterpret_cast<uint16_t *>(row + 30) = (uint16_t)(cur[u] >> 16);
+                        } else {
+                            *reinterpret_cast<uint16_t *>(row + 29) = (uint16_t)(cur[u] >> 8);
+                            row[31] = (uint8_t)(cur[u] >> 24);
                         }
                     }
                 }

@@ -295,6 +295,16 @@ def test_packed_records_and_gaps_roundtrip(gpu_device, orc):
         dbuf[:, :223] = msg
         assert h.encode_batch(dbuf, 300, 223, pbuf, 40, n)
         assert (pbuf[:, :32] == want_par).all() and (pbuf[:, 32:] == 0x3C).all() and (dbuf[:, 223:] == 0xC3).all()
+        # parity rows far apart at odd addresses (the encoder merges whole sectors there): canaries in the gaps,
+        # before the first and after the last row
+        for pstride, off in ((100, 1), (63, 2), (97, 3), (64, 0)):
+            raw = np.full(n * pstride + 128, 0x5A, np.uint8)
+            base = raw.ctypes.data + 64 + off
+            assert h.encode_batch(dbuf, 300, 223, base, pstride, n)
+            rows = np.lib.stride_tricks.as_strided(raw[64 + off:], (n, pstride), (pstride, 1))
+            assert (rows[:, :32] == want_par).all(), (pstride, off)
+            assert (rows[:-1, 32:] == 0x5A).all() and (raw[:64 + off] == 0x5A).all()
+            assert (raw[64 + off + (n - 1) * pstride + 32:] == 0x5A).all()
 
 
 def _fast_path_counts(h):
