@@ -88,6 +88,7 @@ typedef struct {
 /* ---- device management ------------------------------------------------------------------- */
 int poporon_cuda_device_count(void);                 /* >= 0, or a negative error */
 const char *poporon_cuda_last_error(void);           /* thread-local text of the last failure */
+void poporon_cuda_note_error(const char *text);      /* lets the host library leave its own text there */
 int poporon_cuda_device_sm_count(int device);
 
 /* ---- memory / stream helpers so a C host never needs cuda_runtime.h ------------------------ */

@@ -93,6 +93,8 @@ struct poporon_cuda_rs {
     uint8_t *d_slab;          // rs255_fft: one 255 KB bit-plane slab per SM (allocated on first use)
     uint32_t *d_synplanes;    // rs255_fft encoder: syndrome planes of the chunk in flight (grow-only)
     size_t synplane_cap;      // codewords it holds
+    cudaEvent_t busy;         // recorded after the last kernel that uses the scratch above; the next call's stream waits on it
+    int correct_ctas_per_sm;  // resident CTAs of the general correction stage (per device, rs255_init)
     int use_lfsr;             // PP_RS255_LFSR=1: the round-1 LFSR kernels instead of the transform kernels (A/B runs)
     // opt-in per-kernel timing (poporon_cuda_rs_profile): CUDA event pairs around each launch
     bool prof_on;

@@ -88,6 +88,11 @@ const char *poporon_cuda_last_error(void)
     return g_err;
 }
 
+void poporon_cuda_note_error(const char *text)
+{
+    set_error("%s", text ? text : "");
+}
+
 int poporon_cuda_device_count(void)
 {
     int n = 0;
@@ -262,6 +267,20 @@ int poporon_cuda_stream_wait_event(int device, void *stream, void *event)
 
 /* ------------------------------------------------------------------------------------------ RS */
 
+namespace {
+/* A context owns ONE set of scratch (dirty queue, syndrome rows, counters, bit-plane slab, syndrome planes), so two
+ * calls on the same handle must not overlap on the device even when the caller puts them on different streams: the
+ * stream of a call first waits for the event recorded behind the previous call's last kernel (a no-op on the same
+ * stream), and records it again behind its own.  Host-side the calls of one handle must still come from one thread
+ * at a time (include/poporon_cuda.h). */
+struct ScratchOrder {
+    poporon_cuda_rs *ctx;
+    cudaStream_t stream;
+    ScratchOrder(poporon_cuda_rs *c, cudaStream_t s) : ctx(c), stream(s) { cudaStreamWaitEvent(stream, ctx->busy, 0); }
+    ~ScratchOrder() { cudaEventRecord(ctx->busy, stream); }
+};
+} // namespace
+
 int poporon_cuda_rs_create(const poporon_cuda_rs_desc_t *d, int device, poporon_cuda_rs_t **out)
 {
     if (!d || !out || !d->alpha_to || !d->index_of || !d->genpoly_index)
@@ -297,6 +316,8 @@ int poporon_cuda_rs_create(const poporon_cuda_rs_desc_t *d, int device, poporon_
     int rc = check(cudaMalloc((void **)&ctx->d_tables, sizeof h), "cudaMalloc tables");
     if (rc == 0)
         rc = check(cudaMemcpy(ctx->d_tables, &h, sizeof h, cudaMemcpyHostToDevice), "upload tables");
+    if (rc == 0)
+        rc = check(cudaEventCreateWithFlags(&ctx->busy, cudaEventDisableTiming), "cudaEventCreate");
     if (rc == 0 && ctx->fast255)
         rc = rs255_init(ctx);
     if (rc != 0) {
@@ -313,6 +334,8 @@ void poporon_cuda_rs_destroy(poporon_cuda_rs_t *ctx)
         return;
     DeviceGuard g(ctx->device);
     prof_release(ctx);
+    if (ctx->busy)
+        cudaEventDestroy(ctx->busy);
     cudaFree(ctx->d_tables);
     cudaFree(ctx->d_queue);
     cudaFree(ctx->d_rem);
@@ -405,8 +428,10 @@ int poporon_cuda_rs_encode_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size
     if (size >= 65536) /* the reference's loop counter is a uint16_t (src/encode.c:121) */
         return POPORON_CUDA_ERR_UNSUPP;
     GUARD(ctx->device);
-    if (poporon_cuda_rs_path(ctx, 0, data, data_stride, size, parity, parity_stride) == 1)
+    if (poporon_cuda_rs_path(ctx, 0, data, data_stride, size, parity, parity_stride) == 1) {
+        ScratchOrder order(ctx, (cudaStream_t)stream);
         return rs255_encode(ctx, data, data_stride, size, parity, parity_stride, n, ok, (cudaStream_t)stream);
+    }
     return launch_rs_encode_generic(ctx, data, data_stride, size, parity, parity_stride, n, ok, (cudaStream_t)stream);
 }
 
@@ -425,9 +450,11 @@ int poporon_cuda_rs_decode_dev(poporon_cuda_rs_t *ctx, int mode, uint8_t *data, 
         return POPORON_CUDA_ERR_ARG;
     GUARD(ctx->device);
     if (mode != POPORON_CUDA_MODE_EXTSYN && n < ((size_t)1 << 30) &&
-        poporon_cuda_rs_path(ctx, 1, data, data_stride, size, parity, parity_stride) == 1)
+        poporon_cuda_rs_path(ctx, 1, data, data_stride, size, parity, parity_stride) == 1) {
+        ScratchOrder order(ctx, (cudaStream_t)stream);
         return rs255_decode(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt, ok,
                             corrected, (cudaStream_t)stream);
+    }
     return launch_rs_decode_generic(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt,
                                     syn, ok, corrected, (cudaStream_t)stream);
 }

@@ -1218,6 +1218,12 @@ int rs255_init(poporon_cuda_rs *ctx)
                                      kPairs * kSmemScreen));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_correct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCorrectSmem));
+    {
+        int v = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, rs255_correct_kernel, kWorkThreads, kCorrectSmem) != cudaSuccess || v < 1)
+            v = 4;
+        ctx->correct_ctas_per_sm = v;
+    }
     const char *env = getenv("PP_RS255_LFSR");
     ctx->use_lfsr = env && env[0] == '1';
     return rs255_fft_init(ctx);
@@ -1361,14 +1367,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     }
     // one resident wave of the general stage (its shared-memory work arrays limit it to a few CTAs per SM); a grid
     // larger than one wave would leave a thin second wave behind the grid-stride loop
-    static int correct_ctas_per_sm = 0;
-    if (correct_ctas_per_sm == 0) {
-        int v = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, rs255_correct_kernel, kWorkThreads, kCorrectSmem) != cudaSuccess || v < 1)
-            v = 4;
-        correct_ctas_per_sm = v;
-    }
-    const unsigned cblocks = (unsigned)(ctx->sm_count * correct_ctas_per_sm);
+    const unsigned cblocks = (unsigned)(ctx->sm_count * ctx->correct_ctas_per_sm);
     const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
     if (mode == POPORON_CUDA_MODE_PLAIN) {
         // bitsliced solver first; what it declines lands in queue2 for the literal stage below

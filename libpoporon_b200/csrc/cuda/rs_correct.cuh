@@ -332,7 +332,8 @@ __device__ bool rs_correct(const RsCode &c, const SmemTables &T, uint8_t *data, 
 
     // Re-syndrome check.  When no exponent can reach 2^16 (the reference truncates its gf_mod argument to 16 bits)
     // the exponent of correction j at syndrome i is ib_j + (fcr + i) * step_j (mod nn): one running sum per j.
-    const bool plain_exponents = (uint32_t)(c.fcr + nr) * (uint32_t)c.prim * (uint32_t)(nn - 1) + (uint32_t)nn < 65536u;
+    const bool plain_exponents =
+        (uint64_t)((uint32_t)c.fcr + (uint32_t)nr) * (uint64_t)c.prim * (uint64_t)(nn - 1) + (uint64_t)nn < 65536ull; // (64-bit: a large prim must not wrap)
     if (MAXR <= 32 && plain_exponents) {
         uint32_t acc[MAXR <= 32 ? MAXR : 1];
 #pragma unroll

@@ -219,17 +219,11 @@ bool poporon_decode(poporon_t *h, uint8_t *data, size_t size, uint8_t *parity, s
         const uint32_t nroots = h->rs->nroots;
         uint32_t row[256];
         uint32_t cnt = e->count, i;
-        if (cnt > nroots) {
-            /* more erasures than roots overruns the reference's scratch arrays; report failure */
-            ok = 0;
-            nc = 0;
-            ran = true;
-        } else {
-            for (i = 0; i < nroots; i++)
-                row[i] = (i < e->capacity) ? e->positions[i] : 0u;
-            ran = poporon_decode_batch_erasure(h, data, size, size, parity, h->parity_bytes, 1, row, nroots, &cnt, &ok,
-                                               &nc);
-        }
+        /* count > nroots is passed on unchanged: the reference looks at the syndromes first (src/decode.c:466-470) and
+         * returns true / 0 for a clean codeword whatever the erasure count; only a dirty one fails, in the kernel */
+        for (i = 0; i < nroots; i++)
+            row[i] = (i < e->capacity) ? e->positions[i] : 0u;
+        ran = poporon_decode_batch_erasure(h, data, size, size, parity, h->parity_bytes, 1, row, nroots, &cnt, &ok, &nc);
     } else {
         ran = poporon_decode_batch(h, data, size, size, parity, h->parity_bytes, 1, &ok, &nc);
     }

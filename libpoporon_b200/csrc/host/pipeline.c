@@ -269,8 +269,9 @@ typedef struct {
     bool ok;
 } lane_task_t;
 
-/* Streams the codewords [t->lo, t->hi) of the job through the lane's staging slots. */
-static void run_lane(lane_task_t *t)
+/* Streams the codewords [t->lo, t->hi) of the job through the lane's staging slots.  Returns false at the first
+ * failure, possibly with copies and kernels of earlier chunks still in flight (run_lane drains them). */
+static bool run_lane_body(lane_task_t *t)
 {
     poporon_t *h = t->h;
     pp_lane_t *lane = t->lane;
@@ -283,7 +284,6 @@ static void run_lane(lane_task_t *t)
     unsigned turn = 0;
     int s;
 
-    t->ok = false;
     for (c0 = t->lo; c0 < t->hi; c0 += chunk, turn++) {
         pp_slot_t *sl = &lane->slot[turn % PP_SLOTS];
         const size_t m = (t->hi - c0 < chunk) ? t->hi - c0 : chunk;
@@ -300,7 +300,7 @@ static void run_lane(lane_task_t *t)
 
         /* the slot's previous chunk (two turns ago) must have drained before its buffers are reused */
         if (poporon_cuda_stream_sync(dev, sl->stream) != 0)
-            return;
+            return false;
 
         if (merged) {
             if (hp < lo_ptr)
@@ -308,12 +308,12 @@ static void run_lane(lane_task_t *t)
             if (hp + pspan > hi_ptr)
                 hi_ptr = hp + pspan;
             if (!ensure(dev, &sl->d_span, &sl->span_cap, (size_t)(hi_ptr - lo_ptr)))
-                return;
+                return false;
             dd = sl->d_span + (hd - lo_ptr);
             dp = sl->d_span + (hp - lo_ptr);
         } else {
             if (!ensure(dev, &sl->d_span, &sl->span_cap, dspan) || !ensure(dev, &sl->d_pspan, &sl->pspan_cap, pspan))
-                return;
+                return false;
             dd = sl->d_span;
             dp = sl->d_pspan;
         }
@@ -323,7 +323,7 @@ static void run_lane(lane_task_t *t)
         if (j->mode == POPORON_CUDA_MODE_EXTSYN)
             aux_need += m * nroots * 2;
         if (!ensure(dev, &sl->d_aux, &sl->aux_cap, aux_need))
-            return;
+            return false;
         d_ok = sl->d_aux;
         off = align_up(m, 16);
         d_cor = sl->d_aux + off;
@@ -332,13 +332,13 @@ static void run_lane(lane_task_t *t)
         /* ---- host -> device ---- */
         if (merged) {
             if (poporon_cuda_memcpy_h2d(dev, sl->d_span, lo_ptr, (size_t)(hi_ptr - lo_ptr), sl->stream) != 0)
-                return;
+                return false;
         } else {
             if (poporon_cuda_memcpy_h2d(dev, dd, hd, dspan, sl->stream) != 0)
-                return;
+                return false;
             /* encode only writes parity, but gaps between parity records must survive the round trip */
             if ((j->op == 1 || j->parity_stride != P) && poporon_cuda_memcpy_h2d(dev, dp, hp, pspan, sl->stream) != 0)
-                return;
+                return false;
         }
         if (j->mode == POPORON_CUDA_MODE_ERASURE && j->op == 1) {
             d_pos = sl->d_aux + off;
@@ -347,13 +347,13 @@ static void run_lane(lane_task_t *t)
             off += m * 4;
             if (poporon_cuda_memcpy_h2d(dev, d_pos, j->pos + c0 * j->pos_stride, m * j->pos_stride * 4, sl->stream) ||
                 poporon_cuda_memcpy_h2d(dev, d_cnt, j->cnt + c0, m * 4, sl->stream))
-                return;
+                return false;
         }
         if (j->mode == POPORON_CUDA_MODE_EXTSYN && j->op == 1) {
             d_syn = sl->d_aux + off;
             off += m * nroots * 2;
             if (poporon_cuda_memcpy_h2d(dev, d_syn, j->syn + c0 * nroots, m * nroots * 2, sl->stream))
-                return;
+                return false;
         }
 
         /* ---- kernels ---- */
@@ -375,39 +375,51 @@ static void run_lane(lane_task_t *t)
                 pp_slot_t *other = &lane->slot[o];
                 if (other != sl && other->kdone_set &&
                     poporon_cuda_stream_wait_event(dev, sl->stream, other->kdone) != 0)
-                    return;
+                    return false;
             }
         }
         if (launch(h, lane, &dj, sl->stream) != 0)
-            return;
+            return false;
         if (poporon_cuda_event_record(dev, sl->kdone, sl->stream) != 0)
-            return;
+            return false;
         sl->kdone_set = true;
 
         /* ---- device -> host ---- */
         if (j->op == 0) {
             if (poporon_cuda_memcpy_d2h(dev, hp, dp, pspan, sl->stream) != 0)
-                return;
+                return false;
         } else if (merged) {
             if (poporon_cuda_memcpy_d2h(dev, lo_ptr, sl->d_span, (size_t)(hi_ptr - lo_ptr), sl->stream) != 0)
-                return;
+                return false;
         } else {
             if (poporon_cuda_memcpy_d2h(dev, hd, dd, dspan, sl->stream) != 0)
-                return;
+                return false;
             /* RS corrects parity in place as well; BCH leaves it untouched */
             if (h->fec_type == PPLN_FEC_RS && poporon_cuda_memcpy_d2h(dev, hp, dp, pspan, sl->stream) != 0)
-                return;
+                return false;
         }
         if (j->ok && poporon_cuda_memcpy_d2h(dev, j->ok + c0, d_ok, m, sl->stream) != 0)
-            return;
+            return false;
         if (j->op == 1 && j->corrected &&
             poporon_cuda_memcpy_d2h(dev, j->corrected + c0, d_cor, m * 4, sl->stream) != 0)
-            return;
+            return false;
     }
     for (s = 0; s < PP_SLOTS; s++)
         if (poporon_cuda_stream_sync(dev, lane->slot[s].stream) != 0)
-            return;
-    t->ok = true;
+            return false;
+    return true;
+}
+
+
+static void run_lane(lane_task_t *t)
+{
+    t->ok = run_lane_body(t);
+    if (!t->ok) {
+        /* nothing may still be writing into the caller's buffers when the job reports failure */
+        int s;
+        for (s = 0; s < PP_SLOTS; s++)
+            (void)poporon_cuda_stream_sync(t->lane->device, t->lane->slot[s].stream);
+    }
 }
 
 static void *lane_thread(void *arg)

@@ -12,24 +12,28 @@ poporon_config_t *poporon_ldpc_config_create(size_t block_size, poporon_ldpc_rat
     (void)block_size, (void)rate, (void)matrix_type, (void)column_weight, (void)use_soft_decode;
     (void)use_outer_interleave, (void)use_inner_interleave, (void)interleave_depth, (void)lifting_factor;
     (void)max_iterations, (void)soft_llr, (void)soft_llr_size, (void)seed;
+    poporon_cuda_note_error("LDPC (reference src/ldpc.c) is not part of poporon-b200: RS and BCH only");
     return NULL;
 }
 
 poporon_config_t *poporon_config_ldpc_default(size_t block_size, poporon_ldpc_rate_t rate)
 {
     (void)block_size, (void)rate;
+    poporon_cuda_note_error("LDPC (reference src/ldpc.c) is not part of poporon-b200: RS and BCH only");
     return NULL;
 }
 
 poporon_config_t *poporon_config_ldpc_burst_resistant(size_t block_size, poporon_ldpc_rate_t rate)
 {
     (void)block_size, (void)rate;
+    poporon_cuda_note_error("LDPC (reference src/ldpc.c) is not part of poporon-b200: RS and BCH only");
     return NULL;
 }
 
 poporon_rng_t *poporon_rng_create(poporon_rng_type_t type, void *seed, size_t seed_size)
 {
     (void)type, (void)seed, (void)seed_size;
+    poporon_cuda_note_error("poporon_rng_* (reference src/rng.c) is not part of poporon-b200");
     return NULL;
 }
 
