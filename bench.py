@@ -51,6 +51,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="codewords in the CPU baseline sample (0 = auto)")
     ap.add_argument("--mem-budget-gb", type=float, default=140.0)
+    ap.add_argument("--verify", choices=["sample", "all", "none"], default="sample",
+                    help="untimed comparison with the CPU reference after the timed loop: a 1 Mi prefix + a 64 Ki "
+                         "strided sample of the batch (default), the whole batch, or nothing")
     return ap.parse_args()
 
 
@@ -448,6 +451,44 @@ def run_ours(args):
                "sample": f"first {sample} codewords of the GPU batch (encode + decode), one handle per thread; "
                          "outputs compared with the GPU's"}
 
+    # ---- oracle comparison at size (untimed, rank 0, N = 1): data, parity, ok and corrected_num of a 1 Mi prefix
+    # plus a 64 Ki strided sample of the 16 Mi batch - or of all of it - against the compiled reference ------------
+    verify = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.verify != "none":
+        lib, kind = load_cpu_lib()
+        cores = os.cpu_count() or 1
+        if args.verify == "all":
+            idx = torch.arange(n, device=dev)
+        else:
+            pre = min(n, 1 << 20)
+            stride = max(1, n // 65536)
+            idx = torch.unique(torch.cat([torch.arange(pre, device=dev), torch.arange(0, n, stride, device=dev)]))
+        if not dirty[0]:
+            corrupt(0)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        mism = 0
+        # in slices of 1 Mi codewords: the received words of the slice, the GPU's decode of the WHOLE buffer, the
+        # reference's decode of the slice
+        rx = bufs[0].view(n, K_CW)
+        parts = [idx[i:i + (1 << 20)] for i in range(0, idx.numel(), 1 << 20)]
+        rxs = [rx[p_].cpu().numpy() for p_ in parts]
+        assert h.decode_batch_async(bufs[0].data_ptr(), K_CW, K_MSG, bufs[0].data_ptr() + K_MSG, K_CW, n, ok.data_ptr(),
+                                    cor.data_ptr(), stream=stream)
+        torch.cuda.synchronize()
+        dirty[0] = False
+        for p_, r_ in zip(parts, rxs):
+            got = rx[p_].cpu().numpy()
+            gok = ok[p_].cpu().numpy()
+            gcor = cor[p_].cpu().numpy().astype(np.uint32)
+            wd, wp, wok, wcor = lib.rs_decode(np.ascontiguousarray(r_[:, :K_MSG]), np.ascontiguousarray(r_[:, K_MSG:]),
+                                              threads=cores)
+            mism += int(((got[:, :K_MSG] != wd).any(1) | (got[:, K_MSG:] != wp).any(1) | (gok != wok) |
+                         (gcor != wcor)).sum())
+        verify = {"codewords": int(idx.numel()), "mismatches": mism, "against": kind, "mode": args.verify,
+                  "fields": "data, parity, ok, corrected_num", "seconds": round(time.perf_counter() - t0, 1)}
+        assert mism == 0, f"GPU decode differs from the CPU {kind} on {mism} codewords"
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
@@ -461,6 +502,8 @@ def run_ours(args):
             line["e2e"] = e2e
         if cpu:
             line["cpu_baseline"] = cpu
+        if verify:
+            line["verify"] = verify
         print(json.dumps(line), flush=True)
     h.close()
     if world > 1:

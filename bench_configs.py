@@ -13,7 +13,9 @@ the same C ABI on device-resident data and prints one JSON line per workload (ap
             0 %, 1 % and 5 % (uncorrectable codewords are part of the 5 % load); check: every codeword reported
             ok is a codeword again (second, clean decode of the corrected buffer: 0 corrections)
 
-No oracle is used here (properties only).  Timing: CUDA events on the launching stream, one untimed warm-up on
+Besides the size-independent properties, a 256 Ki sample of configs[2] (rows WITH unknown errors and with
+2v + c > 32 included) and of configs[4] at 5 % (14 % of it uncorrectable) is byte-compared - data, parity, ok,
+corrected_num - with the CPU reference (oracle/_ref when present, else the pinned restatement), untimed.  Timing: CUDA events on the launching stream, one untimed warm-up on
 a different buffer, inputs far larger than L2.
 """
 from __future__ import annotations
@@ -42,6 +44,28 @@ def hbm_peak():
     if os.path.exists(p):
         return float(json.load(open(p))["hbm_gbs"])
     return 6650.0
+
+
+def sample_index(torch, n, dev, total=256 * 1024):
+    """a prefix of 3/4 of the sample plus a strided quarter over the whole batch"""
+    pre = min(n, total * 3 // 4)
+    stride = max(1, n // (total // 4))
+    return torch.unique(torch.cat([torch.arange(pre, device=dev), torch.arange(0, n, stride, device=dev)]))
+
+
+def oracle_compare(rx, got, ok, cor, mode=0, pos=None, cnt=None):
+    """rx/got: [m, 255] numpy (received / decoded records).  Returns (mismatching rows, oracle ok fraction, kind)."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oraclelib import Oracle, have_reference
+
+    kind = "reference" if have_reference() else "port"
+    orc = Oracle(kind)
+    wd, wp, wok, wcor = orc.rs_decode(np.ascontiguousarray(rx[:, :K_MSG]), np.ascontiguousarray(rx[:, K_MSG:]),
+                                      mode=mode, pos=pos, cnt=cnt, threads=os.cpu_count() or 1)
+    bad = (got[:, :K_MSG] != wd).any(1) | (got[:, K_MSG:] != wp).any(1) | (ok != wok) | (cor.astype(np.uint32) != wcor)
+    return int(bad.sum()), float(wok.mean()), kind
 
 
 def timed(torch, fn, reps):
@@ -80,6 +104,8 @@ def run_erasure(args, torch, api, dev):
                                     ok.data_ptr(), cor.data_ptr(), pos=poss[b].data_ptr(), pos_stride=32,
                                     cnt=cnts[b].data_ptr(), stream=stream)
 
+    idx = sample_index(torch, n, dev)
+    rx_s = bufs[reps - 1].view(n, K_CW)[idx].cpu().numpy()
     dec(reps)  # warm-up on the extra buffer
     torch.cuda.synchronize()
     h.profile(True)
@@ -96,6 +122,14 @@ def run_erasure(args, torch, api, dev):
     # synth_erasures leaves 90 % of the rows without unknown errors: all of those must be restored and ok
     assert frac_restored > 0.895, frac_restored
     assert bool((okb | ~restored).all().item()), "a restored row was reported as failed"
+    # oracle comparison of the sample, every outcome class included (unknown errors, 2v + c > 32, failures)
+    import numpy as np
+
+    pos_s = poss[last].view(n, 32)[idx].cpu().numpy().astype(np.uint32)
+    cnt_s = cnts[last][idx].cpu().numpy().astype(np.uint32)
+    mism, ork, kind = oracle_compare(rx_s, bufs[last].view(n, K_CW)[idx].cpu().numpy(), ok[idx].cpu().numpy(),
+                                     cor[idx].cpu().numpy(), mode=1, pos=pos_s, cnt=cnt_s)
+    assert mism == 0, f"erasure decode differs from the CPU {kind} on {mism} of {idx.numel()} sampled codewords"
     t = sum(ms) / len(ms)
     mean_cnt = float(cnts[last].float().mean().item())
     alg = n * (K_CW + 5 + 4 * mean_cnt + 4 + float(cor.float().mean().item()))
@@ -104,6 +138,8 @@ def run_erasure(args, torch, api, dev):
                 "hbm_frac": alg / t / 1e6 / hbm_peak(), "bound": "integer ALU / shared memory (general per-thread stage)",
                 "dirty_fraction": float(dirty_rows[last].float().mean().item()), "ok_fraction": frac_ok,
                 "restored_fraction": frac_restored, "mean_erasures": mean_cnt,
+                "verify": {"codewords": int(idx.numel()), "mismatches": mism, "against": kind,
+                           "oracle_ok_fraction": ork, "fields": "data, parity, ok, corrected_num"},
                 "kernels": {k: {"launches": c, "avg_ms": m / c} for k, (c, m) in prof.items()}})
     h.close()
 
@@ -243,6 +279,9 @@ def run_load(args, torch, api, dev):
             work.copy_(clean)
             if p_ppm:
                 api.synth_inject(0, work.data_ptr(), K_CW, K_CW, n, 0x5EED0500 + rep, 0, 1, 0, 0, p_ppm, stream)
+            if rep == args.reps:
+                idx = sample_index(torch, n, dev)
+                rx_s = work.view(n, K_CW)[idx].cpu().numpy()
             h.profile(True)
             ev[0].record()
             assert h.decode_batch_async(work.data_ptr(), K_CW, K_MSG, work.data_ptr() + K_MSG, K_CW, n, ok.data_ptr(),
@@ -253,6 +292,9 @@ def run_load(args, torch, api, dev):
             h.profile(False)
             if rep:
                 times.append(ev[0].elapsed_time(ev[1]))
+        mism, ork, kind = oracle_compare(rx_s, work.view(n, K_CW)[idx].cpu().numpy(), ok[idx].cpu().numpy(),
+                                         cor[idx].cpu().numpy())
+        assert mism == 0, f"decode differs from the CPU {kind} on {mism} of {idx.numel()} sampled codewords"
         okb = ok.bool()
         ok_frac = float(okb.float().mean().item())
         mean_cor = float(cor.float().mean().item())
@@ -276,6 +318,8 @@ def run_load(args, torch, api, dev):
                     "alg_GBps": alg / t / 1e6, "hbm_frac": alg / t / 1e6 / hbm_peak(), "ok_fraction": ok_frac,
                     "restored_fraction": restored_frac, "mean_corrected": mean_cor, "dirty_fraction": dirty,
                     "encode_ms": enc_ms, "encode_payload_GBps": n * K_MSG / enc_ms / 1e6,
+                    "verify": {"codewords": int(idx.numel()), "mismatches": mism, "against": kind,
+                               "oracle_ok_fraction": ork, "fields": "data, parity, ok, corrected_num"},
                     "kernels": {k: {"launches": c, "avg_ms": m / c} for k, (c, m) in prof.items()}})
     h.close()
 

@@ -28,6 +28,8 @@ def test_config2_erasure_16mi(gpu_device, tmp_path):
     (line,) = _run("erasure", tmp_path)
     assert line["codewords"] == 16 * 1024 * 1024
     assert line["restored_fraction"] > 0.895  # every row without unknown errors is restored (asserted inside too)
+    # 256 Ki sampled rows, quirk rows included, byte-compared with the CPU reference
+    assert line["verify"]["mismatches"] == 0 and line["verify"]["codewords"] >= 250000
 
 
 def test_config3_bch_64mi(gpu_device, tmp_path):
@@ -43,3 +45,5 @@ def test_config4_load_sweep_128mi(gpu_device, tmp_path):
     assert lines[1]["ok_fraction"] == 1.0 and lines[1]["restored_fraction"] == 1.0
     assert 0.80 < lines[2]["ok_fraction"] < 0.90  # P(more than 16 of 255 symbols hit at 5 %) is about 14 %
     assert lines[2]["ok_fraction"] == lines[2]["restored_fraction"]
+    assert all(l["verify"]["mismatches"] == 0 for l in lines)
+    assert 0.80 < lines[2]["verify"]["oracle_ok_fraction"] < 0.90  # the sample holds the failures too

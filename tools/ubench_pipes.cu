@@ -1,6 +1,8 @@
 // ubench_pipes.cu — throughput of the integer pipes the bitsliced kernels live on (B200, sm_100a).
 // Build: nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o ubench_pipes ubench_pipes.cu
-// Prints warp-instructions per clock per SM for LOP3, IMAD, LOP3+IMAD mix, SHF, PRMT, SHFL, LOP3+SHFL mix.
+// Prints warp-instructions per clock per SM for LOP3, IMAD, LOP3+IMAD mix, SHF, PRMT, SHFL, LOP3+SHFL mix, IMAD.HI
+// (a right shift on the FMA pipe) and LOP3+IMAD.HI; with an argument, also writes them as JSON to that file
+// (profiles/r02_ubench_pipes.json: the ALU-roofline denominator of bench.py).
 #include <cstdio>
 #include <cuda_runtime.h>
 
@@ -93,11 +95,41 @@ __global__ void k(unsigned *out, unsigned seed)
                 asm volatile("mul.lo.u32 %0,%0,%1;" : "+r"(a6) : "r"(s));
                 asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a3) : "r"(a0), "r"(m));
                 asm volatile("mul.lo.u32 %0,%0,%1;" : "+r"(a7) : "r"(s));
+            } else if (MODE == 9) { // mul.hi (right shift by a constant on the fma pipe?)
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a0) : "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a1) : "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a2) : "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a3) : "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a4) : "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a5) : "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a6) : "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a7) : "r"(m));
+            } else if (MODE == 10) { // 4 LOP3 + 4 mul.hi
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a0) : "r"(a1), "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a4) : "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a1) : "r"(a2), "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a5) : "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a2) : "r"(a3), "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a6) : "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a3) : "r"(a0), "r"(m));
+                asm volatile("mul.hi.u32 %0,%0,%1;" : "+r"(a7) : "r"(m));
+            } else if (MODE == 11) { // 6 LOP3 + 2 IMAD (3:1)
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a0) : "r"(a1), "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a1) : "r"(a2), "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a2) : "r"(a3), "r"(m));
+                asm volatile("mad.lo.u32 %0,%0,%1,%2;" : "+r"(a6) : "r"(a7), "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a3) : "r"(a4), "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a4) : "r"(a5), "r"(m));
+                asm volatile("lop3.b32 %0,%0,%1,%2,0x96;" : "+r"(a5) : "r"(a0), "r"(m));
+                asm volatile("mad.lo.u32 %0,%0,%1,%2;" : "+r"(a7) : "r"(a6), "r"(m));
             }
         }
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
 }
+
+static FILE *g_json = nullptr;
+static int g_first = 1;
 
 template <int MODE>
 void run(const char *name, int sms, double ghz_guess)
@@ -120,10 +152,15 @@ void run(const char *name, int sms, double ghz_guess)
     double per_s = winstr / (ms * 1e-3);
     printf("%-28s %8.3f ms  %8.2f Gwarp-instr/s  = %6.2f warp-instr/clk/SM @%.3f GHz (lanes/clk/SM %.1f)\n", name, ms,
            per_s / 1e9, per_s / sms / (ghz_guess * 1e9), ghz_guess, 32 * per_s / sms / (ghz_guess * 1e9));
+    if (g_json) {
+        fprintf(g_json, "%s\n  \"%s\": {\"warp_instr_per_clk_per_sm\": %.4f, \"lanes_per_clk_per_sm\": %.2f, \"gwarp_instr_per_s\": %.2f}",
+                g_first ? "" : ",", name, per_s / sms / (ghz_guess * 1e9), 32 * per_s / sms / (ghz_guess * 1e9), per_s / 1e9);
+        g_first = 0;
+    }
     cudaFree(out);
 }
 
-int main()
+int main(int argc, char **argv)
 {
     cudaDeviceProp p;
     cudaGetDeviceProperties(&p, 0);
@@ -132,6 +169,8 @@ int main()
     cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, 0);
     double ghz = khz / 1e6;
     printf("%s, %d SMs, clock attr %.3f GHz\n", p.name, sms, ghz);
+    if (argc > 1 && (g_json = fopen(argv[1], "w")))
+        fprintf(g_json, "{\"device\": \"%s\", \"sms\": %d, \"clock_ghz\": %.3f, \"warps_per_sm\": 32, \"note\": \"8 independent chains per thread, 4096 x 4 x 8 instructions per thread; rates are per clock of the attribute clock\", \"pipes\": {", p.name, sms, ghz);
     run<0>("LOP3 xor3", sms, ghz);
     run<1>("IMAD", sms, ghz);
     run<2>("LOP3+IMAD 1:1", sms, ghz);
@@ -141,5 +180,12 @@ int main()
     run<6>("LOP3x7 + SHFL", sms, ghz);
     run<7>("IADD", sms, ghz);
     run<8>("LOP3+IMUL 1:1", sms, ghz);
+    run<9>("IMAD.HI (mul.hi)", sms, ghz);
+    run<10>("LOP3+IMAD.HI 1:1", sms, ghz);
+    run<11>("LOP3+IMAD 3:1", sms, ghz);
+    if (g_json) {
+        fprintf(g_json, "\n}}\n");
+        fclose(g_json);
+    }
     return 0;
 }
