@@ -65,6 +65,34 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def alu_peak(sm_mhz):
+    """Integer-ALU roof in lane-operations per second: the LOP3 rate measured by tools/ubench_pipes.cu
+    (profiles/r02_ubench_pipes.json, warp-instructions per clock and SM at the attribute clock) x 32 lanes x SMs x
+    the SM clock sampled during the timed region."""
+    path = os.path.join(ROOT, "profiles", "r02_ubench_pipes.json")
+    lanes, sms, src = 64.0, 148, "fallback: 64 lanes/clk/SM (DESIGN.md section 4)"
+    if os.path.exists(path):
+        with open(path) as f:
+            u = json.load(f)
+        lanes, sms, src = float(u["pipes"]["LOP3 xor3"]["lanes_per_clk_per_sm"]), int(u["sms"]), "profiles/r02_ubench_pipes.json (LOP3 xor3)"
+    return lanes * sms * sm_mhz * 1e6, src
+
+
+# Useful integer-ALU lane-operations per codeword of each ALU-bound kernel: the operation count of its formulation
+# with nothing but the GF(2) arithmetic counted (DESIGN.md section 4 derives every term).
+ALU_FLOOR = {
+    # BM 332 coefficient steps x 228 + evaluator 9.2 K + sweep 255 x 158 + sweep seed 2.7 K + Forney on 16 list
+    # slots 44.9 K + 28 bit-matrix transposes x 256, per 32 queued codewords
+    "rs255_solve_kernel": (75696 + 9152 + 40290 + 2686 + 44900 + 7168) / 32.0,
+    # transform 18598 + 64 word-columns x (256 transpose + 32 realign) + 255 x 8 basis change, per 32 codewords
+    "rs255_fft_kernel<SCREEN>": (18598 + 64 * 288 + 255 * 8) / 32.0,
+    "rs255_fft_kernel<ENCODE>": (18598 + 56 * 288 + 223 * 8) / 32.0,
+    # 32 syndromes x (two subset tables 22 + 256 plane updates), per 32 codewords
+    "rs255_parity_kernel": 32 * (22 + 256) / 32.0,
+    "rs255_rows_kernel": 8 * 256 / 32.0,
+}
+
+
 def ncu_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum per codeword for each kernel, from the committed
     `ncu --set full` capture summary (profiles/ncu_traffic.json; written by tools/ncu_traffic.py)."""
@@ -363,25 +391,45 @@ def run_ours(args):
         "rs255_solve_kernel": n * dirty_frac * (4 + 32 + 5) + n * mean_err * (2 + 2),
         "rs255_correct_kernel": 8,
     }
+    sm_mhz = float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0) if isinstance(clocks, dict) else 1965.0
+    apeak, apeak_src = alu_peak(sm_mhz)
+    units = {"rs255_solve_kernel": n * dirty_frac}  # codewords a launch works on (default: the whole batch)
     kernels = {}
     for name, (cnt, ms) in kprof.items():
         avg = ms / cnt
         kernels[name] = {"launches_per_step": cnt / K, "avg_ms": avg, "share_of_step": ms / elapsed_ms,
                          "alg_GBps": alg_bytes.get(name, 0) / (avg * 1e-3) / 1e9}
+        if name in ALU_FLOOR:
+            ops = ALU_FLOOR[name] * units.get(name, n)
+            kernels[name].update({"alu_floor_lane_ops_per_codeword": ALU_FLOOR[name],
+                                  "alu_Tlaneops": ops / (avg * 1e-3) / 1e12,
+                                  "alu_frac": ops / (avg * 1e-3) / apeak})
     traffic = ncu_traffic()
     dom = max(kernels, key=lambda k: kernels[k]["avg_ms"] * kernels[k]["launches_per_step"]) if kernels else None
     if dom:
-        roof = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["alg_GBps"],
-                "bytes_per_launch": alg_bytes.get(dom, 0), "avg_launch_ms": kernels[dom]["avg_ms"],
-                "share_of_step": kernels[dom]["share_of_step"]}
         tr = traffic.get(dom)
-        roof["traffic"] = tr["bytes_per_codeword"] * n if tr else None
+        hbm = {"achieved_GBps": kernels[dom]["alg_GBps"], "bytes_per_launch": alg_bytes.get(dom, 0), "peak_GBps": peak,
+               "frac": kernels[dom]["alg_GBps"] / peak, "peak_source": peak_src,
+               "traffic": tr["bytes_per_codeword"] * n if tr else None}
+        if dom in ALU_FLOOR:
+            # error-heavy decode is bound by the integer ALU pipe (north_star): useful lane-operations per second
+            # against the measured LOP3 rate; the HBM view of the same kernel stays beside it
+            roof = {"kernel": dom, "bound": "alu", "achieved": kernels[dom]["alu_Tlaneops"], "peak": apeak / 1e12,
+                    "unit": "Tlane-op/s", "frac": kernels[dom]["alu_frac"], "peak_source": apeak_src,
+                    "floor_lane_ops_per_codeword": ALU_FLOOR[dom], "codewords_per_launch": units.get(dom, n),
+                    "avg_launch_ms": kernels[dom]["avg_ms"], "share_of_step": kernels[dom]["share_of_step"],
+                    "traffic": hbm["traffic"], "hbm": hbm}
+        else:
+            roof = {"kernel": dom, "bound": "hbm", "achieved": hbm["achieved_GBps"], "peak": peak, "unit": "GB/s",
+                    "frac": hbm["frac"], "peak_source": peak_src, "bytes_per_launch": hbm["bytes_per_launch"],
+                    "avg_launch_ms": kernels[dom]["avg_ms"], "share_of_step": kernels[dom]["share_of_step"],
+                    "traffic": hbm["traffic"]}
         if tr:
             roof["traffic_source"] = tr["source"]
     else:
         roof = {"kernel": "rs decode (whole phase)", "bound": "hbm", "achieved": dec_alg / (dec_ms * 1e-3) / 1e9,
-                "traffic": None}
-    roof.update({"peak": peak, "unit": "GB/s", "frac": roof["achieved"] / peak, "peak_source": peak_src})
+                "traffic": None, "peak": peak, "unit": "GB/s", "peak_source": peak_src}
+        roof["frac"] = roof["achieved"] / peak
     phases = {"encode_ms": enc_ms, "decode_ms": dec_ms,
               "encode_payload_GBps": n * K_MSG / (enc_ms * 1e-3) / 1e9,
               "decode_payload_GBps": n * K_MSG / (dec_ms * 1e-3) / 1e9,
