@@ -67,6 +67,13 @@ bool poporon_decode_batch_syndrome(struct _poporon_t *pprn, uint8_t *data, size_
                                    uint8_t *parity, size_t parity_stride, size_t n, const uint16_t *syndromes,
                                    uint8_t *ok, uint32_t *corrected_num);
 
+/* Syndromes only: the stage the reference keeps internal (calculate_syndrome_u8, src/decode.c:232-416).  Writes
+ * syndromes[i * num_roots + j] = index (log) form of S_j of codeword i, 2^m-1 meaning zero - exactly the array a
+ * handle configured with an external syndrome pointer, or poporon_decode_batch_syndrome, takes back.  Nothing is
+ * corrected.  1 <= size <= 2^m - 1 - num_roots.  RS handles only; host or device pointers as above. */
+bool poporon_syndromes_batch(struct _poporon_t *pprn, const uint8_t *data, size_t data_stride, size_t size,
+                             const uint8_t *parity, size_t parity_stride, size_t n, uint16_t *syndromes);
+
 /* Device-pointer forms that enqueue on a caller-owned cudaStream_t (passed as void*) and return
  * without synchronising.  All pointers must be device memory on the same device. */
 bool poporon_encode_batch_async(struct _poporon_t *pprn, const uint8_t *data, size_t data_stride, size_t size,

@@ -120,14 +120,17 @@ void poporon_cuda_rs_destroy(poporon_cuda_rs_t *ctx);
 int poporon_cuda_rs_device(const poporon_cuda_rs_t *ctx);
 
 /* Which kernel family a call with these arguments would take: 0 = general-parameter table kernels,
- * 1 = RS(255,223)/0x11D bitsliced fast path (encode: any strides, data 16-byte aligned; decode: packed
- * records, i.e. parity == data + size and equal strides, data 16-byte aligned).  op: 0 encode, 1 decode.
- * Introspection for tests and the bench. */
+ * 1 = RS(255,223)/0x11D bitsliced fast path: any base alignment, message rows and parity rows as separate arrays
+ * (the two-pointer shape of reference include/poporon.h:90-91) or interleaved in one record, as long as 32
+ * consecutive rows of each fit a ~8 KB staging buffer (strides up to ~260 bytes); longer strides take it with a
+ * 16-byte aligned base (decode: packed records only).  op: 0 encode, 1 decode.  Introspection for tests and the bench. */
 int poporon_cuda_rs_path(const poporon_cuda_rs_t *ctx, int op, const uint8_t *data, size_t data_stride, size_t size,
                          const uint8_t *parity, size_t parity_stride);
 /* Force the generic kernels even where the fast path applies (tests compare the two). */
 void poporon_cuda_rs_force_generic(poporon_cuda_rs_t *ctx, int on);
 
+/* Calls on one context share its scratch: they are ordered on the device by an internal event whatever stream each
+ * is given (two calls never overlap), and must be issued from one host thread at a time. */
 int poporon_cuda_rs_encode_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size_t data_stride, size_t size,
                                uint8_t *parity, size_t parity_stride, size_t n, uint8_t *ok /* nullable */,
                                void *stream);
@@ -142,6 +145,13 @@ int poporon_cuda_rs_decode_dev(poporon_cuda_rs_t *ctx, int mode, uint8_t *data, 
                                uint8_t *parity, size_t parity_stride, size_t n, const uint32_t *pos,
                                size_t pos_stride, const uint32_t *cnt, const uint16_t *syn, uint8_t *ok,
                                uint32_t *corrected, void *stream);
+/* Syndromes only (reference calculate_syndrome_u8, src/decode.c:232-416, a stage the reference keeps internal):
+ * syndromes[i * nroots + j] = index_of[S_(j)] of codeword i, nn = 2^m - 1 meaning zero - the form
+ * poporon_cuda_rs_decode_dev(mode = EXTSYN) takes back.  Nothing is corrected.  size must satisfy the reference's
+ * padding rule (1 <= size <= nn - nroots), else POPORON_CUDA_ERR_ARG. */
+int poporon_cuda_rs_syndromes_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size_t data_stride, size_t size,
+                                  const uint8_t *parity, size_t parity_stride, size_t n, uint16_t *syndromes,
+                                  void *stream);
 
 /* Number of kernels this context has launched since creation (bench.py's gpu_launches). */
 uint64_t poporon_cuda_rs_launch_count(const poporon_cuda_rs_t *ctx);

@@ -107,6 +107,8 @@ _sig(host, "poporon_decode_batch_erasure", C.c_bool, C.c_void_p, C.c_void_p, C.c
      C.c_size_t, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p)
 _sig(host, "poporon_decode_batch_syndrome", C.c_bool, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p,
      C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p)
+_sig(host, "poporon_syndromes_batch", C.c_bool, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_size_t,
+     C.c_size_t, C.c_void_p)
 _sig(host, "poporon_encode_batch_async", C.c_bool, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p,
      C.c_size_t, C.c_size_t, C.c_void_p)
 _sig(host, "poporon_decode_batch_async", C.c_bool, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p,
@@ -290,6 +292,11 @@ class Poporon:
                               corrected=None) -> bool:
         return bool(host.poporon_decode_batch_syndrome(self.ptr, _addr(data), data_stride, size, _addr(parity),
                                                        parity_stride, n, _addr(syn), _addr(ok), _addr(corrected)))
+
+    def syndromes_batch(self, data, data_stride, size, parity, parity_stride, n, syn) -> bool:
+        """syn: [n, nroots] uint16, receives the index-form syndromes (2^m - 1 = zero); nothing is corrected"""
+        return bool(host.poporon_syndromes_batch(self.ptr, _addr(data), data_stride, size, _addr(parity),
+                                                 parity_stride, n, _addr(syn)))
 
     def encode_batch_async(self, data, data_stride, size, parity, parity_stride, n, stream=0) -> bool:
         return bool(host.poporon_encode_batch_async(self.ptr, _addr(data), data_stride, size, _addr(parity),

@@ -449,14 +449,38 @@ int poporon_cuda_rs_decode_dev(poporon_cuda_rs_t *ctx, int mode, uint8_t *data, 
     if (mode < 0 || mode > 2)
         return POPORON_CUDA_ERR_ARG;
     GUARD(ctx->device);
-    if (mode != POPORON_CUDA_MODE_EXTSYN && n < ((size_t)1 << 30) &&
+    /* caller-supplied syndromes also take the bitsliced solver (their rows must be 16-byte aligned for it) */
+    if ((mode != POPORON_CUDA_MODE_EXTSYN || ((uintptr_t)syn & 15u) == 0) && n < ((size_t)1 << 30) &&
         poporon_cuda_rs_path(ctx, 1, data, data_stride, size, parity, parity_stride) == 1) {
         ScratchOrder order(ctx, (cudaStream_t)stream);
-        return rs255_decode(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt, ok,
+        return rs255_decode(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt, syn, ok,
                             corrected, (cudaStream_t)stream);
     }
     return launch_rs_decode_generic(ctx, mode, data, data_stride, size, parity, parity_stride, n, pos, pos_stride, cnt,
                                     syn, ok, corrected, (cudaStream_t)stream);
+}
+
+int poporon_cuda_rs_syndromes_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size_t data_stride, size_t size,
+                                  const uint8_t *parity, size_t parity_stride, size_t n, uint16_t *syndromes,
+                                  void *stream)
+{
+    if (!ctx || (n && (!data || !parity || !syndromes)))
+        return POPORON_CUDA_ERR_ARG;
+    /* the reference computes syndromes only for sizes its padding rule accepts (src/decode.c:418-429) */
+    if (size < 1 || size > (size_t)(ctx->code.nn - ctx->code.nroots))
+        return POPORON_CUDA_ERR_ARG;
+    GUARD(ctx->device);
+    if (n < ((size_t)1 << 30) && ((uintptr_t)syndromes & 7u) == 0 &&
+        poporon_cuda_rs_path(ctx, 1, data, data_stride, size, parity, parity_stride) == 1) {
+        ScratchOrder order(ctx, (cudaStream_t)stream);
+        const int rc = rs255_syndromes(ctx, data, data_stride, size, parity, parity_stride, n, syndromes,
+                                       (cudaStream_t)stream);
+        if (rc != POPORON_CUDA_ERR_UNSUPP)
+            return rc;
+    }
+    return launch_rs_decode_generic(ctx, POPORON_CUDA_MODE_PLAIN, const_cast<uint8_t *>(data), data_stride, size,
+                                    const_cast<uint8_t *>(parity), parity_stride, n, nullptr, 0, nullptr, nullptr,
+                                    nullptr, nullptr, (cudaStream_t)stream, syndromes);
 }
 
 /* ------------------------------------------------------------------------------------------ BCH */

@@ -1156,6 +1156,83 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
     hook.drain();
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Caller-supplied syndromes (reference src/decode.c:446-464: index form, nn = zero) -> the raw syndrome rows and the
+// dirty queue the solver and the general stage work from.  A word is dirty when any entry differs from nn, as in
+// the reference; entries above nn cannot index the reference's tables and are taken as zero (rs_generic.cu does
+// the same).  Clean words are finished here (ok = 1, corrected = 0).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+rs255_extsyn_ingest_kernel(const uint16_t *__restrict__ extsyn, size_t n, const RsTables *__restrict__ gtab,
+                           uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ queue, uint32_t *__restrict__ counter,
+                           uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+{
+    __shared__ uint8_t exp_tab[256];
+    exp_tab[threadIdx.x] = threadIdx.x < 255 ? gtab->alpha_to[threadIdx.x] : (uint8_t)0;
+    __syncthreads();
+    const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t flag = 0;
+    if (cw < n) {
+        const uint4 *row = reinterpret_cast<const uint4 *>(extsyn + cw * 32); // 64 bytes, 16-byte aligned
+        uint32_t out[8];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint4 v = row[q];
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            uint32_t b[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t sidx = (w[k >> 1] >> (16 * (k & 1))) & 0xFFFFu;
+                flag |= sidx != 255u;
+                b[k] = exp_tab[sidx > 255u ? 255u : sidx];
+            }
+            out[2 * q] = b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24);
+            out[2 * q + 1] = b[4] | (b[5] << 8) | (b[6] << 16) | (b[7] << 24);
+        }
+        if (flag) {
+            uint4 *dst = reinterpret_cast<uint4 *>(syn_raw + cw * 32);
+            dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
+            dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
+        } else {
+            if (ok)
+                ok[cw] = 1;
+            if (corrected)
+                corrected[cw] = 0;
+        }
+    }
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, flag != 0);
+    if (ballot) {
+        const int lane = threadIdx.x & 31;
+        uint32_t base = 0;
+        if (lane == 0)
+            base = atomicAdd(counter, (uint32_t)__popc(ballot));
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (flag)
+            queue[base + __popc(ballot & ((1u << lane) - 1u))] = (uint32_t)cw | (3u << 30);
+    }
+}
+
+// The 32 syndromes of every codeword in the reference's index form (calculate_syndrome_u8, src/decode.c:232-416,
+// leaves index_of[S_j], nn = 255 for zero): from the screen kernel's dirty bitmap and raw rows.  One thread per
+// group of four syndromes.
+__global__ void __launch_bounds__(256)
+rs255_syn_export_kernel(const uint32_t *__restrict__ dirty, const uint8_t *__restrict__ syn_raw, size_t n,
+                        const RsTables *__restrict__ gtab, uint16_t *__restrict__ out)
+{
+    __shared__ uint8_t log_tab[256];
+    log_tab[threadIdx.x] = gtab->index_of[threadIdx.x];
+    __syncthreads();
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t cw = t >> 3;
+    if (cw >= n)
+        return;
+    uint32_t v = 0;
+    if ((dirty[cw >> 5] >> (cw & 31u)) & 1u)
+        v = reinterpret_cast<const uint32_t *>(syn_raw + cw * 32)[t & 7u];
+    const uint32_t a = log_tab[v & 0xFFu], b = log_tab[(v >> 8) & 0xFFu], c = log_tab[(v >> 16) & 0xFFu], d = log_tab[v >> 24];
+    reinterpret_cast<uint2 *>(out + cw * 32)[t & 7u] = make_uint2(a | (b << 16), c | (d << 16));
+}
+
 int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
 {
     if (n <= ctx->queue_cap)
@@ -1316,7 +1393,7 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
 
 int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stride, size_t size, uint8_t *parity,
                  size_t parity_stride, size_t n, const uint32_t *pos, size_t pos_stride, const uint32_t *cnt,
-                 uint8_t *ok, uint32_t *corrected, cudaStream_t stream)
+                 const uint16_t *extsyn, uint8_t *ok, uint32_t *corrected, cudaStream_t stream)
 {
     if (n == 0)
         return 0;
@@ -1335,7 +1412,12 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     A.dmask = dmask;
     A.syn = ctx->d_rem;
     FftShape shape;
-    if (!ctx->use_lfsr && rs255_fft_shape_ok(1, data, data_stride, size, parity, parity_stride, &shape)) {
+    if (mode == POPORON_CUDA_MODE_EXTSYN) {
+        // the syndromes come from the caller: no screen pass, the rows and the queue are built from them
+        ProfScope prof(ctx, PROF_COMPACT, stream);
+        rs255_extsyn_ingest_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(
+            extsyn, n, ctx->d_tables, ctx->d_rem, ctx->d_queue, ctx->d_counters, ok, corrected);
+    } else if (!ctx->use_lfsr && rs255_fft_shape_ok(1, data, data_stride, size, parity, parity_stride, &shape)) {
         rc = ensure_slab(ctx);
         if (rc != 0)
             return rc;
@@ -1369,8 +1451,8 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     // larger than one wave would leave a thin second wave behind the grid-stride loop
     const unsigned cblocks = (unsigned)(ctx->sm_count * ctx->correct_ctas_per_sm);
     const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
-    if (mode == POPORON_CUDA_MODE_PLAIN) {
-        // bitsliced solver first; what it declines lands in queue2 for the literal stage below
+    if (mode == POPORON_CUDA_MODE_PLAIN || mode == POPORON_CUDA_MODE_EXTSYN) {
+        // bitsliced solver first (with the caller's syndromes error_correction_u8 runs exactly as in plain mode); what it declines lands in queue2 for the literal stage below
         uint32_t *queue2 = dmask + tiles * 64;
         const size_t groups = (n + 1023) / 1024;
         const size_t cap = (size_t)ctx->sm_count * kSolveWarpsPerSM;
@@ -1395,6 +1477,32 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     }
     ctx->launches += 3;
     return check(cudaGetLastError(), "rs255 decode launch");
+}
+
+int rs255_syndromes(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
+                    size_t parity_stride, size_t n, uint16_t *out, cudaStream_t stream)
+{
+    if (n == 0)
+        return 0;
+    FftShape shape;
+    if (!rs255_fft_shape_ok(1, data, data_stride, size, parity, parity_stride, &shape))
+        return POPORON_CUDA_ERR_UNSUPP;
+    int rc = ensure_scratch(ctx, n);
+    if (rc == 0)
+        rc = ensure_slab(ctx);
+    if (rc != 0)
+        return rc;
+    uint32_t *dmask = ctx->d_queue + ((n + 3) & ~(size_t)3);
+    {
+        ProfScope prof(ctx, PROF_SCREEN, stream);
+        rc = rs255_fft_screen(ctx, shape, data, data_stride, size, parity, parity_stride, n, ctx->d_slab, dmask,
+                              ctx->d_rem, stream);
+    }
+    if (rc != 0)
+        return rc;
+    rs255_syn_export_kernel<<<(unsigned)((n * 8 + 255) / 256), 256, 0, stream>>>(dmask, ctx->d_rem, n, ctx->d_tables, out);
+    ctx->launches += 2;
+    return check(cudaGetLastError(), "rs255 syndrome export launch");
 }
 
 } // namespace ppcu

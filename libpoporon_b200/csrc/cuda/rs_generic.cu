@@ -109,7 +109,7 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
                          size_t size, uint8_t *parity, size_t parity_stride, size_t n,
                          const uint32_t *__restrict__ pos, size_t pos_stride, const uint32_t *__restrict__ cnt,
                          const uint16_t *__restrict__ extsyn, uint8_t *__restrict__ ok,
-                         uint32_t *__restrict__ corrected)
+                         uint32_t *__restrict__ corrected, uint16_t *__restrict__ synout)
 {
     __shared__ SmemTables T;
     __shared__ uint8_t mtab[MAXR <= 32 ? 32 * 256 : 4]; // mtab[i][v] = v * alpha^((fcr + i) * prim), src/decode.c:375-415
@@ -195,7 +195,11 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
                 any |= syn[i];
                 syn[i] = T.index_of[syn[i]];
             }
-            if (!any) {
+            if (synout) { // syndromes-only call: index form, as calculate_syndrome_u8 leaves them (src/decode.c:405-413)
+                for (int i = 0; i < nr; i++)
+                    synout[cw * (size_t)nr + i] = syn[i];
+                success = true;
+            } else if (!any) {
                 success = true;
             } else if (mode == POPORON_CUDA_MODE_ERASURE) {
                 ec = cnt[cw];
@@ -205,7 +209,9 @@ rs_decode_generic_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, 
             }
         }
     }
-    if constexpr (MAXR <= 32) {
+    if (synout != nullptr) {
+        // (uniform over the launch: nobody enters the correction stage)
+    } else if constexpr (MAXR <= 32) {
         const bool r = rs_correct<MAXR, CtaPhaseSync>(c, T, d, size, p, wk, syn, erasure ? ec : 0u,
                                                       erasure ? pos + cw * pos_stride : nullptr, pos_stride, erasure, pad,
                                                       ncorr, need);
@@ -253,7 +259,7 @@ int launch_rs_encode_generic(poporon_cuda_rs *ctx, const uint8_t *data, size_t d
 int launch_rs_decode_generic(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stride, size_t size,
                              uint8_t *parity, size_t parity_stride, size_t n, const uint32_t *pos, size_t pos_stride,
                              const uint32_t *cnt, const uint16_t *syn, uint8_t *ok, uint32_t *corrected,
-                             cudaStream_t stream)
+                             cudaStream_t stream, uint16_t *synout)
 {
     if (n == 0)
         return 0;
@@ -262,11 +268,11 @@ int launch_rs_decode_generic(poporon_cuda_rs *ctx, int mode, uint8_t *data, size
     if (ctx->code.nroots <= 32)
         rs_decode_generic_kernel<32><<<blocks, threads, SmemWork<32>::kBytes, stream>>>(ctx->code, ctx->d_tables, mode, data, data_stride,
                                                                      size, parity, parity_stride, n, pos, pos_stride,
-                                                                     cnt, syn, ok, corrected);
+                                                                     cnt, syn, ok, corrected, synout);
     else
         rs_decode_generic_kernel<255><<<blocks, threads, 0, stream>>>(ctx->code, ctx->d_tables, mode, data,
                                                                       data_stride, size, parity, parity_stride, n, pos,
-                                                                      pos_stride, cnt, syn, ok, corrected);
+                                                                      pos_stride, cnt, syn, ok, corrected, synout);
     ctx->launches++;
     return check(cudaGetLastError(), "rs_decode_generic launch");
 }

@@ -40,9 +40,9 @@ static int classify(const void *const *ptrs, size_t count, int *device)
 
 static bool run_job(poporon_t *h, const pp_job_t *job, void *stream, bool async)
 {
-    const void *ptrs[7] = {job->data, job->parity, job->pos, job->cnt, job->syn, job->ok, job->corrected};
+    const void *ptrs[8] = {job->data, job->parity, job->pos, job->cnt, job->syn, job->ok, job->corrected, job->syn_out};
     int device = -1;
-    const int kind = classify(ptrs, 7, &device);
+    const int kind = classify(ptrs, 8, &device);
     if (kind < 0)
         return false;
     if (kind == 2)
@@ -109,6 +109,27 @@ bool poporon_encode_batch_async(poporon_t *h, const uint8_t *data, size_t data_s
     if (!job_args_ok(h, &j))
         return false;
     return run_job(h, &j, stream, true);
+}
+
+bool poporon_syndromes_batch(poporon_t *h, const uint8_t *data, size_t data_stride, size_t size,
+                             const uint8_t *parity, size_t parity_stride, size_t n, uint16_t *syndromes)
+{
+    pp_job_t j;
+    memset(&j, 0, sizeof j);
+    j.op = 2;
+    j.data = (uint8_t *)data;
+    j.data_stride = data_stride;
+    j.size = size;
+    j.parity = (uint8_t *)parity;
+    j.parity_stride = parity_stride;
+    j.n = n;
+    j.syn_out = syndromes;
+    if (!h || !rs_handle(h) || !data || !parity || !syndromes)
+        return false;
+    /* the reference reaches calculate_syndrome_u8 only for sizes its padding rule accepts (src/decode.c:418-429) */
+    if (size < 1 || size > (size_t)(h->rs->gf->nn - h->rs->nroots))
+        return false;
+    return run_job(h, &j, NULL, false);
 }
 
 static bool decode_common(poporon_t *h, int mode, uint8_t *data, size_t data_stride, size_t size, uint8_t *parity,

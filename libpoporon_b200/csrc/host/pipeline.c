@@ -192,6 +192,9 @@ const char *poporon_kernel_profile_read(poporon_t *h, int kernel, uint64_t *laun
 static int launch(poporon_t *h, pp_lane_t *lane, const pp_job_t *j, void *stream)
 {
     if (h->fec_type == PPLN_FEC_RS) {
+        if (j->op == 2)
+            return poporon_cuda_rs_syndromes_dev(lane->rs, j->data, j->data_stride, j->size, j->parity,
+                                                 j->parity_stride, j->n, j->syn_out, stream);
         if (j->op == 0)
             return poporon_cuda_rs_encode_dev(lane->rs, j->data, j->data_stride, j->size, j->parity, j->parity_stride,
                                               j->n, j->ok, stream);
@@ -294,7 +297,7 @@ static bool run_lane_body(lane_task_t *t)
         /* merged when the two spans overlap (e.g. packed records) */
         const bool merged = !(hp >= hd + dspan || hd >= hp + pspan);
         uint8_t *lo_ptr = hd, *hi_ptr = hd + dspan;
-        uint8_t *dd, *dp, *d_ok, *d_cor, *d_pos = NULL, *d_cnt = NULL, *d_syn = NULL;
+        uint8_t *dd, *dp, *d_ok, *d_cor, *d_pos = NULL, *d_cnt = NULL, *d_syn = NULL, *d_sout = NULL;
         size_t aux_need, off;
         pp_job_t dj;
 
@@ -321,7 +324,9 @@ static bool run_lane_body(lane_task_t *t)
         if (j->mode == POPORON_CUDA_MODE_ERASURE)
             aux_need += m * j->pos_stride * 4 + m * 4;
         if (j->mode == POPORON_CUDA_MODE_EXTSYN)
-            aux_need += m * nroots * 2;
+            aux_need = align_up(aux_need, 16) + m * nroots * 2;
+        if (j->op == 2)
+            aux_need = align_up(aux_need, 16) + m * nroots * 2;
         if (!ensure(dev, &sl->d_aux, &sl->aux_cap, aux_need))
             return false;
         d_ok = sl->d_aux;
@@ -337,7 +342,7 @@ static bool run_lane_body(lane_task_t *t)
             if (poporon_cuda_memcpy_h2d(dev, dd, hd, dspan, sl->stream) != 0)
                 return false;
             /* encode only writes parity, but gaps between parity records must survive the round trip */
-            if ((j->op == 1 || j->parity_stride != P) && poporon_cuda_memcpy_h2d(dev, dp, hp, pspan, sl->stream) != 0)
+            if ((j->op != 0 || j->parity_stride != P) && poporon_cuda_memcpy_h2d(dev, dp, hp, pspan, sl->stream) != 0)
                 return false;
         }
         if (j->mode == POPORON_CUDA_MODE_ERASURE && j->op == 1) {
@@ -350,10 +355,17 @@ static bool run_lane_body(lane_task_t *t)
                 return false;
         }
         if (j->mode == POPORON_CUDA_MODE_EXTSYN && j->op == 1) {
+            off = align_up(off, 16); /* 16-byte aligned rows: the bitsliced path reads them as vectors */
             d_syn = sl->d_aux + off;
             off += m * nroots * 2;
             if (poporon_cuda_memcpy_h2d(dev, d_syn, j->syn + c0 * nroots, m * nroots * 2, sl->stream))
                 return false;
+        }
+
+        if (j->op == 2) {
+            off = align_up(off, 16);
+            d_sout = sl->d_aux + off;
+            off += m * nroots * 2;
         }
 
         /* ---- kernels ---- */
@@ -366,6 +378,7 @@ static bool run_lane_body(lane_task_t *t)
         dj.syn = (const uint16_t *)d_syn;
         dj.ok = d_ok;
         dj.corrected = (uint32_t *)d_cor;
+        dj.syn_out = (uint16_t *)d_sout;
         /* The device context owns ONE set of decode scratch (dirty queue, syndrome rows, counters), so the kernel
          * sections of consecutive chunks must not overlap even though they sit on different streams: wait for the
          * other slot's kernels; copies on either side still overlap them. */
@@ -385,6 +398,11 @@ static bool run_lane_body(lane_task_t *t)
         sl->kdone_set = true;
 
         /* ---- device -> host ---- */
+        if (j->op == 2) {
+            if (poporon_cuda_memcpy_d2h(dev, j->syn_out + c0 * nroots, d_sout, m * nroots * 2, sl->stream) != 0)
+                return false;
+            continue;
+        }
         if (j->op == 0) {
             if (poporon_cuda_memcpy_d2h(dev, hp, dp, pspan, sl->stream) != 0)
                 return false;

@@ -114,7 +114,7 @@ void pp_handle_release_lanes(poporon_t *h);
 
 /* pipeline.c */
 typedef struct {
-    int op; /* 0 encode, 1 decode */
+    int op; /* 0 encode, 1 decode, 2 syndromes only (RS) */
     int mode;
     uint8_t *data;
     size_t data_stride, size;
@@ -127,6 +127,7 @@ typedef struct {
     const uint16_t *syn;
     uint8_t *ok;
     uint32_t *corrected;
+    uint16_t *syn_out; /* op 2: [n][nroots] */
 } pp_job_t;
 
 bool pp_lane_prepare(poporon_t *h, pp_lane_t *lane);

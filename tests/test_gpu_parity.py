@@ -204,7 +204,7 @@ def test_rs_default_erasures_vs_oracle(gpu_device, orc):
 
 def test_rs_default_extsyn_vs_oracle(gpu_device, orc):
     rng = np.random.default_rng(13)
-    n, size = 3000, 223
+    n, size = 9000, 223
     msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
     with api.Poporon.rs_default() as h:
         par = _gpu_encode(h, msg, 32)
@@ -218,9 +218,99 @@ def test_rs_default_extsyn_vs_oracle(gpu_device, orc):
         for i in range(500):
             L, a = int(rng.integers(0, 255)), int(rng.integers(0, 255))
             syn[i] = (a + (1 + np.arange(32)) * (254 - L)) % 255
+        assert h.profile(True)
         got = _gpu_decode(h, msg, par, MODE_EXTSYN, syn=syn)
+        prof = h.profile_read()
+        # caller-supplied syndromes run on the bitsliced solver, not on the per-thread kernels
+        assert prof.get("rs255_solve_kernel", (0, 0))[0] >= 1 and "rs_generic kernels" not in prof, prof
         _assert_same(got, orc.rs_decode(msg, par, RS_DEFAULT, MODE_EXTSYN, syn=syn), "extsyn")
         assert got[2][:500].all() and (got[3][:500] == 1).all()
+
+
+def _np_syndromes(cw, m, poly, fcr, prim, nr):
+    """index-form syndromes of full-length words cw [n, nn] by Horner in numpy: S_i = r(alpha^((fcr + i) * prim)),
+    r_0 first = highest power (reference src/decode.c:232-416); nn = zero"""
+    nn = (1 << m) - 1
+    exp = np.zeros(2 * nn + 2, np.int64)
+    log = np.full(nn + 1, nn, np.int64)
+    x = 1
+    for i in range(nn):
+        exp[i] = x
+        log[x] = i
+        x <<= 1
+        if x > nn:
+            x ^= poly
+    exp[nn:2 * nn] = exp[:nn]
+    out = np.zeros((cw.shape[0], nr), np.uint16)
+    for i in range(nr):
+        root = ((fcr + i) * prim) % nn
+        acc = np.zeros(cw.shape[0], np.int64)
+        for j in range(cw.shape[1]):
+            nz = acc != 0
+            acc = np.where(nz, exp[(log[acc] + root) % nn], 0) ^ cw[:, j]
+        out[:, i] = log[acc]
+    return out
+
+
+def test_syndromes_only_output(gpu_device, orc):
+    """the 32 index-form syndromes as calculate_syndrome_u8 leaves them, handed to the caller; the
+    array round-trips through the external-syndrome decode with the outcome of a plain decode."""
+    rng = np.random.default_rng(31)
+    n = 40000
+    msg = rng.integers(0, 256, (n, 223), dtype=np.uint8)
+    with api.Poporon.rs_default() as h:
+        par = _gpu_encode(h, msg, 32)
+        cw = np.concatenate([msg, par], 1)
+        # SURVEY A.7 known answer: one error of magnitude 1 on the first symbol -> 254, 253, ..., 223
+        cw[0, 0] ^= 1
+        _inject(rng, cw[1:], 255, 18)
+        cw[5] = np.concatenate([msg[5], par[5]])  # a clean word: all syndromes 255
+        syn = np.full((n, 32), 0xBEEF, np.uint16)
+        d, p = np.ascontiguousarray(cw[:, :223]), np.ascontiguousarray(cw[:, 223:])
+        assert h.syndromes_batch(d, 223, 223, p, 32, n, syn)
+        assert (d == cw[:, :223]).all() and (p == cw[:, 223:]).all()  # nothing corrected
+        assert syn[0].tolist() == list(range(254, 222, -1)) and (syn[5] == 255).all()
+        assert (syn[:1500] == _np_syndromes(cw[:1500], 8, 0x11D, 1, 1, 32)).all()
+        # packed records give the same array
+        syn2 = np.zeros((n, 32), np.uint16)
+        rec = np.ascontiguousarray(cw)
+        assert h.syndromes_batch(rec.ctypes.data, 255, 223, rec.ctypes.data + 223, 255, n, syn2)
+        assert (syn2 == syn).all()
+        # round trip: decoding from these syndromes = plain decode (reference src/decode.c:446-464 against :475-477)
+        want = orc.rs_decode(cw[:, :223], cw[:, 223:])
+        _assert_same(_gpu_decode(h, cw[:, :223], cw[:, 223:], MODE_EXTSYN, syn=syn), want, "syndromes round trip")
+        # shortened words
+        size = 100
+        par_s = _gpu_encode(h, msg[:2000, :size], 32)
+        cws = np.concatenate([msg[:2000, :size], par_s], 1)
+        _inject(rng, cws, 255, 10)
+        syn_s = np.zeros((2000, 32), np.uint16)
+        assert h.syndromes_batch(np.ascontiguousarray(cws[:, :size]), size, size, np.ascontiguousarray(cws[:, size:]), 32,
+                                 2000, syn_s)
+        full = np.concatenate([np.zeros((2000, 223 - size), np.uint8), cws], 1)
+        assert (syn_s == _np_syndromes(full, 8, 0x11D, 1, 1, 32)).all()
+        # sizes outside the padding rule are refused
+        assert not h.syndromes_batch(d, 224, 224, p, 32, 4, syn) and not h.syndromes_batch(d, 0, 0, p, 32, 4, syn)
+
+
+@pytest.mark.parametrize("params", [(8, 0x11D, 1, 1, 16), (8, 0x187, 112, 11, 32), (4, 0x13, 1, 2, 8)])
+def test_syndromes_only_general_parameters(gpu_device, orc, params):
+    m, poly, fcr, prim, nr = params
+    nn = (1 << m) - 1
+    K = nn - nr
+    rng = np.random.default_rng(77)
+    n = 600
+    with _rs(params) as h:
+        msg = rng.integers(0, nn + 1, (n, K), dtype=np.uint8)
+        par = _gpu_encode(h, msg, nr)
+        cw = np.concatenate([msg, par], 1)
+        _inject(rng, cw[1:], nn, nr // 2 + 1)
+        syn = np.zeros((n, nr), np.uint16)
+        assert h.syndromes_batch(np.ascontiguousarray(cw[:, :K]), K, K, np.ascontiguousarray(cw[:, K:]), nr, n, syn)
+        assert (syn[0] == nn).all()
+        assert (syn == _np_syndromes(cw, m, poly, fcr, prim, nr)).all()
+        want = orc.rs_decode(cw[:, :K], cw[:, K:], params)
+        _assert_same(_gpu_decode(h, cw[:, :K], cw[:, K:], MODE_EXTSYN, syn=syn), want, f"{params} syndromes round trip")
 
 
 @pytest.mark.parametrize("params", [(8, 0x187, 112, 11, 32), (8, 0x11D, 0, 1, 16), (8, 0x11D, 1, 2, 16),
