@@ -51,6 +51,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="codewords in the CPU baseline sample (0 = auto)")
     ap.add_argument("--mem-budget-gb", type=float, default=140.0)
+    ap.add_argument("--split", choices=["ranks", "threads"], default="ranks",
+                    help="ranks: one process per GPU (torchrun, the contract line).  threads: ONE process, one host "
+                         "thread per device inside libpoporon (poporon_use_devices), host-resident batch, no "
+                         "torch.distributed / NCCL - the arrangement north_star describes")
     ap.add_argument("--verify", choices=["sample", "all", "none"], default="sample",
                     help="untimed comparison with the CPU reference after the timed loop: a 1 Mi prefix + a 64 Ki "
                          "strided sample of the batch (default), the whole batch, or nothing")
@@ -558,10 +562,97 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_threads(args):
+    """north_star's multi-GPU arrangement: one process, the batch split contiguously over the devices by the library
+    (one host thread per device, csrc/host/pipeline.c), no collective.  Host-resident data only, so `value` IS the
+    end-to-end number (copies inside the timed region)."""
+    import numpy as np
+    import torch
+
+    import libpoporon_b200.api as api
+
+    N = args.gpus
+    if torch.cuda.device_count() < N:
+        raise SystemExit(f"--split threads --gpus {N}: only {torch.cuda.device_count()} devices visible")
+    n_per, n = args.ncw, args.ncw * N
+    h = api.Poporon.rs_default()
+    assert h.use_devices(list(range(N)))
+    hmsg = torch.empty(n * K_MSG, dtype=torch.uint8).pin_memory()
+    hpar = torch.empty(n * K_PAR, dtype=torch.uint8).pin_memory()
+    hrec = torch.empty(n * K_CW, dtype=torch.uint8).pin_memory()
+    bad = torch.empty(n * K_CW, dtype=torch.uint8)  # the corrupted records, copied into hrec before every step
+    hok = torch.empty(n, dtype=torch.uint8).pin_memory()
+    hcor = torch.empty(n, dtype=torch.int32).pin_memory()
+    # workload: generated on device 0 slice by slice (same generators and seeds as the ranks split)
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    stream = torch.cuda.current_stream().cuda_stream
+    gen = api.Poporon.rs_default()
+    want_par = torch.empty(n * K_PAR, dtype=torch.uint8)
+    for r in range(N):
+        rec = torch.empty(n_per * K_CW, dtype=torch.uint8, device=dev)
+        api.synth_fill(0, rec.data_ptr(), K_CW, K_MSG, n_per, SEED_MSG, r * n_per, stream)
+        assert gen.encode_batch_async(rec.data_ptr(), K_CW, K_MSG, rec.data_ptr() + K_MSG, K_CW, n_per, stream)
+        torch.cuda.synchronize()
+        v = rec.view(n_per, K_CW)
+        hmsg.view(n, K_MSG)[r * n_per:(r + 1) * n_per].copy_(v[:, :K_MSG])
+        want_par.view(n, K_PAR)[r * n_per:(r + 1) * n_per].copy_(v[:, K_MSG:])
+        api.synth_inject(0, rec.data_ptr(), K_CW, K_CW, n_per, SEED_ERR, r * n_per, 0, 0, args.emax, 0, stream)
+        torch.cuda.synchronize()
+        bad.view(n, K_CW)[r * n_per:(r + 1) * n_per].copy_(v)
+        del rec, v
+    gen.close()
+    torch.cuda.empty_cache()
+    samplers = [ClockSampler(i) for i in range(N)]
+    K, W = max(1, args.e2e_steps), 1
+    tot = enc_tot = 0.0
+    for s in range(W + K):
+        hrec.copy_(bad)
+        hpar.zero_()
+        if s == W:
+            for sp in samplers:
+                sp.start()
+            l0 = h.launches
+        t0 = time.perf_counter()
+        assert h.encode_batch(hmsg.data_ptr(), K_MSG, K_MSG, hpar.data_ptr(), K_PAR, n)
+        t1 = time.perf_counter()
+        assert h.decode_batch(hrec.data_ptr(), K_CW, K_MSG, hrec.data_ptr() + K_MSG, K_CW, n, hok.data_ptr(),
+                              hcor.data_ptr())
+        t2 = time.perf_counter()
+        if s >= W:
+            tot += t2 - t0
+            enc_tot += t1 - t0
+    clocks = [sp.stop() for sp in samplers]
+    launches = h.launches - l0
+    assert bool(hok.all().item()), "a correctable codeword failed to decode"
+    assert torch.equal(hpar, want_par), "parity differs from the single-device encode"
+    assert torch.equal(hrec.view(n, K_CW)[:, :K_MSG], hmsg.view(n, K_MSG)) and \
+        torch.equal(hrec.view(n, K_CW)[:, K_MSG:], want_par.view(n, K_PAR)), "decoded records differ"
+    per_step = tot / K
+    value = 2 * n * K_MSG / per_step / 1e9
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": N, "steps": K, "warmup": W,
+            "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic", "split": "threads (one process, one host thread per device, no NCCL)",
+            "config": workload_config(args, corrupted_buffers=1, reinject_in_timed_region=False,
+                                      mean_errors_per_codeword=float(hcor.float().mean().item())),
+            "phases": {"encode_ms": enc_tot / K * 1e3, "decode_ms": (tot - enc_tot) / K * 1e3},
+            "clocks": {"sm_mhz": min(c.get("sm_mhz") or 0 for c in clocks), "sm_max_mhz": clocks[0].get("sm_max_mhz"),
+                       "reasons": sorted({r for c in clocks for r in c.get("reasons", [])})},
+            "gpu_launches": int(launches),
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": n * (K_MSG + K_CW),
+                    "d2h_bytes_per_step": n * (K_PAR + K_CW + 5), "ms_per_step": per_step * 1e3, "steps": K,
+                    "api": "poporon_use_devices + poporon_encode_batch + poporon_decode_batch on page-locked host "
+                           "buffers, ONE call over all devices"}}
+    print(json.dumps(line), flush=True)
+    h.close()
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.split == "threads":
+        run_threads(args)
     else:
         run_ours(args)
 

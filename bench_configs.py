@@ -324,9 +324,93 @@ def run_load(args, torch, api, dev):
     h.close()
 
 
+def run_load5(args, torch, api, dev):
+    """BASELINE configs[4] as written: 128 Mi codewords in total, sharded contiguously over --gpus N devices (strong
+    scaling), i.i.d. symbol-error rates 0 / 1 / 5 %, next to the reference's CPU path on all host cores.  One process:
+    the devices are driven from one host thread through the asynchronous device-pointer API (no collective, no NCCL);
+    the time of a pass is the largest per-device time between CUDA events on that device's stream."""
+    import time
+
+    import numpy as np
+
+    N = args.gpus
+    total = args.ncw or 128 * 1024 * 1024
+    per = total // N
+    hs, cleans, works, oks, cors, streams = [], [], [], [], [], []
+    for d in range(N):
+        torch.cuda.set_device(d)
+        dv = torch.device("cuda", d)
+        st = torch.cuda.current_stream(dv).cuda_stream
+        h = api.Poporon.rs_default()
+        clean = torch.empty(per * K_CW, dtype=torch.uint8, device=dv)
+        api.synth_fill(d, clean.data_ptr(), K_CW, K_MSG, per, 0x5EED0001, d * per, st)
+        assert h.encode_batch_async(clean.data_ptr(), K_CW, K_MSG, clean.data_ptr() + K_MSG, K_CW, per, st)
+        hs.append(h), cleans.append(clean), works.append(torch.empty_like(clean)), streams.append(st)
+        oks.append(torch.empty(per, dtype=torch.uint8, device=dv))
+        cors.append(torch.empty(per, dtype=torch.int32, device=dv))
+    for d in range(N):
+        torch.cuda.synchronize(d)
+    # CPU arm: the compiled reference (else the restatement) on all cores, on a bounded sample per load
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oraclelib import Oracle, have_reference
+
+    kind = "reference" if have_reference() else "port"
+    orc = Oracle(kind)
+    cores = os.cpu_count() or 1
+    sample = min(per, cores * 20000)
+    for p_ppm in (0, 10000, 50000):
+        times = []
+        for rep in range(args.reps + 1):
+            evs = []
+            for d in range(N):
+                torch.cuda.set_device(d)
+                works[d].copy_(cleans[d])
+                if p_ppm:
+                    api.synth_inject(d, works[d].data_ptr(), K_CW, K_CW, per, 0x5EED0500 + rep, d * per, 1, 0, 0, p_ppm,
+                                     streams[d])
+            for d in range(N):
+                torch.cuda.synchronize(d)
+            if rep == args.reps:
+                rx_s = works[0].view(per, K_CW)[:sample].cpu().numpy()
+            for d in range(N):
+                torch.cuda.set_device(d)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                assert hs[d].decode_batch_async(works[d].data_ptr(), K_CW, K_MSG, works[d].data_ptr() + K_MSG, K_CW, per,
+                                                oks[d].data_ptr(), cors[d].data_ptr(), stream=streams[d])
+                e1.record()
+                evs.append((e0, e1))
+            for d in range(N):
+                torch.cuda.synchronize(d)
+            if rep:
+                times.append(max(e0.elapsed_time(e1) for e0, e1 in evs))
+        ok_frac = float(np.mean([float(o.float().mean().item()) for o in oks]))
+        mean_cor = float(np.mean([float(c.float().mean().item()) for c in cors]))
+        t0 = time.perf_counter()
+        wd, wp, wok, wcor = orc.rs_decode(np.ascontiguousarray(rx_s[:, :K_MSG]), np.ascontiguousarray(rx_s[:, K_MSG:]),
+                                          threads=cores)
+        cpu_s = time.perf_counter() - t0
+        got = works[0].view(per, K_CW)[:sample].cpu().numpy()
+        mism = int(((got[:, :K_MSG] != wd).any(1) | (got[:, K_MSG:] != wp).any(1) |
+                    (oks[0][:sample].cpu().numpy() != wok) | (cors[0][:sample].cpu().numpy().astype(np.uint32) != wcor)).sum())
+        assert mism == 0, f"decode differs from the CPU {kind} on {mism} sampled codewords"
+        t = sum(times) / len(times)
+        emit(args, {"workload": "configs[4]: RS(255,223) decode, 128 Mi codewords in total, i.i.d. symbol error rate %.0f %%"
+                                % (p_ppm / 1e4), "gpus": N, "codewords_total": per * N, "codewords_per_gpu": per,
+                    "scaling": "strong", "decode_ms": t, "payload_GBps": per * N * K_MSG / t / 1e6,
+                    "alg_GBps": per * N * (K_CW + 5 + mean_cor) / t / 1e6,
+                    "hbm_frac_per_gpu": per * (K_CW + 5 + mean_cor) / t / 1e6 / hbm_peak(), "ok_fraction": ok_frac,
+                    "mean_corrected": mean_cor,
+                    "cpu": {"kind": kind, "cores": cores, "sample": sample, "payload_GBps": sample * K_MSG / cpu_s / 1e9,
+                            "mismatches_vs_gpu": mism}})
+    for h in hs:
+        h.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("which", nargs="*", default=["erasure", "bch", "load"])
+    ap.add_argument("--gpus", type=int, default=1, help="load5: devices the 128 Mi codewords are sharded over")
     ap.add_argument("--ncw", type=int, default=0, help="codewords (0 = the configuration's own size)")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--out", default="")
@@ -340,7 +424,7 @@ def main():
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
     for w in args.which:
-        {"erasure": run_erasure, "bch": run_bch, "bch31": run_bch31, "load": run_load}[w](args, torch, api, dev)
+        {"erasure": run_erasure, "bch": run_bch, "bch31": run_bch31, "load": run_load, "load5": run_load5}[w](args, torch, api, dev)
         torch.cuda.empty_cache()
 
 
