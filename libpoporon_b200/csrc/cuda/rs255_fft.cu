@@ -36,7 +36,8 @@ namespace ppcu {
 namespace {
 
 constexpr int kTile = 1024;  // codewords per CTA tile
-constexpr int kWarps = 8;
+constexpr int kWarps = 16;                           // 128 registers per thread: four warps per scheduler
+constexpr int kS1Warps = 8, kS2Warps = 8;            // phase B roles: warps 0..7 / 8..15
 constexpr int kSubPerWarp = 32 / kWarps;
 constexpr int kSlotBytes = 1024;                    // one symbol of the tile: [lane-slot 32][8 planes]
 constexpr size_t kSlabBytes = 255 * kSlotBytes;     // per CTA
@@ -44,7 +45,8 @@ constexpr int kRingSlots = 4;
 constexpr int kRingSlotBytes = 15 * 1024;           // R_c: [k 15][half 2][lane 32][4 planes]
 constexpr int kRingBytes = kRingSlots * kRingSlotBytes;
 constexpr int kMaxBuf = 8448;                       // bytes of one sub-tile buffer (rows of 32 codewords)
-constexpr int kBarBytes = 1024;                      // mbarriers [0, 192) + the S2 warps' dirty words [256, 768)
+constexpr int kBarBytes = 2048;                      // mbarriers [0, 192) + the S2 warps' dirty words [256, 1280)
+constexpr int kOutStageBytes = 256 * 128;            // SCREEN: the 256 syndrome planes of a tile, [plane][lane-slot]
 
 enum { MODE_SCREEN = 0, MODE_ENCODE = 1 };
 
@@ -228,24 +230,21 @@ __device__ __forceinline__ void subset_table(uint32_t b0, uint32_t b1, uint32_t 
 
 // ---------------------------------------------------------------------------------------------------
 // shared memory map
-//   [0, kBarBytes)                       mbarriers: buffer-full [kWarps][2], ring full [4], ring empty [4]; nz words
+//   [0, kBarBytes)                       mbarriers: buffer-full [kWarps], ring full [4], ring empty [4]; nz words
 //   [kBarBytes, +kRingBytes)             S1 -> S2 ring
-//   [.., + kWarps * 2 * bufbytes)        sub-tile buffers: warp w, buffer b at (2w + b) * bufbytes
-// The output stage (256 planes x 128 B = 32 KB) reuses buffer 1 of warps 0..3 (free during phase B and the output).
+//   [.., + kWarps * bufbytes)            sub-tile buffers, one per warp
+//   [.., + kOutStageBytes)               SCREEN: the output stage (256 planes x 128 B)
 // ---------------------------------------------------------------------------------------------------
 struct Smem {
-    uint32_t base, bars, ring, bufs;
+    uint32_t base, bars, ring, bufs, outstage;
     int bufbytes;
-    __device__ __forceinline__ uint32_t bar_buf(int w, int b) const { return bars + 8u * (uint32_t)(2 * w + b); }
+    __device__ __forceinline__ uint32_t bar_buf(int w) const { return bars + 8u * (uint32_t)w; }
     __device__ __forceinline__ uint32_t bar_full(int s) const { return bars + 128u + 8u * (uint32_t)s; }
     __device__ __forceinline__ uint32_t bar_empty(int s) const { return bars + 160u + 8u * (uint32_t)s; }
     __device__ __forceinline__ uint32_t nzword(int u, int lane) const { return bars + 256u + 4u * (uint32_t)(32 * u + lane); }
-    __device__ __forceinline__ uint32_t buf(int w, int b) const { return bufs + (uint32_t)((2 * w + b) * bufbytes); }
+    __device__ __forceinline__ uint32_t buf(int w) const { return bufs + (uint32_t)(w * bufbytes); }
     // plane p (0..255) of the output stage, this lane
-    __device__ __forceinline__ uint32_t outplane(int p, int lane) const
-    {
-        return buf(p >> 6, 1) + (uint32_t)((p & 63) * 128 + lane * 4);
-    }
+    __device__ __forceinline__ uint32_t outplane(int p, int lane) const { return outstage + (uint32_t)(p * 128 + lane * 4); }
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -365,67 +364,74 @@ __device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t buf
 // ---------------------------------------------------------------------------------------------------
 // phase B
 // ---------------------------------------------------------------------------------------------------
-// S1: the class tasks t = warp, warp + 4, ... (class c = 16 - t, so that S2 meets the classes in Horner order)
-__device__ __forceinline__ void s1_run(const Smem &sm, const uint8_t *slab, int warp, int lane, uint32_t &gtask)
+// S1: 34 half-class tasks g2 = 2 t + lh (class c = 16 - t, so that S2 meets the classes in Horner order; lh = which
+// sixteen lane-slots of the tile).  A lane owns one GF(16) half (4 planes) of one lane-slot: lane = 2 * slot + half,
+// so that a warp reads 512 contiguous bytes per symbol and a thread holds 15 x 4 planes only.
+__device__ __forceinline__ void ldg128(const void *p, uint32_t (&v)[4])
 {
-    uint32_t lo[15][4], hi[15][4];
+    asm volatile("ld.global.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void s1_run(const Smem &sm, const uint8_t *slab, int warp, int lane, uint32_t gtask)
+{
+    uint32_t x[15][4];
 #pragma unroll 1
-    for (int t = warp; t < 17; t += 4) {
+    for (int g2 = warp; g2 < 34; g2 += kS1Warps) {
+        const int t = g2 >> 1, lh = g2 & 1;
         const int c = 16 - t;
-        const uint8_t *src = slab + (size_t)(c * 15) * kSlotBytes + (size_t)lane * 32;
+        const uint8_t *src = slab + (size_t)(c * 15) * kSlotBytes + (size_t)(lh * 512 + lane * 16);
 #pragma unroll
         for (int d = 0; d < 15; d++)
-            ldg256(src + (size_t)d * kSlotBytes, lo[d], hi[d]);
-        rsfft::dft15(lo);
-        rsfft::dft15(hi);
+            ldg128(src + (size_t)d * kSlotBytes, x[d]);
+        rsfft::dft15(x);
         const uint32_t g = gtask + (uint32_t)t;
         const int slot = (int)(g & (kRingSlots - 1));
         mbar_wait(sm.bar_empty(slot), ((g / kRingSlots) & 1u) ^ 1u);
-        const uint32_t dst = sm.ring + (uint32_t)(slot * kRingSlotBytes + lane * 16);
+        // ring slot: [k 15][half 2][lane-slot 32][4 planes]
+        const uint32_t dst = sm.ring + (uint32_t)(slot * kRingSlotBytes + (lane & 1) * 512 + (lh * 16 + (lane >> 1)) * 16);
 #pragma unroll
-        for (int k = 0; k < 15; k++) {
-            sts128(dst + (uint32_t)(k * 1024), lo[k]);
-            sts128(dst + (uint32_t)(k * 1024 + 512), hi[k]);
-        }
+        for (int k = 0; k < 15; k++)
+            sts128(dst + (uint32_t)(k * 1024), x[k]);
         __syncwarp();
         if (lane == 0)
-            mbar_arrive(sm.bar_full(slot));
+            mbar_arrive(sm.bar_full(slot)); // (two arrivals complete a class: one per half of the lane-slots)
     }
-    gtask += 17;
 }
 
-// the syndromes of S2 warp U: residues k = j mod 15 and their j's (U = 0 has three residues with 3 + 3 + 2 syndromes,
-// the others four residues with two each)
-__host__ __device__ constexpr int s2_nk(int u) { return u == 0 ? 3 : 4; }
-__host__ __device__ constexpr int s2_k(int u, int i)
+// the syndromes of S2 warp U (0..7): four syndromes fed by two residues k = j mod 15.
+//   U = 0: residues (1, 3): S_1, S_16, S_31, S_3        U = 1: residues (2, 3): S_2, S_17, S_32, S_18
+//   U >= 2: residues (2U, 2U + 1 mod 15): S_2U, S_(2U+15), S_(2U+1), S_(2U+16)
+__host__ __device__ constexpr int s2_k(int u, int i) { return u == 0 ? (i ? 3 : 1) : u == 1 ? (i ? 3 : 2) : (2 * u + i) % 15; }
+__host__ __device__ constexpr int s2_kj(int u, int q) { return u < 2 ? (q < 3 ? 0 : 1) : q >> 1; } // residue feeding slot q
+__host__ __device__ constexpr int s2_j(int u, int q)                                               // syndrome of slot q
 {
-    return u == 0 ? (i < 3 ? i + 1 : 3) : u == 3 ? (i < 3 ? 12 + i : 0) : 4 * u + i;
+    return u == 0 ? (q < 3 ? 1 + 15 * q : 3) : u == 1 ? (q < 3 ? 2 + 15 * q : 18) : (2 * u + (q >> 1)) + 15 * (q & 1);
 }
-__host__ __device__ constexpr int s2_kj(int u, int q) // which of the warp's residues feeds syndrome slot q
+constexpr bool s2_table_ok()
 {
-    return u == 0 ? (q < 3 ? 0 : q < 6 ? 1 : 2) : q >> 1;
+    bool seen[33] = {};
+    for (int u = 0; u < 8; u++)
+        for (int q = 0; q < 4; q++) {
+            const int j = s2_j(u, q);
+            if (j < 1 || j > 32 || seen[j] || j % 15 != s2_k(u, s2_kj(u, q)))
+                return false;
+            seen[j] = true;
+        }
+    return true;
 }
-__host__ __device__ constexpr int s2_j(int u, int q) // syndrome number of slot q
-{
-    return u == 0 ? (q < 6 ? (q / 3 + 1) + 15 * (q % 3) : 3 + 15 * (q - 6))
-                  : (s2_k(u, q >> 1) == 0 ? 15 : s2_k(u, q >> 1)) + 15 * (q & 1);
-}
-static_assert(s2_j(0, 0) == 1 && s2_j(0, 1) == 16 && s2_j(0, 2) == 31 && s2_j(0, 3) == 2 && s2_j(0, 5) == 32 &&
-              s2_j(0, 6) == 3 && s2_j(0, 7) == 18 && s2_j(1, 0) == 4 && s2_j(1, 1) == 19 && s2_j(3, 6) == 15 &&
-              s2_j(3, 7) == 30 && s2_j(2, 7) == 26, "syndrome assignment");
+static_assert(s2_table_ok(), "syndrome assignment");
 
 template <int U, int... Q>
-__device__ __forceinline__ void s2_step(uint32_t (&acc)[8][8], const uint32_t (&r)[4][8], std::integer_sequence<int, Q...>)
+__device__ __forceinline__ void s2_step(uint32_t (&acc)[4][8], const uint32_t (&r)[2][8], std::integer_sequence<int, Q...>)
 {
     (rsfft::hstep<s2_j(U, Q)>(acc[Q], r[s2_kj(U, Q)]), ...);
 }
 
-// S2: Horner over the 17 classes for this warp's eight syndromes; leaves them (tower planes) in acc
+// S2: Horner over the 17 classes for this warp's four syndromes; leaves them (tower planes) in acc
 template <int U>
-__device__ __forceinline__ void s2_run(const Smem &sm, int lane, uint32_t &gtask, uint32_t (&acc)[8][8])
+__device__ __forceinline__ void s2_run(const Smem &sm, int lane, uint32_t gtask, uint32_t (&acc)[4][8])
 {
 #pragma unroll
-    for (int q = 0; q < 8; q++)
+    for (int q = 0; q < 4; q++)
 #pragma unroll
         for (int t = 0; t < 8; t++)
             acc[q][t] = 0;
@@ -435,9 +441,9 @@ __device__ __forceinline__ void s2_run(const Smem &sm, int lane, uint32_t &gtask
         const int slot = (int)(g & (kRingSlots - 1));
         mbar_wait(sm.bar_full(slot), (g / kRingSlots) & 1u);
         const uint32_t src = sm.ring + (uint32_t)(slot * kRingSlotBytes + lane * 16);
-        uint32_t r[4][8];
+        uint32_t r[2][8];
 #pragma unroll
-        for (int i = 0; i < s2_nk(U); i++) {
+        for (int i = 0; i < 2; i++) {
             uint32_t a[4], b[4];
             lds128(src + (uint32_t)(s2_k(U, i) * 1024), a);
             lds128(src + (uint32_t)(s2_k(U, i) * 1024 + 512), b);
@@ -447,27 +453,21 @@ __device__ __forceinline__ void s2_run(const Smem &sm, int lane, uint32_t &gtask
                 r[i][4 + q] = b[q];
             }
         }
-        if (s2_nk(U) < 4) {
-#pragma unroll
-            for (int q = 0; q < 8; q++)
-                r[3][q] = 0;
-        }
-        s2_step<U>(acc, r, std::make_integer_sequence<int, 8>{});
+        s2_step<U>(acc, r, std::make_integer_sequence<int, 4>{});
         __syncwarp(); // every lane has its operands in registers (and used them)
         if (lane == 0)
             mbar_arrive(sm.bar_empty(slot));
     }
-    gtask += 17;
 }
 
 // S2 epilogue.  SCREEN: dirty mask of the warp's syndromes + their standard-basis planes to the output stage.
 // ENCODE: the tower planes go to the global syndrome-plane array of the tile (32 bytes per lane and syndrome).
 template <int MODE, int U>
-__device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t (&acc)[8][8], uint32_t *tileplanes)
+__device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t (&acc)[4][8], uint32_t *tileplanes)
 {
     uint32_t nz = 0;
 #pragma unroll
-    for (int q = 0; q < 8; q++) {
+    for (int q = 0; q < 4; q++) {
         if (MODE == MODE_SCREEN) {
             uint32_t s[8];
             rsfft::conv_out(acc[q], s);
@@ -483,6 +483,16 @@ __device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t 
     return nz;
 }
 
+template <int MODE, int U>
+__device__ __forceinline__ void s2_role(const Smem &sm, int lane, uint32_t gtask, uint32_t *tileplanes)
+{
+    uint32_t acc[4][8];
+    s2_run<U>(sm, lane, gtask, acc);
+    const uint32_t nz = s2_store<MODE, U>(sm, lane, acc, tileplanes);
+    if (MODE == MODE_SCREEN)
+        sts32(sm.nzword(U, lane), nz);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
 {
@@ -494,17 +504,16 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
     sm.ring = sm.base + kBarBytes;
     sm.bufs = sm.ring + kRingBytes;
     sm.bufbytes = A.bufbytes;
+    sm.outstage = sm.bufs + (uint32_t)(kWarps * A.bufbytes);
     uint8_t *slab = A.slab + (size_t)blockIdx.x * kSlabBytes;
     const size_t ntiles = (A.n + kTile - 1) / kTile;
 
     if (threadIdx.x == 0) {
-        for (int w = 0; w < kWarps; w++) {
-            mbar_init(sm.bar_buf(w, 0), 1);
-            mbar_init(sm.bar_buf(w, 1), 1);
-        }
+        for (int w = 0; w < kWarps; w++)
+            mbar_init(sm.bar_buf(w), 1);
         for (int s = 0; s < kRingSlots; s++) {
-            mbar_init(sm.bar_full(s), 1);
-            mbar_init(sm.bar_empty(s), 4);
+            mbar_init(sm.bar_full(s), 2);          // the two half-class tasks of S1
+            mbar_init(sm.bar_empty(s), kS2Warps);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -519,8 +528,9 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
     }
     __syncthreads();
 
-    // sub-tile s of a tile is lane-slot ls = kWarps * s + warp; its buffer is s & 1
-    uint32_t use[2] = {0, 0};     // completed uses of this warp's two buffers (mbarrier phase)
+    // sub-tile s of a tile is lane-slot ls = kWarps * s + warp; every warp has ONE buffer, refilled as soon as the warp
+    // has read it (with four warps per scheduler the copy hides behind the other warps' transposes)
+    uint32_t use = 0;             // completed uses of this warp's buffer (mbarrier phase)
     uint32_t gtask = 0;           // class tasks handed through the ring so far (ring phase)
     auto rows_of = [&](size_t tile, int ls) -> int {
         const size_t cwb = tile * kTile + (size_t)ls * 32;
@@ -531,88 +541,77 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
     };
     size_t tile = blockIdx.x;
     if (tile < ntiles)
-        issue_subtile<MODE>(A, sm.buf(warp, 0), sm.bar_buf(warp, 0), tile * kTile + (size_t)warp * 32, rows_of(tile, warp), lane);
+        issue_subtile<MODE>(A, sm.buf(warp), sm.bar_buf(warp), tile * kTile + (size_t)warp * 32, rows_of(tile, warp), lane);
 
     for (; tile < ntiles; tile += gridDim.x) {
         // ---------------- phase A ----------------
 #pragma unroll 1
         for (int s = 0; s < kSubPerWarp; s++) {
             const int ls = kWarps * s + warp;
-            // next sub-tile (of this tile, or the first one of this CTA's next tile) into the other buffer
+            mbar_wait(sm.bar_buf(warp), use & 1u);
+            use++;
+            __syncwarp();
+            transpose_subtile<MODE>(A, sm.buf(warp), tile * kTile + (size_t)ls * 32, ls, slab, lane);
+            // next sub-tile (of this tile, or the first one of this CTA's next tile) into the same buffer
             if (s + 1 < kSubPerWarp) {
                 const int nls = ls + kWarps;
-                issue_subtile<MODE>(A, sm.buf(warp, (s + 1) & 1), sm.bar_buf(warp, (s + 1) & 1), tile * kTile + (size_t)nls * 32,
-                                    rows_of(tile, nls), lane);
+                issue_subtile<MODE>(A, sm.buf(warp), sm.bar_buf(warp), tile * kTile + (size_t)nls * 32, rows_of(tile, nls), lane);
             } else if (tile + gridDim.x < ntiles) {
                 const size_t nt = tile + gridDim.x;
-                issue_subtile<MODE>(A, sm.buf(warp, 0), sm.bar_buf(warp, 0), nt * kTile + (size_t)warp * 32, rows_of(nt, warp), lane);
+                issue_subtile<MODE>(A, sm.buf(warp), sm.bar_buf(warp), nt * kTile + (size_t)warp * 32, rows_of(nt, warp), lane);
             }
-            const int b = s & 1;
-            mbar_wait(sm.bar_buf(warp, b), use[b] & 1u);
-            use[b]++;
-            __syncwarp();
-            transpose_subtile<MODE>(A, sm.buf(warp, b), tile * kTile + (size_t)ls * 32, ls, slab, lane);
         }
         __syncthreads(); // the slab is complete
 
         // ---------------- phase B ----------------
-        uint32_t nz = 0;
         uint32_t *tileplanes = MODE == MODE_ENCODE ? A.synplanes + tile * (size_t)(32 * 32 * 8) : nullptr; // kTilePlaneWords
-        if (warp < 4) {
+        if (warp < kS1Warps) {
             s1_run(sm, slab, warp, lane, gtask);
         } else {
-            uint32_t acc[8][8];
-            switch (warp) {
-            case 4:
-                s2_run<0>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 0>(sm, lane, acc, tileplanes);
-                break;
-            case 5:
-                s2_run<1>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 1>(sm, lane, acc, tileplanes);
-                break;
-            case 6:
-                s2_run<2>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 2>(sm, lane, acc, tileplanes);
-                break;
-            default:
-                s2_run<3>(sm, lane, gtask, acc);
-                nz = s2_store<MODE, 3>(sm, lane, acc, tileplanes);
-                break;
+            switch (warp - kS1Warps) {
+            case 0: s2_role<MODE, 0>(sm, lane, gtask, tileplanes); break;
+            case 1: s2_role<MODE, 1>(sm, lane, gtask, tileplanes); break;
+            case 2: s2_role<MODE, 2>(sm, lane, gtask, tileplanes); break;
+            case 3: s2_role<MODE, 3>(sm, lane, gtask, tileplanes); break;
+            case 4: s2_role<MODE, 4>(sm, lane, gtask, tileplanes); break;
+            case 5: s2_role<MODE, 5>(sm, lane, gtask, tileplanes); break;
+            case 6: s2_role<MODE, 6>(sm, lane, gtask, tileplanes); break;
+            default: s2_role<MODE, 7>(sm, lane, gtask, tileplanes); break;
             }
-            if (MODE == MODE_SCREEN)
-                sts32(sm.nzword(warp - 4, lane), nz);
         }
+        gtask += 17;
         __syncthreads(); // S1 is done with the slab; SCREEN: all 256 syndrome planes are in the output stage
 
         // ---------------- output (SCREEN; the encoder's syndromes went to global memory) ----------------
         if (MODE == MODE_SCREEN) {
-            const size_t cw0 = tile * kTile + (size_t)lane * 32; // this lane-slot's first codeword
-            uint32_t valid = 0;                                  // bit i: codeword cw0 + i exists
-            if (cw0 < A.n) {
-                const size_t left = A.n - cw0;
-                valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (unsigned)left) - 1u);
+            if (warp < 8) {
+                const size_t cw0 = tile * kTile + (size_t)lane * 32; // this lane-slot's first codeword
+                uint32_t valid = 0;                                  // bit i: codeword cw0 + i exists
+                if (cw0 < A.n) {
+                    const size_t left = A.n - cw0;
+                    valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (unsigned)left) - 1u);
+                }
+                uint32_t dirty = 0;
+#pragma unroll
+                for (int u = 0; u < kS2Warps; u++)
+                    dirty |= lds32(sm.nzword(u, lane));
+                dirty &= valid;
+                if (warp == 0 && cw0 < A.n)
+                    A.dirty[cw0 >> 5] = dirty;
+                if (__any_sync(0xFFFFFFFFu, dirty != 0)) {
+                    // syndrome word-column `warp`: S_{4w+1} .. S_{4w+4} of the lane-slot's 32 codewords
+                    uint32_t X[32];
+#pragma unroll
+                    for (int p = 0; p < 32; p++)
+                        X[p] = lds32(sm.outplane(32 * warp + p, lane));
+                    transpose32(X);
+#pragma unroll
+                    for (int i = 0; i < 32; i++)
+                        if ((dirty >> i) & 1u)
+                            *reinterpret_cast<uint32_t *>(A.syn + (cw0 + (size_t)i) * 32 + 4 * warp) = X[i];
+                }
             }
-            uint32_t dirty = 0;
-#pragma unroll
-            for (int u = 0; u < 4; u++)
-                dirty |= lds32(sm.nzword(u, lane));
-            dirty &= valid;
-            if (warp == 0 && cw0 < A.n)
-                A.dirty[cw0 >> 5] = dirty;
-            if (__any_sync(0xFFFFFFFFu, dirty != 0)) {
-                // syndrome word-column `warp`: S_{4w+1} .. S_{4w+4} of the lane-slot's 32 codewords
-                uint32_t X[32];
-#pragma unroll
-                for (int p = 0; p < 32; p++)
-                    X[p] = lds32(sm.outplane(32 * warp + p, lane));
-                transpose32(X);
-#pragma unroll
-                for (int i = 0; i < 32; i++)
-                    if ((dirty >> i) & 1u)
-                        *reinterpret_cast<uint32_t *>(A.syn + (cw0 + (size_t)i) * 32 + 4 * warp) = X[i];
-            }
-            __syncthreads(); // the output stage (buffer 1 of warps 0..3) is free again
+            __syncthreads(); // the output stage and the dirty words are free again
         }
     }
 }
@@ -880,7 +879,7 @@ rs255_fft_compact_kernel(const uint32_t *__restrict__ dirty, size_t n, uint32_t 
 
 int smem_bytes(int bufbytes)
 {
-    return kBarBytes + kRingBytes + 2 * kWarps * bufbytes + 64;
+    return kBarBytes + kRingBytes + kWarps * bufbytes + kOutStageBytes + 64;
 }
 
 } // namespace
@@ -911,7 +910,7 @@ bool rs255_fft_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t 
     if (shape) {
         shape->packed = packed ? 1 : 0;
         shape->prow_off = packed ? (int)(parity - data) : 0;
-        shape->bufbytes = (int)(total < 8192 ? 8192 : total); // the output stage borrows buffers: 64 planes x 128 B each
+        shape->bufbytes = (int)total;
         shape->poff = (int)poff;
     }
     return true;
