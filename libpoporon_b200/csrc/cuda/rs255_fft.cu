@@ -347,15 +347,19 @@ __device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t buf
             X[i] = __byte_perm(lo, hi, sel[i & 3]);
         }
         transpose32(X); // X[8 y + t] = plane t of byte y of the column
+        // basis change in place, then the four plane stores together: their source registers are not written
+        // again before the next column's loads have come back (a store that waits in the LSU queue holds its
+        // registers: rewriting them at once cost 20 % of this loop's time in scoreboard stalls)
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            uint32_t(&xs)[8] = *reinterpret_cast<uint32_t(*)[8]>(&X[8 * y]);
+            rsfft::conv_in(xs, xs);
+        }
 #pragma unroll
         for (int y = 0; y < 4; y++) {
             if (y < nvalid) {
-                uint32_t s[8], t[8];
-#pragma unroll
-                for (int q = 0; q < 8; q++)
-                    s[q] = X[8 * y + q];
-                rsfft::conv_in(s, t);
-                stg256(slab + (size_t)slot_of((uint32_t)(e0 - y)) * kSlotBytes + (size_t)ls * 32, t);
+                uint32_t(&xs)[8] = *reinterpret_cast<uint32_t(*)[8]>(&X[8 * y]);
+                stg256(slab + (size_t)slot_of((uint32_t)(e0 - y)) * kSlotBytes + (size_t)ls * 32, xs);
             }
         }
     }
@@ -365,20 +369,22 @@ __device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t buf
 // phase B
 // ---------------------------------------------------------------------------------------------------
 // S1: 34 half-class tasks g2 = 2 t + lh (class c = 16 - t, so that S2 meets the classes in Horner order; lh = which
-// sixteen lane-slots of the tile).  A lane owns one GF(16) half (4 planes) of one lane-slot: lane = 2 * slot + half,
-// so that a warp reads 512 contiguous bytes per symbol and a thread holds 15 x 4 planes only.
+// sixteen lane-slots of the tile).  A lane owns one GF(16) half (4 planes) of one lane-slot: lane = 16 * half + slot,
+// so that a warp reads 512 contiguous bytes per symbol, a thread holds 15 x 4 planes only, and the ring stores of a
+// quarter warp are 128 contiguous bytes (no bank conflicts).
 __device__ __forceinline__ void ldg128(const void *p, uint32_t (&v)[4])
 {
-    asm volatile("ld.global.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "l"(p) : "memory");
+    asm volatile("ld.global.cg.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "l"(p) : "memory"); // (L2 only: the slab is rewritten every other tile)
 }
-__device__ __forceinline__ void s1_run(const Smem &sm, const uint8_t *slab, int warp, int lane, uint32_t gtask)
+__device__ __forceinline__ void s1_run(const Smem &sm, const uint8_t *slab, int u, int lane, uint32_t gtask)
 {
     uint32_t x[15][4];
+    const int half = lane >> 4, sl = lane & 15;
 #pragma unroll 1
-    for (int g2 = warp; g2 < 34; g2 += kS1Warps) {
+    for (int g2 = u; g2 < 34; g2 += kS1Warps) {
         const int t = g2 >> 1, lh = g2 & 1;
         const int c = 16 - t;
-        const uint8_t *src = slab + (size_t)(c * 15) * kSlotBytes + (size_t)(lh * 512 + lane * 16);
+        const uint8_t *src = slab + (size_t)(c * 15) * kSlotBytes + (size_t)((lh * 16 + sl) * 32 + half * 16);
 #pragma unroll
         for (int d = 0; d < 15; d++)
             ldg128(src + (size_t)d * kSlotBytes, x[d]);
@@ -387,7 +393,7 @@ __device__ __forceinline__ void s1_run(const Smem &sm, const uint8_t *slab, int 
         const int slot = (int)(g & (kRingSlots - 1));
         mbar_wait(sm.bar_empty(slot), ((g / kRingSlots) & 1u) ^ 1u);
         // ring slot: [k 15][half 2][lane-slot 32][4 planes]
-        const uint32_t dst = sm.ring + (uint32_t)(slot * kRingSlotBytes + (lane & 1) * 512 + (lh * 16 + (lane >> 1)) * 16);
+        const uint32_t dst = sm.ring + (uint32_t)(slot * kRingSlotBytes + half * 512 + (lh * 16 + sl) * 16);
 #pragma unroll
         for (int k = 0; k < 15; k++)
             sts128(dst + (uint32_t)(k * 1024), x[k]);
