@@ -15,14 +15,16 @@
 // codewords in two phases, with the planes parked in a CTA-private 255 KB slab of global memory that is written
 // and read back by the same SM and therefore lives in L2:
 //   phase A  every warp takes sub-tiles of 32 consecutive codewords (one lane-slot of the tile).  The rows arrive
-//            by ONE bulk copy (cp.async.bulk + mbarrier: the 32 rows are contiguous in memory), double-buffered per
-//            warp.  Lane x transposes word-column x of the 32 rows (4 symbols x 32 codewords) into bit-planes,
-//            changes basis and stores each symbol's 8 planes (32 bytes) to slab[slot(e)][lane-slot].
-//   phase B  warps 0-3 ("S1") run the 15-point DFTs class by class (class c = 15 slab slots = 15 KB contiguous) and
-//            hand R_c to warps 4-7 ("S2") through a 4-slot shared-memory ring (mbarrier full/empty); S2 warp u owns
-//            the eight syndromes of four residues j mod 15 and runs their Horner recurrences in registers.
-//   output   SCREEN: a dirty bit per codeword + the 32 syndrome bytes of dirty codewords; ENCODE: the solve and the
-//            parity rows.
+//            by ONE bulk copy (cp.async.bulk + mbarrier: the 32 rows are contiguous in memory) into the warp's
+//            buffer, which is refilled as soon as the warp has read it.  Lane x transposes word-column x of the 32
+//            rows (4 symbols x 32 codewords) into bit-planes, changes basis and stores each symbol's 8 planes
+//            (32 bytes) to slab[slot(e)][lane-slot].
+//   phase B  warps 0-7 ("S1") run the 15-point DFTs, one GF(16) half of sixteen lane-slots per task (class c = 15
+//            slab slots = 15 KB contiguous), and hand R_c to warps 8-15 ("S2") through a 4-slot shared-memory ring
+//            (mbarrier full/empty); S2 warp u owns four syndromes fed by two residues j mod 15 and runs their Horner
+//            recurrences in registers.
+//   output   SCREEN: a dirty bit per codeword + the 32 syndrome bytes of dirty codewords.  ENCODE: the syndrome planes
+//            of message * x^32 go to global memory; rs255_parity_kernel (V^-1) and rs255_rows_kernel finish the job.
 #include "rs255_fft.cuh"
 
 #include <stdlib.h>
@@ -36,7 +38,12 @@ namespace ppcu {
 namespace {
 
 constexpr int kTile = 1024;  // codewords per CTA tile
-constexpr int kWarps = 16;                           // 128 registers per thread: four warps per scheduler
+// One CTA of 16 warps per SM (128 registers per thread, four warps per scheduler), all warps in the same phase of the
+// same tile.  Measured alternatives (16 Mi codewords, dirty screen / clean decode): 8 warps at 208 registers 2.61 /
+// 2.20 ms; this 2.47 / 2.08 ms; 16 warps as a software pipeline of specialised warps (8 byte->plane, 4 + 4 transform)
+// coupled by mbarriers over two slabs 3.5 / 2.47 ms - the byte->plane warps became the critical path; two independent
+// CTAs of 8 warps per SM 2.61 / 2.18 ms.
+constexpr int kWarps = 16;
 constexpr int kS1Warps = 8, kS2Warps = 8;            // phase B roles: warps 0..7 / 8..15
 constexpr int kSubPerWarp = 32 / kWarps;
 constexpr int kSlotBytes = 1024;                    // one symbol of the tile: [lane-slot 32][8 planes]
