@@ -37,13 +37,18 @@ def _load():
                 "(there is no Python/CPU fallback for the codecs)")
     cuda = C.CDLL(cuda_path, mode=C.RTLD_GLOBAL)
     host = C.CDLL(host_path)
-    return cuda, host
+    # workload generators of the bench and the tests: a library of their own, not part of the product
+    synth_path = os.path.join(d, "libpoporon_synth.so")
+    synth = C.CDLL(synth_path) if os.path.exists(synth_path) else None
+    return cuda, host, synth
 
 
-cuda, host = _load()
+cuda, host, synth = _load()
 
 
 def _sig(lib, name, restype, *argtypes):
+    if lib is None:  # (libpoporon_synth.so absent: only the harness helpers are unavailable)
+        return None
     fn = getattr(lib, name)
     fn.restype = restype
     fn.argtypes = list(argtypes)
@@ -120,11 +125,11 @@ _sig(host, "poporon_last_error", C.c_char_p)
 # ---- include/poporon_cuda.h (the part tests/bench bind directly) ----------------------------------
 _sig(cuda, "poporon_cuda_device_count", C.c_int)
 _sig(cuda, "poporon_cuda_last_error", C.c_char_p)
-_sig(cuda, "poporon_cuda_synth_fill", C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint64,
+_sig(synth, "poporon_cuda_synth_fill", C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint64,
      C.c_uint64, C.c_void_p)
-_sig(cuda, "poporon_cuda_synth_inject", C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint64,
+_sig(synth, "poporon_cuda_synth_inject", C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint64,
      C.c_uint64, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p)
-_sig(cuda, "poporon_cuda_synth_erasures", C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+_sig(synth, "poporon_cuda_synth_erasures", C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
      C.c_size_t, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p)
 
 
@@ -311,20 +316,20 @@ class Poporon:
 
 # ---- synthetic workloads (harness) ----------------------------------------------------------------
 def synth_fill(device, data, stride, size, n, seed, i0=0, stream=0):
-    rc = cuda.poporon_cuda_synth_fill(device, _addr(data), stride, size, n, seed, i0, stream)
+    rc = synth.poporon_cuda_synth_fill(device, _addr(data), stride, size, n, seed, i0, stream)
     if rc != 0:
         raise RuntimeError(cuda.poporon_cuda_last_error().decode())
 
 
 def synth_inject(device, cw, stride, length, n, seed, i0=0, kind=0, emin=0, emax=16, p_ppm=0, stream=0):
-    rc = cuda.poporon_cuda_synth_inject(device, _addr(cw), stride, length, n, seed, i0, kind, emin, emax, p_ppm,
+    rc = synth.poporon_cuda_synth_inject(device, _addr(cw), stride, length, n, seed, i0, kind, emin, emax, p_ppm,
                                         stream)
     if rc != 0:
         raise RuntimeError(cuda.poporon_cuda_last_error().decode())
 
 
 def synth_erasures(device, cw, stride, size, length, n, seed, pos, pos_stride, cnt, i0=0, cmax=32, stream=0):
-    rc = cuda.poporon_cuda_synth_erasures(device, _addr(cw), stride, size, length, n, seed, i0, cmax, _addr(pos),
+    rc = synth.poporon_cuda_synth_erasures(device, _addr(cw), stride, size, length, n, seed, i0, cmax, _addr(pos),
                                           pos_stride, _addr(cnt), stream)
     if rc != 0:
         raise RuntimeError(cuda.poporon_cuda_last_error().decode())

@@ -3,11 +3,20 @@
 // Counter-based: every byte is a pure function of (seed, codeword index, byte index), so any slice
 // of a workload can be regenerated anywhere (each GPU of a sharded run fills its own slice; the CPU
 // baseline receives a device-to-host copy of a sample).  SURVEY §8(d) configs 2, 3 and 5.
+// Built into its own library (libpoporon_synth.so): the product library libpoporon_cuda.so holds the codec only.
 #include "common.cuh"
+#include "synth.h"
 
 namespace ppcu {
 
 namespace {
+
+// (this library does not share the product library's error text)
+int scheck(cudaError_t e, const char *what)
+{
+    (void)what;
+    return e == cudaSuccess ? 0 : POPORON_CUDA_ERR_DEVICE;
+}
 
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z)
 {
@@ -129,7 +138,7 @@ extern "C" int poporon_cuda_synth_fill(int device, uint8_t *data, size_t stride,
 {
     DeviceGuard g(device);
     if (!g.ok)
-        return check(cudaErrorInvalidDevice, "set device");
+        return scheck(cudaErrorInvalidDevice, "set device");
     if (n == 0 || size == 0)
         return 0;
     const size_t total = n * ((size + 7) / 8);
@@ -138,7 +147,7 @@ extern "C" int poporon_cuda_synth_fill(int device, uint8_t *data, size_t stride,
     if (blocks > cap)
         blocks = cap;
     synth_fill_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(data, stride, size, n, seed, i0);
-    return check(cudaGetLastError(), "synth_fill launch");
+    return scheck(cudaGetLastError(), "synth_fill launch");
 }
 
 extern "C" int poporon_cuda_synth_inject(int device, uint8_t *cw, size_t stride, size_t len, size_t n, uint64_t seed,
@@ -147,14 +156,14 @@ extern "C" int poporon_cuda_synth_inject(int device, uint8_t *cw, size_t stride,
 {
     DeviceGuard g(device);
     if (!g.ok)
-        return check(cudaErrorInvalidDevice, "set device");
+        return scheck(cudaErrorInvalidDevice, "set device");
     if (len == 0 || len > 256 || emax < emin)
         return POPORON_CUDA_ERR_ARG;
     if (n == 0)
         return 0;
     synth_inject_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(cw, stride, len, n, seed, i0,
                                                                                      kind, emin, emax, p_ppm, 255u);
-    return check(cudaGetLastError(), "synth_inject launch");
+    return scheck(cudaGetLastError(), "synth_inject launch");
 }
 
 extern "C" int poporon_cuda_synth_erasures(int device, uint8_t *cw, size_t stride, size_t size, size_t len, size_t n,
@@ -163,12 +172,12 @@ extern "C" int poporon_cuda_synth_erasures(int device, uint8_t *cw, size_t strid
 {
     DeviceGuard g(device);
     if (!g.ok)
-        return check(cudaErrorInvalidDevice, "set device");
+        return scheck(cudaErrorInvalidDevice, "set device");
     if (len == 0 || len > 256 || size > len || size == 0)
         return POPORON_CUDA_ERR_ARG;
     if (n == 0)
         return 0;
     synth_erasures_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
         cw, stride, size, len, n, seed, i0, cmax, pos, pos_stride, cnt, 255u);
-    return check(cudaGetLastError(), "synth_erasures launch");
+    return scheck(cudaGetLastError(), "synth_erasures launch");
 }
