@@ -865,7 +865,7 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 #endif
 constexpr int kSolveWarpsPerCTA = PP_SOLVE_WARPS_PER_CTA; // warps of a CTA move from tile to tile together (see the kernel)
 constexpr int kSolveSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 256; // work areas + the root table (256 B)
-constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO;  // per lane, in global memory (L2-resident)
+constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO + bs::kWordsM;  // per lane, in global memory (L2-resident)
 #ifndef PP_SOLVE_WARPS_PER_SM
 #define PP_SOLVE_WARPS_PER_SM 8
 #endif
@@ -979,6 +979,42 @@ struct ApplyHook {
     }
     __device__ __forceinline__ void after(int) {}
     __device__ __forceinline__ void end() { flush(); }
+    // Codeword-wide form for the transform-form Chien search (33 steps per tile instead of 256): step c applies the
+    // record loaded by step c - 1, loads the record of codeword c and fetches the queue entry of codeword c + 1.
+    uint4 wxs, wmg;
+    __device__ __forceinline__ void wbegin()
+    {
+        begin();
+        entry_app = 0xFFFFFFFFu;
+    }
+    __device__ __forceinline__ void wapply()
+    {
+        if (entry_app != 0xFFFFFFFFu) {
+            const uint32_t xw[4] = {wxs.x, wxs.y, wxs.z, wxs.w}, mw[4] = {wmg.x, wmg.y, wmg.z, wmg.w};
+#pragma unroll
+            for (int h = 0; h < 8; h++) {
+                p2 = (xw[h >> 1] >> (16 * (h & 1))) & 0xFFFFu;
+                m2 = (mw[h >> 1] >> (16 * (h & 1))) & 0xFFFFu;
+                flush();
+            }
+        }
+    }
+    __device__ __forceinline__ void wstep(int c)
+    {
+        wapply();
+        entry_app = c < 32 ? entry_cur : 0xFFFFFFFFu;
+        if (entry_app != 0xFFFFFFFFu) {
+            const uint4 *row = reinterpret_cast<const uint4 *>(records + (size_t)(entry_app & 0x3FFFFFFFu) * 32);
+            wxs = row[0];
+            wmg = row[1];
+        }
+        entry_cur = entry_of((uint32_t)c + 1u);
+    }
+    __device__ __forceinline__ void wend()
+    {
+        wapply();
+        entry_app = 0xFFFFFFFFu;
+    }
     // everything still pending (after a warp's last tile): whole records, four codewords per round so that the
     // exposed round trips (entry -> record -> XORs) are few
     __device__ __forceinline__ void drain()
@@ -1035,6 +1071,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
     uint32_t *gs = scratch + (size_t)gw * (kSolveScratchWords * 32) + lane;
     const bs::Mem<32> Syn{gs};
     const bs::Mem<32> B{gs + bs::kWordsS * 32}; // the evaluator
+    const bs::Mem<32> Mk{gs + (bs::kWordsS + bs::kWordsO) * 32}; // root masks of the transform-form Chien search
     uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWarpsPerCTA * bs::kWordsW * 32);
     {
         // root_tab[0] = 0 (empty list slot), root_tab[v] = alpha^v for v = 1..255: each lane fills 8 consecutive powers
@@ -1081,7 +1118,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
             solve_load_syndromes(ent, syn_raw, Syn);
         }
         bs::LaneOut out;
-        bs::solve_lane<32, 32>(Syn, B, S, pad, out, hook); // also drains the previous tile's corrections
+        bs::solve_lane<32, 32>(Syn, B, Mk, S, pad, out, hook); // also drains the previous tile's corrections
 
         // Outcome of every codeword of the lane.  What the solver declines goes to the literal stage.  A decodable
         // codeword gets an error record in place of its (now dead) raw syndrome row: bytes 0..15 the error locations

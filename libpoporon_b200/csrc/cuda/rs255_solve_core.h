@@ -37,6 +37,7 @@
 #include <utility>
 
 #include "gf256_consts.cuh"
+#include "rs255_fft_gen.cuh"
 
 #if defined(__CUDACC__)
 #define BS_FN __host__ __device__ __forceinline__
@@ -690,6 +691,10 @@ struct NoHook {
     BS_FN void before(int) {}
     BS_FN void after(int) {}
     BS_FN void end() {}
+    // codeword-wide form (transform-form Chien search): wstep(c), c = 0..32, handles the whole record of codeword c
+    BS_FN void wbegin() {}
+    BS_FN void wstep(int) {}
+    BS_FN void wend() {}
 };
 
 template <int STRIDE, int SL, class Hook>
@@ -737,6 +742,150 @@ BS_FN void chien_collect(const Mem<SL> LM, const Mem<STRIDE> S, int pad, LaneOut
     for (int c = 0; c < 32; c++)
         append_roots<STRIDE>(S, c, 7, S.ld(kParkBase + c), S.ld_byte(kCntBase + (c >> 2), c & 3));
     hook.end();
+    out.padfail = padfail;
+}
+
+// ---- Chien search as a 15 x 17 transform -----------------------------------------------------------------------
+// Lambda(alpha^j) for ALL 255 j from the 17 locator coefficients at ~14 K plane-operations per 32 codewords instead of
+// 255 x 158 = 40 K for the sequence generator above (tools/gen_rs255_fft.py derives and checks the algebra):
+//   j <-> (u = j mod 17, w = j mod 15);   alpha^(j d) = beta^(8 w d) gamma^(8 u d),  beta = alpha^17, gamma = alpha^15
+//   Lambda(alpha^j) = sum_{d < 15} beta^(8 w d) Z_d(u),   Z_d(u) = gamma^(8 u d) (Lambda_d + [d < 2] gamma^u Lambda_(d+15))
+// so every u is one 15-point DFT with GF(16) twiddles (rsfft::dft15 on the two 4-plane halves of tower-basis symbols;
+// its output k belongs to j = 120 u + 17 k mod 255) of fifteen values that advance from u to u + 1 by constant
+// multipliers (rsfft::cmulT, 12 operations each on average).  Location k = j - 1 (mod 255) is a root where all eight
+// planes vanish.  The 255 root masks go to MK (256 words per lane, word 255 = 0); afterwards they are transposed in
+// blocks of 32 locations into the per-codeword root lists exactly as above (the order of a list's entries differs -
+// nothing depends on it: every root is corrected independently).  The hook gets its 256 steps during the transform.
+static_assert(rsfft::kChienJ[1] == 17 && rsfft::kChienJ[7] == 119 && rsfft::kChienJ[14] == 238, "kChienJ[k] = 17 k");
+BS_FN uint32_t or4(const uint32_t (&a)[4])
+{
+    return (a[0] | a[1]) | (a[2] | a[3]);
+}
+
+template <int D>
+BS_FN void chien_advance(uint32_t (&Z)[13][8])
+{
+    if constexpr (D < 13) {
+        rsfft::cmulT<rsfft::kChienZ[D]>(Z[D]);
+        chien_advance<D + 1>(Z);
+    }
+}
+
+template <int STRIDE, int SL, class Hook>
+BS_FN void chien_transform(const Mem<SL> LM, const Mem<SL> MK, const Mem<STRIDE> S, int pad, LaneOut &out, Hook &hook)
+{
+    {
+        uint32_t Z[13][8], A0[8], Tb[8], Tc[8], Td[8];
+        {
+            uint32_t l[8];
+            ld8(LM, 0, l);
+            rsfft::conv_in(l, A0);
+            ld8(LM, 15, l);
+            rsfft::conv_in(l, Tb);
+            ld8(LM, 1, l);
+            rsfft::conv_in(l, Tc);
+            ld8(LM, 16, l);
+            rsfft::conv_in(l, Td);
+#pragma unroll
+            for (int d = 2; d < 15; d++) {
+                ld8(LM, d, l);
+                rsfft::conv_in(l, Z[d - 2]);
+            }
+        }
+        for (int w = kListBase; w < kParkBase + 32; w++)
+            S.st(w, 0u);
+        hook.wbegin();
+        int jb = 0; // jb = 120 u mod 255
+#pragma unroll 1
+        for (int u = 0; u < 17; u++) {
+            uint32_t acc[15];
+            {
+                uint32_t x[15][4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    x[0][i] = A0[i] ^ Tb[i];
+                    x[1][i] = Tc[i] ^ Td[i];
+                }
+#pragma unroll
+                for (int d = 2; d < 15; d++)
+#pragma unroll
+                    for (int i = 0; i < 4; i++)
+                        x[d][i] = Z[d - 2][i];
+                rsfft::dft15(x);
+#pragma unroll
+                for (int k = 0; k < 15; k++)
+                    acc[k] = or4(x[k]);
+            }
+            hook.wstep(2 * u); // (the previous tile's corrections: two codewords per step, loads one step ahead of use)
+            {
+                uint32_t x[15][4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    x[0][i] = A0[4 + i] ^ Tb[4 + i];
+                    x[1][i] = Tc[4 + i] ^ Td[4 + i];
+                }
+#pragma unroll
+                for (int d = 2; d < 15; d++)
+#pragma unroll
+                    for (int i = 0; i < 4; i++)
+                        x[d][i] = Z[d - 2][4 + i];
+                rsfft::dft15(x);
+#pragma unroll
+                for (int k = 0; k < 15; k++)
+                    acc[k] |= or4(x[k]);
+            }
+            hook.wstep(2 * u + 1);
+#pragma unroll
+            for (int k = 0; k < 15; k++) {
+                int j = jb + 17 * k; // rsfft::kChienJ[k]
+                j = j >= 255 ? j - 255 : j;
+                const int loc = j == 0 ? 254 : j - 1;
+                MK.st(loc, ~acc[k]);
+            }
+            jb += 120;
+            jb = jb >= 255 ? jb - 255 : jb;
+            chien_advance<0>(Z);
+            rsfft::cmulT<rsfft::kChienB>(Tb);
+            rsfft::cmulT<rsfft::kChienC>(Tc);
+            rsfft::cmulT<rsfft::kChienD>(Td);
+        }
+        MK.st(255, 0u);
+        hook.wend();
+    }
+    uint32_t padfail = 0;
+    uint32_t X[32];
+#pragma unroll
+    for (int c = 0; c < 32; c++)
+        X[c] = MK.ld(c);
+#pragma unroll 1
+    for (int blk = 0; blk < 8; blk++) {
+        const int npad = pad - 32 * blk; // locations below the padding boundary in this block
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            padfail |= c < npad ? X[c] : 0u;
+        transpose32(X);
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            S.st(kParkBase + c, X[c]);
+        // the next block's masks are on their way while this block's roots are appended
+        const int nb = blk < 7 ? blk + 1 : 7;
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            X[c] = MK.ld(32 * nb + c);
+        // four codewords per trip: their (latency-bound) list updates overlap
+#pragma unroll 1
+        for (int c0 = 0; c0 < 32; c0 += 4) {
+            uint32_t bits[4], cnt[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                bits[q] = S.ld(kParkBase + c0 + q);
+                cnt[q] = S.ld_byte(kCntBase + (c0 >> 2), q);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                append_roots<STRIDE>(S, c0 + q, blk, bits[q], cnt[q]);
+        }
+    }
     out.padfail = padfail;
 }
 
@@ -892,8 +1041,15 @@ BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots)
 //      [kListBase, kListBase + 128) double as the BM scratch and as the parking space of the evaluator loop.
 // Syn and Om may live in slower memory than W (on the device: an L2-resident scratch in global memory, so that
 // a warp needs 25 KB of shared memory and eight warps fit one SM).
+//   Mk: 256 words for the root masks of the transform form of the Chien search (same kind of memory as Syn).
+#ifndef BS_CHIEN_TRANSFORM
+#define BS_CHIEN_TRANSFORM 1
+#endif
+constexpr int kWordsM = 256;
+
 template <int STRIDE, int SO, class Hook>
-BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<STRIDE> W, int pad, LaneOut &out, Hook &hook)
+BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<SO> Mk, const Mem<STRIDE> W, int pad, LaneOut &out,
+                      Hook &hook)
 {
     const Mem<STRIDE> B{W.base + kListBase * STRIDE};
     {
@@ -908,7 +1064,12 @@ BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<STRIDE> W, 
             st8(Syn, j, L[j]);
         }
     }
+#if BS_CHIEN_TRANSFORM
+    chien_transform<STRIDE, SO, Hook>(Syn, Mk, W, pad, out, hook);
+#else
+    (void)Mk;
     chien_collect<STRIDE, SO, Hook>(Syn, W, pad, out, hook);
+#endif
 }
 
 } // namespace bs

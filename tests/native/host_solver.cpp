@@ -16,7 +16,7 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
     for (int i = 1; i < 256; i++)
         root_tab[i] = gf256::pow_alpha(i);
     for (size_t g = 0; g < n; g += 32) {
-        uint32_t Syn[bs::kWordsS], B[bs::kWordsO], S[bs::kWordsW];
+        uint32_t Syn[bs::kWordsS], B[bs::kWordsO], S[bs::kWordsW], Mk[bs::kWordsM];
         memset(Syn, 0, sizeof Syn);
         memset(B, 0, sizeof B);
         memset(S, 0, sizeof S);
@@ -27,9 +27,9 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
                     if ((syn[(g + c) * 32 + m] >> t) & 1)
                         Syn[8 * m + t] |= 1u << c;
         bs::LaneOut out;
-        const bs::Mem<1> Sm{S}, Bm{B}, Synm{Syn};
+        const bs::Mem<1> Sm{S}, Bm{B}, Synm{Syn}, Mkm{Mk};
         bs::NoHook hook;
-        bs::solve_lane<1, 1>(Synm, Bm, Sm, pad, out, hook);
+        bs::solve_lane<1, 1>(Synm, Bm, Mkm, Sm, pad, out, hook);
         for (size_t c = 0; c < cnt; c++) {
             int nr = 0;
             status[g + c] = (int8_t)bs::classify<1>(Sm, out, (int)c, nr);

@@ -437,8 +437,68 @@ def direct_syndromes(r):
     return out
 
 
+# ---------------------------------------------------------------------------------------------------------
+# Chien search as a transform (rs255_solve_core.h): Lambda(alpha^j) for all 255 j from the 17 locator coefficients.
+#   j <-> (u = j mod 17, w = j mod 15);  alpha^(j d) = beta^(8 w d) * gamma^(8 u d),  beta = alpha^17, gamma = alpha^15
+#   Lambda(alpha^j) = sum_{d<15} beta^(8 w d) Z_d(u),   Z_d(u) = gamma^(8 u d) (Lambda_d + [d < 2] gamma^u Lambda_(d+15))
+# i.e. for every u one 15-point DFT (the generated dft15 has root beta: its output k is w = 2 k mod 15) of 15 values
+# that advance from u to u + 1 by constant multipliers: Z_d *= gamma^(8 d) for d >= 2, and the four running terms
+# Lambda_15 gamma^u, Lambda_1 gamma^(8u), Lambda_16 gamma^(9u) (Z_0 = Lambda_0 + the first, Z_1 = the other two).
+# ---------------------------------------------------------------------------------------------------------
+GAMMA_E = 15
+
+
+def chien_exponents():
+    """alpha-exponents of the per-step multipliers: [Z_2 .. Z_14], then the three running terms"""
+    zs = [(GAMMA_E * ((8 * d) % 17)) % 255 for d in range(2, 15)]
+    return zs, [(GAMMA_E * 1) % 255, (GAMMA_E * 8) % 255, (GAMMA_E * 9) % 255]
+
+
+def chien_j_of(u, k):
+    """the j of DFT output k in step u"""
+    w = (2 * k) % 15
+    return (120 * u + 136 * w) % 255
+
+
+def check_chien_algebra(rnd):
+    zs, (eb, ec, ed) = chien_exponents()
+    for _ in range(20):
+        lam = [rnd.randrange(256) for _ in range(17)]
+        if rnd.random() < 0.5:  # plant roots
+            lam = [1]
+            for _r in range(rnd.randrange(1, 17)):
+                x = gpow(rnd.randrange(255))
+                lam = [a ^ gmul(b, x) for a, b in zip(lam + [0], [0] + lam)]
+            lam = (lam + [0] * 17)[:17]
+        direct = [0] * 255
+        for j in range(255):
+            v = 0
+            for e in range(17):
+                v ^= gmul(lam[e], gpow(j * e))
+            direct[j] = v
+        z = list(lam[:15])
+        tb, tc, td = lam[15], lam[1], lam[16]
+        seen = set()
+        for u in range(17):
+            z[0] = lam[0] ^ tb
+            z[1] = tc ^ td
+            for k in range(15):
+                v = 0
+                for d in range(15):
+                    v ^= gmul(z[d], gpow(17 * ((d * k) % 15)))
+                j = chien_j_of(u, k)
+                assert j % 17 == u and j not in seen
+                seen.add(j)
+                assert v == direct[j], (u, k, j)
+            for i, d in enumerate(range(2, 15)):
+                z[d] = gmul(z[d], gpow(zs[i]))
+            tb, tc, td = gmul(tb, gpow(eb)), gmul(tc, gpow(ec)), gmul(td, gpow(ed))
+        assert len(seen) == 255
+
+
 def generate(tw, path, total, parts):
     rnd = random.Random(1)
+    check_chien_algebra(rnd)
     # ---- matrices and their programs -------------------------------------------------------------------
     conv_in = build_slp(tw.C, 8)
     check_slp(conv_in, tw.C)
@@ -537,6 +597,13 @@ def generate(tw, path, total, parts):
             for u in range(8):
                 enc_mask[jj][31 - t][u] = m[u]
 
+    zs, run3 = chien_exponents()
+    cm = {}
+    for e in sorted(set(zs + run3)):
+        rows = tw.mul_tower(gpow(e))
+        cm[e] = build_slp(rows, 8)
+        check_slp(cm[e], rows)
+
     # ---- emit -------------------------------------------------------------------------------------------
     L = []
     L.append("// rs255_fft_gen.cuh - GENERATED by tools/gen_rs255_fft.py; do not edit.")
@@ -616,6 +683,24 @@ def generate(tw, path, total, parts):
         L += emit_slp_body(hs[j], [f"acc[{i}]" for i in range(8)] + [f"r[{i}]" for i in range(8)],
                            [f"acc[{i}]" for i in range(8)], tmp="h")
         L.append("}")
+    L.append("")
+    L.append("// Chien search as a transform (rs255_solve_core.h; algebra and check in the generator): in-place product of")
+    L.append("// a tower-basis symbol with alpha^E, for the per-step multipliers of the 15 DFT inputs")
+    L.append("template <int E>")
+    L.append("PPFN void cmulT(uint32_t (&x)[8]);")
+    for e in sorted(cm):
+        L.append(f"template <>  // {cm[e].cost()} ops")
+        L.append(f"PPFN void cmulT<{e}>(uint32_t (&x)[8])")
+        L.append("{")
+        L += emit_slp_body(cm[e], [f"x[{i}]" for i in range(8)], [f"x[{i}]" for i in range(8)], tmp="m")
+        L.append("}")
+    L.append("// multiplier exponents: DFT inputs d = 2..14 (Z_d *= alpha^kChienZ[d - 2] per step), then the running terms")
+    L.append("// Lambda_15 gamma^u, Lambda_1 gamma^(8u), Lambda_16 gamma^(9u)")
+    L.append("constexpr int kChienZ[13] = {" + ", ".join(str(e) for e in zs) + "};")
+    L.append(f"constexpr int kChienB = {run3[0]}, kChienC = {run3[1]}, kChienD = {run3[2]};")
+    L.append("// DFT output k of step u is Lambda(alpha^j) with j = (120 u + kChienJ[k]) mod 255")
+    L.append("constexpr int kChienJ[15] = {" + ", ".join(str((136 * ((2 * k) % 15)) % 255) for k in range(15)) + "};")
+    L.append(f"// model: per step 2 x dft15 + {sum(cm[e].cost() for e in zs) + sum(cm[e].cost() for e in run3)} multiplier ops")
     L.append("")
     L.append("// encoder: parity byte q (memory order), bit u = XOR over j of the subset kEncMask[j-1][q][u] of the 8 tower")
     L.append("// planes of S_j, S_j = syndromes of message * x^32  (parity = V^-1 S, V[j][t] = alpha^(j t))")
