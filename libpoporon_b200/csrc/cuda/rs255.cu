@@ -865,7 +865,7 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 #endif
 constexpr int kSolveWarpsPerCTA = PP_SOLVE_WARPS_PER_CTA; // warps of a CTA move from tile to tile together (see the kernel)
 constexpr int kSolveSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 256; // work areas + the root table (256 B)
-constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO + bs::kWordsM;  // per lane, in global memory (L2-resident)
+constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO + bs::kWordsM + 32;  // per lane, in global memory (L2-resident)
 #ifndef PP_SOLVE_WARPS_PER_SM
 #define PP_SOLVE_WARPS_PER_SM 8
 #endif
@@ -1072,6 +1072,9 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
     const bs::Mem<32> Syn{gs};
     const bs::Mem<32> B{gs + bs::kWordsS * 32}; // the evaluator
     const bs::Mem<32> Mk{gs + (bs::kWordsS + bs::kWordsO) * 32}; // root masks of the transform-form Chien search
+    // the tile's 32 queue entries of this lane (L2-resident copy: the queue itself is 64 MB of DRAM by the time the
+    // outcomes are written, and three loops below would wait for it entry by entry)
+    const bs::Mem<32> Qs{gs + (bs::kWordsS + bs::kWordsO + bs::kWordsM) * 32};
     uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWarpsPerCTA * bs::kWordsW * 32);
     {
         // root_tab[0] = 0 (empty list slot), root_tab[v] = alpha^v for v = 1..255: each lane fills 8 consecutive powers
@@ -1115,6 +1118,9 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
                 const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
                 ent[c] = q < total ? queue[q] : 0xFFFFFFFFu;
             }
+#pragma unroll
+            for (int c = 0; c < 32; c++)
+                Qs.st(c, ent[c]);
             solve_load_syndromes(ent, syn_raw, Syn);
         }
         bs::LaneOut out;
@@ -1127,31 +1133,39 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
         uint32_t okmask = 0;
         int maxroots = 0;
 #pragma unroll 1
-        for (int c = 0; c < 32; c++) {
-            const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
-            if (q >= total)
-                continue;
-            const uint32_t entry = queue[q];
-            int nroots = 0;
-            const int st = bs::classify<32>(S, out, c, nroots);
-            if (st == bs::kOk) {
-                okmask |= 1u << c;
-                maxroots = nroots > maxroots ? nroots : maxroots;
-                uint4 *row = reinterpret_cast<uint4 *>(syn_raw + (size_t)(entry & 0x3FFFFFFFu) * 32);
-                row[0] = make_uint4(S.ld(bs::kListBase + 4 * c), S.ld(bs::kListBase + 4 * c + 1),
-                                    S.ld(bs::kListBase + 4 * c + 2), S.ld(bs::kListBase + 4 * c + 3));
-                row[1] = make_uint4(0u, 0u, 0u, 0u);
-                continue;
-            }
-            queue[q] = 0xFFFFFFFFu;
-            if (st == bs::kDeclined) {
-                queue2[atomicAdd(counter2, 1u)] = entry;
-            } else {
-                const size_t cw = entry & 0x3FFFFFFFu;
-                if (ok)
-                    ok[cw] = 0;
-                if (corrected)
-                    corrected[cw] = 0;
+        for (int c0 = 0; c0 < 32; c0 += 4) {
+            uint32_t e4[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                e4[u] = Qs.ld(c0 + u);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int c = c0 + u;
+                const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
+                if (q >= total)
+                    continue;
+                const uint32_t entry = e4[u];
+                int nroots = 0;
+                const int st = bs::classify<32>(S, out, c, nroots);
+                if (st == bs::kOk) {
+                    okmask |= 1u << c;
+                    maxroots = nroots > maxroots ? nroots : maxroots;
+                    uint4 *row = reinterpret_cast<uint4 *>(syn_raw + (size_t)(entry & 0x3FFFFFFFu) * 32);
+                    row[0] = make_uint4(S.ld(bs::kListBase + 4 * c), S.ld(bs::kListBase + 4 * c + 1),
+                                        S.ld(bs::kListBase + 4 * c + 2), S.ld(bs::kListBase + 4 * c + 3));
+                    row[1] = make_uint4(0u, 0u, 0u, 0u);
+                    continue;
+                }
+                queue[q] = 0xFFFFFFFFu;
+                if (st == bs::kDeclined) {
+                    queue2[atomicAdd(counter2, 1u)] = entry;
+                } else {
+                    const size_t cw = entry & 0x3FFFFFFFu;
+                    if (ok)
+                        ok[cw] = 0;
+                    if (corrected)
+                        corrected[cw] = 0;
+                }
             }
         }
 
@@ -1165,26 +1179,38 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
             uint32_t X[32];
             bs::magnitude_words<32>(S, X);
 #pragma unroll
-            for (int c = 0; c < 32; c++) {
-                if (((okmask >> c) & 1u) && X[c] != 0u) {
-                    const uint32_t entry = queue[g0 + 32u * (uint32_t)c + (uint32_t)lane];
-                    reinterpret_cast<uint32_t *>(syn_raw + (size_t)(entry & 0x3FFFFFFFu) * 32 + 16)[w] = X[c];
-                }
+            for (int c0 = 0; c0 < 32; c0 += 8) {
+                uint32_t e8[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++)
+                    e8[u] = Qs.ld(c0 + u);
+#pragma unroll
+                for (int u = 0; u < 8; u++)
+                    if (((okmask >> (c0 + u)) & 1u) && X[c0 + u] != 0u)
+                        reinterpret_cast<uint32_t *>(syn_raw + (size_t)(e8[u] & 0x3FFFFFFFu) * 32 + 16)[w] = X[c0 + u];
             }
         }
 #pragma unroll 1
-        for (int c = 0; c < 32; c++) {
-            if (!((okmask >> c) & 1u))
-                continue;
-            const size_t cw = queue[g0 + 32u * (uint32_t)c + (uint32_t)lane] & 0x3FFFFFFFu;
-            uint32_t nnz = 0;
+        for (int c0 = 0; c0 < 32; c0 += 4) {
+            uint32_t e4[4];
 #pragma unroll
-            for (int b = 0; b < 5; b++)
-                nnz |= ((nzc[b] >> c) & 1u) << b;
-            if (ok)
-                ok[cw] = 1;
-            if (corrected)
-                corrected[cw] = nnz;
+            for (int u = 0; u < 4; u++)
+                e4[u] = Qs.ld(c0 + u);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int c = c0 + u;
+                if (!((okmask >> c) & 1u))
+                    continue;
+                const size_t cw = e4[u] & 0x3FFFFFFFu;
+                uint32_t nnz = 0;
+#pragma unroll
+                for (int b = 0; b < 5; b++)
+                    nnz |= ((nzc[b] >> c) & 1u) << b;
+                if (ok)
+                    ok[cw] = 1;
+                if (corrected)
+                    corrected[cw] = nnz;
+            }
         }
         hook.g0p = g0; // this tile's records are final: applied during the next sweep (or by the drain below)
         }
