@@ -832,7 +832,7 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
         }
         uint8_t *d = data + cw * data_stride;
         uint8_t *p = parity + cw * parity_stride;
-        const int16_t pad = (int16_t)(255 - 32 - (int)size);
+        const int16_t pad = (int16_t)(255 - (int)c.nroots - (int)size);
         uint32_t ncorr = 0;
         bool success;
         if (mode == POPORON_CUDA_MODE_ERASURE) {
@@ -1059,7 +1059,7 @@ struct ApplyHook {
 // The warps of a CTA meet at a barrier after every tile: they then run the same phase (BM, sweep, Forney) at the
 // same time and share its code in the 32 KB instruction cache, which eight warps drifting apart do not.
 __global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, kSolveWarpsPerSM / kSolveWarpsPerCTA)
-rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ counter, uint8_t *syn_raw,
+rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restrict__ counter, uint8_t *syn_raw,
                    uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2,
                    uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data, size_t data_stride,
                    uint8_t *parity, size_t parity_stride)
@@ -1093,7 +1093,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
     }
     __syncthreads(); // (every warp wrote the same table)
     const uint32_t total = *counter;
-    const int pad = kMsg - (int)size;
+    const int pad = 255 - nr - (int)size; // nr = roots of the code = syndromes per codeword (32, 16 or 8)
     ApplyHook hook;
     hook.records = syn_raw;
     hook.data = data;
@@ -1124,7 +1124,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
             solve_load_syndromes(ent, syn_raw, Syn);
         }
         bs::LaneOut out;
-        bs::solve_lane<32, 32>(Syn, B, Mk, S, pad, out, hook); // also drains the previous tile's corrections
+        bs::solve_lane<32, 32>(Syn, B, Mk, S, pad, out, hook, nr); // also drains the previous tile's corrections
 
         // Outcome of every codeword of the lane.  What the solver declines goes to the literal stage.  A decodable
         // codeword gets an error record in place of its (now dead) raw syndrome row: bytes 0..15 the error locations
@@ -1146,7 +1146,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
                     continue;
                 const uint32_t entry = e4[u];
                 int nroots = 0;
-                const int st = bs::classify<32>(S, out, c, nroots);
+                const int st = bs::classify<32>(S, out, c, nroots, nr);
                 if (st == bs::kOk) {
                     okmask |= 1u << c;
                     maxroots = nroots > maxroots ? nroots : maxroots;
@@ -1226,7 +1226,7 @@ rs255_solve_kernel(size_t size, uint32_t *queue, const uint32_t *__restrict__ co
 // the same).  Clean words are finished here (ok = 1, corrected = 0).
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-rs255_extsyn_ingest_kernel(const uint16_t *__restrict__ extsyn, size_t n, const RsTables *__restrict__ gtab,
+rs255_extsyn_ingest_kernel(int nr, const uint16_t *__restrict__ extsyn, size_t n, const RsTables *__restrict__ gtab,
                            uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ queue, uint32_t *__restrict__ counter,
                            uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
 {
@@ -1236,10 +1236,12 @@ rs255_extsyn_ingest_kernel(const uint16_t *__restrict__ extsyn, size_t n, const 
     const size_t cw = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t flag = 0;
     if (cw < n) {
-        const uint4 *row = reinterpret_cast<const uint4 *>(extsyn + cw * 32); // 64 bytes, 16-byte aligned
-        uint32_t out[8];
+        const uint4 *row = reinterpret_cast<const uint4 *>(extsyn + cw * (size_t)nr); // 2 nr bytes, 16-byte aligned
+        uint32_t out[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll
         for (int q = 0; q < 4; q++) {
+            if (8 * q >= nr)
+                break; // (a code with fewer roots has shorter rows; the raw row is zero beyond them)
             const uint4 v = row[q];
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
             uint32_t b[8];
@@ -1279,21 +1281,23 @@ rs255_extsyn_ingest_kernel(const uint16_t *__restrict__ extsyn, size_t n, const 
 // leaves index_of[S_j], nn = 255 for zero): from the screen kernel's dirty bitmap and raw rows.  One thread per
 // group of four syndromes.
 __global__ void __launch_bounds__(256)
-rs255_syn_export_kernel(const uint32_t *__restrict__ dirty, const uint8_t *__restrict__ syn_raw, size_t n,
+rs255_syn_export_kernel(int nr, const uint32_t *__restrict__ dirty, const uint8_t *__restrict__ syn_raw, size_t n,
                         const RsTables *__restrict__ gtab, uint16_t *__restrict__ out)
 {
     __shared__ uint8_t log_tab[256];
     log_tab[threadIdx.x] = gtab->index_of[threadIdx.x];
     __syncthreads();
     const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const size_t cw = t >> 3;
+    const uint32_t wpr = (uint32_t)nr >> 2; // groups of four syndromes per codeword
+    const size_t cw = t / wpr;
+    const uint32_t g = (uint32_t)(t - cw * wpr);
     if (cw >= n)
         return;
     uint32_t v = 0;
     if ((dirty[cw >> 5] >> (cw & 31u)) & 1u)
-        v = reinterpret_cast<const uint32_t *>(syn_raw + cw * 32)[t & 7u];
+        v = reinterpret_cast<const uint32_t *>(syn_raw + cw * 32)[g];
     const uint32_t a = log_tab[v & 0xFFu], b = log_tab[(v >> 8) & 0xFFu], c = log_tab[(v >> 16) & 0xFFu], d = log_tab[v >> 24];
-    reinterpret_cast<uint2 *>(out + cw * 32)[t & 7u] = make_uint2(a | (b << 16), c | (d << 16));
+    reinterpret_cast<uint2 *>(out + cw * (size_t)nr)[g] = make_uint2(a | (b << 16), c | (d << 16));
 }
 
 int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
@@ -1322,7 +1326,9 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
 
 bool rs255_matches(const poporon_cuda_rs_desc_t *d)
 {
-    return d->symbol_size == 8 && d->gfpoly == 0x11D && d->fcr == 1 && d->prim == 1 && d->nroots == 32;
+    // RS(255,223) and the reference's other two documented codes RS(255,239), RS(255,247) (README.md:417-419)
+    return d->symbol_size == 8 && d->gfpoly == 0x11D && d->fcr == 1 && d->prim == 1 &&
+           (d->nroots == 32 || d->nroots == 16 || d->nroots == 8);
 }
 
 // round-1 LFSR kernels: any message size 1..223; a lane's 32 codewords must be equally aligned inside their 16-byte
@@ -1344,10 +1350,11 @@ static bool lfsr_shape_ok(int op, const uint8_t *data, size_t data_stride, size_
 bool rs255_shape_ok(const poporon_cuda_rs *ctx, int op, const uint8_t *data, size_t data_stride, size_t size,
                     const uint8_t *parity, size_t parity_stride)
 {
-    if (!ctx->use_lfsr && data_stride <= 0xFFFFFFFFull && parity_stride <= 0xFFFFFFFFull &&
-        rs255_fft_shape_ok(op, data, data_stride, size, parity, parity_stride, nullptr))
+    const int nr = ctx->code.nroots;
+    if ((!ctx->use_lfsr || nr != 32) && data_stride <= 0xFFFFFFFFull && parity_stride <= 0xFFFFFFFFull &&
+        rs255_fft_shape_ok(nr, op, data, data_stride, size, parity, parity_stride, nullptr))
         return true;
-    return lfsr_shape_ok(op, data, data_stride, size, parity, parity_stride);
+    return nr == 32 && lfsr_shape_ok(op, data, data_stride, size, parity, parity_stride); // LFSR kernels: RS(255,223) only
 }
 
 int rs255_init(poporon_cuda_rs *ctx)
@@ -1410,7 +1417,8 @@ int rs255_encode(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_stride, 
     if (n == 0)
         return 0;
     FftShape shape;
-    if (!ctx->use_lfsr && rs255_fft_shape_ok(0, data, data_stride, size, parity, parity_stride, &shape)) {
+    if ((!ctx->use_lfsr || ctx->code.nroots != 32) &&
+        rs255_fft_shape_ok(ctx->code.nroots, 0, data, data_stride, size, parity, parity_stride, &shape)) {
         int rc = ensure_slab(ctx);
         if (rc != 0)
             return rc;
@@ -1460,6 +1468,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
 {
     if (n == 0)
         return 0;
+    const int nr = ctx->code.nroots; // 32, 16 or 8
     int rc = ensure_scratch(ctx, n);
     if (rc != 0)
         return rc;
@@ -1479,8 +1488,9 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         // the syndromes come from the caller: no screen pass, the rows and the queue are built from them
         ProfScope prof(ctx, PROF_COMPACT, stream);
         rs255_extsyn_ingest_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(
-            extsyn, n, ctx->d_tables, ctx->d_rem, ctx->d_queue, ctx->d_counters, ok, corrected);
-    } else if (!ctx->use_lfsr && rs255_fft_shape_ok(1, data, data_stride, size, parity, parity_stride, &shape)) {
+            nr, extsyn, n, ctx->d_tables, ctx->d_rem, ctx->d_queue, ctx->d_counters, ok, corrected);
+    } else if ((!ctx->use_lfsr || ctx->code.nroots != 32) &&
+               rs255_fft_shape_ok(ctx->code.nroots, 1, data, data_stride, size, parity, parity_stride, &shape)) {
         rc = ensure_slab(ctx);
         if (rc != 0)
             return rc;
@@ -1525,7 +1535,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
             const size_t warps = groups < cap ? groups : cap;
             rs255_solve_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
                                  kSolveSmem, stream>>>(
-                size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected,
+                nr, size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected,
                 data, data_stride, parity, parity_stride);
         }
         cq = queue2;
@@ -1548,7 +1558,7 @@ int rs255_syndromes(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_strid
     if (n == 0)
         return 0;
     FftShape shape;
-    if (!rs255_fft_shape_ok(1, data, data_stride, size, parity, parity_stride, &shape))
+    if (!rs255_fft_shape_ok(ctx->code.nroots, 1, data, data_stride, size, parity, parity_stride, &shape))
         return POPORON_CUDA_ERR_UNSUPP;
     int rc = ensure_scratch(ctx, n);
     if (rc == 0)
@@ -1563,7 +1573,9 @@ int rs255_syndromes(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_strid
     }
     if (rc != 0)
         return rc;
-    rs255_syn_export_kernel<<<(unsigned)((n * 8 + 255) / 256), 256, 0, stream>>>(dmask, ctx->d_rem, n, ctx->d_tables, out);
+    const int nr = ctx->code.nroots;
+    rs255_syn_export_kernel<<<(unsigned)((n * (size_t)(nr / 4) + 255) / 256), 256, 0, stream>>>(nr, dmask, ctx->d_rem, n,
+                                                                                               ctx->d_tables, out);
     ctx->launches += 2;
     return check(cudaGetLastError(), "rs255 syndrome export launch");
 }

@@ -60,7 +60,8 @@ enum { MODE_SCREEN = 0, MODE_ENCODE = 1 };
 struct FftArgs {
     const uint8_t *data;   // message rows
     size_t dstride;
-    int size;              // message bytes per codeword, 1..223
+    int size;              // message bytes per codeword, 1..255 - npar
+    int npar;              // parity bytes per codeword = roots of the code: 32, 16 or 8 (RS(255,223) / (255,239) / (255,247))
     const uint8_t *parity; // SCREEN: parity rows (32 bytes each)
     size_t pstride;
     int packed;            // SCREEN: parity rows interleaved with the message rows (one stride, one span per sub-tile)
@@ -265,7 +266,7 @@ __device__ __forceinline__ void issue_subtile(const FftArgs &A, uint32_t bufaddr
 {
     __syncwarp(); // every lane is done reading the buffer's previous contents
     uint32_t tx = 0;
-    const int rowlen = (MODE == MODE_SCREEN && A.packed) ? A.prow_off + 32 : A.size;
+    const int rowlen = (MODE == MODE_SCREEN && A.packed) ? A.prow_off + A.npar : A.size;
     const uint8_t *g = A.data + cwb * A.dstride;
     const uint32_t a = (uint32_t)((uintptr_t)g & 15u);
     const uint32_t total = rows > 0 ? a + (uint32_t)(rows - 1) * (uint32_t)A.dstride + (uint32_t)rowlen : 0u;
@@ -276,7 +277,7 @@ __device__ __forceinline__ void issue_subtile(const FftArgs &A, uint32_t bufaddr
     if (MODE == MODE_SCREEN && !A.packed) {
         gp = A.parity + cwb * A.pstride;
         ap = (uint32_t)((uintptr_t)gp & 15u);
-        total_p = rows > 0 ? ap + (uint32_t)(rows - 1) * (uint32_t)A.pstride + 32u : 0u;
+        total_p = rows > 0 ? ap + (uint32_t)(rows - 1) * (uint32_t)A.pstride + (uint32_t)A.npar : 0u;
         bulk_p = total_p & ~15u;
         tx += bulk_p;
     }
@@ -302,9 +303,9 @@ __device__ __forceinline__ void issue_subtile(const FftArgs &A, uint32_t bufaddr
 template <int MODE>
 __device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t bufaddr, size_t cwb, int ls, uint8_t *slab, int lane)
 {
-    const int L = A.size + 32;
-    const int ncd = (A.size + 3) >> 2;                        // word-columns of the message
-    const int ncols = MODE == MODE_SCREEN ? ncd + 8 : ncd;    // + 8 of the parity
+    const int L = A.size + A.npar;
+    const int ncd = (A.size + 3) >> 2;                                   // word-columns of the message
+    const int ncols = MODE == MODE_SCREEN ? ncd + (A.npar >> 2) : ncd;    // + those of the parity
     const uint32_t ad = (uint32_t)((uintptr_t)(A.data + cwb * A.dstride) & 15u);
     uint32_t pbase, pstr;
     if (MODE == MODE_SCREEN) {
@@ -334,7 +335,7 @@ __device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t buf
             base = pbase + 4u * (uint32_t)(pc & 7);
             stride = pstr;
             nvalid = col < ncols ? 4 : 0;
-            e0 = 31 - 4 * (pc & 7);
+            e0 = A.npar - 1 - 4 * (pc & 7);
         }
         // rows i and i + 4 are 4 * stride bytes apart: same byte offset inside their words.  Four aligned row bases
         // and four PRMT selectors serve all 32 rows.
@@ -476,7 +477,7 @@ __device__ __forceinline__ void s2_run(const Smem &sm, int lane, uint32_t gtask,
 // S2 epilogue.  SCREEN: dirty mask of the warp's syndromes + their standard-basis planes to the output stage.
 // ENCODE: the tower planes go to the global syndrome-plane array of the tile (32 bytes per lane and syndrome).
 template <int MODE, int U>
-__device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t (&acc)[4][8], uint32_t *tileplanes)
+__device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t (&acc)[4][8], uint32_t *tileplanes, int npar)
 {
     uint32_t nz = 0;
 #pragma unroll
@@ -486,7 +487,7 @@ __device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t 
             rsfft::conv_out(acc[q], s);
 #pragma unroll
             for (int t = 0; t < 8; t++) {
-                nz |= s[t];
+                nz |= s2_j(U, q) <= npar ? s[t] : 0u; // (a 16- or 8-root code has no syndromes beyond its roots)
                 sts32(sm.outplane(8 * (s2_j(U, q) - 1) + t, lane), s[t]);
             }
         } else {
@@ -497,11 +498,11 @@ __device__ __forceinline__ uint32_t s2_store(const Smem &sm, int lane, uint32_t 
 }
 
 template <int MODE, int U>
-__device__ __forceinline__ void s2_role(const Smem &sm, int lane, uint32_t gtask, uint32_t *tileplanes)
+__device__ __forceinline__ void s2_role(const Smem &sm, int lane, uint32_t gtask, uint32_t *tileplanes, int npar)
 {
     uint32_t acc[4][8];
     s2_run<U>(sm, lane, gtask, acc);
-    const uint32_t nz = s2_store<MODE, U>(sm, lane, acc, tileplanes);
+    const uint32_t nz = s2_store<MODE, U>(sm, lane, acc, tileplanes, npar);
     if (MODE == MODE_SCREEN)
         sts32(sm.nzword(U, lane), nz);
 }
@@ -533,10 +534,10 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
     // symbols nobody writes are zero: exponents >= size + 32 (shortened code) and, for the encoder, the parity
     // positions e < 32
     {
-        const int L = A.size + 32;
+        const int L = A.size + A.npar;
         const uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         for (int e = warp; e < 255; e += kWarps)
-            if (e >= L || (MODE == MODE_ENCODE && e < 32))
+            if (e >= L || (MODE == MODE_ENCODE && e < A.npar))
                 stg256(slab + (size_t)slot_of((uint32_t)e) * kSlotBytes + (size_t)lane * 32, z);
     }
     __syncthreads();
@@ -582,14 +583,14 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
             s1_run(sm, slab, warp, lane, gtask);
         } else {
             switch (warp - kS1Warps) {
-            case 0: s2_role<MODE, 0>(sm, lane, gtask, tileplanes); break;
-            case 1: s2_role<MODE, 1>(sm, lane, gtask, tileplanes); break;
-            case 2: s2_role<MODE, 2>(sm, lane, gtask, tileplanes); break;
-            case 3: s2_role<MODE, 3>(sm, lane, gtask, tileplanes); break;
-            case 4: s2_role<MODE, 4>(sm, lane, gtask, tileplanes); break;
-            case 5: s2_role<MODE, 5>(sm, lane, gtask, tileplanes); break;
-            case 6: s2_role<MODE, 6>(sm, lane, gtask, tileplanes); break;
-            default: s2_role<MODE, 7>(sm, lane, gtask, tileplanes); break;
+            case 0: s2_role<MODE, 0>(sm, lane, gtask, tileplanes, A.npar); break;
+            case 1: s2_role<MODE, 1>(sm, lane, gtask, tileplanes, A.npar); break;
+            case 2: s2_role<MODE, 2>(sm, lane, gtask, tileplanes, A.npar); break;
+            case 3: s2_role<MODE, 3>(sm, lane, gtask, tileplanes, A.npar); break;
+            case 4: s2_role<MODE, 4>(sm, lane, gtask, tileplanes, A.npar); break;
+            case 5: s2_role<MODE, 5>(sm, lane, gtask, tileplanes, A.npar); break;
+            case 6: s2_role<MODE, 6>(sm, lane, gtask, tileplanes, A.npar); break;
+            default: s2_role<MODE, 7>(sm, lane, gtask, tileplanes, A.npar); break;
             }
         }
         gtask += 17;
@@ -612,7 +613,8 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
                 if (warp == 0 && cw0 < A.n)
                     A.dirty[cw0 >> 5] = dirty;
                 if (__any_sync(0xFFFFFFFFu, dirty != 0)) {
-                    // syndrome word-column `warp`: S_{4w+1} .. S_{4w+4} of the lane-slot's 32 codewords
+                    // syndrome word-column `warp`: S_{4w+1} .. S_{4w+4} of the lane-slot's 32 codewords (columns beyond
+                    // the code's roots are written as well: nobody reads them)
                     uint32_t X[32];
 #pragma unroll
                     for (int p = 0; p < 32; p++)
@@ -647,7 +649,11 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
 // ---------------------------------------------------------------------------------------------------
 constexpr int kParWarps = 16;
 constexpr int kParPlanes = 64;                         // output planes per pass
-constexpr int kParPasses = 256 / kParPlanes;
+// the mask table of a code with NR roots (32: RS(255,223); 16, 8: the reference's other documented codes)
+template <int NR> struct EncOf;
+template <> struct EncOf<32> { using M = rsfft::EncM; };
+template <> struct EncOf<16> { using M = rsfft::EncM16; };
+template <> struct EncOf<8> { using M = rsfft::EncM8; };
 constexpr size_t kTilePlaneWords = 32 * 32 * 8;        // one tile of syndrome planes / parity planes
 
 struct ParArgs {
@@ -656,24 +662,24 @@ struct ParArgs {
     size_t ntiles;
 };
 
-template <int H, int J, int QU>
+template <int NR, int H, int J, int QU>
 __device__ __forceinline__ void par_one(uint32_t (&acc)[kParPlanes], const uint32_t (&T1)[16], const uint32_t (&T2)[16])
 {
-    constexpr unsigned m = rsfft::EncM::v.m[J][(kParPlanes / 8) * H + (QU >> 3)][QU & 7];
+    constexpr unsigned m = EncOf<NR>::M::v.m[J][(kParPlanes / 8) * H + (QU >> 3)][QU & 7];
     acc[QU] = xor3(acc[QU], T1[m & 15], T2[m >> 4]);
 }
-template <int H, int J, int... QU>
+template <int NR, int H, int J, int... QU>
 __device__ __forceinline__ void par_acc(uint32_t (&acc)[kParPlanes], const uint32_t (&T1)[16], const uint32_t (&T2)[16],
                                         std::integer_sequence<int, QU...>)
 {
-    (par_one<H, J, QU>(acc, T1, T2), ...);
+    (par_one<NR, H, J, QU>(acc, T1, T2), ...);
 }
-template <int H, int J>
+template <int NR, int H, int J>
 __device__ __forceinline__ void par_j(const uint32_t *tp, int lane, uint32_t (&in)[8], uint32_t (&acc)[kParPlanes])
 {
-    if constexpr (J < 32) {
+    if constexpr (J < NR) {
         uint32_t nx[8], T1[16], T2[16];
-        if constexpr (J + 1 < 32) {
+        if constexpr (J + 1 < NR) {
             uint32_t lo[4], hi[4];
             ldg256(tp + ((size_t)(J + 1) * 32 + (size_t)lane) * 8, lo, hi);
 #pragma unroll
@@ -684,19 +690,19 @@ __device__ __forceinline__ void par_j(const uint32_t *tp, int lane, uint32_t (&i
         }
         subset_table(in[0], in[1], in[2], in[3], T1);
         subset_table(in[4], in[5], in[6], in[7], T2);
-        par_acc<H, J>(acc, T1, T2, std::make_integer_sequence<int, kParPlanes>{});
+        par_acc<NR, H, J>(acc, T1, T2, std::make_integer_sequence<int, kParPlanes>{});
         if constexpr ((J & 3) == 3)
             __syncthreads(); // keeps the CTA's warps on the same stretch of code
-        if constexpr (J + 1 < 32) {
+        if constexpr (J + 1 < NR) {
 #pragma unroll
             for (int t = 0; t < 8; t++)
                 in[t] = nx[t];
-            par_j<H, J + 1>(tp, lane, in, acc);
+            par_j<NR, H, J + 1>(tp, lane, in, acc);
         }
     }
 }
 
-template <int H>
+template <int NR, int H>
 __device__ __forceinline__ void parity_pass(const uint32_t *tp, uint32_t *op, bool active, int lane)
 {
     uint32_t acc[kParPlanes];
@@ -711,7 +717,7 @@ __device__ __forceinline__ void parity_pass(const uint32_t *tp, uint32_t *op, bo
             in[t] = lo[t];
             in[4 + t] = hi[t];
         }
-        par_j<H, 0>(tp, lane, in, acc);
+        par_j<NR, H, 0>(tp, lane, in, acc);
     }
     if (active) {
 #pragma unroll
@@ -720,13 +726,14 @@ __device__ __forceinline__ void parity_pass(const uint32_t *tp, uint32_t *op, bo
                 make_uint4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
     }
 }
-template <int... H>
+template <int NR, int... H>
 __device__ __forceinline__ void parity_passes(const uint32_t *tp, uint32_t *op, bool active, int lane,
                                               std::integer_sequence<int, H...>)
 {
-    (parity_pass<H>(tp, op, active, lane), ...);
+    (parity_pass<NR, H>(tp, op, active, lane), ...);
 }
 
+template <int NR>
 __global__ void __launch_bounds__(32 * kParWarps, 1) rs255_parity_kernel(ParArgs A)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -737,8 +744,8 @@ __global__ void __launch_bounds__(32 * kParWarps, 1) rs255_parity_kernel(ParArgs
         const bool active = tile < A.ntiles;
         if (!active)
             tile = A.ntiles - 1; // walks through the barriers on a tile that exists, stores nothing
-        parity_passes(A.synplanes + tile * kTilePlaneWords, A.parplanes + tile * kTilePlaneWords, active, lane,
-                      std::make_integer_sequence<int, kParPasses>{});
+        parity_passes<NR>(A.synplanes + tile * kTilePlaneWords, A.parplanes + tile * kTilePlaneWords, active, lane,
+                          std::make_integer_sequence<int, 8 * NR / kParPlanes>{});
     }
 }
 
@@ -763,8 +770,11 @@ __device__ __forceinline__ uint32_t row_word(uint32_t ls, uint32_t i, uint32_t w
     return ((ls * 32u + sigma) * 8u + ((w ^ ls) & 7u)) * 4u;
 }
 
+template <int NR> // parity bytes per row: 32, 16 or 8
 __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A)
 {
+    constexpr int KW = NR / 4;  // words per row
+    constexpr int RPS = 32 / KW; // rows per copy-out step
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t stage = smem_u32(smem_raw) + (uint32_t)(warp * kRowStageBytes);
@@ -778,9 +788,9 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
         for (int d = 0; d < 3; d++)
 #pragma unroll
             for (int q = 0; q < 8; q++)
-                nx[d][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * d + q) * 32 + (size_t)lane) * 4);
+                nx[d][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * (d < KW ? d : KW - 1) + q) * 32 + (size_t)lane) * 4);
 #pragma unroll 1
-        for (int w = 0; w < 8; w++) {
+        for (int w = 0; w < KW; w++) {
             uint32_t X[32];
 #pragma unroll
             for (int q = 0; q < 8; q++) {
@@ -789,7 +799,7 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
                 X[4 * q + 2] = nx[0][q].z;
                 X[4 * q + 3] = nx[0][q].w;
             }
-            const int wn = w + 3 < 8 ? w + 3 : 7;
+            const int wn = w + 3 < KW ? w + 3 : KW - 1;
 #pragma unroll
             for (int q = 0; q < 8; q++) {
                 nx[0][q] = nx[1][q];
@@ -813,24 +823,24 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
         // of a misaligned row leaves from lane k = 0, its tail from lane k = 7, as bytes.
         const size_t cwt = tile * kTile;
         const uint32_t left = A.n - cwt >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt);
-        const uint32_t rr = (uint32_t)lane >> 3, k = (uint32_t)lane & 7u;
+        const uint32_t rr = (uint32_t)lane / KW, k = (uint32_t)lane % KW;
 #pragma unroll 1
         for (uint32_t c = 0; c < 4; c++) {
             const uint32_t a = (uint32_t)(((uintptr_t)A.parity + (cwt + c) * A.pstride) & 3u);
             const uint32_t sel = 0x3210u + 0x1111u * (4u - a); // bytes 4 - a .. 7 - a of (previous word, this word)
             const bool inner = a == 0 || k != 0;
 #pragma unroll 1
-            for (uint32_t it0 = 0; it0 < 64; it0 += 8) {
+            for (uint32_t it0 = 0; it0 < 256 / RPS; it0 += 8) {
                 uint32_t cur[8], prv[8];
 #pragma unroll
                 for (uint32_t u = 0; u < 8; u++) { // all sixteen loads first, then the stores
-                    const uint32_t r = 4u * (4u * (it0 + u) + rr) + c;
+                    const uint32_t r = 4u * ((uint32_t)RPS * (it0 + u) + rr) + c;
                     cur[u] = lds32(stage + row_word(r >> 5, r & 31u, k));
-                    prv[u] = lds32(stage + row_word(r >> 5, r & 31u, (k + 7u) & 7u));
+                    prv[u] = lds32(stage + row_word(r >> 5, r & 31u, (k + KW - 1u) % KW));
                 }
 #pragma unroll
                 for (uint32_t u = 0; u < 8; u++) {
-                    const uint32_t r = 4u * (4u * (it0 + u) + rr) + c;
+                    const uint32_t r = 4u * ((uint32_t)RPS * (it0 + u) + rr) + c;
                     if (r >= left)
                         continue;
                     uint8_t *row = A.parity + (cwt + r) * A.pstride;
@@ -846,14 +856,14 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
                             row[0] = (uint8_t)cur[u];
                         }
                     }
-                    if (a != 0 && k == 7) { // tail: row bytes 32 - a .. 31, the top a bytes of word 7
+                    if (a != 0 && k == KW - 1) { // tail: row bytes NR - a .. NR - 1, the top a bytes of the last word
                         if (a == 1) {
-                            row[31] = (uint8_t)(cur[u] >> 24);
+                            row[NR - 1] = (uint8_t)(cur[u] >> 24);
                         } else if (a == 2) {
-                            *reinterpret_cast<uint16_t *>(row + 30) = (uint16_t)(cur[u] >> 16);
+                            *reinterpret_cast<uint16_t *>(row + NR - 2) = (uint16_t)(cur[u] >> 16);
                         } else {
-                            *reinterpret_cast<uint16_t *>(row + 29) = (uint16_t)(cur[u] >> 8);
-                            row[31] = (uint8_t)(cur[u] >> 24);
+                            *reinterpret_cast<uint16_t *>(row + NR - 3) = (uint16_t)(cur[u] >> 8);
+                            row[NR - 1] = (uint8_t)(cur[u] >> 24);
                         }
                     }
                 }
@@ -897,30 +907,31 @@ int smem_bytes(int bufbytes)
 
 } // namespace
 
-bool rs255_fft_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
+bool rs255_fft_shape_ok(int npar, int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
                         size_t parity_stride, FftShape *shape)
 {
-    if (size < 1 || size > 223 || data_stride < size)
+    if ((npar != 32 && npar != 16 && npar != 8) || size < 1 || size > (size_t)(255 - npar) || data_stride < size)
         return false;
     // "packed": every parity row sits between its message row and the next one (packed 255-byte records are the
     // case parity == data + size); the sub-tile is then one span
     const bool packed = op == 1 && parity_stride == data_stride && parity >= data + size &&
-                        (size_t)(parity - data) + 32 <= data_stride;
-    const size_t rowlen = packed ? (size_t)(parity - data) + 32 : size;
+                        (size_t)(parity - data) + (size_t)npar <= data_stride;
+    const size_t rowlen = packed ? (size_t)(parity - data) + (size_t)npar : size;
     size_t dspan = 31 * data_stride + rowlen + 15 + 8; // + alignment of the span + the funnel's second word
     dspan = (dspan + 15) & ~(size_t)15;
     size_t total = dspan, poff = 0;
     if (op == 1 && !packed) {
-        if (parity_stride < 32)
+        if (parity_stride < (size_t)npar)
             return false;
         poff = dspan;
-        size_t pspan = 31 * parity_stride + 32 + 15 + 8;
+        size_t pspan = 31 * parity_stride + (size_t)npar + 15 + 8;
         pspan = (pspan + 15) & ~(size_t)15;
         total += pspan;
     }
     if (total > (size_t)kMaxBuf)
         return false;
     if (shape) {
+        shape->npar = npar;
         shape->packed = packed ? 1 : 0;
         shape->prow_off = packed ? (int)(parity - data) : 0;
         shape->bufbytes = (int)total;
@@ -941,7 +952,9 @@ int rs255_fft_init(poporon_cuda_rs *ctx)
                                      smem_bytes(kMaxBuf)));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_fft_kernel<MODE_ENCODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      smem_bytes(kMaxBuf)));
-    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRowSmem));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_rows_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRowSmem));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_rows_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRowSmem));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_rows_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRowSmem));
     return 0;
 }
 
@@ -959,6 +972,7 @@ int rs255_fft_screen(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     A.data = data;
     A.dstride = data_stride;
     A.size = (int)size;
+    A.npar = shape.npar;
     A.parity = parity;
     A.pstride = parity_stride;
     A.packed = shape.packed;
@@ -994,6 +1008,7 @@ int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     A.data = data;
     A.dstride = data_stride;
     A.size = (int)size;
+    A.npar = shape.npar;
     A.packed = 0;
     A.n = n;
     A.slab = slab;
@@ -1016,9 +1031,14 @@ int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
         P.parplanes = parplanes;
         P.ntiles = ntiles;
         const size_t ctas = (ntiles + kParWarps - 1) / kParWarps;
+        const unsigned grid = (unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count);
         ProfScope prof(ctx, PROF_PARITY, stream);
-        rs255_parity_kernel<<<(unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count), 32 * kParWarps, 0,
-                              stream>>>(P);
+        if (shape.npar == 32)
+            rs255_parity_kernel<32><<<grid, 32 * kParWarps, 0, stream>>>(P);
+        else if (shape.npar == 16)
+            rs255_parity_kernel<16><<<grid, 32 * kParWarps, 0, stream>>>(P);
+        else
+            rs255_parity_kernel<8><<<grid, 32 * kParWarps, 0, stream>>>(P);
         rc = check(cudaGetLastError(), "rs255 parity launch");
     }
     if (rc != 0)
@@ -1030,9 +1050,14 @@ int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     R.parity = parity;
     R.pstride = parity_stride;
     const size_t ctas = (ntiles + kRowWarps - 1) / kRowWarps;
+    const unsigned grid = (unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count);
     ProfScope prof(ctx, PROF_ROWS, stream);
-    rs255_rows_kernel<<<(unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count), 32 * kRowWarps, kRowSmem,
-                        stream>>>(R);
+    if (shape.npar == 32)
+        rs255_rows_kernel<32><<<grid, 32 * kRowWarps, kRowSmem, stream>>>(R);
+    else if (shape.npar == 16)
+        rs255_rows_kernel<16><<<grid, 32 * kRowWarps, kRowSmem, stream>>>(R);
+    else
+        rs255_rows_kernel<8><<<grid, 32 * kRowWarps, kRowSmem, stream>>>(R);
     return check(cudaGetLastError(), "rs255 rows launch");
 }
 

@@ -4,6 +4,7 @@
 
 namespace ppcu {
 struct FftShape {
+    int npar;     // parity bytes per codeword (32, 16 or 8)
     int packed;   // SCREEN: parity rows interleaved with the message rows (one stride): one span per sub-tile
     int prow_off; // packed: parity - data
     int bufbytes; // shared-memory bytes of one 32-codeword sub-tile
@@ -11,7 +12,7 @@ struct FftShape {
 };
 // op 0 = encode (message rows only), 1 = screen (message + parity rows).  Any base alignment, any strides whose
 // 32-row span fits a sub-tile buffer.
-bool rs255_fft_shape_ok(int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
+bool rs255_fft_shape_ok(int npar, int op, const uint8_t *data, size_t data_stride, size_t size, const uint8_t *parity,
                         size_t parity_stride, FftShape *shape);
 size_t rs255_fft_slab_bytes(int sm_count);
 int rs255_fft_init(poporon_cuda_rs *ctx);

@@ -300,8 +300,10 @@ BS_FN void rotate_groups(uint32_t (&L)[kLS][8])
         }
 }
 
+// ns = number of syndromes = BM iterations: 32 for RS(255,223); 16 / 8 for RS(255,239) / RS(255,247), whose register
+// lengths stay <= ns / 2 (the counter k = r - 2 el declines everything longer, as for t = 16).
 template <int STRIDE, int SO>
-BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uint32_t (&K)[7])
+BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uint32_t (&K)[7], int ns)
 {
     uint32_t gamma[8], delta[8];
 #pragma unroll
@@ -321,7 +323,7 @@ BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uin
     ld8(S, 0, delta); // Delta_1 = L_0 * S_1 = S_1
 
 #pragma unroll 1
-    for (int r = 1; r <= kNS; r++) {
+    for (int r = 1; r <= ns; r++) {
         const uint32_t chg = or8(delta) & ~K[6]; // delta != 0 and k >= 0
         const int top = r < kT ? r : kT;         // highest coefficient that can be non-zero after this iteration
         // the counters first (they depend on chg only): afterwards k = r - 2*el with el the NEW register length
@@ -403,14 +405,20 @@ BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uin
 // ---- evaluator: Omega_i = sum_{j <= i} S_{i-j+1} * L_j, i = 0..15 (src/decode.c:147-158) -------------------
 // Rolled loops: L_0..L_15 are parked in P (16 blocks; the BM scratch, dead by now), Omega_i goes to word block i
 // of O.
+// (teff = ns / 2: for a code with fewer than 32 roots only Omega_0 .. Omega_(teff-1) exist; the rest is stored as zero)
 template <int STRIDE, int SO>
-BS_FN void omega(const Mem<SO> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE> P, const Mem<SO> O)
+BS_FN void omega(const Mem<SO> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE> P, const Mem<SO> O, int teff)
 {
 #pragma unroll
     for (int j = 0; j < kT; j++)
         st8(P, j, L[j]);
 #pragma unroll 1
-    for (int i = 0; i < kT; i++) {
+    for (int i = teff; i < kT; i++) {
+        const uint32_t z[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        st8(O, i, z);
+    }
+#pragma unroll 1
+    for (int i = 0; i < teff; i++) {
         // the syndromes come from the slower memory: fetched two terms ahead (s, s1, s2 = S_{i-j}, S_{i-j-1}, S_{i-j-2})
         uint32_t acc[15], o[8], a[8], s[8], s1[8], s2[8];
         clear15(acc);
@@ -1013,7 +1021,7 @@ enum { kDeclined = 0, kFail = 1, kOk = 2 };
 
 // Outcome of codeword c of a lane (see the header comment for the rules).  nroots = roots found.
 template <int STRIDE>
-BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots)
+BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots, int ns = kNS)
 {
     int k = 0;
 #pragma unroll
@@ -1021,7 +1029,7 @@ BS_FN int classify(const Mem<STRIDE> S, const LaneOut &o, int c, int &nroots)
         k |= (int)((o.K[b] >> c) & 1u) << b;
     if (k & 64)
         return kDeclined; // k < 0: L > 16
-    const int el = (32 - k) >> 1;
+    const int el = (ns - k) >> 1;
     uint32_t lead = 0;
 #pragma unroll
     for (int j = 0; j < kNL; j++)
@@ -1049,13 +1057,13 @@ constexpr int kWordsM = 256;
 
 template <int STRIDE, int SO, class Hook>
 BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<SO> Mk, const Mem<STRIDE> W, int pad, LaneOut &out,
-                      Hook &hook)
+                      Hook &hook, int ns = kNS)
 {
     const Mem<STRIDE> B{W.base + kListBase * STRIDE};
     {
         uint32_t L[kLS][8];
-        ribm<STRIDE, SO>(Syn, B, L, out.K);
-        omega<STRIDE, SO>(Syn, L, B, Om);
+        ribm<STRIDE, SO>(Syn, B, L, out.K, ns);
+        omega<STRIDE, SO>(Syn, L, B, Om, ns >> 1);
         // the syndromes are dead now: their first 17 word blocks receive the locator (read by the sweep set-up
         // and by Forney)
 #pragma unroll

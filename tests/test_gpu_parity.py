@@ -461,6 +461,69 @@ def test_every_layout_takes_the_bitsliced_path(gpu_device, orc, layout):
             assert (gap == 0xC3).all()
 
 
+@pytest.mark.parametrize("nr", [16, 8])
+def test_rs255_239_and_247_on_the_bitsliced_path(gpu_device, orc, nr):
+    """The reference's other documented codes RS(255,239) and RS(255,247) (README.md:417-419, tests/test_rs.c:36-83):
+    same field, fcr and prim as the default code, so they run on the transform kernels + the bitsliced solver (with 16 /
+    8 syndromes) instead of the per-thread generic kernels.  Every mode against the oracle."""
+    params = (8, 0x11D, 1, 1, nr)
+    K = 255 - nr
+    rng = np.random.default_rng(900 + nr)
+    n = 50000
+    msg = rng.integers(0, 256, (n, K), dtype=np.uint8)
+    want_par = orc.rs_encode(msg, params, threads=8)
+    with _rs(params) as h:
+        assert h.encode_batch(np.zeros((1, K), np.uint8), K, K, np.zeros((1, nr), np.uint8), nr, 1)  # touch the device
+        assert h.profile(True)
+        # encode: split arrays and packed records
+        par = np.full((n, nr), 0xEE, np.uint8)
+        assert h.encode_batch(msg, K, K, par, nr, n)
+        assert (par == want_par).all()
+        rec = np.zeros((n, 255), np.uint8)
+        rec[:, :K] = msg
+        assert h.encode_batch(rec.ctypes.data, 255, K, rec.ctypes.data + K, 255, n)
+        assert (rec[:, K:] == want_par).all() and (rec[:, :K] == msg).all()
+        prof = h.profile_read()
+        assert prof.get("rs255_fft_kernel<ENCODE>", (0, 0))[0] >= 2 and "rs_generic kernels" not in prof, prof
+        # decode, 0 .. t + 2 errors
+        cw = np.concatenate([msg, want_par], 1)
+        _inject(rng, cw, 255, nr // 2 + 2)
+        want = orc.rs_decode(cw[:, :K], cw[:, K:], params, threads=8)
+        assert 0 < want[2].mean() < 1  # decodable and undecodable words both present
+        assert h.profile(True)
+        got = _gpu_decode(h, cw[:, :K], cw[:, K:])  # split and packed, compared with each other inside
+        prof = h.profile_read()
+        assert prof.get("rs255_solve_kernel", (0, 0))[0] >= 2 and "rs_generic kernels" not in prof, prof
+        _assert_same(got, want, f"RS(255,{K}) plain")
+        # syndromes only, and the round trip through the external-syndrome decode
+        syn = np.zeros((n, nr), np.uint16)
+        assert h.syndromes_batch(np.ascontiguousarray(cw[:, :K]), K, K, np.ascontiguousarray(cw[:, K:]), nr, n, syn)
+        assert (syn[:1000] == _np_syndromes(cw[:1000], 8, 0x11D, 1, 1, nr)).all()
+        _assert_same(_gpu_decode(h, cw[:, :K], cw[:, K:], MODE_EXTSYN, syn=syn), want, f"RS(255,{K}) extsyn")
+        # shortened words
+        size = 57
+        par_s = _gpu_encode(h, msg[:8000, :size], nr)
+        assert (par_s == orc.rs_encode(msg[:8000, :size], params)).all()
+        cws = np.concatenate([msg[:8000, :size], par_s], 1)
+        _inject(rng, cws, 255, nr // 2 + 1)
+        _assert_same(_gpu_decode(h, cws[:, :size], cws[:, size:]), orc.rs_decode(cws[:, :size], cws[:, size:], params),
+                     f"RS(255,{K}) size {size}")
+        # erasure mode (general stage behind the transform screen)
+        m = 6000
+        cwe = np.concatenate([msg[:m], want_par[:m]], 1)
+        pos = np.zeros((m, nr), np.uint32)
+        cnt = rng.integers(0, nr + 1, m).astype(np.uint32)
+        for i in range(m):
+            c = int(cnt[i])
+            pp = np.sort(rng.choice(K, c, replace=False))
+            pos[i, :c] = pp
+            cwe[i, pp] ^= rng.integers(0, 256, c, dtype=np.uint8)
+            if rng.random() < 0.2:
+                cwe[i, rng.integers(0, 255)] ^= rng.integers(1, 256)
+        _assert_same(_gpu_decode(h, cwe[:, :K], cwe[:, K:], MODE_ERASURE, pos, cnt),
+                     orc.rs_decode(cwe[:, :K], cwe[:, K:], params, MODE_ERASURE, pos, cnt), f"RS(255,{K}) erasure")
+
+
 def test_device_pointer_path_matches_host_path(gpu_device, orc):
     torch = pytest.importorskip("torch")
     rng = np.random.default_rng(23)

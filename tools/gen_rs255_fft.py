@@ -564,38 +564,44 @@ def generate(tw, path, total, parts):
         got = [from_tower(acc[j]) for j in range(1, 33)]
         assert got == want, "transform mismatch"
 
-    # ---- encoder solve: parity symbols p_t (coefficient of x^t) from S_j = (m x^32)(alpha^j) ----------
-    # V[j][t] = alpha^(j t), j = 1..32, t = 0..31;  p = V^-1 S
-    n = 32
-    V = [[gpow(j * t) for t in range(n)] for j in range(1, n + 1)]
-    A = [row[:] + [1 if i == k else 0 for k in range(n)] for i, row in enumerate(V)]
-    for col in range(n):
-        piv = next(r_ for r_ in range(col, n) if A[r_][col])
-        A[col], A[piv] = A[piv], A[col]
-        iv = ginv(A[col][col])
-        A[col] = [gmul(iv, v) for v in A[col]]
-        for r_ in range(n):
-            if r_ != col and A[r_][col]:
-                f = A[r_][col]
-                A[r_] = [a ^ gmul(f, bb) for a, bb in zip(A[r_], A[col])]
-    W = [row[n:] for row in A]  # W[t][j-1]
-    # check on a random message
-    msg = [0] * 32 + [rnd.randrange(256) for _ in range(223)]
-    S = direct_syndromes(msg)
-    par = [0] * 32
-    for t in range(32):
-        for jj in range(32):
-            par[t] ^= gmul(W[t][jj], S[jj])
-    cw = par + msg[32:]
-    assert direct_syndromes(cw) == [0] * 32, "encoder solve mismatch"
-    # masks: output bit (parity byte index q = 31 - t in memory order, bit u) as a subset of the 8 tower planes of S_j:
-    # std(p_t) = sum_j Mstd(W[t][j]) * B * tower(S_j)
-    enc_mask = [[[0] * 8 for _ in range(32)] for _ in range(32)]  # [j-1][q][u]
-    for jj in range(32):
-        for t in range(32):
-            m = mat_mul(mulmat_std(W[t][jj]), tw.B, 8)
-            for u in range(8):
-                enc_mask[jj][31 - t][u] = m[u]
+    # ---- encoder solve: parity symbols p_t (coefficient of x^t) from S_j = (m x^n)(alpha^j), j = 1..n ---------
+    # V[j][t] = alpha^(j t), j = 1..n, t = 0..n-1;  p = V^-1 S.  n = 32 (the default code) and the reference's other
+    # documented codes RS(255,239), RS(255,247): n = 16, 8 (reference README.md:417-419).
+    def solve_masks(n):
+        V = [[gpow(j * t) for t in range(n)] for j in range(1, n + 1)]
+        A = [row[:] + [1 if i == k else 0 for k in range(n)] for i, row in enumerate(V)]
+        for col in range(n):
+            piv = next(r_ for r_ in range(col, n) if A[r_][col])
+            A[col], A[piv] = A[piv], A[col]
+            iv = ginv(A[col][col])
+            A[col] = [gmul(iv, v) for v in A[col]]
+            for r_ in range(n):
+                if r_ != col and A[r_][col]:
+                    f = A[r_][col]
+                    A[r_] = [a ^ gmul(f, bb) for a, bb in zip(A[r_], A[col])]
+        W = [row[n:] for row in A]  # W[t][j-1]
+        # check on a random message
+        msg = [0] * n + [rnd.randrange(256) for _ in range(255 - n)]
+        S = direct_syndromes(msg)
+        par = [0] * n
+        for t in range(n):
+            for jj in range(n):
+                par[t] ^= gmul(W[t][jj], S[jj])
+        cw = par + msg[n:]
+        assert direct_syndromes(cw)[:n] == [0] * n, "encoder solve mismatch"
+        # masks: output bit (parity byte index q = n - 1 - t in memory order, bit u) as a subset of the 8 tower planes
+        # of S_j:  std(p_t) = sum_j Mstd(W[t][j]) * B * tower(S_j)
+        mask = [[[0] * 8 for _ in range(n)] for _ in range(n)]  # [j-1][q][u]
+        for jj in range(n):
+            for t in range(n):
+                m = mat_mul(mulmat_std(W[t][jj]), tw.B, 8)
+                for u in range(8):
+                    mask[jj][n - 1 - t][u] = m[u]
+        return mask
+
+    enc_mask = solve_masks(32)
+    enc_mask16 = solve_masks(16)
+    enc_mask8 = solve_masks(8)
 
     zs, run3 = chien_exponents()
     cm = {}
@@ -704,18 +710,22 @@ def generate(tw, path, total, parts):
     L.append("")
     L.append("// encoder: parity byte q (memory order), bit u = XOR over j of the subset kEncMask[j-1][q][u] of the 8 tower")
     L.append("// planes of S_j, S_j = syndromes of message * x^32  (parity = V^-1 S, V[j][t] = alpha^(j t))")
-    L.append("struct EncMasks {")
-    L.append("    uint8_t m[32][32][8];")
-    L.append("};")
-    L.append("struct EncM {")
-    L.append("    static constexpr EncMasks v = {{")
-    for jj in range(32):
-        L.append("        {")
-        for q in range(32):
-            L.append("            {" + ", ".join(f"0x{enc_mask[jj][q][u]:02X}" for u in range(8)) + "},")
-        L.append("        },")
-    L.append("    }};")
-    L.append("};")
+    for n_, mk in ((32, enc_mask), (16, enc_mask16), (8, enc_mask8)):
+        sfx = "" if n_ == 32 else str(n_)
+        if n_ != 32:
+            L.append(f"// the same for the {n_}-root code RS(255,{255 - n_}): parity = V^-1 S over S_1..S_{n_}")
+        L.append(f"struct EncMasks{sfx} {{")
+        L.append(f"    uint8_t m[{n_}][{n_}][8];")
+        L.append("};")
+        L.append(f"struct EncM{sfx} {{")
+        L.append(f"    static constexpr EncMasks{sfx} v = {{{{")
+        for jj in range(n_):
+            L.append("        {")
+            for q in range(n_):
+                L.append("            {" + ", ".join(f"0x{mk[jj][q][u]:02X}" for u in range(8)) + "},")
+            L.append("        },")
+        L.append("    }};")
+        L.append("};")
     L.append("")
     L.append("} // namespace rsfft")
     with open(path, "w") as f:
