@@ -758,6 +758,7 @@ struct RowArgs {
     size_t n, ntiles;
     uint8_t *parity;
     size_t pstride;
+    int bytewise; // rows at addresses that are not all multiples of four
 };
 
 // stage word of (lane-slot ls, codeword i of the slot, word w of its row): rows of 8 words; the row of (ls, i) in
@@ -813,14 +814,41 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
         }
         __syncwarp();
         // rows out.  A parity row inside a packed record covers two 32-byte sectors partially; the L2 merges partial
-        // writes (a fill from DRAM per sector), which costs 3.4x the time of aligned contiguous rows (0.34 against
-        // 0.10 ms per 4 Mi rows, tools/enc_probe.py).  Tried and slower: merging in the SM by read-modify-write of
-        // the two-sector window (0.59 ms), prefetching the sectors into the L2 first (0.40 ms), head/tail bytes in a
-        // loop of their own (0.33 -> 0.34 ms: the partial writes of a sector should follow each other closely).
+        // writes (a fill from DRAM per sector), which costs 2-3x the time of aligned contiguous rows (tools/
+        // enc_probe.py).  Tried and slower: merging in the SM by read-modify-write of the two-sector window (0.59 ms
+        // per 4 Mi rows), the same with the windows saved by the transform kernel while the records were in the L2
+        // (0.57 ms: sixteen lanes per row make the copy-out instruction-bound), prefetching the sectors into the L2
+        // first (0.40 ms), head/tail bytes in a loop of their own (0.34 ms).
         // Rows of a class c = r mod 4 have the same alignment a = address mod 4 (r * pstride mod 4 depends on r mod 4
         // only), so a is uniform over a step.  Lane = (row rr of four consecutive rows of the class, word k of eight):
         // one aligned 32-bit word per lane, its bytes picked from (previous word, this word) by one PRMT; the head
         // of a misaligned row leaves from lane k = 0, its tail from lane k = 7, as bytes.
+        if (A.bytewise) {
+            // rows at odd addresses: one byte per lane, 32 / NR whole rows per store instruction, so that every sector
+            // a row touches gets ONE partial write (0.262 against 0.282 ms per 4 Mi rows with word stores + edge bytes;
+            // for 4-byte aligned rows the word stores below are faster, 0.158 against 0.258 ms)
+            const size_t cwt2 = tile * kTile;
+            const uint32_t left2 = A.n - cwt2 >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt2);
+            constexpr uint32_t RPI = 32 / NR; // rows per instruction
+            const uint32_t rsub = (uint32_t)lane / NR, b = (uint32_t)lane % NR;
+#pragma unroll 1
+            for (uint32_t r0 = 0; r0 < (uint32_t)kTile; r0 += 8 * RPI) {
+                uint32_t v[8];
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++) {
+                    const uint32_t r = r0 + u * RPI + rsub;
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v[u]) : "r"(stage + row_word(r >> 5, r & 31u, b >> 2) + (b & 3u)));
+                }
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++) {
+                    const uint32_t r = r0 + u * RPI + rsub;
+                    if (r < left2)
+                        A.parity[(cwt2 + r) * A.pstride + b] = (uint8_t)v[u];
+                }
+            }
+            __syncwarp();
+            continue;
+        }
         const size_t cwt = tile * kTile;
         const uint32_t left = A.n - cwt >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt);
         const uint32_t rr = (uint32_t)lane / KW, k = (uint32_t)lane % KW;
@@ -1049,6 +1077,7 @@ int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     R.ntiles = ntiles;
     R.parity = parity;
     R.pstride = parity_stride;
+    R.bytewise = (((uintptr_t)parity | parity_stride) & 3u) != 0;
     const size_t ctas = (ntiles + kRowWarps - 1) / kRowWarps;
     const unsigned grid = (unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count);
     ProfScope prof(ctx, PROF_ROWS, stream);
