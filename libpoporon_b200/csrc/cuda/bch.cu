@@ -280,7 +280,7 @@ bch_decode_map_kernel(BchParams P, const uint32_t *__restrict__ map, uint8_t *da
 //   s = (data * x^p mod g) ^ parity      (the encoder's remainder, byte tables in shared memory)
 //   entry = smap[s]:  bit 31 ok, bits 26..29 num_errors, bits 0..25 the flips that fall on data bits
 // BCH(31,16) decode of 64 Mi codewords: 66 ms with the per-thread decoder.
-constexpr int kSmapMaxBits = 20;
+constexpr int kSmapMaxBits = 25; // BCH(31,6) t = 7: 2^25 entries = 128 MB
 
 __global__ void __launch_bounds__(128)
 bch_build_smap_kernel(BchParams P, const uint8_t *__restrict__ gtab, uint32_t *__restrict__ smap)
@@ -327,6 +327,100 @@ bch_decode_smap_kernel(BchParams P, const uint32_t *__restrict__ smap, uint8_t *
             ok[cw] = good ? 1 : 0;
         if (corrected)
             corrected[cw] = nc;
+    }
+}
+
+// Dense batches of any n <= 31 code (data rows of db bytes and parity rows of pb bytes back to back, db, pb <= 4): four
+// codewords per thread, everything moved as aligned 32-bit words (4 db bytes = db words, 4 pb bytes = pb words), status
+// as one word and one uint4.  Byte j of codeword u of a group sits at byte u * w + j of the group's words.
+template <int width>
+__device__ __forceinline__ uint32_t group_be(const uint32_t (&w)[4], int u)
+{
+    uint32_t v = 0;
+#pragma unroll
+    for (int j = 0; j < width; j++) {
+        const int b = u * width + j;
+        v = (v << 8) | ((w[b >> 2] >> (8 * (b & 3))) & 0xFFu);
+    }
+    return v;
+}
+template <int width>
+__device__ __forceinline__ void group_put_be(uint32_t (&w)[4], int u, uint32_t v)
+{
+#pragma unroll
+    for (int j = 0; j < width; j++) {
+        const int b = u * width + j, sh = 8 * (b & 3);
+        w[b >> 2] = (w[b >> 2] & ~(0xFFu << sh)) | (((v >> (8 * (width - 1 - j))) & 0xFFu) << sh);
+    }
+}
+
+template <int db, int pb> // bytes per data row / parity row (compile-time: every shift becomes a constant)
+__global__ void __launch_bounds__(256)
+bch_decode_smap4_kernel(BchParams P, const uint32_t *__restrict__ smap, uint32_t *data, const uint32_t *__restrict__ parity,
+                        size_t n4, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected)
+{
+    __shared__ uint32_t rem[4][256];
+    bch_build_rem_tables(P, rem);
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += (size_t)gridDim.x * blockDim.x) {
+        uint32_t dw[4] = {0, 0, 0, 0}, pw[4] = {0, 0, 0, 0}, nc[4], okw = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (i < db)
+                dw[i] = data[g * db + i];
+            if (i < pb)
+                pw[i] = parity[g * pb + i];
+        }
+        uint32_t s[4], dv[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            dv[u] = group_be<db>(dw, u) & low_mask(P.k);
+            s[u] = bch_rem(rem, dv[u]) ^ (group_be<pb>(pw, u) & low_mask(P.parity_bits));
+        }
+        uint32_t e[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            e[u] = __ldg(smap + s[u]);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const bool good = (e[u] & 0x80000000u) != 0;
+            if (good) // failure leaves the data bytes alone; success also clears the pad bits
+                group_put_be<db>(dw, u, dv[u] ^ (e[u] & low_mask(P.k)));
+            okw |= (good ? 1u : 0u) << (8 * u);
+            nc[u] = good ? ((e[u] >> 26) & 15u) : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            if (i < db)
+                data[g * db + i] = dw[i];
+        if (ok)
+            reinterpret_cast<uint32_t *>(ok)[g] = okw;
+        if (corrected)
+            reinterpret_cast<uint4 *>(corrected)[g] = make_uint4(nc[0], nc[1], nc[2], nc[3]);
+    }
+}
+
+template <int db, int pb>
+__global__ void __launch_bounds__(256)
+bch_encode_dense4_kernel(BchParams P, const uint32_t *__restrict__ data, uint32_t *__restrict__ parity, size_t n4,
+                         uint8_t *__restrict__ ok)
+{
+    __shared__ uint32_t rem[4][256];
+    bch_build_rem_tables(P, rem);
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += (size_t)gridDim.x * blockDim.x) {
+        uint32_t dw[4] = {0, 0, 0, 0}, pw[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            if (i < db)
+                dw[i] = data[g * db + i];
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            group_put_be<pb>(pw, u, bch_rem(rem, group_be<db>(dw, u) & low_mask(P.k)));
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            if (i < pb)
+                parity[g * pb + i] = pw[i];
+        if (ok)
+            reinterpret_cast<uint32_t *>(ok)[g] = 0x01010101u;
     }
 }
 
@@ -400,6 +494,28 @@ static bool packed_1_2(const poporon_cuda_bch *ctx, const void *data, size_t dat
            ((uintptr_t)parity & 7u) == 0 && ((uintptr_t)ok & 3u) == 0 && ((uintptr_t)corrected & 15u) == 0;
 }
 
+// (db, pb) of the n <= 31 codes: k + p = n <= 31 bits
+#define PP_BCH_DENSE_DISPATCH(KERNEL, db, pb, ...)                                          \
+    do {                                                                                    \
+        switch ((int)(db) * 8 + (int)(pb)) {                                                \
+        case 1 * 8 + 1: KERNEL<1, 1> __VA_ARGS__; break;                                    \
+        case 1 * 8 + 2: KERNEL<1, 2> __VA_ARGS__; break;                                    \
+        case 1 * 8 + 3: KERNEL<1, 3> __VA_ARGS__; break;                                    \
+        case 1 * 8 + 4: KERNEL<1, 4> __VA_ARGS__; break;                                    \
+        case 2 * 8 + 1: KERNEL<2, 1> __VA_ARGS__; break;                                    \
+        case 2 * 8 + 2: KERNEL<2, 2> __VA_ARGS__; break;                                    \
+        case 2 * 8 + 3: KERNEL<2, 3> __VA_ARGS__; break;                                    \
+        case 3 * 8 + 1: KERNEL<3, 1> __VA_ARGS__; break;                                    \
+        case 3 * 8 + 2: KERNEL<3, 2> __VA_ARGS__; break;                                    \
+        case 4 * 8 + 1: KERNEL<4, 1> __VA_ARGS__; break;                                    \
+        default: break;                                                                     \
+        }                                                                                   \
+    } while (0)
+static bool dense_widths_ok(size_t db, size_t pb)
+{
+    return db >= 1 && pb >= 1 && db + pb <= 5 && !(db == 2 && pb == 4) && !(db == 3 && pb == 3);
+}
+
 BchParams params_of(const poporon_cuda_bch *ctx)
 {
     BchParams P;
@@ -432,6 +548,24 @@ int launch_bch_encode(poporon_cuda_bch *ctx, const uint8_t *data, size_t data_st
         if (done == n)
             return check(cudaGetLastError(), "bch_encode4 launch");
         data += done, parity += done * 2, ok = ok ? ok + done : ok, n -= done;
+    }
+    {
+        // any code, dense rows: four codewords per thread on aligned words
+        const size_t db = (size_t)(ctx->k + 7) / 8, pb = (size_t)(ctx->parity_bits + 7) / 8;
+        if (n >= 4 && data_stride == db && size == db && parity_stride == pb && dense_widths_ok(db, pb) &&
+            (((uintptr_t)data | (uintptr_t)parity | (uintptr_t)ok) & 3u) == 0) {
+            const size_t n4 = n / 4, cap = (size_t)ctx->sm_count * 16;
+            const size_t blocks = (n4 + threads - 1) / threads;
+            PP_BCH_DENSE_DISPATCH(bch_encode_dense4_kernel, db, pb,
+                                  <<<(unsigned)(blocks < cap ? blocks : cap), threads, 0, stream>>>(
+                                      params_of(ctx), reinterpret_cast<const uint32_t *>(data),
+                                      reinterpret_cast<uint32_t *>(parity), n4, ok));
+            ctx->launches++;
+            const size_t done = n4 * 4;
+            if (done == n)
+                return check(cudaGetLastError(), "bch_encode (dense4) launch");
+            data += done * db, parity += done * pb, ok = ok ? ok + done : ok, n -= done;
+        }
     }
     const size_t eblocks = (n + threads - 1) / threads, ecap = (size_t)ctx->sm_count * 8;
     bch_encode_kernel<<<(unsigned)(eblocks < ecap ? eblocks : ecap), threads, 0, stream>>>(
@@ -486,6 +620,23 @@ int launch_bch_decode(poporon_cuda_bch *ctx, uint8_t *data, size_t data_stride, 
         return check(cudaGetLastError(), "bch_decode (map) launch");
     }
     if (ctx->d_smap) {
+        const size_t db = (size_t)(ctx->k + 7) / 8, pb = (size_t)(ctx->parity_bits + 7) / 8;
+        if (n >= 4 && data_stride == db && size == db && parity_stride == pb && dense_widths_ok(db, pb) &&
+            (((uintptr_t)data | (uintptr_t)parity | (uintptr_t)ok) & 3u) == 0 && ((uintptr_t)corrected & 15u) == 0) {
+            const size_t n4 = n / 4, cap4 = (size_t)ctx->sm_count * 16;
+            const size_t blocks4 = (n4 + 255) / 256;
+            PP_BCH_DENSE_DISPATCH(bch_decode_smap4_kernel, db, pb,
+                                  <<<(unsigned)(blocks4 < cap4 ? blocks4 : cap4), 256, 0, stream>>>(
+                                      params_of(ctx), ctx->d_smap, reinterpret_cast<uint32_t *>(data),
+                                      reinterpret_cast<const uint32_t *>(parity), n4, ok, corrected));
+            ctx->launches++;
+            const size_t done = n4 * 4;
+            if (done == n)
+                return check(cudaGetLastError(), "bch_decode (remainder map, dense4) launch");
+            data += done * db, parity += done * pb, ok = ok ? ok + done : ok;
+            corrected = corrected ? corrected + done : corrected;
+            n -= done;
+        }
         size_t blocks = (n + 255) / 256;
         const size_t cap = (size_t)ctx->sm_count * 8;
         bch_decode_smap_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(

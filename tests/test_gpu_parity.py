@@ -694,13 +694,14 @@ def test_bch_default_single_api(gpu_device):
 
 @pytest.mark.parametrize("t", [1, 2, 3, 5, 7])
 def test_bch31_batches_vs_oracle(gpu_device, orc, t):
-    """BCH(31,k): the remainder-indexed decode map (parity bits <= 20: t = 1, 2, 3, 5) and the exact per-thread
-    decoder (t = 7) against the oracle, 0 .. t + 3 flipped bits anywhere in the 31, garbage above the k data bits."""
+    """BCH(31,k): the remainder-indexed decode map (up to the 25 parity bits of t = 7: a 128 MB map) against the oracle,
+    0 .. t + 3 flipped bits anywhere in the 31, garbage above the k data bits; dense rows take the four-codewords-per-
+    thread kernels, the last three codewords (n = 4 q + 3) the scalar ones."""
     info = orc.bch_info(5, 0x25, t)
     k, pbits = info["k"], info["parity_bits"]
     db, pb = (k + 7) // 8, (pbits + 7) // 8
     rng = np.random.default_rng(3100 + t)
-    n = 20000
+    n = 20003
     with api.Poporon.bch(5, 0x25, t) as h:
         msg = rng.integers(0, 256, (n, db), dtype=np.uint8)
         par = np.full((n, pb), 0xEE, np.uint8)
