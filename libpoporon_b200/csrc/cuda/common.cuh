@@ -95,6 +95,7 @@ struct poporon_cuda_rs {
     size_t synplane_cap;      // codewords it holds
     cudaEvent_t busy;         // recorded after the last kernel that uses the scratch above; the next call's stream waits on it
     int correct_ctas_per_sm;  // resident CTAs of the general correction stage (per device, rs255_init)
+    int no_fuse;              // PP_RS255_NOFUSE=1: compaction kernel instead of the fused zero-syndrome exit (A/B runs)
     int use_lfsr;             // PP_RS255_LFSR=1: the round-1 LFSR kernels instead of the transform kernels (A/B runs)
     // opt-in per-kernel timing (poporon_cuda_rs_profile): CUDA event pairs around each launch
     bool prof_on;

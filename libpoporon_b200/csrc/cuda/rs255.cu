@@ -1371,6 +1371,10 @@ int rs255_init(poporon_cuda_rs *ctx)
             v = 4;
         ctx->correct_ctas_per_sm = v;
     }
+    {
+        const char *e = getenv("PP_RS255_NOFUSE"); // A/B: zero-syndrome exit as a kernel of its own
+        ctx->no_fuse = e && e[0] == '1';
+    }
     const char *env = getenv("PP_RS255_LFSR");
     ctx->use_lfsr = env && env[0] == '1';
     return rs255_fft_init(ctx);
@@ -1494,14 +1498,18 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         rc = ensure_slab(ctx);
         if (rc != 0)
             return rc;
+        // the zero-syndrome exit rides in the screen kernel when the status arrays allow vector stores
+        const bool fused = (((uintptr_t)ok | (uintptr_t)corrected) & 15u) == 0 && !ctx->no_fuse;
+        if (fused)
+            ctx->launches -= 1; // (no separate compaction kernel: see the count at the end)
         {
             ProfScope prof(ctx, PROF_SCREEN, stream);
             rc = rs255_fft_screen(ctx, shape, data, data_stride, size, parity, parity_stride, n, ctx->d_slab, dmask,
-                                  ctx->d_rem, stream);
+                                  ctx->d_rem, stream, ctx->d_queue, ctx->d_counters, ok, corrected, fused);
         }
         if (rc != 0)
             return rc;
-        {
+        if (!fused) {
             ProfScope prof(ctx, PROF_COMPACT, stream);
             rc = rs255_fft_compact(ctx, dmask, n, ctx->d_queue, ctx->d_counters, ok, corrected, stream);
         }

@@ -72,7 +72,12 @@ struct FftArgs {
     int poff;              // offset of the parity span inside a buffer (split layout)
     // SCREEN outputs
     uint32_t *dirty;       // bitmap, bit (cw & 31) of word cw >> 5
-    uint8_t *syn;          // [n][32]
+    uint8_t *syn;          // [tiles * 1024][32]: rows of the tiles that hold a dirty codeword
+    // SCREEN, fused zero-syndrome exit (when ok / corrected are 16-byte aligned; else rs255_fft_compact_kernel runs):
+    uint32_t *queue, *counter; // dirty codeword indices | 3 << 30, their count
+    uint8_t *ok;               // nullable; clean: 1, dirty: 0 for now (the correction stages write the outcome)
+    uint32_t *corrected;       // nullable; 0
+    int fused;
     // ENCODE output: the syndromes of message * x^32 as tower planes, [tile][j - 1][lane-slot][8 planes] words
     // (rs255_parity_kernel turns them into parity rows)
     uint32_t *synplanes;
@@ -234,6 +239,16 @@ __device__ __forceinline__ void subset_table(uint32_t b0, uint32_t b1, uint32_t 
     T[13] = T[12] ^ b0;
     T[14] = T[12] ^ b1;
     T[15] = T[12] ^ T[3];
+}
+
+// stage word of (lane-slot ls, codeword i of the slot, word w of its row): rows of 8 words; the row of (ls, i) in
+// slot ls * 32 + sigma with sigma mod 4 = ((i >> 2) + (ls >> 3)) mod 4, word w at position (w ^ ls) & 7.  Bank =
+// 8 * (sigma mod 4) + position: the 32 lanes of a store (fixed i, w) hit 32 different banks, and so do the loads of
+// the rows i, i + 4, i + 8, i + 12 of one lane-slot (the four rows of a copy-out step).
+__device__ __forceinline__ uint32_t row_word(uint32_t ls, uint32_t i, uint32_t w)
+{
+    const uint32_t sigma = (((i >> 2) + (ls >> 3)) & 3u) | ((i & 3u) << 2) | (i & 16u);
+    return ((ls * 32u + sigma) * 8u + ((w ^ ls) & 7u)) * 4u;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -507,6 +522,34 @@ __device__ __forceinline__ void s2_role(const Smem &sm, int lane, uint32_t gtask
         sts32(sm.nzword(U, lane), nz);
 }
 
+// SCREEN output of a tile that holds a dirty codeword: its 1024 syndrome rows (32 bytes each, contiguous in syn).
+// Word-column w is transposed by warp w < 8, staged in the (now idle) output stage and written as whole rows by all
+// warps.  Called by the whole CTA; kept out of line so that its 32 transpose registers do not weigh on the register
+// allocation of the main loop (the kernel sits at its 128-register limit).
+__device__ __noinline__ void write_syndrome_rows(const Smem &sm, uint8_t *syn, size_t tile, int warp, int lane)
+{
+    uint32_t X[32];
+    if (warp < 8) {
+#pragma unroll
+        for (int p = 0; p < 32; p++)
+            X[p] = lds32(sm.outplane(32 * warp + p, lane));
+        transpose32(X);
+    }
+    __syncthreads(); // every plane has been read
+    if (warp < 8) {
+#pragma unroll
+        for (int i = 0; i < 32; i++)
+            sts32(sm.outstage + row_word((uint32_t)lane, (uint32_t)i, (uint32_t)warp), X[i]);
+    }
+    __syncthreads();
+    uint32_t *dst = reinterpret_cast<uint32_t *>(syn) + tile * (size_t)(kTile * 8);
+#pragma unroll 4
+    for (uint32_t L = threadIdx.x; L < (uint32_t)(kTile * 8); L += 32 * kWarps) {
+        const uint32_t row = L >> 3;
+        dst[L] = lds32(sm.outstage + row_word(row >> 5, row & 31u, L & 7u));
+    }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
 {
@@ -598,34 +641,77 @@ __global__ void __launch_bounds__(32 * kWarps, 1) rs255_fft_kernel(FftArgs A)
 
         // ---------------- output (SCREEN; the encoder's syndromes went to global memory) ----------------
         if (MODE == MODE_SCREEN) {
-            if (warp < 8) {
-                const size_t cw0 = tile * kTile + (size_t)lane * 32; // this lane-slot's first codeword
-                uint32_t valid = 0;                                  // bit i: codeword cw0 + i exists
-                if (cw0 < A.n) {
-                    const size_t left = A.n - cw0;
-                    valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (unsigned)left) - 1u);
-                }
-                uint32_t dirty = 0;
+            const size_t cw0 = tile * kTile + (size_t)lane * 32; // this lane-slot's first codeword
+            uint32_t valid = 0;                                  // bit i: codeword cw0 + i exists
+            if (cw0 < A.n) {
+                const size_t left = A.n - cw0;
+                valid = left >= 32 ? 0xFFFFFFFFu : ((1u << (unsigned)left) - 1u);
+            }
+            uint32_t dirty = 0;
 #pragma unroll
-                for (int u = 0; u < kS2Warps; u++)
-                    dirty |= lds32(sm.nzword(u, lane));
-                dirty &= valid;
-                if (warp == 0 && cw0 < A.n)
-                    A.dirty[cw0 >> 5] = dirty;
-                if (__any_sync(0xFFFFFFFFu, dirty != 0)) {
-                    // syndrome word-column `warp`: S_{4w+1} .. S_{4w+4} of the lane-slot's 32 codewords (columns beyond
-                    // the code's roots are written as well: nobody reads them)
-                    uint32_t X[32];
+            for (int u = 0; u < kS2Warps; u++)
+                dirty |= lds32(sm.nzword(u, lane));
+            dirty &= valid;
+            const bool any = __any_sync(0xFFFFFFFFu, dirty != 0); // (the same in every warp: lanes = the tile's lane-slots)
+            // zero-syndrome exit: clean codewords are finished here (status stores spread over the CTA: one uint4 per
+            // thread), dirty ones queued for the solver by warp 8
+            const bool full_tile = tile * kTile + kTile <= A.n;
+            if (A.fused && full_tile) {
+                if (A.corrected && threadIdx.x < 256)
+                    reinterpret_cast<uint4 *>(A.corrected + tile * kTile)[threadIdx.x] = make_uint4(0u, 0u, 0u, 0u);
+                if (A.ok && threadIdx.x >= 256 && threadIdx.x < 320) {
+                    const uint32_t q = threadIdx.x - 256u; // sixteen codewords: half q & 1 of lane-slot q >> 1
+                    uint32_t d = 0;
 #pragma unroll
-                    for (int p = 0; p < 32; p++)
-                        X[p] = lds32(sm.outplane(32 * warp + p, lane));
-                    transpose32(X);
+                    for (int u = 0; u < kS2Warps; u++)
+                        d |= lds32(sm.nzword(u, (int)(q >> 1)));
+                    const uint32_t c = ~d >> (16u * (q & 1u));
+                    uint32_t w[4];
 #pragma unroll
-                    for (int i = 0; i < 32; i++)
-                        if ((dirty >> i) & 1u)
-                            *reinterpret_cast<uint32_t *>(A.syn + (cw0 + (size_t)i) * 32 + 4 * warp) = X[i];
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t cj = c >> (4 * j);
+                        w[j] = (cj & 1u) | ((cj & 2u) << 7) | ((cj & 4u) << 14) | ((cj & 8u) << 21);
+                    }
+                    reinterpret_cast<uint4 *>(A.ok + tile * kTile)[q] = make_uint4(w[0], w[1], w[2], w[3]);
                 }
             }
+            if (warp == 8) {
+                if (cw0 < A.n)
+                    A.dirty[cw0 >> 5] = dirty;
+                if (A.fused) {
+                    if (!full_tile) {
+                        for (int i = 0; i < 32; i++)
+                            if ((valid >> i) & 1u) {
+                                if (A.ok)
+                                    A.ok[cw0 + i] = (uint8_t)((~dirty >> i) & 1u);
+                                if (A.corrected)
+                                    A.corrected[cw0 + i] = 0u;
+                            }
+                    }
+                    if (any) {
+                        const uint32_t cnt = (uint32_t)__popc(dirty);
+                        uint32_t pre = cnt; // inclusive prefix sum over the lanes
+#pragma unroll
+                        for (int d = 1; d < 32; d <<= 1) {
+                            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, pre, d);
+                            if (lane >= d)
+                                pre += v;
+                        }
+                        uint32_t base = 0;
+                        if (lane == 31)
+                            base = atomicAdd(A.counter, pre);
+                        base = __shfl_sync(0xFFFFFFFFu, base, 31) + pre - cnt;
+                        uint32_t bits = dirty;
+                        while (bits) {
+                            const int i = __ffs((int)bits) - 1;
+                            bits &= bits - 1;
+                            A.queue[base++] = (uint32_t)(cw0 + (size_t)i) | (3u << 30); // both syndrome halves are live
+                        }
+                    }
+                }
+            }
+            if (any)
+                write_syndrome_rows(sm, A.syn, tile, warp, lane);
             __syncthreads(); // the output stage and the dirty words are free again
         }
     }
@@ -760,16 +846,6 @@ struct RowArgs {
     size_t pstride;
     int bytewise; // rows at addresses that are not all multiples of four
 };
-
-// stage word of (lane-slot ls, codeword i of the slot, word w of its row): rows of 8 words; the row of (ls, i) in
-// slot ls * 32 + sigma with sigma mod 4 = ((i >> 2) + (ls >> 3)) mod 4, word w at position (w ^ ls) & 7.  Bank =
-// 8 * (sigma mod 4) + position: the 32 lanes of a store (fixed i, w) hit 32 different banks, and so do the loads of
-// the rows i, i + 4, i + 8, i + 12 of one lane-slot (the four rows of a copy-out step).
-__device__ __forceinline__ uint32_t row_word(uint32_t ls, uint32_t i, uint32_t w)
-{
-    const uint32_t sigma = (((i >> 2) + (ls >> 3)) & 3u) | ((i & 3u) << 2) | (i & 16u);
-    return ((ls * 32u + sigma) * 8u + ((w ^ ls) & 7u)) * 4u;
-}
 
 template <int NR> // parity bytes per row: 32, 16 or 8
 __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A)
@@ -994,7 +1070,8 @@ static unsigned fft_grid(const poporon_cuda_rs *ctx, size_t n)
 
 int rs255_fft_screen(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t *data, size_t data_stride, size_t size,
                      const uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, uint32_t *dirty,
-                     uint8_t *syn, cudaStream_t stream)
+                     uint8_t *syn, cudaStream_t stream, uint32_t *queue, uint32_t *counter, uint8_t *ok,
+                     uint32_t *corrected, bool fused)
 {
     FftArgs A{};
     A.data = data;
@@ -1011,6 +1088,11 @@ int rs255_fft_screen(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     A.poff = shape.poff;
     A.dirty = dirty;
     A.syn = syn;
+    A.queue = queue;
+    A.counter = counter;
+    A.ok = ok;
+    A.corrected = corrected;
+    A.fused = fused ? 1 : 0;
     rs255_fft_kernel<MODE_SCREEN><<<fft_grid(ctx, n), 32 * kWarps, smem_bytes(shape.bufbytes), stream>>>(A);
     return check(cudaGetLastError(), "rs255 fft screen launch");
 }

@@ -19,7 +19,10 @@ int rs255_fft_init(poporon_cuda_rs *ctx);
 // dirty: bitmap over codewords (bit cw & 31 of word cw >> 5); syn: [n][32], rows of dirty codewords only
 int rs255_fft_screen(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t *data, size_t data_stride, size_t size,
                      const uint8_t *parity, size_t parity_stride, size_t n, uint8_t *slab, uint32_t *dirty,
-                     uint8_t *syn, cudaStream_t stream);
+                     uint8_t *syn, cudaStream_t stream, uint32_t *queue = nullptr, uint32_t *counter = nullptr,
+                     uint8_t *ok = nullptr, uint32_t *corrected = nullptr, bool fused = false);
+// fused = the kernel also does the zero-syndrome exit (ok / corrected of clean codewords, queue of dirty ones); needs
+// ok and corrected 16-byte aligned (or NULL).  Otherwise rs255_fft_compact does it from the dirty bitmap.
 int rs255_fft_compact(poporon_cuda_rs *ctx, const uint32_t *dirty, size_t n, uint32_t *queue, uint32_t *counter,
                       uint8_t *ok, uint32_t *corrected, cudaStream_t stream);
 // synplanes: scratch of rs255_fft_synplane_bytes(n) bytes (the syndromes of message * x^32, tower planes)
