@@ -85,9 +85,10 @@ def alu_peak(sm_mhz):
 # Useful integer-ALU lane-operations per codeword of each ALU-bound kernel: the operation count of its formulation
 # with nothing but the GF(2) arithmetic counted (DESIGN.md section 4 derives every term).
 ALU_FLOOR = {
-    # BM 332 coefficient steps x 228 + evaluator 9.2 K + sweep 255 x 158 + sweep seed 2.7 K + Forney on 16 list
-    # slots 44.9 K + 28 bit-matrix transposes x 256, per 32 queued codewords
-    "rs255_solve_kernel": (75696 + 9152 + 40290 + 2686 + 44900 + 7168) / 32.0,
+    # BM 332 coefficient steps x 228 + evaluator 9.2 K + Chien search as a transform 17 x (2 x 244 DFT + 192 multipliers
+    # + 16 + 120 zero tests) + 136 basis change + Forney on 16 list slots 44.9 K + 28 bit-matrix transposes x 256, per
+    # 32 queued codewords
+    "rs255_solve_kernel": (75696 + 9152 + 17 * 816 + 136 + 44900 + 7168) / 32.0,
     # transform 18598 + 64 word-columns x (256 transpose + 32 realign) + 255 x 8 basis change, per 32 codewords
     "rs255_fft_kernel<SCREEN>": (18598 + 64 * 288 + 255 * 8) / 32.0,
     "rs255_fft_kernel<ENCODE>": (18598 + 56 * 288 + 223 * 8) / 32.0,
@@ -388,8 +389,9 @@ def run_ours(args):
         "rs255_fft_kernel<ENCODE>": n * K_MSG,
         "rs255_parity_kernel": n * K_PAR,
         "rs255_rows_kernel": n * K_PAR,
-        "rs255_fft_kernel<SCREEN>": n * (K_CW + 0.25 + 32 * dirty_frac),
-        "rs255_compact_kernel": n * (0.25 + 5 + 4 * dirty_frac),
+        # (with the zero-syndrome exit fused in: + status 5 B per codeword + a queue entry per dirty one)
+        "rs255_fft_kernel<SCREEN>": n * (K_CW + 0.125 + 5 + (32 + 4) * dirty_frac),
+        "rs255_compact_kernel": n * (0.25 + 5 + 4 * dirty_frac),  # (only when the status arrays are not 16-byte aligned)
         # queue entry + syndrome row + status per dirty codeword; error record (2 B) + read-modify-write of the
         # corrected byte (2 B) per correction (the solver applies its own corrections)
         "rs255_solve_kernel": n * dirty_frac * (4 + 32 + 5) + n * mean_err * (2 + 2),

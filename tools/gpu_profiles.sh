@@ -13,6 +13,6 @@ timeout 900 ncu --set full --clock-control none --import-source on \
   -k regex:'rs255_fft_kernel|rs255_parity_kernel|rs255_rows_kernel' -c 4 -o $O/${TAG}_full_a -f \
   python bench.py --ncw 4194304 --steps 1 --warmup 0 --no-e2e --no-cpu-baseline --verify none > $O/${TAG}_ncu_full_a.log 2>&1; echo "ncu full a rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on \
-  -k regex:'rs255_solve_kernel|rs255_fft_compact_kernel|rs255_correct_kernel' --launch-skip 18 -c 3 -o $O/${TAG}_full_b -f \
+  -k regex:'rs255_solve_kernel|rs255_correct_kernel' --launch-skip 12 -c 2 -o $O/${TAG}_full_b -f \
   python bench.py --ncw 4194304 --steps 1 --warmup 0 --no-e2e --no-cpu-baseline --verify none > $O/${TAG}_ncu_full_b.log 2>&1; echo "ncu full b rc=$?"
 ls -la $O | grep ${TAG}_
