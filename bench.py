@@ -108,6 +108,27 @@ def ncu_traffic():
         return json.load(f)
 
 
+# ----------------------------------------------------------------------------------------- multi-rank plumbing
+def shard_of(rank, ncw_per_rank):
+    """The contiguous slice of the global codeword index space a rank works on (weak scaling: every rank holds
+    ncw_per_rank codewords; the workload generators are pure functions of the global index, so any rank can produce
+    any slice).  Returns (first global index, count)."""
+    return rank * ncw_per_rank, ncw_per_rank
+
+
+def max_over_ranks(values, device=None):
+    """Element-wise maximum of a list of floats over all ranks (identity without torch.distributed): the job's time is
+    the slowest rank's.  Works on any backend (nccl under torchrun on GPUs, gloo in the CPU tests)."""
+    import torch
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [float(v) for v in values]
+    t = torch.tensor(list(values), dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t.tolist()]
+
+
 # ----------------------------------------------------------------------------------------- clocks
 class ClockSampler:
     """Samples SM clock and throttle reasons of one GPU during the timed region (pynvml)."""
@@ -276,7 +297,7 @@ def run_ours(args):
             os.close(keep)
 
     n = args.ncw
-    i0 = rank * n  # this rank's slice of the global codeword index space
+    i0, _ = shard_of(rank, n)  # this rank's slice of the global codeword index space
     K, W = args.steps, args.warmup
     rec_bytes = n * K_CW
     nbuf = max(1, min(K + W, int(args.mem_budget_gb * 1e9 // rec_bytes) - 1))
@@ -367,10 +388,7 @@ def run_ours(args):
     elapsed_ms = t_start.elapsed_time(t_stop)
     enc_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / K
     dec_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / K
-    tt = torch.tensor([elapsed_ms, enc_ms, dec_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    elapsed_ms, enc_ms, dec_ms = (float(x) for x in tt.tolist())
+    elapsed_ms, enc_ms, dec_ms = max_over_ranks([elapsed_ms, enc_ms, dec_ms], dev)
     ms_per_step = elapsed_ms / K
     payload_step = 2 * n * K_MSG * world
     value = payload_step / (ms_per_step * 1e-3) / 1e9
