@@ -345,12 +345,19 @@ __device__ __forceinline__ void transpose_subtile(const FftArgs &A, uint32_t buf
             stride = (uint32_t)A.dstride;
             nvalid = A.size - 4 * col;
             e0 = L - 1 - 4 * col;
-        } else {
+        } else if (col < ncols) {
             const int pc = col - ncd;
             base = pbase + 4u * (uint32_t)(pc & 7);
             stride = pstr;
-            nvalid = col < ncols ? 4 : 0;
+            nvalid = 4;
             e0 = A.npar - 1 - 4 * (pc & 7);
+        } else {
+            // idle lane of the last trip: it re-reads the words of the last message column (a broadcast, not a second
+            // wavefront on some other bank) and stores nothing
+            base = bufaddr + ad + 4u * (uint32_t)(ncd - 1);
+            stride = (uint32_t)A.dstride;
+            nvalid = 0;
+            e0 = 0;
         }
         // rows i and i + 4 are 4 * stride bytes apart: same byte offset inside their words.  Four aligned row bases
         // and four PRMT selectors serve all 32 rows.
@@ -543,10 +550,14 @@ __device__ __noinline__ void write_syndrome_rows(const Smem &sm, uint8_t *syn, s
     }
     __syncthreads();
     uint32_t *dst = reinterpret_cast<uint32_t *>(syn) + tile * (size_t)(kTile * 8);
+    // a warp moves four rows i, i + 4, i + 8, i + 12 of one lane-slot per step (the four bank groups of the stage), eight
+    // lanes per row: whole 32-byte sectors, no bank conflicts
+    const uint32_t rr = (uint32_t)lane >> 3, k = (uint32_t)lane & 7u;
 #pragma unroll 4
-    for (uint32_t L = threadIdx.x; L < (uint32_t)(kTile * 8); L += 32 * kWarps) {
-        const uint32_t row = L >> 3;
-        dst[L] = lds32(sm.outstage + row_word(row >> 5, row & 31u, L & 7u));
+    for (uint32_t it = (uint32_t)warp; it < 256u; it += kWarps) {
+        const uint32_t ls = it >> 3, q = it & 7u;
+        const uint32_t i = (q & 3u) + 16u * (q >> 2) + 4u * rr;
+        dst[(ls * 32u + i) * 8u + k] = lds32(sm.outstage + row_word(ls, i, k));
     }
 }
 
