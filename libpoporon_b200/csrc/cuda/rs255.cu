@@ -1175,7 +1175,7 @@ rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restr
         for (int w = 0; w < 4; w++) {
             if (!__any_sync(0xFFFFFFFFu, maxroots > 4 * w))
                 break;
-            bs::forney_slots<32, 32>(Syn, B, S, w, root_tab, nzc);
+            bs::forney_slots<32, 32>(Syn, B, S, w, root_tab, nzc, nr >> 1);
             uint32_t X[32];
             bs::magnitude_words<32>(S, X);
 #pragma unroll

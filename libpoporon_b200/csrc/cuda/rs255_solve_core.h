@@ -911,8 +911,10 @@ BS_FN void chien_transform(const Mem<SL> LM, const Mem<SL> MK, const Mem<STRIDE>
 // instructions and the chains overlap each other's dependent steps.
 template <int STRIDE, int SO>
 BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, int w,
-                        const uint8_t *root_tab /* [0] = 0, [v] = alpha^v */, uint32_t (&cnt)[5])
+                        const uint8_t *root_tab /* [0] = 0, [v] = alpha^v */, uint32_t (&cnt)[5], int teff = kT)
 {
+    // teff = ns / 2 (16, 8 or 4): Omega has teff coefficients and the locator degree is <= teff, so the two Horner
+    // chains start there
     {
         uint32_t X[32];
 #pragma unroll
@@ -928,16 +930,16 @@ BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, 
     }
     {
         uint32_t x[4][8], num[4][8], o[8];
-        ld8(O, kT - 1, o);
+        ld8(O, teff - 1, o);
 #pragma unroll
         for (int y = 0; y < 4; y++) {
             ld8(S, y, x[y]);
             cp8(num[y], o);
         }
-        // x * Omega(x): Horner from Omega_15 down, then one more factor x
-        ld8(O, kT - 2, o);
+        // x * Omega(x): Horner from Omega_(teff-1) down, then one more factor x
+        ld8(O, teff - 2, o);
 #pragma unroll 1
-        for (int j = kT - 2; j >= 0; j--) {
+        for (int j = teff - 2; j >= 0; j--) {
             // (unconditional, index clamped: a conditionally loaded array is demoted to local memory and its
             // spill store then waits for the load)
             uint32_t on[8];
@@ -960,15 +962,15 @@ BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, 
         }
         // x * Lambda'(x) = x * sum over odd j of L_j x^(j-1): Horner in x^2 from L_15 down
         uint32_t x2[4][8], odd[4][8];
-        ld8(LM, kT - 1, o);
+        ld8(LM, teff - 1, o);
 #pragma unroll
         for (int y = 0; y < 4; y++) {
             sqr(x[y], x2[y]);
             cp8(odd[y], o);
         }
-        ld8(LM, kT - 3, o);
+        ld8(LM, teff - 3, o);
 #pragma unroll 1
-        for (int j = kT - 3; j >= 1; j -= 2) {
+        for (int j = teff - 3; j >= 1; j -= 2) {
             uint32_t on[8];
             ld8(LM, j > 1 ? j - 2 : 1, on);
 #pragma unroll

@@ -7,9 +7,23 @@
 
 #include "rs255_solve_core.h"
 
+static int host_solve_ns(const uint8_t *syn, size_t n, int pad, int ns, int8_t *status, uint8_t *nroots, uint16_t *lists);
+
 extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elements */, size_t n, int pad,
                           int8_t *status /* [n] 0 declined, 1 fail, 2 ok */, uint8_t *nroots /* [n] */,
                           uint16_t *lists /* [n][16]: location | magnitude << 8 */)
+{
+    return host_solve_ns(syn, n, pad, 32, status, nroots, lists);
+}
+
+// the same for a code with ns = 16 or 8 roots (RS(255,239), RS(255,247)): only S_1..S_ns of a row are meaningful
+extern "C" int host_solve_roots(const uint8_t *syn, size_t n, int pad, int ns, int8_t *status, uint8_t *nroots,
+                                uint16_t *lists)
+{
+    return host_solve_ns(syn, n, pad, ns, status, nroots, lists);
+}
+
+static int host_solve_ns(const uint8_t *syn, size_t n, int pad, int ns, int8_t *status, uint8_t *nroots, uint16_t *lists)
 {
     uint8_t root_tab[256];
     root_tab[0] = 0;
@@ -29,15 +43,15 @@ extern "C" int host_solve(const uint8_t *syn /* [n][32]: S_1..S_32 as field elem
         bs::LaneOut out;
         const bs::Mem<1> Sm{S}, Bm{B}, Synm{Syn}, Mkm{Mk};
         bs::NoHook hook;
-        bs::solve_lane<1, 1>(Synm, Bm, Mkm, Sm, pad, out, hook);
+        bs::solve_lane<1, 1>(Synm, Bm, Mkm, Sm, pad, out, hook, ns);
         for (size_t c = 0; c < cnt; c++) {
             int nr = 0;
-            status[g + c] = (int8_t)bs::classify<1>(Sm, out, (int)c, nr);
+            status[g + c] = (int8_t)bs::classify<1>(Sm, out, (int)c, nr, ns);
             nroots[g + c] = (uint8_t)nr;
         }
         uint32_t nzc[5] = {0, 0, 0, 0, 0};
         for (int w = 0; w < 4; w++) {
-            bs::forney_slots<1, 1>(Synm, Bm, Sm, w, root_tab, nzc);
+            bs::forney_slots<1, 1>(Synm, Bm, Sm, w, root_tab, nzc, ns >> 1);
             uint32_t X[32];
             bs::magnitude_words<1>(Sm, X);
             for (size_t c = 0; c < cnt; c++) {

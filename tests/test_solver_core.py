@@ -26,6 +26,8 @@ def solver():
     lib = C.CDLL(OUT)
     P = C.POINTER
     lib.host_solve.argtypes = [P(C.c_uint8), C.c_size_t, C.c_int, P(C.c_int8), P(C.c_uint8), P(C.c_uint16)]
+    lib.host_solve_roots.argtypes = [P(C.c_uint8), C.c_size_t, C.c_int, C.c_int, P(C.c_int8), P(C.c_uint8),
+                                     P(C.c_uint16)]
     return lib
 
 
@@ -58,25 +60,26 @@ def syndromes(cw):
     return out
 
 
-def run_case(solver, orc, rng, n, size, emin, emax):
+def run_case(solver, orc, rng, n, size, emin, emax, nr=32):
+    params = (8, 0x11D, 1, 1, nr)
     msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
-    par = orc.rs_encode(msg)
+    par = orc.rs_encode(msg, params)
     cw = np.concatenate([msg, par], 1)
-    length = size + 32
+    length = size + nr
     for i in range(n):
         e = int(rng.integers(emin, emax + 1))
         pos = rng.choice(length, e, replace=False)
         cw[i, pos] ^= rng.integers(1, 256, e, dtype=np.uint8)
-    wd, wp, wok, wcor = orc.rs_decode(cw[:, :size], cw[:, size:])
+    wd, wp, wok, wcor = orc.rs_decode(cw[:, :size], cw[:, size:], params)
     syn = np.ascontiguousarray(syndromes(cw))
-    dirty = syn.any(axis=1)
+    dirty = syn[:, :nr].any(axis=1)  # (the entries beyond nr are evaluations the code does not constrain: garbage)
     status = np.zeros(n, np.int8)
     nroots = np.zeros(n, np.uint8)
     lists = np.zeros((n, 16), np.uint16)
-    pad = 223 - size
+    pad = 255 - nr - size
     P = C.POINTER
-    solver.host_solve(syn.ctypes.data_as(P(C.c_uint8)), n, pad, status.ctypes.data_as(P(C.c_int8)),
-                      nroots.ctypes.data_as(P(C.c_uint8)), lists.ctypes.data_as(P(C.c_uint16)))
+    solver.host_solve_roots(syn.ctypes.data_as(P(C.c_uint8)), n, pad, nr, status.ctypes.data_as(P(C.c_int8)),
+                            nroots.ctypes.data_as(P(C.c_uint8)), lists.ctypes.data_as(P(C.c_uint16)))
     declined = 0
     for i in range(n):
         if not dirty[i]:
@@ -122,3 +125,15 @@ def test_solver_core_shortened(solver):
     rng = np.random.default_rng(13)
     for size in (1, 17, 64, 200):
         run_case(solver, orc, rng, 256, size, 0, 19)
+
+
+def test_solver_core_16_and_8_roots(solver):
+    """RS(255,239) and RS(255,247): the same core with 16 / 8 syndromes (BM iterations, length counter, evaluator and
+    Forney bounds follow the syndrome count)"""
+    orc = Oracle("port")
+    rng = np.random.default_rng(14)
+    for nr in (16, 8):
+        declined, dirty = run_case(solver, orc, rng, 640, 255 - nr, 0, nr // 2, nr)
+        assert declined == 0 and dirty > 400
+        run_case(solver, orc, rng, 640, 255 - nr, nr // 2, nr + 4, nr)
+        run_case(solver, orc, rng, 256, 100, 0, nr // 2 + 2, nr)
