@@ -1053,6 +1053,37 @@ struct ApplyHook {
     }
 };
 
+// Erasure mode on the plain solver.  A row whose actual errors all sit on declared erasure positions decodes, in the
+// reference's erasure mode, to exactly what plain decoding gives - provided the reference's erasure path is on its
+// quirk-free ground (src/decode.c:34-47,211-214: positions strictly ascending, so that the i-th root belongs to the
+// i-th slot; 1 <= count <= 32; positions inside the message) and the word has at most 16 actual errors: the locator
+// stays the erasure locator, every declared position is a root, magnitudes are zero where the byte was right, and
+// corrected_num counts the non-zero ones.  This checks those conditions for codeword c of the lane (its roots are in
+// the work area's list); everything else goes to the general stage, which restates the reference literally.
+__device__ __noinline__ bool erasure_row_covers_roots(const uint32_t *pp, uint32_t count, uint32_t size, int pad,
+                                                      const bs::Mem<32> S, int c, int nroots)
+{
+    if (count == 0u || count > 32u)
+        return false;
+    uint32_t bm[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}; // declared locations (position + padding), 256 bits
+    int prev = -1;
+    for (uint32_t j = 0; j < count; j++) {
+        const uint32_t p = pp[j];
+        if (p >= size || (int)p <= prev)
+            return false;
+        prev = (int)p;
+        const uint32_t loc = p + (uint32_t)pad;
+        bm[loc >> 5] |= 1u << (loc & 31u);
+    }
+    for (int e = 0; e < nroots; e++) {
+        const uint32_t v = S.ld_byte(bs::kListBase + 4 * c + (e >> 2), e & 3); // location + 1
+        const uint32_t loc = v - 1u;
+        if (v == 0u || !((bm[(loc >> 5) & 7u] >> (loc & 31u)) & 1u))
+            return false;
+    }
+    return true;
+}
+
 // One warp per CTA, eight CTAs per SM: a warp keeps only its 25 KB work area in shared memory; the syndrome planes
 // and the evaluator live in a per-warp scratch in global memory (48 KB, written and read by the same lane, so it
 // stays in L2).  With one warp per scheduler the ALU pipe idled ~45 % of the time behind fixed-latency waits.
@@ -1062,7 +1093,8 @@ __global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, kSolveWarpsPerSM / kSo
 rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restrict__ counter, uint8_t *syn_raw,
                    uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2, uint32_t *__restrict__ counter2,
                    uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data, size_t data_stride,
-                   uint8_t *parity, size_t parity_stride)
+                   uint8_t *parity, size_t parity_stride, const uint32_t *__restrict__ era_pos, size_t era_stride,
+                   const uint32_t *__restrict__ era_cnt)
 {
     extern __shared__ __align__(16) uint32_t solve_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1146,7 +1178,16 @@ rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restr
                     continue;
                 const uint32_t entry = e4[u];
                 int nroots = 0;
-                const int st = bs::classify<32>(S, out, c, nroots, nr);
+                int st = bs::classify<32>(S, out, c, nroots, nr);
+                if (era_cnt != nullptr) {
+                    // erasure mode: only rows the plain solver decodes AND whose errors all sit on declared, ascending
+                    // erasure positions are finished here; the rest (failures included: more than 16 errors can still
+                    // be erasure-decodable) goes to the general stage with its raw syndromes untouched
+                    const size_t cwi = entry & 0x3FFFFFFFu;
+                    if (st != bs::kOk || !erasure_row_covers_roots(era_pos + cwi * era_stride, era_cnt[cwi], (uint32_t)size,
+                                                                   pad, S, c, nroots))
+                        st = bs::kDeclined;
+                }
                 if (st == bs::kOk) {
                     okmask |= 1u << c;
                     maxroots = nroots > maxroots ? nroots : maxroots;
@@ -1532,8 +1573,8 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     // larger than one wave would leave a thin second wave behind the grid-stride loop
     const unsigned cblocks = (unsigned)(ctx->sm_count * ctx->correct_ctas_per_sm);
     const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
-    if (mode == POPORON_CUDA_MODE_PLAIN || mode == POPORON_CUDA_MODE_EXTSYN) {
-        // bitsliced solver first (with the caller's syndromes error_correction_u8 runs exactly as in plain mode); what it declines lands in queue2 for the literal stage below
+    {
+        // bitsliced solver first (erasure mode: for the rows it can prove equal to plain decoding, see erasure_row_covers_roots) (with the caller's syndromes error_correction_u8 runs exactly as in plain mode); what it declines lands in queue2 for the literal stage below
         uint32_t *queue2 = dmask + tiles * 64;
         const size_t groups = (n + 1023) / 1024;
         const size_t cap = (size_t)ctx->sm_count * kSolveWarpsPerSM;
@@ -1544,7 +1585,8 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
             rs255_solve_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
                                  kSolveSmem, stream>>>(
                 nr, size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2, ctx->d_counters + 1, ok, corrected,
-                data, data_stride, parity, parity_stride);
+                data, data_stride, parity, parity_stride, mode == POPORON_CUDA_MODE_ERASURE ? pos : nullptr, pos_stride,
+                mode == POPORON_CUDA_MODE_ERASURE ? cnt : nullptr);
         }
         cq = queue2;
         cc = ctx->d_counters + 1;
