@@ -135,6 +135,24 @@ int poporon_cuda_rs_encode_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size
                                uint8_t *parity, size_t parity_stride, size_t n, uint8_t *ok /* nullable */,
                                void *stream);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * poporon_cuda_rs_encode_dev on the bitsliced path (RS(255,223/239/247), 0x11D, fcr = 1, prim = 1; row layouts for
+ * which poporon_cuda_rs_path(ctx, 0, ...) == 1 through the transform kernels), but the scratch between its three
+ * kernels is a file-scope device array of 20 905 984 bytes (64 slabs of 255 KB + 64 bytes of planes per codeword)
+ * that every GPU holds from the moment it loads the library until the process exits.  The call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine); its first use on a device looks the array's address up
+ * with cudaGetSymbolAddress.  Limits: n <= POPORON_CUDA_NOALLOC_MAX_CODEWORDS per call, else POPORON_CUDA_ERR_UNSUPP
+ * with the reason in poporon_cuda_last_error (other codes / layouts likewise).  ALL calls on one device share the
+ * array, whatever context or stream: unlike poporon_cuda_rs_encode_dev they are NOT ordered against each other or
+ * against the allocating entry points, so two calls that overlap on the GPU race - keep them on one stream or order
+ * them with events.  Nothing in the array needs clearing between calls (every word read was written by the same
+ * call).  ok is nullable. */
+#define POPORON_CUDA_NOALLOC_MAX_CODEWORDS 65536
+int poporon_cuda_rs_encode_noalloc_dev(poporon_cuda_rs_t *ctx, const uint8_t *data, size_t data_stride, size_t size,
+                                       uint8_t *parity, size_t parity_stride, size_t n, uint8_t *ok /* nullable */,
+                                       void *stream);
+
 /* mode PLAIN:   pos/cnt/syn ignored.
  * mode ERASURE: pos = [n][pos_stride] uint32 data-relative positions, EVERY slot defined by the caller,
  *               pos_stride >= nroots; cnt = [n], each <= nroots.  Reproduces the reference's
