@@ -864,8 +864,11 @@ rs255_correct_kernel(RsCode c, const RsTables *__restrict__ gtab, int mode, uint
 #define PP_SOLVE_WARPS_PER_CTA 8
 #endif
 constexpr int kSolveWarpsPerCTA = PP_SOLVE_WARPS_PER_CTA; // warps of a CTA move from tile to tile together (see the kernel)
-constexpr int kSolveSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 256; // work areas + the root table (256 B)
-constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO + bs::kWordsM + 32;  // per lane, in global memory (L2-resident)
+#ifndef PP_SOLVE_W_GLOBAL
+#define PP_SOLVE_W_GLOBAL 0 // experiment: the work area in the L2 scratch too (frees shared memory for 16 warps per SM)
+#endif
+constexpr int kSolveSmem = (PP_SOLVE_W_GLOBAL ? 0 : kSolveWarpsPerCTA * bs::kWordsW * 128) + 256; // work areas + the root table (256 B)
+constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO + bs::kWordsM + 32 + (PP_SOLVE_W_GLOBAL ? bs::kWordsW : 0);  // per lane, in global memory (L2-resident)
 #ifndef PP_SOLVE_WARPS_PER_SM
 #define PP_SOLVE_WARPS_PER_SM 8
 #endif
@@ -1099,15 +1102,19 @@ rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restr
     extern __shared__ __align__(16) uint32_t solve_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t gw = blockIdx.x * kSolveWarpsPerCTA + (uint32_t)warp, nw = gridDim.x * kSolveWarpsPerCTA;
-    const bs::Mem<32> S{solve_smem + warp * (bs::kWordsW * 32) + lane}; // the work area
     uint32_t *gs = scratch + (size_t)gw * (kSolveScratchWords * 32) + lane;
+#if PP_SOLVE_W_GLOBAL
+    const bs::Mem<32> S{gs + (bs::kWordsS + bs::kWordsO + bs::kWordsM + 32) * 32};
+#else
+    const bs::Mem<32> S{solve_smem + warp * (bs::kWordsW * 32) + lane}; // the work area
+#endif
     const bs::Mem<32> Syn{gs};
     const bs::Mem<32> B{gs + bs::kWordsS * 32}; // the evaluator
     const bs::Mem<32> Mk{gs + (bs::kWordsS + bs::kWordsO) * 32}; // root masks of the transform-form Chien search
     // the tile's 32 queue entries of this lane (L2-resident copy: the queue itself is 64 MB of DRAM by the time the
     // outcomes are written, and three loops below would wait for it entry by entry)
     const bs::Mem<32> Qs{gs + (bs::kWordsS + bs::kWordsO + bs::kWordsM) * 32};
-    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWarpsPerCTA * bs::kWordsW * 32);
+    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + (PP_SOLVE_W_GLOBAL ? 0 : kSolveWarpsPerCTA * bs::kWordsW * 32));
     {
         // root_tab[0] = 0 (empty list slot), root_tab[v] = alpha^v for v = 1..255: each lane fills 8 consecutive powers
         uint32_t x = 1;

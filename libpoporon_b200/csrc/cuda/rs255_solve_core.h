@@ -402,16 +402,184 @@ BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uin
     }
 }
 
+// ---- the same recurrence with the locator in memory -------------------------------------------------------------
+// LM: 17 word blocks, L_i in block i.  One rolled loop over the coefficients 0 .. min(top, elmax) of an iteration:
+// no coefficient registers to rotate (the register form spends ~15 % of the kernel's instructions on those moves),
+// a loop body of one coefficient step, and ~100 live registers instead of ~250.  L_i and the syndrome of the NEXT
+// step are fetched while the current step computes; the old B_i is only needed by the next step anyway.
+#ifndef BS_BM_MEM
+#define BS_BM_MEM 1
+#endif
+// gamma and Delta multiply every coefficient of an iteration: with the eight multiples gamma * x^s (and Delta * x^s)
+// held as planes, a product is 64 AND-XOR with nothing left to reduce
+#ifndef BS_BM_TABLES
+#define BS_BM_TABLES 0
+#endif
+#ifndef BS_BM_UNROLL
+#define BS_BM_UNROLL 1 // coefficient steps per trip of the loop
+#endif
+constexpr int kBmUnroll = BS_BM_UNROLL;
+// times x modulo x^8 + x^4 + x^3 + x^2 + 1
+BS_FN void xtime(const uint32_t (&a)[8], uint32_t (&o)[8])
+{
+    o[0] = a[7];
+    o[1] = a[0];
+    o[2] = a[1] ^ a[7];
+    o[3] = a[2] ^ a[7];
+    o[4] = a[3] ^ a[7];
+    o[5] = a[4];
+    o[6] = a[5];
+    o[7] = a[6];
+}
+BS_FN void xmultiples(const uint32_t (&a)[8], uint32_t (&m)[8][8])
+{
+    cp8(m[0], a);
+#pragma unroll
+    for (int s = 1; s < 8; s++)
+        xtime(m[s - 1], m[s]);
+}
+template <int STRIDE, int SO>
+BS_FN void ribm_mem(const Mem<SO> S, const Mem<STRIDE> B, const Mem<SO> LM, uint32_t (&K)[7], int ns)
+{
+    uint32_t gamma[8], delta[8];
+#pragma unroll 1
+    for (int i = 0; i < kNL; i++)
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            const uint32_t v = (i == 0 && t == 0) ? 0xFFFFFFFFu : 0u;
+            LM.st(8 * i + t, v);
+            if (i < kT)
+                B.st(8 * i + t, v);
+        }
+#pragma unroll
+    for (int t = 0; t < 8; t++)
+        gamma[t] = t == 0 ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+    for (int b = 0; b < 7; b++)
+        K[b] = 0;
+    ld8(S, 0, delta); // Delta_1 = L_0 * S_1 = S_1
+
+#pragma unroll 1
+    for (int r = 1; r <= ns; r++) {
+        const uint32_t chg = or8(delta) & ~K[6]; // delta != 0 and k >= 0
+        const int top = r < kT ? r : kT;         // highest coefficient that can be non-zero after this iteration
+        {
+            uint32_t carry = 0xFFFFFFFFu;
+#pragma unroll
+            for (int b = 0; b < 7; b++) {
+                const uint32_t inc = K[b] ^ carry;
+                carry &= K[b];
+                K[b] = merge_bits(~K[b], inc, chg);
+            }
+        }
+        // largest new register length among the warp's 1024 codewords: T_i = 0 beyond it for every one of them
+        const int elmax = (r - BS_WARP_MIN(min_counter(K))) >> 1;
+        const int lim = top < elmax ? top : elmax; // coefficients 0 .. lim take the complete update
+        uint32_t acc[15], bcur[8], li[8], s[8];
+        clear15(acc);
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            bcur[t] = 0u; // "B_{-1}"
+        ld8(LM, 0, li);
+        ld8(S, r > kNS - 1 ? kNS - 1 : r, s);
+#if BS_BM_TABLES
+        uint32_t gx[8][8], dx[8][8];
+        xmultiples(gamma, gx);
+        xmultiples(delta, dx);
+#endif
+#pragma unroll kBmUnroll
+        for (int i = 0; i <= lim; i++) {
+            uint32_t bold[8], ln[8], sn[8], tacc[15], T[8];
+            const int d = r - i - 1; // the next step's syndrome S_{r+1-(i+1)}, clamped where it is not used
+            const int sidx = d < 0 ? 0 : (d > kNS - 1 ? kNS - 1 : d);
+            const int bidx = i < kT ? i : kT - 1; // ("B_16" = 0: masked below)
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                ln[t] = LM.ld(8 * (i < kT ? i + 1 : kT) + t);
+                sn[t] = S.ld(8 * sidx + t);
+                bold[t] = B.ld(8 * bidx + t);
+            }
+#if BS_BM_TABLES
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                uint32_t v = li[0] & gx[0][t];
+#pragma unroll
+                for (int q = 1; q < 8; q++)
+                    v ^= li[q] & gx[q][t];
+#pragma unroll
+                for (int q = 0; q < 8; q++)
+                    v ^= bcur[q] & dx[q][t];
+                T[t] = v;
+            }
+            (void)tacc;
+            if (i < kT) {
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    B.st(8 * i + t, merge_bits(li[t], bcur[t], chg));
+            }
+#else
+            clear15(tacc);
+            mac(tacc, gamma, li);
+            mac(tacc, delta, bcur);
+            if (i < kT) {
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    B.st(8 * i + t, merge_bits(li[t], bcur[t], chg));
+            }
+            reduce(tacc, T);
+#endif
+            st8(LM, i, T);
+            mac(acc, T, s);
+            const uint32_t live = i < kT ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                bcur[t] = bold[t] & live;
+                li[t] = ln[t];
+                s[t] = sn[t];
+            }
+        }
+        // Coefficients lim+1 .. top were skipped: L_i = T_i = 0 there for all codewords, only B moves,
+        // B_i <- (length change ? L_i = 0 : B_{i-1}); highest index first, bcur = old B_lim.
+        {
+            const int full = lim + 1;
+            const int hi = top < kT - 1 ? top : kT - 1;
+#pragma unroll 1
+            for (int i = hi; i > full; i--) {
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    B.st(8 * i + t, B.ld(8 * (i - 1) + t) & ~chg);
+            }
+            if (full <= hi) {
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    B.st(8 * full + t, bcur[t] & ~chg);
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            gamma[t] = merge_bits(delta[t], gamma[t], chg);
+        reduce(acc, delta);
+    }
+}
+
 // ---- evaluator: Omega_i = sum_{j <= i} S_{i-j+1} * L_j, i = 0..15 (src/decode.c:147-158) -------------------
 // Rolled loops: L_0..L_15 are parked in P (16 blocks; the BM scratch, dead by now), Omega_i goes to word block i
 // of O.
 // (teff = ns / 2: for a code with fewer than 32 roots only Omega_0 .. Omega_(teff-1) exist; the rest is stored as zero)
+template <int STRIDE, int SO>
+BS_FN void omega_parked(const Mem<SO> S, const Mem<STRIDE> P, const Mem<SO> O, int teff);
 template <int STRIDE, int SO>
 BS_FN void omega(const Mem<SO> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE> P, const Mem<SO> O, int teff)
 {
 #pragma unroll
     for (int j = 0; j < kT; j++)
         st8(P, j, L[j]);
+    omega_parked<STRIDE, SO>(S, P, O, teff);
+}
+// P: L_0 .. L_15 in word blocks 0 .. 15
+template <int STRIDE, int SO>
+BS_FN void omega_parked(const Mem<SO> S, const Mem<STRIDE> P, const Mem<SO> O, int teff)
+{
 #pragma unroll 1
     for (int i = teff; i < kT; i++) {
         const uint32_t z[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
@@ -1062,6 +1230,20 @@ BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<SO> Mk, con
                       Hook &hook, int ns = kNS)
 {
     const Mem<STRIDE> B{W.base + kListBase * STRIDE};
+#if BS_BM_MEM
+    {
+        // the locator lives in the root-mask area (free until the sweep) during BM and the evaluator
+        ribm_mem<STRIDE, SO>(Syn, B, Mk, out.K, ns);
+        omega_parked<SO, SO>(Syn, Mk, Om, ns >> 1);
+#pragma unroll
+        for (int j = 0; j < kNL; j++) {
+            uint32_t l[8];
+            ld8(Mk, j, l);
+            out.nzL[j] = or8(l);
+            st8(Syn, j, l);
+        }
+    }
+#else
     {
         uint32_t L[kLS][8];
         ribm<STRIDE, SO>(Syn, B, L, out.K, ns);
@@ -1074,6 +1256,7 @@ BS_FN void solve_lane(const Mem<SO> Syn, const Mem<SO> Om, const Mem<SO> Mk, con
             st8(Syn, j, L[j]);
         }
     }
+#endif
 #if BS_CHIEN_TRANSFORM
     chien_transform<STRIDE, SO, Hook>(Syn, Mk, W, pad, out, hook);
 #else

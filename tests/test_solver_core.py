@@ -19,11 +19,14 @@ INC = os.path.join(ROOT, "libpoporon_b200", "csrc", "cuda")
 OUT = os.path.join(ROOT, "build", "tests", "host_solver.so")
 
 
-@pytest.fixture(scope="module")
-def solver():
+# both forms of Berlekamp-Massey in the header: coefficients rotating through registers / locator in memory
+@pytest.fixture(scope="module", params=[0, 1], ids=["bm-registers", "bm-memory"])
+def solver(request):
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
-    subprocess.run(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", f"-I{INC}", "-o", OUT, SRC], check=True)
-    lib = C.CDLL(OUT)
+    out = OUT.replace(".so", f"_bm{request.param}.so")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", f"-DBS_BM_MEM={request.param}", f"-I{INC}", "-o",
+                    out, SRC], check=True)
+    lib = C.CDLL(out)
     P = C.POINTER
     lib.host_solve.argtypes = [P(C.c_uint8), C.c_size_t, C.c_int, P(C.c_int8), P(C.c_uint8), P(C.c_uint16)]
     lib.host_solve_roots.argtypes = [P(C.c_uint8), C.c_size_t, C.c_int, C.c_int, P(C.c_int8), P(C.c_uint8),
