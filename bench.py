@@ -85,10 +85,11 @@ def alu_peak(sm_mhz):
 # Useful integer-ALU lane-operations per codeword of each ALU-bound kernel: the operation count of its formulation
 # with nothing but the GF(2) arithmetic counted (DESIGN.md section 4 derives every term).
 ALU_FLOOR = {
-    # BM 332 coefficient steps x 228 + evaluator 9.2 K + Chien search as a transform 17 x (2 x 244 DFT + 192 multipliers
-    # + 16 + 120 zero tests) + 136 basis change + Forney on 16 list slots 44.9 K + 28 bit-matrix transposes x 256, per
-    # 32 queued codewords
-    "rs255_solve_kernel": (75696 + 9152 + 17 * 816 + 136 + 44900 + 7168) / 32.0,
+    # BM 304 coefficient steps (sum over the 32 iterations r of ceil(r / 2) + 1: the longest register among a warp's 1024
+    # codewords sets the trip count) x 228 + evaluator 9.2 K + Chien search as a transform 17 x (2 x 244 DFT + 192
+    # multipliers + 16 + 120 zero tests) + 136 basis change + Forney on 16 list slots 44.9 K + 28 bit-matrix transposes
+    # x 256, per 32 queued codewords
+    "rs255_solve_kernel": (304 * 228 + 9152 + 17 * 816 + 136 + 44900 + 7168) / 32.0,
     # transform 18598 + 64 word-columns x (256 transpose + 32 realign) + 255 x 8 basis change, per 32 codewords
     "rs255_fft_kernel<SCREEN>": (18598 + 64 * 288 + 255 * 8) / 32.0,
     "rs255_fft_kernel<ENCODE>": (18598 + 56 * 288 + 223 * 8) / 32.0,

@@ -1077,6 +1077,25 @@ BS_FN void chien_transform(const Mem<SL> LM, const Mem<SL> MK, const Mem<STRIDE>
 // The two Horner recurrences run over the four slots in lock step: one coefficient (fetched from the L2-resident
 // scratch one step ahead) feeds four independent multiply-reduce chains, so its latency hides behind ~340
 // instructions and the chains overlap each other's dependent steps.
+#ifndef BS_FORNEY_TABLES
+#define BS_FORNEY_TABLES 1
+#endif
+// v <- v * m + c, with m given as its multiples m * alpha^s (xmultiples): plane t of the product is the sum over s of
+// v[s] & mm[s][t]
+BS_FN void mul_add_tab(uint32_t (&v)[8], const uint32_t (&mm)[8][8], const uint32_t (&c)[8])
+{
+    uint32_t r[8];
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        uint32_t a = c[t] ^ (v[0] & mm[0][t]);
+#pragma unroll
+        for (int q = 1; q < 8; q++)
+            a ^= v[q] & mm[q][t];
+        r[t] = a;
+    }
+    cp8(v, r);
+}
+
 template <int STRIDE, int SO>
 BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, int w,
                         const uint8_t *root_tab /* [0] = 0, [v] = alpha^v */, uint32_t (&cnt)[5], int teff = kT)
@@ -1096,6 +1115,65 @@ BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, 
         for (int p = 0; p < 32; p++)
             S.st(p, X[p]);
     }
+#if BS_FORNEY_TABLES
+    // Both Horner chains of a slot multiply by the same element at every step (x, then x^2): with its eight multiples
+    // x * alpha^s held as planes a step is 64 AND-XOR, the coefficient folded into the first of them and nothing to
+    // reduce.  Two slots at a time (128 registers of multiples).
+#pragma unroll 1
+    for (int y0 = 0; y0 < 4; y0 += 2) {
+        uint32_t x[2][8], xm[2][8][8], v[2][8], o[8];
+        ld8(O, teff - 1, o);
+#pragma unroll
+        for (int y = 0; y < 2; y++) {
+            ld8(S, y0 + y, x[y]);
+            xmultiples(x[y], xm[y]);
+            cp8(v[y], o);
+        }
+        ld8(O, teff - 2, o);
+#pragma unroll 1
+        for (int j = teff - 2; j >= 0; j--) {
+            uint32_t on[8];
+            ld8(O, j > 0 ? j - 1 : 0, on);
+#pragma unroll
+            for (int y = 0; y < 2; y++)
+                mul_add_tab(v[y], xm[y], o);
+            cp8(o, on);
+        }
+        {
+            const uint32_t z[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+#pragma unroll
+            for (int y = 0; y < 2; y++) {
+                mul_add_tab(v[y], xm[y], z); // one more factor x
+#pragma unroll
+                for (int t = 0; t < 8; t++) // parked in the (idle) parked-mask words until the division
+                    S.st(kParkBase + 8 * (y0 + y) + t, v[y][t]);
+            }
+        }
+        ld8(LM, teff - 1, o);
+#pragma unroll
+        for (int y = 0; y < 2; y++) {
+            uint32_t x2[8];
+            sqr(x[y], x2);
+            xmultiples(x2, xm[y]);
+            cp8(v[y], o);
+        }
+        ld8(LM, teff - 3, o);
+#pragma unroll 1
+        for (int j = teff - 3; j >= 1; j -= 2) {
+            uint32_t on[8];
+            ld8(LM, j > 1 ? j - 2 : 1, on);
+#pragma unroll
+            for (int y = 0; y < 2; y++)
+                mul_add_tab(v[y], xm[y], o);
+            cp8(o, on);
+        }
+#pragma unroll
+        for (int y = 0; y < 2; y++) {
+            mul(v[y], x[y], v[y]);
+            st8(S, y0 + y, v[y]);
+        }
+    }
+#else
     {
         uint32_t x[4][8], num[4][8], o[8];
         ld8(O, teff - 1, o);
@@ -1158,6 +1236,7 @@ BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, 
             st8(S, y, odd[y]);
         }
     }
+#endif
 #pragma unroll 1
     for (int y = 0; y < 4; y++) {
         uint32_t num[8], den[8], mag[8];

@@ -1,5 +1,6 @@
 #!/usr/bin/env python
 """Per-kernel decode times of RS(255,223) / RS(255,239) / RS(255,247) at 0..t errors.  usage: PYTHONPATH=. tools/dec_probe.py [ncw]"""
+import os
 import sys
 import torch
 import libpoporon_b200.api as api
@@ -24,5 +25,6 @@ for nr in (32, 16, 8):
             assert h.decode_batch_async(rec.data_ptr(), 255, K, rec.data_ptr() + K, 255, n, ok.data_ptr(), cor.data_ptr(), stream=st)
             torch.cuda.synchronize()
         prof = h.profile_read()
-        assert bool(ok.all().item()) and torch.equal(rec, clean)
+        if not os.environ.get("DEC_PROBE_NOCHECK"):
+            assert bool(ok.all().item()) and torch.equal(rec, clean)
         print(f"RS(255,{K})", {k: round(v[1] / v[0], 3) for k, v in prof.items()}, "mean errors", float(cor.float().mean().item()))
