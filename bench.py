@@ -85,11 +85,13 @@ def alu_peak(sm_mhz):
 # Useful integer-ALU lane-operations per codeword of each ALU-bound kernel: the operation count of its formulation
 # with nothing but the GF(2) arithmetic counted (DESIGN.md section 4 derives every term).
 ALU_FLOOR = {
-    # BM 304 coefficient steps (sum over the 32 iterations r of ceil(r / 2) + 1: the longest register among a warp's 1024
-    # codewords sets the trip count) x 228 + evaluator 9.2 K + Chien search as a transform 17 x (2 x 244 DFT + 192
-    # multipliers + 16 + 120 zero tests) + 136 basis change + Forney on 16 list slots 44.9 K + 28 bit-matrix transposes
-    # x 256, per 32 queued codewords
-    "rs255_solve_kernel": (304 * 228 + 9152 + 17 * 816 + 136 + 44900 + 7168) / 32.0,
+    # BM: 304 coefficient steps (sum over the 32 iterations r of ceil(r / 2) + 1: the longest register among a warp's
+    # 1024 codewords sets the trip count) x (2 x 64 on the held multiples of gamma and Delta + 8 select + 64 for the
+    # next discrepancy) + 32 x (2 x 21 multiples + 28 reduction); evaluator 9.2 K; Chien search as a transform 17 x
+    # (2 x 244 DFT + 192 multipliers + 16 + 120 zero tests) + 136 basis change; Forney on 16 list slots x (23 Horner steps
+    # x 64 on the root's held multiples + 2 x 21 for the multiples + 18 squaring + 2 products x 92 + a^254 = 4 x 92 + 7 x
+    # 18); 28 bit-matrix transposes x 256 - per 32 queued codewords
+    "rs255_solve_kernel": (304 * 200 + 32 * 70 + 9152 + 17 * 816 + 136 + 16 * 2210 + 7168) / 32.0,
     # transform 18598 + 64 word-columns x (256 transpose + 32 realign) + 255 x 8 basis change, per 32 codewords
     "rs255_fft_kernel<SCREEN>": (18598 + 64 * 288 + 255 * 8) / 32.0,
     "rs255_fft_kernel<ENCODE>": (18598 + 56 * 288 + 223 * 8) / 32.0,

@@ -413,7 +413,7 @@ BS_FN void ribm(const Mem<SO> S, const Mem<STRIDE> B, uint32_t (&L)[kLS][8], uin
 // gamma and Delta multiply every coefficient of an iteration: with the eight multiples gamma * x^s (and Delta * x^s)
 // held as planes, a product is 64 AND-XOR with nothing left to reduce
 #ifndef BS_BM_TABLES
-#define BS_BM_TABLES 0
+#define BS_BM_TABLES 1
 #endif
 #ifndef BS_BM_UNROLL
 #define BS_BM_UNROLL 1 // coefficient steps per trip of the loop
@@ -835,13 +835,17 @@ constexpr int kParkBase = 168; // 32 parked mask words
 
 // bits: the parked mask word of codeword c, n: its root counter (both loaded by the caller, ahead of use).
 // List entries are location + 1 (1..255; 0 = empty slot).
+#ifndef BS_APPEND_FLAT
+#define BS_APPEND_FLAT 2
+#endif
+constexpr int kAppendFlat = BS_APPEND_FLAT;
 template <int STRIDE>
 BS_FN void append_roots(const Mem<STRIDE> S, int c, int blk, uint32_t bits, uint32_t n)
 {
     const uint32_t n0 = n;
-    // a codeword has about one root per block: the first two are taken without branches
+    // a codeword has about one root per block: the first kAppendFlat are taken without branches
 #pragma unroll
-    for (int it = 0; it < 2; it++) {
+    for (int it = 0; it < kAppendFlat; it++) {
         const bool live = bits != 0;
         const int kk = live ? BS_CTZ(bits) : 0;
         if (live && n < (uint32_t)kT)
