@@ -874,12 +874,43 @@ constexpr int kSolveScratchWords = bs::kWordsS + bs::kWordsO + bs::kWordsM + 32 
 #endif
 constexpr int kSolveWarpsPerSM = PP_SOLVE_WARPS_PER_SM;
 
+#ifndef PP_SOLVE_LOAD_ROWS128
+#define PP_SOLVE_LOAD_ROWS128 1
+#endif
 // Syndrome rows (32 bytes per queued codeword: S_1 .. S_32 as field elements, written by the screen kernel) ->
 // bit-planes: word W of the 32 rows of a lane is transposed into the planes of S_{4W+1} .. S_{4W+4}.  A rolled loop
 // (the solver's straight-line code competes with its loop bodies for the instruction cache).
 __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], const uint8_t *__restrict__ syn_raw,
                                                      const bs::Mem<32> S)
 {
+#if PP_SOLVE_LOAD_ROWS128
+    // Half a row (16 bytes) per load: the 32 rows of a lane are read once, as two passes of 32 quad-word loads, instead
+    // of eight passes of word loads that each touched every sector again (the rows of eight warps do not stay in what
+    // is left of the L1 beside 200 KB of shared memory).
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+        uint4 v[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++) {
+            const uint32_t e = ent[c];
+            // a half whose LFSR state was zero has no row written by the screen kernel: its 16 values are 0
+            const bool live = e != 0xFFFFFFFFu && ((e >> (30 + h)) & 1u);
+            v[c] = live ? __ldg(reinterpret_cast<const uint4 *>(syn_raw) + (size_t)(e & 0x3FFFFFFFu) * 2 + h)
+                        : make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll 1
+        for (int q = 0; q < 4; q++) {
+            uint32_t X[32];
+#pragma unroll
+            for (int c = 0; c < 32; c++)
+                X[c] = q == 0 ? v[c].x : q == 1 ? v[c].y : q == 2 ? v[c].z : v[c].w;
+            bs::transpose32(X); // X[8*y + t] = plane t of S_{4W + y + 1}, W = 4 h + q
+#pragma unroll
+            for (int p = 0; p < 32; p++)
+                S.st(32 * (4 * h + q) + p, X[p]);
+        }
+    }
+#else
 #pragma unroll 1
     for (int W = 0; W < 8; W++) {
         uint32_t X[32];
@@ -895,6 +926,7 @@ __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], 
         for (int p = 0; p < 32; p++)
             S.st(32 * W + p, X[p]);
     }
+#endif
 }
 
 // Corrections of the PREVIOUS tile, issued in 256 small portions from inside the Chien sweep of the current one
