@@ -128,6 +128,69 @@ __global__ void k(unsigned *out, unsigned seed)
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
 }
 
+// The bitsliced GF(2^8) product as the kernels issue it: acc[s + t] ^= a[s] & b[t], 64 LOP3 with three DIFFERENT
+// register operands each (8 + 8 inputs, 15 accumulators), 16 products per loop trip with the inputs rotating.  The
+// solver runs 8 warps per SM at 255 registers, the transform kernels 16 at 128: the rate is measured at those warp
+// counts, not only at 32.
+__global__ void kmac(unsigned *out, unsigned seed)
+{
+    unsigned a[8], b[8], acc[15];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        a[i] = threadIdx.x * (2 * i + 3) ^ seed;
+        b[i] = threadIdx.x * (2 * i + 5) + seed;
+    }
+#pragma unroll
+    for (int i = 0; i < 15; i++)
+        acc[i] = i;
+#pragma unroll 1
+    for (int it = 0; it < ITERS / 16; it++) {
+#pragma unroll
+        for (int rep = 0; rep < 16; rep++) {
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    asm volatile("lop3.b32 %0,%1,%2,%0,0x6a;" : "+r"(acc[q + t]) : "r"(a[(q + rep) & 7]), "r"(b[t]));
+        }
+    }
+    unsigned r = 0;
+#pragma unroll
+    for (int i = 0; i < 15; i++)
+        r ^= acc[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+// the same product through the eight held multiples m[s][t] of one factor: v[t] ^= x[s] & m[s][t] (64 + 8 + 8 registers)
+__global__ void __launch_bounds__(256, 1) ktab(unsigned *out, unsigned seed)
+{
+    unsigned m[8][8], x[8], v[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        x[i] = threadIdx.x * (2 * i + 3) ^ seed;
+        v[i] = i;
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            m[i][j] = threadIdx.x * (8 * i + j + 7) + seed;
+    }
+#pragma unroll 1
+    for (int it = 0; it < ITERS / 16; it++) {
+#pragma unroll
+        for (int rep = 0; rep < 16; rep++) {
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    asm volatile("lop3.b32 %0,%1,%2,%0,0x6a;" : "+r"(v[t]) : "r"(x[(q + rep) & 7]), "r"(m[q][t]));
+        }
+    }
+    unsigned r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+        r ^= v[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
 static FILE *g_json = nullptr;
 static int g_first = 1;
 
@@ -160,6 +223,37 @@ void run(const char *name, int sms, double ghz_guess)
     cudaFree(out);
 }
 
+template <class K>
+void run_product(const char *name, K kernel, int warps_per_sm, int sms, double ghz_guess)
+{
+    unsigned *out;
+    const int threads = 256, blocks = sms * warps_per_sm / 8;
+    cudaMalloc(&out, sizeof(unsigned) * threads * blocks);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    kernel<<<blocks, threads>>>(out, 1);
+    cudaDeviceSynchronize();
+    cudaEventRecord(e0);
+    kernel<<<blocks, threads>>>(out, 2);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms;
+    cudaEventElapsedTime(&ms, e0, e1);
+    double winstr = (double)blocks * (threads / 32) * (ITERS / 16) * 16.0 * 64.0;
+    double per_s = winstr / (ms * 1e-3);
+    char full[96];
+    snprintf(full, sizeof full, "%s, %d warps/SM", name, warps_per_sm);
+    printf("%-40s %8.3f ms  %8.2f Gwarp-instr/s  = %6.2f warp-instr/clk/SM (lanes/clk/SM %.1f)\n", full, ms, per_s / 1e9,
+           per_s / sms / (ghz_guess * 1e9), 32 * per_s / sms / (ghz_guess * 1e9));
+    if (g_json) {
+        fprintf(g_json, "%s\n  \"%s\": {\"warp_instr_per_clk_per_sm\": %.4f, \"lanes_per_clk_per_sm\": %.2f, \"gwarp_instr_per_s\": %.2f}",
+                g_first ? "" : ",", full, per_s / sms / (ghz_guess * 1e9), 32 * per_s / sms / (ghz_guess * 1e9), per_s / 1e9);
+        g_first = 0;
+    }
+    cudaFree(out);
+}
+
 int main(int argc, char **argv)
 {
     cudaDeviceProp p;
@@ -183,6 +277,10 @@ int main(int argc, char **argv)
     run<9>("IMAD.HI (mul.hi)", sms, ghz);
     run<10>("LOP3+IMAD.HI 1:1", sms, ghz);
     run<11>("LOP3+IMAD 3:1", sms, ghz);
+    for (int w : {8, 16, 32})
+        run_product("GF product acc[s+t] ^= a[s] & b[t]", kmac, w, sms, ghz);
+    for (int w : {8, 16})
+        run_product("GF product on held multiples", ktab, w, sms, ghz);
     if (g_json) {
         fprintf(g_json, "\n}}\n");
         fclose(g_json);
