@@ -938,6 +938,9 @@ __device__ __forceinline__ void solve_load_syndromes(const uint32_t (&ent)[32], 
 // 16 Mi codewords): the scattered sector read-modify-writes now overlap the ALU-bound solver.
 // Records: the solver leaves, in place of a decodable codeword's raw syndrome row, bytes 0..15 = error
 // locations + 1 (0 = none) and bytes 16..31 = magnitudes; queue entries of all other codewords are blanked.
+#ifndef PP_HOOK_BATCH
+#define PP_HOOK_BATCH 1
+#endif
 struct ApplyHook {
     uint32_t g0p;          // first queue index of the previous tile (0xFFFFFFFF: nothing pending) - the only state
                            // that stays live between sweeps
@@ -1026,12 +1029,38 @@ struct ApplyHook {
     {
         if (entry_app != 0xFFFFFFFFu) {
             const uint32_t xw[4] = {wxs.x, wxs.y, wxs.z, wxs.w}, mw[4] = {wmg.x, wmg.y, wmg.z, wmg.w};
+#if PP_HOOK_BATCH
+            // All sixteen addresses and words first, in registers of their own, then the sixteen predicated RED.XORs
+            // back to back.  A RED holds its operand registers until the load/store unit has taken them, and one RED
+            // with 32 unrelated sectors keeps that unit busy for tens of cycles: computing the next address into the
+            // same registers made every correction wait for the previous one to drain.
+            const size_t cw = entry_app & 0x3FFFFFFFu;
+            const uintptr_t dbase = (uintptr_t)data + cw * (size_t)stride32 - (size_t)(1 + pad);
+            const uintptr_t pbase = (uintptr_t)parity + cw * (size_t)pstride32 - (size_t)(1 + pad) - (size_t)size;
+            const uint32_t split = size + 1u + (uint32_t)pad; // list entries >= split are parity symbols
+            uintptr_t ua[16];
+            uint32_t val[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) {
+                const uint32_t le = (xw[e >> 2] >> (8 * (e & 3))) & 0xFFu; // list entry = location + 1 > pad (0: none)
+                const uint32_t mag = (mw[e >> 2] >> (8 * (e & 3))) & 0xFFu;
+                const uintptr_t a = (le >= split ? pbase : dbase) + le;
+                val[e] = mag << (8u * (unsigned)(a & 3u));
+                ua[e] = a & ~(uintptr_t)3;
+            }
+#pragma unroll
+            for (int e = 0; e < 16; e++)
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p red.relaxed.gpu.global.xor.b32 [%0], %1;\n\t}"
+                             ::"l"(ua[e]), "r"(val[e])
+                             : "memory");
+#else
 #pragma unroll
             for (int h = 0; h < 8; h++) {
                 p2 = (xw[h >> 1] >> (16 * (h & 1))) & 0xFFFFu;
                 m2 = (mw[h >> 1] >> (16 * (h & 1))) & 0xFFFFu;
                 flush();
             }
+#endif
         }
     }
     __device__ __forceinline__ void wstep(int c)
