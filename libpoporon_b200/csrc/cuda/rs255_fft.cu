@@ -846,9 +846,22 @@ __global__ void __launch_bounds__(32 * kParWarps, 1) rs255_parity_kernel(ParArgs
     }
 }
 
-constexpr int kRowWarps = 7;
+#ifndef PP_ROWS_SPLIT
+#define PP_ROWS_SPLIT 2
+#endif
+constexpr int kRowSplit = PP_ROWS_SPLIT;      // warps that share a tile
+constexpr int kRowTeams = 7;                  // tiles in flight per CTA (one 32 KB stage each)
+constexpr int kRowWarps = kRowTeams * kRowSplit;
+constexpr int kRowAhead = kRowSplit == 1 ? 3 : 2; // word-columns of planes in flight per warp
+__device__ __forceinline__ void team_sync(int team)
+{
+    if (kRowSplit == 1)
+        __syncwarp();
+    else
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + team), "n"(32 * kRowSplit) : "memory");
+}
 constexpr int kRowStageBytes = kTile * 32; // the 32-byte parity rows of one tile
-constexpr int kRowSmem = kRowWarps * kRowStageBytes;
+constexpr int kRowSmem = kRowTeams * kRowStageBytes;
 
 struct RowArgs {
     const uint32_t *parplanes;
@@ -863,22 +876,27 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
 {
     constexpr int KW = NR / 4;  // words per row
     constexpr int RPS = 32 / KW; // rows per copy-out step
+    constexpr int CPW = KW / kRowSplit > 0 ? KW / kRowSplit : 1; // word-columns a warp of the team transposes
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t stage = smem_u32(smem_raw) + (uint32_t)(warp * kRowStageBytes);
-    for (size_t tile = (size_t)blockIdx.x * kRowWarps + (size_t)warp; tile < A.ntiles; tile += (size_t)gridDim.x * kRowWarps) {
+    // kRowSplit warps share a tile (and its stage): each transposes its share of the word-columns, then copies out its
+    // share of the rows; they meet at a named barrier of their own.  Twice the warps per SM for the same shared memory.
+    const int team = warp / kRowSplit, part = warp % kRowSplit;
+    const uint32_t stage = smem_u32(smem_raw) + (uint32_t)(team * kRowStageBytes);
+    for (size_t tile = (size_t)blockIdx.x * kRowTeams + (size_t)team; tile < A.ntiles; tile += (size_t)gridDim.x * kRowTeams) {
         const uint32_t *pp = A.parplanes + tile * kTilePlaneWords;
         // planes -> bytes: word-column w = parity bytes 4 w .. 4 w + 3 of the lane-slot's 32 codewords.  The planes of
-        // columns w + 1 .. w + 3 are in flight while column w is transposed (one transpose is ~0.5 us, a DRAM read
-        // under load more than 1 us, and a CTA has only six warps to hide it behind).
-        uint4 nx[3][8];
+        // the next columns are in flight while column w is transposed (one transpose is ~0.5 us, a DRAM read under
+        // load more than 1 us).
+        const int w0 = KW >= kRowSplit ? part * CPW : 0, w1 = KW >= kRowSplit ? w0 + CPW : (part == 0 ? KW : 0);
+        uint4 nx[kRowAhead][8];
 #pragma unroll
-        for (int d = 0; d < 3; d++)
+        for (int d = 0; d < kRowAhead; d++)
 #pragma unroll
             for (int q = 0; q < 8; q++)
-                nx[d][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * (d < KW ? d : KW - 1) + q) * 32 + (size_t)lane) * 4);
+                nx[d][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * (w0 + d < KW ? w0 + d : KW - 1) + q) * 32 + (size_t)lane) * 4);
 #pragma unroll 1
-        for (int w = 0; w < KW; w++) {
+        for (int w = w0; w < w1; w++) {
             uint32_t X[32];
 #pragma unroll
             for (int q = 0; q < 8; q++) {
@@ -887,19 +905,20 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
                 X[4 * q + 2] = nx[0][q].z;
                 X[4 * q + 3] = nx[0][q].w;
             }
-            const int wn = w + 3 < KW ? w + 3 : KW - 1;
+            const int wn = w + kRowAhead < KW ? w + kRowAhead : KW - 1;
 #pragma unroll
             for (int q = 0; q < 8; q++) {
-                nx[0][q] = nx[1][q];
-                nx[1][q] = nx[2][q];
-                nx[2][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * wn + q) * 32 + (size_t)lane) * 4);
+#pragma unroll
+                for (int d = 0; d + 1 < kRowAhead; d++)
+                    nx[d][q] = nx[d + 1][q];
+                nx[kRowAhead - 1][q] = *reinterpret_cast<const uint4 *>(pp + ((size_t)(8 * wn + q) * 32 + (size_t)lane) * 4);
             }
             transpose32(X);
 #pragma unroll
             for (int i = 0; i < 32; i++)
                 sts32(stage + row_word((uint32_t)lane, (uint32_t)i, (uint32_t)w), X[i]);
         }
-        __syncwarp();
+        team_sync(team);
         // rows out.  A parity row inside a packed record covers two 32-byte sectors partially; the L2 merges partial
         // writes (a fill from DRAM per sector), which costs 2-3x the time of aligned contiguous rows (tools/
         // enc_probe.py).  Tried and slower: merging in the SM by read-modify-write of the two-sector window (0.59 ms
@@ -918,8 +937,9 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
             const uint32_t left2 = A.n - cwt2 >= (size_t)kTile ? (uint32_t)kTile : (uint32_t)(A.n - cwt2);
             constexpr uint32_t RPI = 32 / NR; // rows per instruction
             const uint32_t rsub = (uint32_t)lane / NR, b = (uint32_t)lane % NR;
+            constexpr uint32_t span = (uint32_t)kTile / kRowSplit;
 #pragma unroll 1
-            for (uint32_t r0 = 0; r0 < (uint32_t)kTile; r0 += 8 * RPI) {
+            for (uint32_t r0 = (uint32_t)part * span; r0 < ((uint32_t)part + 1u) * span; r0 += 8 * RPI) {
                 uint32_t v[8];
 #pragma unroll
                 for (uint32_t u = 0; u < 8; u++) {
@@ -933,7 +953,7 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
                         A.parity[(cwt2 + r) * A.pstride + b] = (uint8_t)v[u];
                 }
             }
-            __syncwarp();
+            team_sync(team);
             continue;
         }
         const size_t cwt = tile * kTile;
@@ -945,7 +965,7 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
             const uint32_t sel = 0x3210u + 0x1111u * (4u - a); // bytes 4 - a .. 7 - a of (previous word, this word)
             const bool inner = a == 0 || k != 0;
 #pragma unroll 1
-            for (uint32_t it0 = 0; it0 < 256 / RPS; it0 += 8) {
+            for (uint32_t it0 = (uint32_t)part * (256 / RPS / kRowSplit); it0 < ((uint32_t)part + 1u) * (256 / RPS / kRowSplit); it0 += 8) {
                 uint32_t cur[8], prv[8];
 #pragma unroll
                 for (uint32_t u = 0; u < 8; u++) { // all sixteen loads first, then the stores
@@ -984,7 +1004,7 @@ __global__ void __launch_bounds__(32 * kRowWarps, 1) rs255_rows_kernel(RowArgs A
                 }
             }
         }
-        __syncwarp();
+        team_sync(team);
     }
 }
 
@@ -1171,7 +1191,7 @@ int rs255_fft_encode(poporon_cuda_rs *ctx, const FftShape &shape, const uint8_t 
     R.parity = parity;
     R.pstride = parity_stride;
     R.bytewise = (((uintptr_t)parity | parity_stride) & 3u) != 0;
-    const size_t ctas = (ntiles + kRowWarps - 1) / kRowWarps;
+    const size_t ctas = (ntiles + kRowTeams - 1) / kRowTeams;
     const unsigned grid = (unsigned)(ctas < (size_t)ctx->sm_count ? ctas : (size_t)ctx->sm_count);
     ProfScope prof(ctx, PROF_ROWS, stream);
     if (shape.npar == 32)

@@ -10,8 +10,8 @@ while [ $# -ge 2 ]; do
   OUT=$ROOT/build/variants/$NAME
   mkdir -p $OUT
   /usr/local/cuda/bin/nvcc -O3 -std=c++17 -lineinfo --expt-relaxed-constexpr -gencode arch=compute_100a,code=sm_100a \
-    -Xcompiler -fPIC -I$ROOT/include -I. $FLAGS -Xptxas -v -c rs255.cu -o $OUT/rs255.o 2> $OUT/ptxas.txt
-  grep -A2 "rs255_solve_kernel" $OUT/ptxas.txt | grep -E "registers|spill" | sed "s/^/[$NAME] /"
-  OBJS=$(ls $ROOT/build/cuda/*.o | grep -v -E "/(rs255|synth)\.o")
-  /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $OUT/libpoporon_cuda.so $OBJS $OUT/rs255.o -cudart static
+    -Xcompiler -fPIC -I$ROOT/include -I. $FLAGS -Xptxas -v -c ${FILE:-rs255}.cu -o $OUT/${FILE:-rs255}.o 2> $OUT/ptxas.txt
+  grep -A2 "${KERNEL:-rs255_solve_kernel}" $OUT/ptxas.txt | grep -E "registers|spill" | sed "s/^/[$NAME] /"
+  OBJS=$(ls $ROOT/build/cuda/*.o | grep -v -E "/(${FILE:-rs255}|synth)\.o")
+  /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $OUT/libpoporon_cuda.so $OBJS $OUT/${FILE:-rs255}.o -cudart static
 done
