@@ -1,0 +1,126 @@
+// rs255_erasure_core.h — bitsliced erasure-only decoding for RS(255,223)/0x11D, fcr = 1, prim = 1.
+//
+// Replaces the reference's error_correction_u8 (src/decode.c:17-230) for rows of erasure mode whose errors all sit
+// on the declared erasure positions - whatever their number (1 .. 32).  For such a row the reference's path is:
+//   locator initialised to Gamma(x) = prod (1 - X_i x) over the declared positions (src/decode.c:31-47);
+//   Berlekamp-Massey from r = count + 1 finds every discrepancy zero and changes nothing (:51-96);
+//   the Chien search finds the declared positions, in ascending order of location (:112-145);
+//   omega = S * Gamma mod x^count (:147-158), Forney (:159-191), the re-syndrome check passes (:193-209), and the
+//   i-th root's magnitude goes to the i-th declared slot (:211-214) - the root's own position when the declared
+//   positions are strictly ascending.
+// The discrepancy of iteration r is the coefficient r - 1 of the same product S * Gamma, so one triangular product
+//   P_n = sum_{j <= n} Gamma_j S_(n-j+1),  n = 0 .. 31
+// gives both: P_0 .. P_(count-1) is omega, and the row qualifies exactly when P_count .. P_31 all vanish.  For a
+// qualifying row those are zero, and so are Gamma's coefficients above count: the Horner chains of Forney's formula
+// can run over all 32 coefficients for every codeword of a lane alike.  No Berlekamp-Massey, no Chien search.
+//
+// 32 codewords per thread on bit-planes, as in rs255_solve_core.h (whose helpers this uses); plain C++, so that the
+// same code runs on the host for tests (tests/native/host_solver.cpp).
+#pragma once
+#include "rs255_solve_core.h"
+
+namespace bs {
+
+constexpr int kES = 32;            // erasure slots per codeword
+constexpr int kWordsG = 8 * 33;    // Gamma_0 .. Gamma_32
+constexpr int kWordsP = 8 * 32;    // P_0 .. P_31
+constexpr int kWordsEL = 8 * 32;   // slot lists: word 8 c + w = slots 4 w .. 4 w + 3 of codeword c, a byte each:
+                                   // location + 1 (location = position + padding), 0 = slot not declared
+constexpr int kActBase = 32;       // words 32 .. 63 of the work area: act[i] bit c = slot i of codeword c is declared
+
+// the elements tab[list byte] of slots 4 w .. 4 w + 3 as planes in words 0 .. 31 of S (word 8 y + t = plane t of slot y)
+template <int STRIDE, int SO>
+BS_FN void stage_slots(const Mem<SO> EL, const Mem<STRIDE> S, int w, const uint8_t *tab)
+{
+    uint32_t X[32];
+#pragma unroll
+    for (int c = 0; c < 32; c++) {
+        const uint32_t v = EL.ld(8 * c + w);
+        X[c] = (uint32_t)tab[v & 0xFFu] | ((uint32_t)tab[(v >> 8) & 0xFFu] << 8) |
+               ((uint32_t)tab[(v >> 16) & 0xFFu] << 16) | ((uint32_t)tab[v >> 24] << 24);
+    }
+    transpose32(X);
+#pragma unroll
+    for (int p = 0; p < 32; p++)
+        S.st(p, X[p]);
+}
+
+// Gamma(x) = prod over the declared slots of (1 + X_i x), X_i = alpha^(254 - location) = inv_tab[list byte]
+// (inv_tab[0] = 0: an undeclared slot multiplies by 1).  G: 33 word blocks.  One factor at a time: Gamma_k +=
+// X_i Gamma_(k-1), k = i + 1 .. 1, on the eight held multiples of X_i.
+template <int STRIDE, int SO>
+BS_FN void erasure_locator(const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> S, const uint8_t *inv_tab)
+{
+#pragma unroll 1
+    for (int k = 0; k <= kES; k++)
+#pragma unroll
+        for (int t = 0; t < 8; t++)
+            G.st(8 * k + t, (k == 0 && t == 0) ? 0xFFFFFFFFu : 0u);
+#pragma unroll 1
+    for (int w = 0; w < kES / 4; w++) {
+        stage_slots<STRIDE, SO>(EL, S, w, inv_tab);
+#pragma unroll 1
+        for (int y = 0; y < 4; y++) {
+            const int i = 4 * w + y;
+            uint32_t X[8], xm[8][8], lo[8];
+            ld8(S, y, X);
+            S.st(kActBase + i, or8(X));
+            xmultiples(X, xm);
+            ld8(G, i, lo); // Gamma_(k-1) of the first step
+#pragma unroll 1
+            for (int k = i + 1; k >= 1; k--) {
+                uint32_t gk[8], nxt[8];
+                ld8(G, k, gk);
+                ld8(G, k >= 2 ? k - 2 : 0, nxt); // (read before step k - 1 rewrites Gamma_(k-1))
+#pragma unroll
+                for (int t = 0; t < 8; t++) {
+                    uint32_t a = gk[t];
+#pragma unroll
+                    for (int q = 0; q < 8; q++)
+                        a ^= lo[q] & xm[q][t];
+                    gk[t] = a;
+                }
+                st8(G, k, gk);
+                cp8(lo, nxt);
+            }
+        }
+    }
+}
+
+// bit c set: codeword c does NOT qualify (some P_n with n >= its declared count is non-zero)
+template <int STRIDE, int SO>
+BS_FN uint32_t erasure_residue(const Mem<SO> P, const Mem<STRIDE> S)
+{
+    uint32_t bad = 0;
+#pragma unroll 1
+    for (int n = 0; n < kES; n++) {
+        uint32_t p[8];
+        ld8(P, n, p);
+        bad |= or8(p) & ~S.ld(kActBase + n);
+    }
+    return bad;
+}
+
+// Everything up to the magnitudes' inputs: Gamma into G, P into P (= omega below the declared count); returns the
+// mask of codewords that do not qualify.  Syn: the 32 syndromes as planes (word 8 m + t = plane t of S_(m+1)).
+template <int STRIDE, int SO>
+BS_FN uint32_t erasure_lane(const Mem<SO> Syn, const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, const Mem<STRIDE> S,
+                            const uint8_t *inv_tab)
+{
+    erasure_locator<STRIDE, SO>(EL, G, S, inv_tab);
+    omega_parked<SO, SO>(Syn, G, P, kES);
+    return erasure_residue<STRIDE, SO>(P, S);
+}
+
+// Magnitudes of slots 4 w .. 4 w + 3: afterwards words 8 y .. 8 y + 7 of S hold the magnitude planes of slot 4 w + y
+// (magnitude_words() turns them into one word per codeword), cnt (6 bit-planes) has counted the non-zero ones.
+// root_tab[list byte] = alpha^(location + 1), the root of Gamma that belongs to the slot.
+template <int STRIDE, int SO>
+BS_FN void erasure_forney(const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, const Mem<STRIDE> S, int w,
+                          const uint8_t *root_tab, uint32_t (&cnt)[6])
+{
+    stage_slots<STRIDE, SO>(EL, S, w, root_tab);
+    forney_math<STRIDE, SO, 6>(G, P, S, cnt, kES);
+}
+
+} // namespace bs

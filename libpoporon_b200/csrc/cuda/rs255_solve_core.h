@@ -1100,12 +1100,12 @@ BS_FN void mul_add_tab(uint32_t (&v)[8], const uint32_t (&mm)[8][8], const uint3
     cp8(v, r);
 }
 
+template <int STRIDE, int SO, int NC>
+BS_FN void forney_math(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, uint32_t (&cnt)[NC], int teff);
 template <int STRIDE, int SO>
 BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, int w,
                         const uint8_t *root_tab /* [0] = 0, [v] = alpha^v */, uint32_t (&cnt)[5], int teff = kT)
 {
-    // teff = ns / 2 (16, 8 or 4): Omega has teff coefficients and the locator degree is <= teff, so the two Horner
-    // chains start there
     {
         uint32_t X[32];
 #pragma unroll
@@ -1119,6 +1119,15 @@ BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, 
         for (int p = 0; p < 32; p++)
             S.st(p, X[p]);
     }
+    forney_math<STRIDE, SO, 5>(LM, O, S, cnt, teff);
+}
+// The roots of four slots are staged as planes in words 0 .. 31 of S (word 8 y + t = plane t of slot y); cnt: NC
+// bit-planes counting the non-zero magnitudes.
+template <int STRIDE, int SO, int NC>
+BS_FN void forney_math(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, uint32_t (&cnt)[NC], int teff)
+{
+    // teff = ns / 2 (16, 8 or 4; 32 for the erasure form): Omega has teff coefficients and the locator's highest odd
+    // coefficient is teff - 1, so the two Horner chains start there
 #if BS_FORNEY_TABLES
     // Both Horner chains of a slot multiply by the same element at every step (x, then x^2): with its eight multiples
     // x * alpha^s held as planes a step is 64 AND-XOR, the coefficient folded into the first of them and nothing to
@@ -1253,7 +1262,7 @@ BS_FN void forney_slots(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, 
         st8(S, y, mag);
         uint32_t m = or8(mag);
 #pragma unroll
-        for (int b = 0; b < 5; b++) {
+        for (int b = 0; b < NC; b++) {
             const uint32_t t = cnt[b] & m;
             cnt[b] ^= m;
             m = t;

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include "rs255_solve_core.h"
+#include "rs255_erasure_core.h"
 
 static int host_solve_ns(const uint8_t *syn, size_t n, int pad, int ns, int8_t *status, uint8_t *nroots, uint16_t *lists);
 
@@ -64,6 +65,54 @@ static int host_solve_ns(const uint8_t *syn, size_t n, int pad, int ns, int8_t *
             }
         }
         (void)nzc;
+    }
+    return 0;
+}
+
+// Erasure-only form (rs255_erasure_core.h): lists[n][32] = location + 1 of every declared slot (0 = none), ascending.
+// bad[i] = 1: the row does not qualify (errors outside the declared slots); else mags[i][slot] = the magnitudes and
+// count[i] = the number of non-zero ones.
+extern "C" int host_erasure(const uint8_t *syn /* [n][32] */, const uint8_t *lists /* [n][32] */, size_t n, int8_t *bad,
+                            uint8_t *mags /* [n][32] */, uint8_t *count /* [n] */)
+{
+    uint8_t root_tab[256], inv_tab[256];
+    root_tab[0] = inv_tab[0] = 0;
+    for (int v = 1; v < 256; v++) {
+        root_tab[v] = gf256::pow_alpha(v);
+        inv_tab[v] = gf256::pow_alpha((255 - v) % 255);
+    }
+    for (size_t g = 0; g < n; g += 32) {
+        static uint32_t Syn[bs::kWordsS], EL[bs::kWordsEL], G[bs::kWordsG], P[bs::kWordsP], S[bs::kWordsW];
+        memset(Syn, 0, sizeof Syn);
+        memset(EL, 0, sizeof EL);
+        memset(S, 0, sizeof S);
+        const size_t cnt = n - g < 32 ? n - g : 32;
+        for (size_t c = 0; c < cnt; c++) {
+            for (int m = 0; m < 32; m++)
+                for (int t = 0; t < 8; t++)
+                    if ((syn[(g + c) * 32 + m] >> t) & 1)
+                        Syn[8 * m + t] |= 1u << c;
+            for (int e = 0; e < 32; e++)
+                EL[8 * c + (e >> 2)] |= (uint32_t)lists[(g + c) * 32 + e] << (8 * (e & 3));
+        }
+        const bs::Mem<1> Synm{Syn}, ELm{EL}, Gm{G}, Pm{P}, Sm{S};
+        const uint32_t badmask = bs::erasure_lane<1, 1>(Synm, ELm, Gm, Pm, Sm, inv_tab);
+        uint32_t nz[6] = {0, 0, 0, 0, 0, 0};
+        for (int w = 0; w < 8; w++) {
+            bs::erasure_forney<1, 1>(ELm, Gm, Pm, Sm, w, root_tab, nz);
+            uint32_t X[32];
+            bs::magnitude_words<1>(Sm, X);
+            for (size_t c = 0; c < cnt; c++)
+                for (int y = 0; y < 4; y++)
+                    mags[(g + c) * 32 + 4 * w + y] = (uint8_t)(X[c] >> (8 * y));
+        }
+        for (size_t c = 0; c < cnt; c++) {
+            bad[g + c] = (int8_t)((badmask >> c) & 1u);
+            unsigned k = 0;
+            for (int b = 0; b < 6; b++)
+                k |= ((nz[b] >> c) & 1u) << b;
+            count[g + c] = (uint8_t)k;
+        }
     }
     return 0;
 }

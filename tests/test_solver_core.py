@@ -140,3 +140,58 @@ def test_solver_core_16_and_8_roots(solver):
         assert declined == 0 and dirty > 400
         run_case(solver, orc, rng, 640, 255 - nr, nr // 2, nr + 4, nr)
         run_case(solver, orc, rng, 256, 100, 0, nr // 2 + 2, nr)
+
+
+def test_erasure_core(solver):
+    """Erasure-only form (rs255_erasure_core.h) against the oracle's erasure mode: rows whose errors all sit on the
+    declared, ascending positions give the reference's magnitudes and count; rows with an error elsewhere are
+    flagged as not qualifying."""
+    from oraclelib import MODE_ERASURE
+
+    orc = Oracle("port")
+    rng = np.random.default_rng(15)
+    P = C.POINTER
+    solver.host_erasure.argtypes = [P(C.c_uint8), P(C.c_uint8), C.c_size_t, P(C.c_int8), P(C.c_uint8), P(C.c_uint8)]
+    for size in (223, 100, 33):
+        n = 320
+        pad = 223 - size
+        msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+        par = orc.rs_encode(msg)
+        cw = np.concatenate([msg, par], 1)
+        pos = np.zeros((n, 32), np.uint32)
+        cnt = np.zeros(n, np.uint32)
+        lists = np.zeros((n, 32), np.uint8)
+        stray = np.zeros(n, bool)
+        for i in range(n):
+            f = int(rng.integers(1, min(32, size) + 1))
+            p = np.sort(rng.choice(size, f, replace=False))
+            pos[i, :f], cnt[i] = p, f
+            lists[i, :f] = p + pad + 1
+            cw[i, p] ^= rng.integers(0, 256, f, dtype=np.uint8)  # (zero magnitudes allowed)
+            if rng.random() < 0.3:  # an error the caller did not declare, anywhere in the codeword
+                others = np.setdiff1d(np.arange(size + 32), p)
+                q = rng.choice(others, int(rng.integers(1, 3)), replace=False)
+                cw[i, q] ^= rng.integers(1, 256, len(q), dtype=np.uint8)
+                stray[i] = True
+        wd, wp, wok, wcor = orc.rs_decode(cw[:, :size], cw[:, size:], mode=MODE_ERASURE, pos=pos, cnt=cnt)
+        syn = np.ascontiguousarray(syndromes(cw))
+        bad = np.zeros(n, np.int8)
+        mags = np.zeros((n, 32), np.uint8)
+        count = np.zeros(n, np.uint8)
+        solver.host_erasure(syn.ctypes.data_as(P(C.c_uint8)), lists.ctypes.data_as(P(C.c_uint8)), n,
+                            bad.ctypes.data_as(P(C.c_int8)), mags.ctypes.data_as(P(C.c_uint8)),
+                            count.ctypes.data_as(P(C.c_uint8)))
+        # A row qualifies exactly when the reference's Berlekamp-Massey would see only zero discrepancies, i.e. when it
+        # leaves the erasure locator alone: then the reference's result IS these magnitudes at the declared positions,
+        # also in the rare rows where an undeclared error goes unnoticed (32 declared positions explain any syndromes).
+        good = np.nonzero(~stray)[0]
+        assert (bad[good] == 0).all(), "a row without undeclared errors did not qualify"
+        assert bad[stray].mean() > 0.9
+        for i in np.nonzero(bad == 0)[0]:
+            f = int(cnt[i])
+            assert wok[i] == 1, i
+            fixed = cw[i, :size].copy()
+            fixed[pos[i, :f]] ^= mags[i, :f]
+            assert (mags[i, f:] == 0).all()
+            assert (fixed == wd[i]).all() and (cw[i, size:] == wp[i]).all(), i
+            assert count[i] == wcor[i] == np.count_nonzero(mags[i, :f]), (i, count[i], wcor[i])
