@@ -34,6 +34,7 @@
 #include "gf256_consts.cuh"
 #include "rs_correct.cuh"
 #include "rs255_solve_core.h"
+#include "rs255_erasure_core.h"
 #include "rs255_fft.cuh"
 #include <stdlib.h>
 
@@ -1329,6 +1330,164 @@ rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restr
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Erasure mode, bitsliced (rs255_erasure_core.h): every queued row whose declared positions are regular (1 .. 32 of
+// them, strictly ascending, inside the message) and whose syndromes are explained by errors ON those positions - the
+// reference's Berlekamp-Massey would see only zero discrepancies - is finished here, corrections included; everything
+// else goes to queue2 for the literal stage with its raw syndromes untouched.  Same shape as the solver kernel: a lane
+// owns 32 queue entries, a warp's scratch (syndrome planes, Gamma, S * Gamma, slot lists) sits in the L2-resident
+// scratch, the 200-word work area in shared memory.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kEraScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsP + bs::kWordsEL + 32;
+constexpr int kEraSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 512; // work areas + the two tables
+__global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, 1)
+rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+                     const uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2,
+                     uint32_t *__restrict__ counter2, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected,
+                     uint8_t *data, size_t data_stride, const uint32_t *__restrict__ era_pos, size_t era_stride,
+                     const uint32_t *__restrict__ era_cnt)
+{
+    extern __shared__ __align__(16) uint32_t solve_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t gw = blockIdx.x * kSolveWarpsPerCTA + (uint32_t)warp, nw = gridDim.x * kSolveWarpsPerCTA;
+    const bs::Mem<32> S{solve_smem + warp * (bs::kWordsW * 32) + lane};
+    uint32_t *gs = scratch + (size_t)gw * (kEraScratchWords * 32) + lane;
+    const bs::Mem<32> Syn{gs};
+    const bs::Mem<32> G{gs + bs::kWordsS * 32};
+    const bs::Mem<32> P{gs + (bs::kWordsS + bs::kWordsG) * 32};
+    const bs::Mem<32> EL{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsP) * 32};
+    const bs::Mem<32> Qs{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsP + bs::kWordsEL) * 32};
+    // root_tab[v] = alpha^v (the root of Gamma that belongs to list byte v = location + 1), inv_tab[v] = alpha^(255 - v)
+    // (the X of that location); [0] = 0 in both: an undeclared slot
+    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWarpsPerCTA * bs::kWordsW * 32);
+    uint8_t *inv_tab = root_tab + 256;
+    {
+        uint32_t x = 1;
+        for (int i = 0; i < 8 * lane; i++) {
+            x <<= 1;
+            if (x & 0x100u)
+                x ^= gf256::kPoly;
+        }
+        for (int i = 8 * lane; i < 8 * lane + 8; i++) { // x = alpha^i
+            if (i != 0) {
+                root_tab[i] = (uint8_t)x;
+                if (i != 255)
+                    inv_tab[255 - i] = (uint8_t)x;
+            }
+            x <<= 1;
+            if (x & 0x100u)
+                x ^= gf256::kPoly;
+        }
+        if (lane == 0) {
+            root_tab[0] = 0;
+            inv_tab[0] = 0;
+            inv_tab[255] = 1; // alpha^0
+        }
+    }
+    __syncthreads(); // (every warp wrote the same tables)
+    const uint32_t total = *counter;
+    const int pad = 255 - 32 - (int)size;
+    const uint32_t rounds = (total + nw * 1024u - 1u) / (nw * 1024u);
+    for (uint32_t it = 0; it < rounds; it++) {
+        const uint32_t g0 = (it * nw + gw) * 1024u;
+        if (g0 < total) {
+            {
+                uint32_t ent[32];
+#pragma unroll
+                for (int c = 0; c < 32; c++) {
+                    const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
+                    ent[c] = q < total ? queue[q] : 0xFFFFFFFFu;
+                }
+#pragma unroll
+                for (int c = 0; c < 32; c++)
+                    Qs.st(c, ent[c]);
+                solve_load_syndromes(ent, syn_raw, Syn);
+            }
+            // the declared positions of every codeword -> slot lists (location + 1 per byte); regular rows only
+            uint32_t regular = 0, present = 0;
+            int maxf = 0;
+#pragma unroll 1
+            for (int c = 0; c < 32; c++) {
+                const uint32_t entry = Qs.ld(c);
+                uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                bool good = false;
+                if (entry != 0xFFFFFFFFu) {
+                    present |= 1u << c;
+                    const size_t cw = entry & 0x3FFFFFFFu;
+                    const uint32_t f = era_cnt[cw];
+                    const uint32_t *row = era_pos + cw * era_stride;
+                    good = f >= 1u && f <= 32u;
+                    int prev = -1;
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const uint32_t pj = __ldg(row + j); // (every slot is defined by the caller, include/poporon_cuda.h)
+                        const bool act = (uint32_t)j < f;
+                        good = good && (!act || (pj < (uint32_t)size && (int)pj > prev));
+                        prev = act ? (int)pj : prev;
+                        const uint32_t v = act ? ((pj + (uint32_t)pad + 1u) & 0xFFu) : 0u;
+                        w[j >> 2] |= v << (8 * (j & 3));
+                    }
+                    if (good)
+                        maxf = (int)f > maxf ? (int)f : maxf;
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    EL.st(8 * c + k, good ? w[k] : 0u);
+                regular |= good ? 1u << c : 0u;
+            }
+            const uint32_t bad = bs::erasure_lane<32, 32>(Syn, EL, G, P, S, inv_tab);
+            const uint32_t accept = regular & ~bad;
+            // what does not qualify goes to the literal stage
+#pragma unroll 1
+            for (int c = 0; c < 32; c++)
+                if (((present & ~accept) >> c) & 1u)
+                    queue2[atomicAdd(counter2, 1u)] = Qs.ld(c);
+            uint32_t nz[6] = {0u, 0u, 0u, 0u, 0u, 0u};
+#pragma unroll 1
+            for (int w = 0; w < 8; w++) {
+                if (!__any_sync(0xFFFFFFFFu, accept != 0u && maxf > 4 * w))
+                    break;
+                bs::erasure_forney<32, 32>(EL, G, P, S, w, root_tab, nz);
+                uint32_t X[32];
+                bs::magnitude_words<32>(S, X);
+#pragma unroll
+                for (int c = 0; c < 32; c++) {
+                    if (!((accept >> c) & 1u) || X[c] == 0u)
+                        continue;
+                    const size_t cw = Qs.ld(c) & 0x3FFFFFFFu;
+                    const uint32_t lw = EL.ld(8 * c + w);
+                    const uintptr_t base = (uintptr_t)data + cw * data_stride - (size_t)(1 + pad);
+#pragma unroll
+                    for (int y = 0; y < 4; y++) {
+                        const uint32_t mag = (X[c] >> (8 * y)) & 0xFFu;
+                        if (mag) {
+                            const uintptr_t a = base + ((lw >> (8 * y)) & 0xFFu);
+                            asm volatile("red.relaxed.gpu.global.xor.b32 [%0], %1;" ::"l"(a & ~(uintptr_t)3),
+                                         "r"(mag << (8u * (unsigned)(a & 3u)))
+                                         : "memory");
+                        }
+                    }
+                }
+            }
+#pragma unroll 1
+            for (int c = 0; c < 32; c++) {
+                if (!((accept >> c) & 1u))
+                    continue;
+                const size_t cw = Qs.ld(c) & 0x3FFFFFFFu;
+                uint32_t k = 0;
+#pragma unroll
+                for (int b = 0; b < 6; b++)
+                    k |= ((nz[b] >> c) & 1u) << b;
+                if (ok)
+                    ok[cw] = 1;
+                if (corrected)
+                    corrected[cw] = k;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Caller-supplied syndromes (reference src/decode.c:446-464: index form, nn = zero) -> the raw syndrome rows and the
 // dirty queue the solver and the general stage work from.  A word is dirty when any entry differs from nn, as in
 // the reference; entries above nn cannot index the reference's tables and are taken as zero (rs_generic.cu does
@@ -1425,7 +1584,7 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64 + n) * sizeof(uint32_t)));
     // raw syndrome rows / error records [tiles * 1024][32 B] | solver scratch, one slab per resident solver warp
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32 + (size_t)ctx->sm_count * kSolveWarpsPerSM *
-                                                                          kSolveScratchWords * 128));
+                                                                          (kSolveScratchWords > kEraScratchWords ? kSolveScratchWords : kEraScratchWords) * 128));
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, 64));
     ctx->queue_cap = n;
     return 0;
@@ -1473,6 +1632,11 @@ int rs255_init(poporon_cuda_rs *ctx)
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_lfsr_kernel<MODE_SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      kPairs * kSmemScreen));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
+    PP_CUDA_TRY(cudaFuncSetAttribute(rs255_erasure_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEraSmem));
+    {
+        const char *e = getenv("PP_RS255_NO_ERASURE_KERNEL"); // A/B: erasure mode on the plain solver + the literal stage only
+        ctx->no_erasure_kernel = e && e[0] == '1';
+    }
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_correct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCorrectSmem));
     {
         int v = 0;
@@ -1647,7 +1811,15 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         const size_t groups = (n + 1023) / 1024;
         const size_t cap = (size_t)ctx->sm_count * kSolveWarpsPerSM;
         uint32_t *scratch = reinterpret_cast<uint32_t *>(ctx->d_rem + tiles * kTile * 32);
-        {
+        if (mode == POPORON_CUDA_MODE_ERASURE && nr == 32 && pos_stride >= 32 && !ctx->no_erasure_kernel) {
+            // erasure mode: the erasure-only kernel takes every regular row whose errors sit on its declared positions
+            ProfScope prof(ctx, PROF_SOLVE, stream);
+            const size_t warps = groups < cap ? groups : cap;
+            rs255_erasure_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
+                                   kEraSmem, stream>>>(size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2,
+                                                       ctx->d_counters + 1, ok, corrected, data, data_stride, pos,
+                                                       pos_stride, cnt);
+        } else {
             ProfScope prof(ctx, PROF_SOLVE, stream);
             const size_t warps = groups < cap ? groups : cap;
             rs255_solve_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
