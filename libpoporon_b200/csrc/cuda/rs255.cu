@@ -1386,6 +1386,7 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
     __syncthreads(); // (every warp wrote the same tables)
     const uint32_t total = *counter;
     const int pad = 255 - 32 - (int)size;
+    const bool vec_rows = (((uintptr_t)era_pos | (era_stride * 4u)) & 15u) == 0;
     const uint32_t rounds = (total + nw * 1024u - 1u) / (nw * 1024u);
     for (uint32_t it = 0; it < rounds; it++) {
         const uint32_t g0 = (it * nw + gw) * 1024u;
@@ -1417,9 +1418,26 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
                     const uint32_t *row = era_pos + cw * era_stride;
                     good = f >= 1u && f <= 32u;
                     int prev = -1;
+                    // (every slot is defined by the caller, include/poporon_cuda.h: all 32 are read, as quad-words when
+                    // the rows allow)
+                    uint32_t pv[32];
+                    if (vec_rows) {
+#pragma unroll
+                        for (int j = 0; j < 8; j++) {
+                            const uint4 q = __ldg(reinterpret_cast<const uint4 *>(row) + j);
+                            pv[4 * j] = q.x;
+                            pv[4 * j + 1] = q.y;
+                            pv[4 * j + 2] = q.z;
+                            pv[4 * j + 3] = q.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; j++)
+                            pv[j] = __ldg(row + j);
+                    }
 #pragma unroll
                     for (int j = 0; j < 32; j++) {
-                        const uint32_t pj = __ldg(row + j); // (every slot is defined by the caller, include/poporon_cuda.h)
+                        const uint32_t pj = pv[j];
                         const bool act = (uint32_t)j < f;
                         good = good && (!act || (pj < (uint32_t)size && (int)pj > prev));
                         prev = act ? (int)pj : prev;
@@ -1449,20 +1467,28 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
                 bs::erasure_forney<32, 32>(EL, G, P, S, w, root_tab, nz);
                 uint32_t X[32];
                 bs::magnitude_words<32>(S, X);
+                // eight codewords per trip: their queue entries and list words (L2) are all on their way before the
+                // first correction leaves
+#pragma unroll 1
+                for (int c0 = 0; c0 < 32; c0 += 8) {
+                    uint32_t e8[8], l8[8];
 #pragma unroll
-                for (int c = 0; c < 32; c++) {
-                    if (!((accept >> c) & 1u) || X[c] == 0u)
-                        continue;
-                    const size_t cw = Qs.ld(c) & 0x3FFFFFFFu;
-                    const uint32_t lw = EL.ld(8 * c + w);
-                    const uintptr_t base = (uintptr_t)data + cw * data_stride - (size_t)(1 + pad);
+                    for (int u = 0; u < 8; u++) {
+                        e8[u] = Qs.ld(c0 + u);
+                        l8[u] = EL.ld(8 * (c0 + u) + w);
+                    }
 #pragma unroll
-                    for (int y = 0; y < 4; y++) {
-                        const uint32_t mag = (X[c] >> (8 * y)) & 0xFFu;
-                        if (mag) {
-                            const uintptr_t a = base + ((lw >> (8 * y)) & 0xFFu);
-                            asm volatile("red.relaxed.gpu.global.xor.b32 [%0], %1;" ::"l"(a & ~(uintptr_t)3),
-                                         "r"(mag << (8u * (unsigned)(a & 3u)))
+                    for (int u = 0; u < 8; u++) {
+                        const uint32_t xc = c0 == 0 ? X[u] : c0 == 8 ? X[8 + u] : c0 == 16 ? X[16 + u] : X[24 + u];
+                        if (!((accept >> (c0 + u)) & 1u) || xc == 0u)
+                            continue;
+                        const uintptr_t base = (uintptr_t)data + (size_t)(e8[u] & 0x3FFFFFFFu) * data_stride - (size_t)(1 + pad);
+#pragma unroll
+                        for (int y = 0; y < 4; y++) {
+                            const uintptr_t a = base + ((l8[u] >> (8 * y)) & 0xFFu);
+                            const uint32_t val = ((xc >> (8 * y)) & 0xFFu) << (8u * (unsigned)(a & 3u));
+                            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p red.relaxed.gpu.global.xor.b32 [%0], %1;\n\t}"
+                                         ::"l"(a & ~(uintptr_t)3), "r"(val)
                                          : "memory");
                         }
                     }

@@ -66,22 +66,28 @@ BS_FN void erasure_locator(const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> 
             ld8(S, y, X);
             S.st(kActBase + i, or8(X));
             xmultiples(X, xm);
-            ld8(G, i, lo); // Gamma_(k-1) of the first step
+            // step k: Gamma_k += X_i Gamma_(k-1).  The next step's Gamma_k is this step's Gamma_(k-1), still unchanged
+            // and in registers: one block is loaded per step, two steps ahead of its use.
+            uint32_t cur[8], nx1[8];
+            ld8(G, i + 1, cur);
+            ld8(G, i, lo);
+            ld8(G, i >= 1 ? i - 1 : 0, nx1);
 #pragma unroll 1
             for (int k = i + 1; k >= 1; k--) {
-                uint32_t gk[8], nxt[8];
-                ld8(G, k, gk);
-                ld8(G, k >= 2 ? k - 2 : 0, nxt); // (read before step k - 1 rewrites Gamma_(k-1))
+                uint32_t nx2[8];
+                ld8(G, k >= 3 ? k - 3 : 0, nx2); // Gamma_(k-3), the multiplicand of step k - 2
 #pragma unroll
                 for (int t = 0; t < 8; t++) {
-                    uint32_t a = gk[t];
+                    uint32_t a = cur[t];
 #pragma unroll
                     for (int q = 0; q < 8; q++)
                         a ^= lo[q] & xm[q][t];
-                    gk[t] = a;
+                    cur[t] = a;
                 }
-                st8(G, k, gk);
-                cp8(lo, nxt);
+                st8(G, k, cur);
+                cp8(cur, lo);
+                cp8(lo, nx1);
+                cp8(nx1, nx2);
             }
         }
     }

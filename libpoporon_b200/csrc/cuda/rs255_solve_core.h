@@ -1142,15 +1142,20 @@ BS_FN void forney_math(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, u
             xmultiples(x[y], xm[y]);
             cp8(v[y], o);
         }
+        // (the coefficients come from the L2: a step on held multiples is shorter than that round trip, so they are
+        // fetched two steps ahead)
+        uint32_t o1[8];
         ld8(O, teff - 2, o);
+        ld8(O, teff >= 3 ? teff - 3 : 0, o1);
 #pragma unroll 1
         for (int j = teff - 2; j >= 0; j--) {
             uint32_t on[8];
-            ld8(O, j > 0 ? j - 1 : 0, on);
+            ld8(O, j > 1 ? j - 2 : 0, on);
 #pragma unroll
             for (int y = 0; y < 2; y++)
                 mul_add_tab(v[y], xm[y], o);
-            cp8(o, on);
+            cp8(o, o1);
+            cp8(o1, on);
         }
         {
             const uint32_t z[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
@@ -1171,14 +1176,16 @@ BS_FN void forney_math(const Mem<SO> LM, const Mem<SO> O, const Mem<STRIDE> S, u
             cp8(v[y], o);
         }
         ld8(LM, teff - 3, o);
+        ld8(LM, teff >= 6 ? teff - 5 : 1, o1);
 #pragma unroll 1
         for (int j = teff - 3; j >= 1; j -= 2) {
             uint32_t on[8];
-            ld8(LM, j > 1 ? j - 2 : 1, on);
+            ld8(LM, j > 3 ? j - 4 : 1, on);
 #pragma unroll
             for (int y = 0; y < 2; y++)
                 mul_add_tab(v[y], xm[y], o);
-            cp8(o, on);
+            cp8(o, o1);
+            cp8(o1, on);
         }
 #pragma unroll
         for (int y = 0; y < 2; y++) {
