@@ -605,6 +605,59 @@ def test_single_api_null_and_size_rules(gpu_device):
         assert not ok and c == 0 and (rx == keep).all()
 
 
+@pytest.mark.parametrize("size", [223, 100, 32, 5])
+def test_erasure_kernel_edges(gpu_device, orc, size):
+    """rs255_erasure_kernel (erasure-only rows of erasure mode): counts 1 and 32, first / last message position,
+    shortened messages, zero magnitudes, position rows wider than 32 slots and at addresses that do not allow
+    quad-word loads, a batch that is not a multiple of the 1024-codeword tile; with duplicate, unsorted, empty
+    and undeclared-error rows mixed in (those go to the general stage)."""
+    rng = np.random.default_rng(1000 + size)
+    with api.Poporon.rs_default() as h:
+        # (the host pipeline puts the position rows behind n status bytes and n counts on the device: they are
+        # 16-byte aligned - the kernel's quad-word loads - for n = 3148 with strides 32 and 40, and not otherwise)
+        for n, stride, shift in ((3148, 32, 0), (3148, 40, 0), (3149, 32, 0), (3148, 33, 1)):
+            msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+            par = _gpu_encode(h, msg, 32)
+            cw = np.concatenate([msg, par], 1)
+            flat = np.zeros(n * stride + 4, np.uint32)
+            pos = flat[shift:shift + n * stride].reshape(n, stride)  # (shift = 1: rows at 4 mod 16)
+            cnt = np.zeros(n, np.uint32)
+            for i in range(n):
+                kind = i % 16
+                c = (1, min(32, size), int(rng.integers(1, min(32, size) + 1)))[i % 3]
+                pp = np.sort(rng.choice(size, c, replace=False))
+                if kind == 1:
+                    pp[0] = 0
+                    pp = np.unique(pp)
+                if kind == 2:
+                    pp[-1] = size - 1
+                    pp = np.unique(pp)
+                c = len(pp)
+                pos[i, :c], cnt[i] = pp, c
+                # slots beyond the count: anything INSIDE the message (the reference - and so the oracle - writes through
+                # them unchecked when a row has undeclared errors, src/decode.c:211-214)
+                pos[i, c:] = rng.integers(0, size, stride - c)
+                cw[i, pp] ^= rng.integers(0, 256, c, dtype=np.uint8)
+                if kind == 3 and c >= 2:  # unsorted
+                    pos[i, [0, c - 1]] = pos[i, [c - 1, 0]]
+                elif kind == 4 and c >= 2:  # duplicate
+                    pos[i, 1] = pos[i, 0]
+                elif kind == 6:  # undeclared error in the parity
+                    cw[i, size + int(rng.integers(0, 32))] ^= 0x80
+                elif kind == 7:  # undeclared error in the message
+                    cw[i, int(rng.integers(0, size))] ^= 0x01
+                elif kind == 8:  # nothing declared
+                    cnt[i] = 0
+            d = np.array(cw[:, :size], order="C")
+            p = np.array(cw[:, size:], order="C")
+            ok = np.full(n, 7, np.uint8)
+            cor = np.full(n, 0xFFFFFFFF, np.uint32)
+            assert h.decode_batch_erasure(d, size, size, p, 32, n, pos.ctypes.data, stride, cnt, ok, cor)
+            want = orc.rs_decode(cw[:, :size], cw[:, size:], RS_DEFAULT, MODE_ERASURE,
+                                 np.ascontiguousarray(pos), cnt)
+            _assert_same((d, p, ok, cor), want, f"erasure kernel size={size} n={n} stride={stride} shift={shift}")
+
+
 def test_single_api_erasure_object(gpu_device, orc):
     """reference tests/test_codec.c:123-168, tests/test_unified.c:82-112 and SURVEY B.6"""
     er = api.Erasure(32, 16)
