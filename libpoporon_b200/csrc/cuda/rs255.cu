@@ -1337,6 +1337,71 @@ rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restr
 // owns 32 queue entries, a warp's scratch (syndrome planes, Gamma, S * Gamma, slot lists) sits in the L2-resident
 // scratch, the 200-word work area in shared memory.
 // ---------------------------------------------------------------------------------------------------
+// The dirty queue ordered by declared count (a counting sort, 34 buckets): a lane's 32 codewords then declare about the
+// same number of positions, and the kernel's loops - locator build, S * Gamma, the Forney rounds - stop at the largest
+// count of the warp instead of running to 32 for everybody.
+constexpr int kEraBuckets = 34;   // counts 0 .. 32, 33 = anything larger
+constexpr int kCntHist = 32;      // counters: [0] dirty rows, [1] rows for the literal stage, [32, 66) histogram,
+constexpr int kCntCursor = 96;    //           [96, 130) bucket cursors
+constexpr int kCountersBytes = 1024;
+__global__ void __launch_bounds__(256) rs255_era_hist_kernel(const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+                                                             const uint32_t *__restrict__ era_cnt, uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t h[kEraBuckets];
+    if (threadIdx.x < kEraBuckets)
+        h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t total = *counter;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
+        const uint32_t f = era_cnt[queue[q] & 0x3FFFFFFFu];
+        atomicAdd(&h[f < 33u ? f : 33u], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < kEraBuckets && h[threadIdx.x])
+        atomicAdd(&hist[threadIdx.x], h[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256) rs255_era_scatter_kernel(const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+                                                                const uint32_t *__restrict__ era_cnt, const uint32_t *__restrict__ hist,
+                                                                uint32_t *__restrict__ cursor, uint32_t *__restrict__ out)
+{
+    __shared__ uint32_t start[kEraBuckets], local[kEraBuckets], base[kEraBuckets];
+    if (threadIdx.x < kEraBuckets) {
+        uint32_t s0 = 0;
+        for (int b = 0; b < (int)threadIdx.x; b++)
+            s0 += hist[b];
+        start[threadIdx.x] = s0;
+    }
+    const uint32_t total = *counter;
+    // chunks of 1024 queue entries per trip of the block: ranks inside the chunk from shared-memory counters, one
+    // reservation per bucket and chunk in the global cursors
+    for (uint32_t c0 = blockIdx.x * 1024u; c0 < total; c0 += gridDim.x * 1024u) {
+        if (threadIdx.x < kEraBuckets)
+            local[threadIdx.x] = 0;
+        __syncthreads();
+        uint32_t ent[4], bk[4], rk[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t q = c0 + (uint32_t)u * 256u + threadIdx.x;
+            bk[u] = 0xFFFFFFFFu;
+            if (q < total) {
+                ent[u] = queue[q];
+                const uint32_t f = era_cnt[ent[u] & 0x3FFFFFFFu];
+                bk[u] = f < 33u ? f : 33u;
+                rk[u] = atomicAdd(&local[bk[u]], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < kEraBuckets)
+            base[threadIdx.x] = start[threadIdx.x] + (local[threadIdx.x] ? atomicAdd(&cursor[threadIdx.x], local[threadIdx.x]) : 0u);
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (bk[u] != 0xFFFFFFFFu)
+                out[base[bk[u]] + rk[u]] = ent[u];
+        __syncthreads();
+    }
+}
+
 constexpr int kEraScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsP + bs::kWordsEL + 32;
 constexpr int kEraSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 512; // work areas + the two tables
 __global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, 1)
@@ -1452,7 +1517,9 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
                     EL.st(8 * c + k, good ? w[k] : 0u);
                 regular |= good ? 1u << c : 0u;
             }
-            const uint32_t bad = bs::erasure_lane<32, 32>(Syn, EL, G, P, S, inv_tab);
+            // (the queue is ordered by declared count: the warp's largest count bounds every loop below)
+            const int wmaxf = (int)__reduce_max_sync(0xFFFFFFFFu, (unsigned)maxf);
+            const uint32_t bad = wmaxf ? bs::erasure_lane<32, 32>(Syn, EL, G, P, S, inv_tab, wmaxf) : 0xFFFFFFFFu;
             const uint32_t accept = regular & ~bad;
             // what does not qualify goes to the literal stage
 #pragma unroll 1
@@ -1611,7 +1678,7 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
     // raw syndrome rows / error records [tiles * 1024][32 B] | solver scratch, one slab per resident solver warp
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32 + (size_t)ctx->sm_count * kSolveWarpsPerSM *
                                                                           (kSolveScratchWords > kEraScratchWords ? kSolveScratchWords : kEraScratchWords) * 128));
-    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, 64));
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, kCountersBytes));
     ctx->queue_cap = n;
     return 0;
 }
@@ -1777,7 +1844,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         return rc;
     const size_t tiles = 4 * ((n + 4095) / 4096);
     uint32_t *dmask = ctx->d_queue + ((n + 3) & ~(size_t)3);
-    PP_CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 64, stream));
+    PP_CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, kCountersBytes, stream));
     LfsrArgs A{};
     A.stream = data;
     A.stride = data_stride;
@@ -1838,13 +1905,24 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         const size_t cap = (size_t)ctx->sm_count * kSolveWarpsPerSM;
         uint32_t *scratch = reinterpret_cast<uint32_t *>(ctx->d_rem + tiles * kTile * 32);
         if (mode == POPORON_CUDA_MODE_ERASURE && nr == 32 && pos_stride >= 32 && !ctx->no_erasure_kernel) {
-            // erasure mode: the erasure-only kernel takes every regular row whose errors sit on its declared positions
+            // erasure mode: the erasure-only kernel takes every regular row whose errors sit on its declared positions.
+            // The queue is first ordered by declared count (into the buffer of the second queue; what the kernel
+            // declines then goes where the unordered queue was).
+            {
+                ProfScope prof(ctx, PROF_COMPACT, stream);
+                const unsigned sblocks = (unsigned)ctx->sm_count * 8u;
+                rs255_era_hist_kernel<<<sblocks, 256, 0, stream>>>(ctx->d_queue, ctx->d_counters, cnt, ctx->d_counters + kCntHist);
+                rs255_era_scatter_kernel<<<sblocks, 256, 0, stream>>>(ctx->d_queue, ctx->d_counters, cnt, ctx->d_counters + kCntHist,
+                                                                      ctx->d_counters + kCntCursor, queue2);
+                ctx->launches += 2;
+            }
             ProfScope prof(ctx, PROF_SOLVE, stream);
             const size_t warps = groups < cap ? groups : cap;
             rs255_erasure_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
-                                   kEraSmem, stream>>>(size, ctx->d_queue, ctx->d_counters, ctx->d_rem, scratch, queue2,
+                                   kEraSmem, stream>>>(size, queue2, ctx->d_counters, ctx->d_rem, scratch, ctx->d_queue,
                                                        ctx->d_counters + 1, ok, corrected, data, data_stride, pos,
                                                        pos_stride, cnt);
+            queue2 = ctx->d_queue; // (the literal stage reads what was declined)
         } else {
             ProfScope prof(ctx, PROF_SOLVE, stream);
             const size_t warps = groups < cap ? groups : cap;

@@ -48,16 +48,20 @@ BS_FN void stage_slots(const Mem<SO> EL, const Mem<STRIDE> S, int w, const uint8
 // Gamma(x) = prod over the declared slots of (1 + X_i x), X_i = alpha^(254 - location) = inv_tab[list byte]
 // (inv_tab[0] = 0: an undeclared slot multiplies by 1).  G: 33 word blocks.  One factor at a time: Gamma_k +=
 // X_i Gamma_(k-1), k = i + 1 .. 1, on the eight held multiples of X_i.
+// nslots: no codeword of the lane (of the warp, on the device) declares more slots than that
 template <int STRIDE, int SO>
-BS_FN void erasure_locator(const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> S, const uint8_t *inv_tab)
+BS_FN void erasure_locator(const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> S, const uint8_t *inv_tab, int nslots = kES)
 {
+#pragma unroll 1
+    for (int i = 0; i < kES; i++)
+        S.st(kActBase + i, 0u);
 #pragma unroll 1
     for (int k = 0; k <= kES; k++)
 #pragma unroll
         for (int t = 0; t < 8; t++)
             G.st(8 * k + t, (k == 0 && t == 0) ? 0xFFFFFFFFu : 0u);
 #pragma unroll 1
-    for (int w = 0; w < kES / 4; w++) {
+    for (int w = 0; 4 * w < nslots; w++) {
         stage_slots<STRIDE, SO>(EL, S, w, inv_tab);
 #pragma unroll 1
         for (int y = 0; y < 4; y++) {
@@ -111,10 +115,10 @@ BS_FN uint32_t erasure_residue(const Mem<SO> P, const Mem<STRIDE> S)
 // mask of codewords that do not qualify.  Syn: the 32 syndromes as planes (word 8 m + t = plane t of S_(m+1)).
 template <int STRIDE, int SO>
 BS_FN uint32_t erasure_lane(const Mem<SO> Syn, const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, const Mem<STRIDE> S,
-                            const uint8_t *inv_tab)
+                            const uint8_t *inv_tab, int nslots = kES)
 {
-    erasure_locator<STRIDE, SO>(EL, G, S, inv_tab);
-    omega_parked<SO, SO>(Syn, G, P, kES);
+    erasure_locator<STRIDE, SO>(EL, G, S, inv_tab, nslots);
+    omega_parked<SO, SO>(Syn, G, P, kES, nslots);
     return erasure_residue<STRIDE, SO>(P, S);
 }
 

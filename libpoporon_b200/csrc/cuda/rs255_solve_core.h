@@ -567,7 +567,7 @@ BS_FN void ribm_mem(const Mem<SO> S, const Mem<STRIDE> B, const Mem<SO> LM, uint
 // of O.
 // (teff = ns / 2: for a code with fewer than 32 roots only Omega_0 .. Omega_(teff-1) exist; the rest is stored as zero)
 template <int STRIDE, int SO>
-BS_FN void omega_parked(const Mem<SO> S, const Mem<STRIDE> P, const Mem<SO> O, int teff);
+BS_FN void omega_parked(const Mem<SO> S, const Mem<STRIDE> P, const Mem<SO> O, int teff, int jmax = 64);
 template <int STRIDE, int SO>
 BS_FN void omega(const Mem<SO> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE> P, const Mem<SO> O, int teff)
 {
@@ -576,9 +576,9 @@ BS_FN void omega(const Mem<SO> S, const uint32_t (&L)[kLS][8], const Mem<STRIDE>
         st8(P, j, L[j]);
     omega_parked<STRIDE, SO>(S, P, O, teff);
 }
-// P: L_0 .. L_15 in word blocks 0 .. 15
+// P: L_0 .. L_15 in word blocks 0 .. 15 (jmax: the highest coefficient of P that can be non-zero, where the caller knows)
 template <int STRIDE, int SO>
-BS_FN void omega_parked(const Mem<SO> S, const Mem<STRIDE> P, const Mem<SO> O, int teff)
+BS_FN void omega_parked(const Mem<SO> S, const Mem<STRIDE> P, const Mem<SO> O, int teff, int jmax)
 {
 #pragma unroll 1
     for (int i = teff; i < kT; i++) {
@@ -593,8 +593,9 @@ BS_FN void omega_parked(const Mem<SO> S, const Mem<STRIDE> P, const Mem<SO> O, i
         ld8(P, 0, a);
         ld8(S, i, s);
         ld8(S, i >= 1 ? i - 1 : 0, s1);
+        const int jtop = i < jmax ? i : jmax;
 #pragma unroll 1
-        for (int j = 0; j <= i; j++) {
+        for (int j = 0; j <= jtop; j++) {
             // unconditional loads with clamped indices (values past the end are never used)
             uint32_t an[8];
             ld8(S, j + 2 <= i ? i - j - 2 : 0, s2);
