@@ -1402,7 +1402,7 @@ __global__ void __launch_bounds__(256) rs255_era_scatter_kernel(const uint32_t *
     }
 }
 
-constexpr int kEraScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsP + bs::kWordsEL + 32;
+constexpr int kEraScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsEL + 32; // (S * Gamma replaces the syndromes in place)
 constexpr int kEraSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 512; // work areas + the two tables
 __global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, 1)
 rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
@@ -1418,9 +1418,8 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
     uint32_t *gs = scratch + (size_t)gw * (kEraScratchWords * 32) + lane;
     const bs::Mem<32> Syn{gs};
     const bs::Mem<32> G{gs + bs::kWordsS * 32};
-    const bs::Mem<32> P{gs + (bs::kWordsS + bs::kWordsG) * 32};
-    const bs::Mem<32> EL{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsP) * 32};
-    const bs::Mem<32> Qs{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsP + bs::kWordsEL) * 32};
+    const bs::Mem<32> EL{gs + (bs::kWordsS + bs::kWordsG) * 32};
+    const bs::Mem<32> Qs{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsEL) * 32};
     // root_tab[v] = alpha^v (the root of Gamma that belongs to list byte v = location + 1), inv_tab[v] = alpha^(255 - v)
     // (the X of that location); [0] = 0 in both: an undeclared slot
     uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWarpsPerCTA * bs::kWordsW * 32);
@@ -1519,7 +1518,7 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
             }
             // (the queue is ordered by declared count: the warp's largest count bounds every loop below)
             const int wmaxf = (int)__reduce_max_sync(0xFFFFFFFFu, (unsigned)maxf);
-            const uint32_t bad = wmaxf ? bs::erasure_lane<32, 32>(Syn, EL, G, P, S, inv_tab, wmaxf) : 0xFFFFFFFFu;
+            const uint32_t bad = wmaxf ? bs::erasure_lane<32, 32>(Syn, EL, G, S, inv_tab, wmaxf) : 0xFFFFFFFFu;
             const uint32_t accept = regular & ~bad;
             // what does not qualify goes to the literal stage
 #pragma unroll 1
@@ -1531,7 +1530,7 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
             for (int w = 0; w < 8; w++) {
                 if (!__any_sync(0xFFFFFFFFu, accept != 0u && maxf > 4 * w))
                     break;
-                bs::erasure_forney<32, 32>(EL, G, P, S, w, root_tab, nz);
+                bs::erasure_forney<32, 32>(EL, G, Syn, S, w, root_tab, nz);
                 uint32_t X[32];
                 bs::magnitude_words<32>(S, X);
                 // eight codewords per trip: their queue entries and list words (L2) are all on their way before the

@@ -97,6 +97,37 @@ BS_FN void erasure_locator(const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> 
     }
 }
 
+// P_n = sum_{j <= min(n, jmax)} Gamma_j S_(n-j+1), n = 31 .. 0, IN PLACE: P_n replaces S_(n+1) (word block n of SP), which
+// no later (smaller) n reads.  Halves the scratch of the product - what keeps the kernel's state inside the L2.
+template <int SO>
+BS_FN void erasure_product(const Mem<SO> SP, const Mem<SO> G, int jmax)
+{
+#pragma unroll 1
+    for (int n = kES - 1; n >= 0; n--) {
+        const int jtop = n < jmax ? n : jmax;
+        uint32_t acc[15], o[8], g[8], s[8], g1[8], s1[8];
+        clear15(acc);
+        ld8(G, 0, g);
+        ld8(SP, n, s);
+        ld8(G, jtop >= 1 ? 1 : 0, g1);
+        ld8(SP, n >= 1 ? n - 1 : 0, s1);
+#pragma unroll 1
+        for (int j = 0; j <= jtop; j++) {
+            // (two terms ahead, indices clamped: values past the end are never used)
+            uint32_t g2[8], s2[8];
+            ld8(G, j + 2 <= jtop ? j + 2 : 0, g2);
+            ld8(SP, n - j >= 2 ? n - j - 2 : 0, s2);
+            mac(acc, g, s);
+            cp8(g, g1);
+            cp8(s, s1);
+            cp8(g1, g2);
+            cp8(s1, s2);
+        }
+        reduce(acc, o);
+        st8(SP, n, o);
+    }
+}
+
 // bit c set: codeword c does NOT qualify (some P_n with n >= its declared count is non-zero)
 template <int STRIDE, int SO>
 BS_FN uint32_t erasure_residue(const Mem<SO> P, const Mem<STRIDE> S)
@@ -111,15 +142,16 @@ BS_FN uint32_t erasure_residue(const Mem<SO> P, const Mem<STRIDE> S)
     return bad;
 }
 
-// Everything up to the magnitudes' inputs: Gamma into G, P into P (= omega below the declared count); returns the
-// mask of codewords that do not qualify.  Syn: the 32 syndromes as planes (word 8 m + t = plane t of S_(m+1)).
+// Everything up to the magnitudes' inputs: Gamma into G, P in place of the syndromes (= omega below the declared count);
+// returns the mask of codewords that do not qualify.  SP: on entry the 32 syndromes as planes (word 8 m + t = plane t
+// of S_(m+1)), on return P_0 .. P_31.
 template <int STRIDE, int SO>
-BS_FN uint32_t erasure_lane(const Mem<SO> Syn, const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, const Mem<STRIDE> S,
+BS_FN uint32_t erasure_lane(const Mem<SO> SP, const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> S,
                             const uint8_t *inv_tab, int nslots = kES)
 {
     erasure_locator<STRIDE, SO>(EL, G, S, inv_tab, nslots);
-    omega_parked<SO, SO>(Syn, G, P, kES, nslots);
-    return erasure_residue<STRIDE, SO>(P, S);
+    erasure_product<SO>(SP, G, nslots);
+    return erasure_residue<STRIDE, SO>(SP, S);
 }
 
 // Magnitudes of slots 4 w .. 4 w + 3: afterwards words 8 y .. 8 y + 7 of S hold the magnitude planes of slot 4 w + y

@@ -82,7 +82,7 @@ extern "C" int host_erasure(const uint8_t *syn /* [n][32] */, const uint8_t *lis
         inv_tab[v] = gf256::pow_alpha((255 - v) % 255);
     }
     for (size_t g = 0; g < n; g += 32) {
-        static uint32_t Syn[bs::kWordsS], EL[bs::kWordsEL], G[bs::kWordsG], P[bs::kWordsP], S[bs::kWordsW];
+        static uint32_t Syn[bs::kWordsS], EL[bs::kWordsEL], G[bs::kWordsG], S[bs::kWordsW];
         memset(Syn, 0, sizeof Syn);
         memset(EL, 0, sizeof EL);
         memset(S, 0, sizeof S);
@@ -95,16 +95,16 @@ extern "C" int host_erasure(const uint8_t *syn /* [n][32] */, const uint8_t *lis
             for (int e = 0; e < 32; e++)
                 EL[8 * c + (e >> 2)] |= (uint32_t)lists[(g + c) * 32 + e] << (8 * (e & 3));
         }
-        const bs::Mem<1> Synm{Syn}, ELm{EL}, Gm{G}, Pm{P}, Sm{S};
+        const bs::Mem<1> Synm{Syn}, ELm{EL}, Gm{G}, Sm{S};
         int nslots = 0; // the largest declared count of the lane, as the kernel passes it
         for (size_t c = 0; c < cnt; c++)
             for (int e = 0; e < 32; e++)
                 if (lists[(g + c) * 32 + e] && e + 1 > nslots)
                     nslots = e + 1;
-        const uint32_t badmask = bs::erasure_lane<1, 1>(Synm, ELm, Gm, Pm, Sm, inv_tab, nslots);
+        const uint32_t badmask = bs::erasure_lane<1, 1>(Synm, ELm, Gm, Sm, inv_tab, nslots);
         uint32_t nz[6] = {0, 0, 0, 0, 0, 0};
         for (int w = 0; w < 8; w++) {
-            bs::erasure_forney<1, 1>(ELm, Gm, Pm, Sm, w, root_tab, nz);
+            bs::erasure_forney<1, 1>(ELm, Gm, Synm, Sm, w, root_tab, nz);
             uint32_t X[32];
             bs::magnitude_words<1>(Sm, X);
             for (size_t c = 0; c < cnt; c++)
