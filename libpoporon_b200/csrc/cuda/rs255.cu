@@ -1520,11 +1520,18 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
             const int wmaxf = (int)__reduce_max_sync(0xFFFFFFFFu, (unsigned)maxf);
             const uint32_t bad = wmaxf ? bs::erasure_lane<32, 32>(Syn, EL, G, S, inv_tab, wmaxf) : 0xFFFFFFFFu;
             const uint32_t accept = regular & ~bad;
-            // what does not qualify goes to the literal stage
-#pragma unroll 1
-            for (int c = 0; c < 32; c++)
-                if (((present & ~accept) >> c) & 1u)
-                    queue2[atomicAdd(counter2, 1u)] = Qs.ld(c);
+            // what does not qualify goes to the literal stage (one reservation per lane)
+            {
+                uint32_t rest = present & ~accept;
+                if (rest) {
+                    uint32_t at = atomicAdd(counter2, (uint32_t)__popc(rest));
+                    while (rest) {
+                        const int c = __ffs((int)rest) - 1;
+                        rest &= rest - 1;
+                        queue2[at++] = Qs.ld(c);
+                    }
+                }
+            }
             uint32_t nz[6] = {0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll 1
             for (int w = 0; w < 8; w++) {
