@@ -51,7 +51,7 @@ struct RsCode {
 };
 
 // kernel ids of the per-kernel profile (poporon_cuda_rs_profile_read)
-enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_PARITY, PROF_GENERAL, PROF_GENERIC, PROF_ROWS, PROF_KINDS };
+enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_PARITY, PROF_GENERAL, PROF_GENERIC, PROF_ROWS, PROF_ERASURE, PROF_KINDS };
 constexpr int kProfCap = 8192;
 
 static inline int sm_count_of(int device)

@@ -406,7 +406,8 @@ const char *poporon_cuda_rs_profile_name(int kernel)
     static const char *names[PROF_KINDS] = {"rs255_fft_kernel<ENCODE>", "rs255_fft_kernel<SCREEN>",
                                             "rs255_compact_kernel",     "rs255_solve_kernel",
                                             "rs255_parity_kernel",      "rs255_correct_kernel",
-                                            "rs_generic kernels",       "rs255_rows_kernel"};
+                                            "rs_generic kernels",       "rs255_rows_kernel",
+                                            "rs255_erasure_kernel"};
     return kernel >= 0 && kernel < PROF_KINDS ? names[kernel] : NULL;
 }
 

@@ -1922,7 +1922,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
                                                                       ctx->d_counters + kCntCursor, queue2);
                 ctx->launches += 2;
             }
-            ProfScope prof(ctx, PROF_SOLVE, stream);
+            ProfScope prof(ctx, PROF_ERASURE, stream);
             const size_t warps = groups < cap ? groups : cap;
             rs255_erasure_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
                                    kEraSmem, stream>>>(size, queue2, ctx->d_counters, ctx->d_rem, scratch, ctx->d_queue,
