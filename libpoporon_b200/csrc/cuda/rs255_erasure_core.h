@@ -10,7 +10,8 @@
 //   positions are strictly ascending.
 // The discrepancy of iteration r is the coefficient r - 1 of the same product S * Gamma, so one triangular product
 //   P_n = sum_{j <= n} Gamma_j S_(n-j+1),  n = 0 .. 31
-// gives both: P_0 .. P_(count-1) is omega, and the row qualifies exactly when P_count .. P_31 all vanish.  For a
+// gives both: P_0 .. P_(count-1) is omega, and the row qualifies exactly when P_count .. P_31 all vanish (P is
+// computed in place of the syndromes: P_n replaces S_(n+1)).  For a
 // qualifying row those are zero, and so are Gamma's coefficients above count: the Horner chains of Forney's formula
 // can run over all 32 coefficients for every codeword of a lane alike.  No Berlekamp-Massey, no Chien search.
 //
@@ -23,7 +24,6 @@ namespace bs {
 
 constexpr int kES = 32;            // erasure slots per codeword
 constexpr int kWordsG = 8 * 33;    // Gamma_0 .. Gamma_32
-constexpr int kWordsP = 8 * 32;    // P_0 .. P_31
 constexpr int kWordsEL = 8 * 32;   // slot lists: word 8 c + w = slots 4 w .. 4 w + 3 of codeword c, a byte each:
                                    // location + 1 (location = position + padding), 0 = slot not declared
 constexpr int kActBase = 32;       // words 32 .. 63 of the work area: act[i] bit c = slot i of codeword c is declared
