@@ -1402,9 +1402,19 @@ __global__ void __launch_bounds__(256) rs255_era_scatter_kernel(const uint32_t *
     }
 }
 
-constexpr int kEraScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsEL + 32; // (S * Gamma replaces the syndromes in place)
-constexpr int kEraSmem = kSolveWarpsPerCTA * bs::kWordsW * 128 + 512; // work areas + the two tables
-__global__ void __launch_bounds__(32 * kSolveWarpsPerCTA, 1)
+// Twelve warps per SM with the work area in the scratch as well: without 200 KB of shared memory the L1 holds a good
+// part of the lanes' state (8 warps: 10.3 -> 9.3 ms per 16 Mi rows), and a third warp per scheduler hides more of the
+// loads that remain (9.0 ms; sixteen warps at 128 registers spill: 9.3).
+#ifndef PP_ERA_WARPS
+#define PP_ERA_WARPS 12
+#endif
+#ifndef PP_ERA_W_GLOBAL
+#define PP_ERA_W_GLOBAL 1
+#endif
+constexpr int kEraWarps = PP_ERA_WARPS; // warps per CTA = per SM
+constexpr int kEraScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsEL + 32 + (PP_ERA_W_GLOBAL ? bs::kWordsW : 0); // (S * Gamma replaces the syndromes in place)
+constexpr int kEraSmem = (PP_ERA_W_GLOBAL ? 0 : kEraWarps * bs::kWordsW * 128) + 512; // work areas + the two tables
+__global__ void __launch_bounds__(32 * kEraWarps, 1)
 rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
                      const uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2,
                      uint32_t *__restrict__ counter2, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected,
@@ -1413,16 +1423,20 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
 {
     extern __shared__ __align__(16) uint32_t solve_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t gw = blockIdx.x * kSolveWarpsPerCTA + (uint32_t)warp, nw = gridDim.x * kSolveWarpsPerCTA;
-    const bs::Mem<32> S{solve_smem + warp * (bs::kWordsW * 32) + lane};
+    const uint32_t gw = blockIdx.x * kEraWarps + (uint32_t)warp, nw = gridDim.x * kEraWarps;
     uint32_t *gs = scratch + (size_t)gw * (kEraScratchWords * 32) + lane;
+#if PP_ERA_W_GLOBAL
+    const bs::Mem<32> S{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsEL + 32) * 32};
+#else
+    const bs::Mem<32> S{solve_smem + warp * (bs::kWordsW * 32) + lane};
+#endif
     const bs::Mem<32> Syn{gs};
     const bs::Mem<32> G{gs + bs::kWordsS * 32};
     const bs::Mem<32> EL{gs + (bs::kWordsS + bs::kWordsG) * 32};
     const bs::Mem<32> Qs{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsEL) * 32};
     // root_tab[v] = alpha^v (the root of Gamma that belongs to list byte v = location + 1), inv_tab[v] = alpha^(255 - v)
     // (the X of that location); [0] = 0 in both: an undeclared slot
-    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + kSolveWarpsPerCTA * bs::kWordsW * 32);
+    uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + (PP_ERA_W_GLOBAL ? 0 : kEraWarps * bs::kWordsW * 32));
     uint8_t *inv_tab = root_tab + 256;
     {
         uint32_t x = 1;
@@ -1682,8 +1696,11 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
     // queue [n rounded up to 4] | dmask [tiles * 64] | queue2 [n]
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64 + n) * sizeof(uint32_t)));
     // raw syndrome rows / error records [tiles * 1024][32 B] | solver scratch, one slab per resident solver warp
-    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32 + (size_t)ctx->sm_count * kSolveWarpsPerSM *
-                                                                          (kSolveScratchWords > kEraScratchWords ? kSolveScratchWords : kEraScratchWords) * 128));
+    {
+        const size_t solver_words = (size_t)kSolveWarpsPerSM * kSolveScratchWords, erasure_words = (size_t)kEraWarps * kEraScratchWords;
+        PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32 + (size_t)ctx->sm_count *
+                                                                              (solver_words > erasure_words ? solver_words : erasure_words) * 128));
+    }
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, kCountersBytes));
     ctx->queue_cap = n;
     return 0;
@@ -1923,8 +1940,9 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
                 ctx->launches += 2;
             }
             ProfScope prof(ctx, PROF_ERASURE, stream);
-            const size_t warps = groups < cap ? groups : cap;
-            rs255_erasure_kernel<<<(unsigned)((warps + kSolveWarpsPerCTA - 1) / kSolveWarpsPerCTA), 32 * kSolveWarpsPerCTA,
+            const size_t ecap = (size_t)ctx->sm_count * kEraWarps;
+            const size_t warps = groups < ecap ? groups : ecap;
+            rs255_erasure_kernel<<<(unsigned)((warps + kEraWarps - 1) / kEraWarps), 32 * kEraWarps,
                                    kEraSmem, stream>>>(size, queue2, ctx->d_counters, ctx->d_rem, scratch, ctx->d_queue,
                                                        ctx->d_counters + 1, ok, corrected, data, data_stride, pos,
                                                        pos_stride, cnt);
