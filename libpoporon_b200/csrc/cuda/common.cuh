@@ -90,6 +90,7 @@ struct poporon_cuda_rs {
     uint8_t *d_rem;           // per-dirty-codeword remainder / syndromes
     uint32_t *d_counters;     // [0] = dirty count
     size_t queue_cap;
+    size_t scratch_words_per_sm; // per-lane scratch words over all the warps of an SM that d_rem has room for
     uint8_t *d_slab;          // rs255_fft: one 255 KB bit-plane slab per SM (allocated on first use)
     uint32_t *d_synplanes;    // rs255_fft encoder: syndrome planes of the chunk in flight (grow-only)
     size_t synplane_cap;      // codewords it holds

@@ -1681,10 +1681,16 @@ rs255_syn_export_kernel(int nr, const uint32_t *__restrict__ dirty, const uint8_
     reinterpret_cast<uint2 *>(out + cw * (size_t)nr)[g] = make_uint2(a | (b << 16), c | (d << 16));
 }
 
-int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
+// words_per_sm: the per-lane scratch words of all the warps an SM runs in the mode of the call (the erasure kernel keeps
+// more state, in more warps, than the solver: only handles that decode in erasure mode pay for it)
+int ensure_scratch(poporon_cuda_rs *ctx, size_t n, size_t words_per_sm)
 {
-    if (n <= ctx->queue_cap)
+    if (n <= ctx->queue_cap && words_per_sm <= ctx->scratch_words_per_sm)
         return 0;
+    if (n < ctx->queue_cap)
+        n = ctx->queue_cap;
+    if (words_per_sm < ctx->scratch_words_per_sm)
+        words_per_sm = ctx->scratch_words_per_sm;
     cudaFree(ctx->d_queue);
     cudaFree(ctx->d_rem);
     cudaFree(ctx->d_counters);
@@ -1692,17 +1698,15 @@ int ensure_scratch(poporon_cuda_rs *ctx, size_t n)
     ctx->d_rem = nullptr;
     ctx->d_counters = nullptr;
     ctx->queue_cap = 0;
+    ctx->scratch_words_per_sm = 0;
     const size_t tiles = 4 * ((n + 4095) / 4096);
     // queue [n rounded up to 4] | dmask [tiles * 64] | queue2 [n]
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_queue, (((n + 3) & ~(size_t)3) + tiles * 64 + n) * sizeof(uint32_t)));
     // raw syndrome rows / error records [tiles * 1024][32 B] | solver scratch, one slab per resident solver warp
-    {
-        const size_t solver_words = (size_t)kSolveWarpsPerSM * kSolveScratchWords, erasure_words = (size_t)kEraWarps * kEraScratchWords;
-        PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32 + (size_t)ctx->sm_count *
-                                                                              (solver_words > erasure_words ? solver_words : erasure_words) * 128));
-    }
+    PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_rem, tiles * kTile * 32 + (size_t)ctx->sm_count * words_per_sm * 128));
     PP_CUDA_TRY(cudaMalloc((void **)&ctx->d_counters, kCountersBytes));
     ctx->queue_cap = n;
+    ctx->scratch_words_per_sm = words_per_sm;
     return 0;
 }
 
@@ -1862,7 +1866,8 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     if (n == 0)
         return 0;
     const int nr = ctx->code.nroots; // 32, 16 or 8
-    int rc = ensure_scratch(ctx, n);
+    const bool era_kernel = mode == POPORON_CUDA_MODE_ERASURE && nr == 32 && pos_stride >= 32 && !ctx->no_erasure_kernel;
+    int rc = ensure_scratch(ctx, n, era_kernel ? (size_t)kEraWarps * kEraScratchWords : (size_t)kSolveWarpsPerSM * kSolveScratchWords);
     if (rc != 0)
         return rc;
     const size_t tiles = 4 * ((n + 4095) / 4096);
@@ -1927,7 +1932,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
         const size_t groups = (n + 1023) / 1024;
         const size_t cap = (size_t)ctx->sm_count * kSolveWarpsPerSM;
         uint32_t *scratch = reinterpret_cast<uint32_t *>(ctx->d_rem + tiles * kTile * 32);
-        if (mode == POPORON_CUDA_MODE_ERASURE && nr == 32 && pos_stride >= 32 && !ctx->no_erasure_kernel) {
+        if (era_kernel) {
             // erasure mode: the erasure-only kernel takes every regular row whose errors sit on its declared positions.
             // The queue is first ordered by declared count (into the buffer of the second queue; what the kernel
             // declines then goes where the unordered queue was).
@@ -1978,7 +1983,7 @@ int rs255_syndromes(poporon_cuda_rs *ctx, const uint8_t *data, size_t data_strid
     FftShape shape;
     if (!rs255_fft_shape_ok(ctx->code.nroots, 1, data, data_stride, size, parity, parity_stride, &shape))
         return POPORON_CUDA_ERR_UNSUPP;
-    int rc = ensure_scratch(ctx, n);
+    int rc = ensure_scratch(ctx, n, (size_t)kSolveWarpsPerSM * kSolveScratchWords);
     if (rc == 0)
         rc = ensure_slab(ctx);
     if (rc != 0)
