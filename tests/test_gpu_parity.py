@@ -658,6 +658,34 @@ def test_erasure_kernel_edges(gpu_device, orc, size):
             _assert_same((d, p, ok, cor), want, f"erasure kernel size={size} n={n} stride={stride} shift={shift}")
 
 
+def test_modes_alternate_on_one_handle(gpu_device, orc):
+    """plain -> erasure -> plain -> erasure with growing batches on ONE handle: the decode scratch is sized by mode and
+    by batch (the erasure kernel's is larger) and regrown in between"""
+    rng = np.random.default_rng(77)
+    size = 223
+    with api.Poporon.rs_default() as h:
+        for step, n in enumerate((3000, 5000, 9000, 4000)):
+            msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+            par = _gpu_encode(h, msg, 32)
+            cw = np.concatenate([msg, par], 1)
+            if step % 2 == 0:
+                _inject(rng, cw, 255, 18)
+                got = _gpu_decode(h, cw[:, :size], cw[:, size:])
+                want = orc.rs_decode(cw[:, :size], cw[:, size:])
+            else:
+                pos = np.zeros((n, 32), np.uint32)
+                cnt = rng.integers(1, 33, n).astype(np.uint32)
+                pick = np.sort(np.argsort(rng.random((n, size)), axis=1)[:, :32], axis=1)
+                act = np.arange(32)[None, :] < cnt[:, None]
+                pos[act] = pick[act]
+                rows = np.repeat(np.arange(n), 32).reshape(n, 32)
+                cw[rows[act], pick[act]] ^= rng.integers(0, 256, int(act.sum()), dtype=np.uint8)
+                cw[::9, 250] ^= 0x33  # an undeclared error on every ninth row
+                got = _gpu_decode(h, cw[:, :size], cw[:, size:], MODE_ERASURE, pos, cnt)
+                want = orc.rs_decode(cw[:, :size], cw[:, size:], RS_DEFAULT, MODE_ERASURE, pos, cnt)
+            _assert_same(got, want, f"step {step}")
+
+
 def test_single_api_erasure_object(gpu_device, orc):
     """reference tests/test_codec.c:123-168, tests/test_unified.c:82-112 and SURVEY B.6"""
     er = api.Erasure(32, 16)
