@@ -1415,7 +1415,7 @@ constexpr int kEraWarps = PP_ERA_WARPS; // warps per CTA = per SM
 constexpr int kEraScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsEL + 32 + (PP_ERA_W_GLOBAL ? bs::kWordsW : 0); // (S * Gamma replaces the syndromes in place)
 constexpr int kEraSmem = (PP_ERA_W_GLOBAL ? 0 : kEraWarps * bs::kWordsW * 128) + 512; // work areas + the two tables
 __global__ void __launch_bounds__(32 * kEraWarps, 1)
-rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+rs255_erasure_kernel(int nr, size_t size, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
                      const uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue2,
                      uint32_t *__restrict__ counter2, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected,
                      uint8_t *data, size_t data_stride, const uint32_t *__restrict__ era_pos, size_t era_stride,
@@ -1463,7 +1463,7 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
     }
     __syncthreads(); // (every warp wrote the same tables)
     const uint32_t total = *counter;
-    const int pad = 255 - 32 - (int)size;
+    const int pad = 255 - nr - (int)size; // nr = roots of the code = syndromes per row = the most slots a row may declare
     const bool vec_rows = (((uintptr_t)era_pos | (era_stride * 4u)) & 15u) == 0;
     const uint32_t rounds = (total + nw * 1024u - 1u) / (nw * 1024u);
     for (uint32_t it = 0; it < rounds; it++) {
@@ -1494,7 +1494,7 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
                     const size_t cw = entry & 0x3FFFFFFFu;
                     const uint32_t f = era_cnt[cw];
                     const uint32_t *row = era_pos + cw * era_stride;
-                    good = f >= 1u && f <= 32u;
+                    good = f >= 1u && f <= (uint32_t)nr;
                     int prev = -1;
                     // (every slot is defined by the caller, include/poporon_cuda.h: all 32 are read, as quad-words when
                     // the rows allow)
@@ -1532,7 +1532,7 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
             }
             // (the queue is ordered by declared count: the warp's largest count bounds every loop below)
             const int wmaxf = (int)__reduce_max_sync(0xFFFFFFFFu, (unsigned)maxf);
-            const uint32_t bad = wmaxf ? bs::erasure_lane<32, 32>(Syn, EL, G, S, inv_tab, wmaxf) : 0xFFFFFFFFu;
+            const uint32_t bad = wmaxf ? bs::erasure_lane<32, 32>(Syn, EL, G, S, inv_tab, wmaxf, nr) : 0xFFFFFFFFu;
             const uint32_t accept = regular & ~bad;
             // what does not qualify goes to the literal stage (one reservation per lane)
             {
@@ -1548,10 +1548,10 @@ rs255_erasure_kernel(size_t size, const uint32_t *__restrict__ queue, const uint
             }
             uint32_t nz[6] = {0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll 1
-            for (int w = 0; w < 8; w++) {
+            for (int w = 0; 4 * w < nr; w++) {
                 if (!__any_sync(0xFFFFFFFFu, accept != 0u && maxf > 4 * w))
                     break;
-                bs::erasure_forney<32, 32>(EL, G, Syn, S, w, root_tab, nz);
+                bs::erasure_forney<32, 32>(EL, G, Syn, S, w, root_tab, nz, nr);
                 uint32_t X[32];
                 bs::magnitude_words<32>(S, X);
                 // eight codewords per trip: their queue entries and list words (L2) are all on their way before the
@@ -1866,7 +1866,9 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     if (n == 0)
         return 0;
     const int nr = ctx->code.nroots; // 32, 16 or 8
-    const bool era_kernel = mode == POPORON_CUDA_MODE_ERASURE && nr == 32 && pos_stride >= 32 && !ctx->no_erasure_kernel;
+    // (the kernel reads 32 slots of every position row, as quad-words where it can: rows narrower than that - allowed
+    // for the codes with 16 and 8 roots - keep the older path)
+    const bool era_kernel = mode == POPORON_CUDA_MODE_ERASURE && pos_stride >= 32 && !ctx->no_erasure_kernel;
     int rc = ensure_scratch(ctx, n, era_kernel ? (size_t)kEraWarps * kEraScratchWords : (size_t)kSolveWarpsPerSM * kSolveScratchWords);
     if (rc != 0)
         return rc;
@@ -1948,7 +1950,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
             const size_t ecap = (size_t)ctx->sm_count * kEraWarps;
             const size_t warps = groups < ecap ? groups : ecap;
             rs255_erasure_kernel<<<(unsigned)((warps + kEraWarps - 1) / kEraWarps), 32 * kEraWarps,
-                                   kEraSmem, stream>>>(size, queue2, ctx->d_counters, ctx->d_rem, scratch, ctx->d_queue,
+                                   kEraSmem, stream>>>(nr, size, queue2, ctx->d_counters, ctx->d_rem, scratch, ctx->d_queue,
                                                        ctx->d_counters + 1, ok, corrected, data, data_stride, pos,
                                                        pos_stride, cnt);
             queue2 = ctx->d_queue; // (the literal stage reads what was declined)

@@ -100,10 +100,10 @@ BS_FN void erasure_locator(const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> 
 // P_n = sum_{j <= min(n, jmax)} Gamma_j S_(n-j+1), n = 31 .. 0, IN PLACE: P_n replaces S_(n+1) (word block n of SP), which
 // no later (smaller) n reads.  Halves the scratch of the product - what keeps the kernel's state inside the L2.
 template <int SO>
-BS_FN void erasure_product(const Mem<SO> SP, const Mem<SO> G, int jmax)
+BS_FN void erasure_product(const Mem<SO> SP, const Mem<SO> G, int jmax, int ns = kES)
 {
 #pragma unroll 1
-    for (int n = kES - 1; n >= 0; n--) {
+    for (int n = ns - 1; n >= 0; n--) {
         const int jtop = n < jmax ? n : jmax;
         uint32_t acc[15], o[8], g[8], s[8], g1[8], s1[8];
         clear15(acc);
@@ -130,11 +130,11 @@ BS_FN void erasure_product(const Mem<SO> SP, const Mem<SO> G, int jmax)
 
 // bit c set: codeword c does NOT qualify (some P_n with n >= its declared count is non-zero)
 template <int STRIDE, int SO>
-BS_FN uint32_t erasure_residue(const Mem<SO> P, const Mem<STRIDE> S)
+BS_FN uint32_t erasure_residue(const Mem<SO> P, const Mem<STRIDE> S, int ns = kES)
 {
     uint32_t bad = 0;
 #pragma unroll 1
-    for (int n = 0; n < kES; n++) {
+    for (int n = 0; n < ns; n++) {
         uint32_t p[8];
         ld8(P, n, p);
         bad |= or8(p) & ~S.ld(kActBase + n);
@@ -147,11 +147,13 @@ BS_FN uint32_t erasure_residue(const Mem<SO> P, const Mem<STRIDE> S)
 // of S_(m+1)), on return P_0 .. P_31.
 template <int STRIDE, int SO>
 BS_FN uint32_t erasure_lane(const Mem<SO> SP, const Mem<SO> EL, const Mem<SO> G, const Mem<STRIDE> S,
-                            const uint8_t *inv_tab, int nslots = kES)
+                            const uint8_t *inv_tab, int nslots = kES, int ns = kES)
 {
+    // ns = roots of the code = syndromes per codeword = the most slots a row may declare (32; 16 / 8 for RS(255,239) /
+    // RS(255,247)): P_0 .. P_(ns-1) are formed and tested
     erasure_locator<STRIDE, SO>(EL, G, S, inv_tab, nslots);
-    erasure_product<SO>(SP, G, nslots);
-    return erasure_residue<STRIDE, SO>(SP, S);
+    erasure_product<SO>(SP, G, nslots, ns);
+    return erasure_residue<STRIDE, SO>(SP, S, ns);
 }
 
 // Magnitudes of slots 4 w .. 4 w + 3: afterwards words 8 y .. 8 y + 7 of S hold the magnitude planes of slot 4 w + y
@@ -159,10 +161,10 @@ BS_FN uint32_t erasure_lane(const Mem<SO> SP, const Mem<SO> EL, const Mem<SO> G,
 // root_tab[list byte] = alpha^(location + 1), the root of Gamma that belongs to the slot.
 template <int STRIDE, int SO>
 BS_FN void erasure_forney(const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, const Mem<STRIDE> S, int w,
-                          const uint8_t *root_tab, uint32_t (&cnt)[6])
+                          const uint8_t *root_tab, uint32_t (&cnt)[6], int ns = kES)
 {
     stage_slots<STRIDE, SO>(EL, S, w, root_tab);
-    forney_math<STRIDE, SO, 6>(G, P, S, cnt, kES);
+    forney_math<STRIDE, SO, 6>(G, P, S, cnt, ns);
 }
 
 } // namespace bs

@@ -72,8 +72,19 @@ static int host_solve_ns(const uint8_t *syn, size_t n, int pad, int ns, int8_t *
 // Erasure-only form (rs255_erasure_core.h): lists[n][32] = location + 1 of every declared slot (0 = none), ascending.
 // bad[i] = 1: the row does not qualify (errors outside the declared slots); else mags[i][slot] = the magnitudes and
 // count[i] = the number of non-zero ones.
+static int host_erasure_ns(const uint8_t *syn, const uint8_t *lists, size_t n, int ns, int8_t *bad, uint8_t *mags, uint8_t *count);
 extern "C" int host_erasure(const uint8_t *syn /* [n][32] */, const uint8_t *lists /* [n][32] */, size_t n, int8_t *bad,
                             uint8_t *mags /* [n][32] */, uint8_t *count /* [n] */)
+{
+    return host_erasure_ns(syn, lists, n, 32, bad, mags, count);
+}
+// a code with ns = 16 or 8 roots: only S_1 .. S_ns of a row and the first ns slots of a list are meaningful
+extern "C" int host_erasure_roots(const uint8_t *syn, const uint8_t *lists, size_t n, int ns, int8_t *bad, uint8_t *mags,
+                                  uint8_t *count)
+{
+    return host_erasure_ns(syn, lists, n, ns, bad, mags, count);
+}
+static int host_erasure_ns(const uint8_t *syn, const uint8_t *lists, size_t n, int ns, int8_t *bad, uint8_t *mags, uint8_t *count)
 {
     uint8_t root_tab[256], inv_tab[256];
     root_tab[0] = inv_tab[0] = 0;
@@ -101,10 +112,11 @@ extern "C" int host_erasure(const uint8_t *syn /* [n][32] */, const uint8_t *lis
             for (int e = 0; e < 32; e++)
                 if (lists[(g + c) * 32 + e] && e + 1 > nslots)
                     nslots = e + 1;
-        const uint32_t badmask = bs::erasure_lane<1, 1>(Synm, ELm, Gm, Sm, inv_tab, nslots);
+        const uint32_t badmask = bs::erasure_lane<1, 1>(Synm, ELm, Gm, Sm, inv_tab, nslots, ns);
         uint32_t nz[6] = {0, 0, 0, 0, 0, 0};
-        for (int w = 0; w < 8; w++) {
-            bs::erasure_forney<1, 1>(ELm, Gm, Synm, Sm, w, root_tab, nz);
+        memset(mags + g * 32, 0, cnt * 32);
+        for (int w = 0; 4 * w < ns; w++) {
+            bs::erasure_forney<1, 1>(ELm, Gm, Synm, Sm, w, root_tab, nz, ns);
             uint32_t X[32];
             bs::magnitude_words<1>(Sm, X);
             for (size_t c = 0; c < cnt; c++)

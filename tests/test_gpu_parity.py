@@ -658,6 +658,38 @@ def test_erasure_kernel_edges(gpu_device, orc, size):
             _assert_same((d, p, ok, cor), want, f"erasure kernel size={size} n={n} stride={stride} shift={shift}")
 
 
+@pytest.mark.parametrize("nr", [16, 8])
+def test_erasure_mode_of_the_shorter_codes(gpu_device, orc, nr):
+    """RS(255,239) / RS(255,247) in erasure mode: rs255_erasure_kernel with 16 / 8 roots (position rows of 32 slots),
+    the older path for rows of nr slots only; undeclared errors, unsorted and over-long rows mixed in"""
+    params = (8, 0x11D, 1, 1, nr)
+    rng = np.random.default_rng(500 + nr)
+    with _rs(params) as h:
+        for size, stride in ((255 - nr, 32), (60, 32), (255 - nr, nr)):
+            n = 4000
+            msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+            par = _gpu_encode(h, msg, nr)
+            cw = np.concatenate([msg, par], 1)
+            pos = np.zeros((n, stride), np.uint32)
+            cnt = np.zeros(n, np.uint32)
+            for i in range(n):
+                c = int(rng.integers(0, nr + 1))
+                pp = np.sort(rng.choice(size, c, replace=False))
+                pos[i, :c], cnt[i] = pp, c
+                pos[i, c:] = rng.integers(0, size, stride - c)
+                cw[i, pp] ^= rng.integers(0, 256, c, dtype=np.uint8)
+                kind = i % 10
+                if kind == 1:
+                    cw[i, int(rng.integers(0, size + nr))] ^= 0x11
+                elif kind == 2 and c >= 2:
+                    pos[i, [0, c - 1]] = pos[i, [c - 1, 0]]
+                elif kind == 3 and stride > nr:
+                    cnt[i] = nr + 1
+            got = _gpu_decode(h, cw[:, :size], cw[:, size:], MODE_ERASURE, pos, cnt)
+            want = orc.rs_decode(cw[:, :size], cw[:, size:], params, MODE_ERASURE, pos, cnt)
+            _assert_same(got, want, f"erasure nr={nr} size={size} stride={stride}")
+
+
 def test_modes_alternate_on_one_handle(gpu_device, orc):
     """plain -> erasure -> plain -> erasure with growing batches on ONE handle: the decode scratch is sized by mode and
     by batch (the erasure kernel's is larger) and regrown in between"""
