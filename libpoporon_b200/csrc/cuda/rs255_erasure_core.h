@@ -167,4 +167,45 @@ BS_FN void erasure_forney(const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, co
     forney_math<STRIDE, SO, 6>(G, P, S, cnt, ns);
 }
 
+// ---- errors on top of the erasures -------------------------------------------------------------------------------
+// A row with regular declared positions AND errors elsewhere: the reference's Berlekamp-Massey, started from Gamma
+// with el = count (src/decode.c:51-96), is the plain algorithm on the sequence T_m = P_(count+m) (the "Forney
+// syndromes": discrepancy, length rule 2 el <= r + count - 1 and updates are the plain ones with r - count and
+// el - count), its locator is Gamma * sigma with sigma the plain locator of T.  So for a lane whose codewords all
+// declare F positions: sigma by the plain ribm_mem on the word blocks F .. 31 of P (32 - F terms), its roots by the
+// plain Chien transform, then Lambda = Gamma * sigma and Omega = P * sigma by the same in-place triangular product,
+// and Forney on the merged, location-ordered list of declared positions and found roots - whose i-th magnitude the
+// reference applies at the caller's i-th SLOT (src/decode.c:211-214), which the caller of this code must do too.
+//
+// ee_lane: everything up to the roots of sigma.  SP: the syndromes as planes, with room for 64 word blocks (the
+// shifted sequence is read up to one block past its end, as the plain solver does); G: 33 blocks; SG: 17 blocks,
+// receives sigma; MK: 256 words; W: the work area (root lists of sigma as after solve_lane).  Afterwards
+// classify(W, out, c, nroots, 32 - F) gives the outcome of sigma for codeword c.
+template <int STRIDE, int SO, class Hook>
+BS_FN void ee_lane(const Mem<SO> SP, const Mem<SO> EL, const Mem<SO> G, const Mem<SO> SG, const Mem<SO> MK,
+                   const Mem<STRIDE> W, const uint8_t *inv_tab, int F, int pad, LaneOut &out, Hook &hook)
+{
+    erasure_locator<STRIDE, SO>(EL, G, W, inv_tab, F);
+    erasure_product<SO>(SP, G, F, kES);
+    const Mem<SO> T{SP.base + 8 * F * SO};
+    const Mem<STRIDE> B{W.base + kListBase * STRIDE};
+    ribm_mem<STRIDE, SO>(T, B, SG, out.K, kES - F);
+#pragma unroll
+    for (int j = 0; j < kNL; j++) {
+        uint32_t l[8];
+        ld8(SG, j, l);
+        out.nzL[j] = or8(l);
+    }
+    chien_transform<STRIDE, SO, Hook>(SG, MK, W, pad, out, hook);
+}
+
+// Lambda = Gamma * sigma (in place of Gamma, 33 blocks) and Omega = P * sigma (in place of P); lmax: the largest degree
+// of sigma among the codewords that will be used
+template <int SO>
+BS_FN void ee_products(const Mem<SO> SP, const Mem<SO> G, const Mem<SO> SG, int lmax)
+{
+    erasure_product<SO>(G, SG, lmax, kES + 1);
+    erasure_product<SO>(SP, SG, lmax, kES);
+}
+
 } // namespace bs

@@ -133,3 +133,93 @@ static int host_erasure_ns(const uint8_t *syn, const uint8_t *lists, size_t n, i
     }
     return 0;
 }
+
+// Errors on top of the erasures (rs255_erasure_core.h, ee_lane): every group of 32 rows declares the same number F of
+// positions (fcount[group]).  lists[n][32]: location + 1 of the declared slots, ascending.
+//   status[i]: 0 declined, 1 fail (the reference returns false without touching anything), 2 ok
+//   merged[i][32]: location + 1 of declared positions and found roots in ascending order of location (rank order)
+//   mags[i][32]: the magnitude of every rank;  count[i]: the non-zero ones
+extern "C" int host_ee(const uint8_t *syn /* [n][32] */, const uint8_t *lists /* [n][32] */, size_t n, const int *fcount,
+                       int pad, int8_t *status, uint8_t *merged, uint8_t *mags, uint8_t *count)
+{
+    uint8_t root_tab[256], inv_tab[256];
+    root_tab[0] = inv_tab[0] = 0;
+    for (int v = 1; v < 256; v++) {
+        root_tab[v] = gf256::pow_alpha(v);
+        inv_tab[v] = gf256::pow_alpha((255 - v) % 255);
+    }
+    for (size_t g = 0; g < n; g += 32) {
+        static uint32_t SP[8 * 64], EL[bs::kWordsEL], G[bs::kWordsG], SG[8 * 17], MK[bs::kWordsM], W[bs::kWordsW];
+        memset(SP, 0, sizeof SP);
+        memset(EL, 0, sizeof EL);
+        memset(W, 0, sizeof W);
+        const size_t cnt = n - g < 32 ? n - g : 32;
+        const int F = fcount[g / 32];
+        for (size_t c = 0; c < cnt; c++) {
+            for (int m = 0; m < 32; m++)
+                for (int t = 0; t < 8; t++)
+                    if ((syn[(g + c) * 32 + m] >> t) & 1)
+                        SP[8 * m + t] |= 1u << c;
+            for (int e = 0; e < 32; e++)
+                EL[8 * c + (e >> 2)] |= (uint32_t)lists[(g + c) * 32 + e] << (8 * (e & 3));
+        }
+        const bs::Mem<1> SPm{SP}, ELm{EL}, Gm{G}, SGm{SG}, MKm{MK}, Wm{W};
+        bs::LaneOut out;
+        bs::NoHook hook;
+        bs::ee_lane<1, 1>(SPm, ELm, Gm, SGm, MKm, Wm, inv_tab, F, pad, out, hook);
+        int lmax = 0;
+        memset(EL, 0, sizeof EL);
+        for (size_t c = 0; c < cnt; c++) {
+            int nroots = 0;
+            int st = bs::classify<1>(Wm, out, (int)c, nroots, 32 - F);
+            uint8_t m[48];
+            int k = 0;
+            if (st == bs::kOk) {
+                // merge (both ascending); a found root on a declared position is a double root of the locator: the
+                // reference's search then finds fewer roots than the degree and fails
+                int a = 0, b = 0;
+                while (a < F || b < nroots) {
+                    const int va = a < F ? lists[(g + c) * 32 + a] : 256;
+                    const int vb = b < nroots ? (int)((W[bs::kListBase + 4 * c + (b >> 2)] >> (8 * (b & 3))) & 0xFF) : 256;
+                    if (va == vb) {
+                        st = bs::kFail;
+                        break;
+                    }
+                    if (va < vb) {
+                        m[k++] = (uint8_t)va;
+                        a++;
+                    } else {
+                        m[k++] = (uint8_t)vb;
+                        b++;
+                    }
+                }
+            }
+            status[g + c] = (int8_t)st;
+            if (st == bs::kOk) {
+                if (nroots > lmax)
+                    lmax = nroots;
+                for (int e = 0; e < k; e++) {
+                    merged[(g + c) * 32 + e] = m[e];
+                    EL[8 * c + (e >> 2)] |= (uint32_t)m[e] << (8 * (e & 3));
+                }
+            }
+        }
+        bs::ee_products<1>(SPm, Gm, SGm, lmax);
+        uint32_t nz[6] = {0, 0, 0, 0, 0, 0};
+        for (int w = 0; w < 8; w++) {
+            bs::erasure_forney<1, 1>(ELm, Gm, SPm, Wm, w, root_tab, nz);
+            uint32_t X[32];
+            bs::magnitude_words<1>(Wm, X);
+            for (size_t c = 0; c < cnt; c++)
+                for (int y = 0; y < 4; y++)
+                    mags[(g + c) * 32 + 4 * w + y] = (uint8_t)(X[c] >> (8 * y));
+        }
+        for (size_t c = 0; c < cnt; c++) {
+            unsigned k = 0;
+            for (int b = 0; b < 6; b++)
+                k |= ((nz[b] >> c) & 1u) << b;
+            count[g + c] = (uint8_t)k;
+        }
+    }
+    return 0;
+}

@@ -200,3 +200,66 @@ def test_erasure_core(solver):
             assert (mags[i, f:] == 0).all()
             assert (fixed == wd[i]).all() and (cw[i, size:] == wp[i]).all(), (nr, size, i)
             assert count[i] == wcor[i] == np.count_nonzero(mags[i, :f]), (nr, size, i, count[i], wcor[i])
+
+
+def test_errors_on_top_of_erasures_core(solver):
+    """ee_lane / ee_products (rs255_erasure_core.h): sigma from the plain BM on the Forney syndromes, the merged rank
+    list and its magnitudes, against the oracle's erasure mode - including its slot-order application: the i-th
+    magnitude goes to the caller's i-th slot, whatever that slot holds beyond the declared count."""
+    from oraclelib import MODE_ERASURE
+
+    orc = Oracle("port")
+    rng = np.random.default_rng(16)
+    P = C.POINTER
+    solver.host_ee.argtypes = [P(C.c_uint8), P(C.c_uint8), C.c_size_t, P(C.c_int), C.c_int, P(C.c_int8), P(C.c_uint8),
+                               P(C.c_uint8), P(C.c_uint8)]
+    for size in (223, 90):
+        n = 32 * 24
+        pad = 223 - size
+        msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+        par = orc.rs_encode(msg)
+        cw = np.concatenate([msg, par], 1)
+        pos = np.zeros((n, 32), np.uint32)
+        cnt = np.zeros(n, np.uint32)
+        lists = np.zeros((n, 32), np.uint8)
+        fcount = np.zeros(n // 32, np.int32)
+        for g in range(n // 32):
+            F = int(rng.integers(1, 31))
+            fcount[g] = F
+            for i in range(32 * g, 32 * g + 32):
+                p = np.sort(rng.choice(size, F, replace=False))
+                pos[i, :F], cnt[i] = p, F
+                pos[i, F:] = rng.integers(0, size, 32 - F)  # stale slots: the reference applies through them
+                lists[i, :F] = p + pad + 1
+                cw[i, p] ^= rng.integers(0, 256, F, dtype=np.uint8)
+                emax = (32 - F) // 2
+                e = int(rng.integers(1, emax + 3)) if emax else 1  # sometimes more than can be corrected
+                others = np.setdiff1d(np.arange(size + 32), p)
+                q = rng.choice(others, min(e, len(others)), replace=False)
+                cw[i, q] ^= rng.integers(1, 256, len(q), dtype=np.uint8)
+        wd, wp, wok, wcor = orc.rs_decode(cw[:, :size], cw[:, size:], mode=MODE_ERASURE, pos=pos, cnt=cnt)
+        syn = np.ascontiguousarray(syndromes(cw))
+        status = np.zeros(n, np.int8)
+        merged = np.zeros((n, 32), np.uint8)
+        mags = np.zeros((n, 32), np.uint8)
+        count = np.zeros(n, np.uint8)
+        solver.host_ee(syn.ctypes.data_as(P(C.c_uint8)), lists.ctypes.data_as(P(C.c_uint8)), n,
+                       fcount.ctypes.data_as(P(C.c_int)), pad, status.ctypes.data_as(P(C.c_int8)),
+                       merged.ctypes.data_as(P(C.c_uint8)), mags.ctypes.data_as(P(C.c_uint8)),
+                       count.ctypes.data_as(P(C.c_uint8)))
+        assert (status == 2).sum() > n // 3
+        for i in range(n):
+            if status[i] == 0:
+                continue
+            if status[i] == 1:
+                assert wok[i] == 0 and wcor[i] == 0, (i, wok[i], wcor[i])
+                assert (wd[i] == cw[i, :size]).all()
+                continue
+            k = int(np.count_nonzero(merged[i]))
+            assert wok[i] == 1, i
+            fixed = cw[i, :size].copy()
+            for r in range(k):  # rank r -> the caller's slot r
+                if pos[i, r] < size:
+                    fixed[pos[i, r]] ^= mags[i, r]
+            assert (fixed == wd[i]).all() and (cw[i, size:] == wp[i]).all(), i
+            assert count[i] == wcor[i], (i, count[i], wcor[i])
