@@ -177,7 +177,7 @@ uint64_t poporon_cuda_rs_launch_count(const poporon_cuda_rs_t *ctx);
 /* Opt-in per-kernel timing of the RS(255,223) fast path: CUDA event pairs recorded around every kernel the
  * context launches, on the stream it launches on.  profile(ctx, 1) starts/restarts accumulation,
  * profile(ctx, 0) stops it; profile_read synchronises on the recorded events and returns launches and the
- * summed duration of kernel id `kernel` (0 .. 8, names from profile_name).  bench.py's roofline leg. */
+ * summed duration of kernel id `kernel` (0 .. 9, names from profile_name).  bench.py's roofline leg. */
 int poporon_cuda_rs_profile(poporon_cuda_rs_t *ctx, int on);
 int poporon_cuda_rs_profile_read(poporon_cuda_rs_t *ctx, int kernel, uint64_t *launches, double *total_ms);
 const char *poporon_cuda_rs_profile_name(int kernel);

@@ -51,7 +51,7 @@ struct RsCode {
 };
 
 // kernel ids of the per-kernel profile (poporon_cuda_rs_profile_read)
-enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_PARITY, PROF_GENERAL, PROF_GENERIC, PROF_ROWS, PROF_ERASURE, PROF_KINDS };
+enum { PROF_ENCODE = 0, PROF_SCREEN, PROF_COMPACT, PROF_SOLVE, PROF_PARITY, PROF_GENERAL, PROF_GENERIC, PROF_ROWS, PROF_ERASURE, PROF_EE, PROF_KINDS };
 constexpr int kProfCap = 8192;
 
 static inline int sm_count_of(int device)
@@ -97,6 +97,7 @@ struct poporon_cuda_rs {
     cudaEvent_t busy;         // recorded after the last kernel that uses the scratch above; the next call's stream waits on it
     int correct_ctas_per_sm;  // resident CTAs of the general correction stage (per device, rs255_init)
     int no_fuse;              // PP_RS255_NOFUSE=1: compaction kernel instead of the fused zero-syndrome exit (A/B runs)
+    int no_ee_kernel;         // PP_RS255_NO_EE_KERNEL=1: erasure mode without its second bitsliced stage (A/B runs)
     int no_erasure_kernel;    // PP_RS255_NO_ERASURE_KERNEL=1: erasure mode without the bitsliced erasure-only kernel (A/B runs)
     int use_lfsr;             // PP_RS255_LFSR=1: the round-1 LFSR kernels instead of the transform kernels (A/B runs)
     // opt-in per-kernel timing (poporon_cuda_rs_profile): CUDA event pairs around each launch

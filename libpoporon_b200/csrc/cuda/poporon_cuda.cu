@@ -407,7 +407,7 @@ const char *poporon_cuda_rs_profile_name(int kernel)
                                             "rs255_compact_kernel",     "rs255_solve_kernel",
                                             "rs255_parity_kernel",      "rs255_correct_kernel",
                                             "rs_generic kernels",       "rs255_rows_kernel",
-                                            "rs255_erasure_kernel"};
+                                            "rs255_erasure_kernel",     "rs255_ee_kernel"};
     return kernel >= 0 && kernel < PROF_KINDS ? names[kernel] : NULL;
 }
 

@@ -1342,7 +1342,8 @@ rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restr
 // count of the warp instead of running to 32 for everybody.
 constexpr int kEraBuckets = 34;   // counts 0 .. 32, 33 = anything larger
 constexpr int kCntHist = 32;      // counters: [0] dirty rows, [1] rows for the literal stage, [32, 66) histogram,
-constexpr int kCntCursor = 96;    //           [96, 130) bucket cursors
+constexpr int kCntCursor = 96;    //           [96, 130) bucket cursors; [128 + 32, ..) / [224, ..): the same for the second ordering
+constexpr int kCntHist2 = 160, kCntCursor2 = 200;
 constexpr int kCountersBytes = 1024;
 __global__ void __launch_bounds__(256) rs255_era_hist_kernel(const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
                                                              const uint32_t *__restrict__ era_cnt, uint32_t *__restrict__ hist)
@@ -1402,6 +1403,67 @@ __global__ void __launch_bounds__(256) rs255_era_scatter_kernel(const uint32_t *
     }
 }
 
+// The declared positions of one row -> its slot list (eight words, a byte per slot: location + 1, 0 = slot not
+// declared).  Returns whether the row is regular: 1 .. nr positions, strictly ascending, inside the message.  Every slot
+// is defined by the caller (include/poporon_cuda.h): all 32 are read, as quad-words when the rows allow.
+__device__ __forceinline__ bool era_row_list(const uint32_t *__restrict__ row, bool vec_rows, uint32_t f, uint32_t size, int pad,
+                                             int nr, uint32_t (&w)[8])
+{
+    bool good = f >= 1u && f <= (uint32_t)nr;
+    int prev = -1;
+    uint32_t pv[32];
+    if (vec_rows) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint4 q = __ldg(reinterpret_cast<const uint4 *>(row) + j);
+            pv[4 * j] = q.x;
+            pv[4 * j + 1] = q.y;
+            pv[4 * j + 2] = q.z;
+            pv[4 * j + 3] = q.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; j++)
+            pv[j] = __ldg(row + j);
+    }
+#pragma unroll
+    for (int j = 0; j < 32; j++) {
+        const uint32_t pj = pv[j];
+        const bool act = (uint32_t)j < f;
+        good = good && (!act || (pj < size && (int)pj > prev));
+        prev = act ? (int)pj : prev;
+        const uint32_t v = act ? ((pj + (uint32_t)pad + 1u) & 0xFFu) : 0u;
+        w[j >> 2] |= v << (8 * (j & 3));
+    }
+    return good;
+}
+// root_tab[v] = alpha^v (the root of the locator that belongs to list byte v = location + 1), inv_tab[v] = alpha^(255 - v)
+// (the X of that location); [0] = 0 in both: an undeclared slot.  Each lane fills eight consecutive powers.
+__device__ __forceinline__ void era_fill_tables(uint8_t *root_tab, uint8_t *inv_tab, int lane)
+{
+    uint32_t x = 1;
+    for (int i = 0; i < 8 * lane; i++) {
+        x <<= 1;
+        if (x & 0x100u)
+            x ^= gf256::kPoly;
+    }
+    for (int i = 8 * lane; i < 8 * lane + 8; i++) { // x = alpha^i
+        if (i != 0) {
+            root_tab[i] = (uint8_t)x;
+            if (i != 255)
+                inv_tab[255 - i] = (uint8_t)x;
+        }
+        x <<= 1;
+        if (x & 0x100u)
+            x ^= gf256::kPoly;
+    }
+    if (lane == 0) {
+        root_tab[0] = 0;
+        inv_tab[0] = 0;
+        inv_tab[255] = 1; // alpha^0
+    }
+}
+
 // Twelve warps per SM with the work area in the scratch as well: without 200 KB of shared memory the L1 holds a good
 // part of the lanes' state (8 warps: 10.3 -> 9.3 ms per 16 Mi rows), and a third warp per scheduler hides more of the
 // loads that remain (9.0 ms; sixteen warps at 128 registers spill: 9.3).
@@ -1438,29 +1500,7 @@ rs255_erasure_kernel(int nr, size_t size, const uint32_t *__restrict__ queue, co
     // (the X of that location); [0] = 0 in both: an undeclared slot
     uint8_t *root_tab = reinterpret_cast<uint8_t *>(solve_smem + (PP_ERA_W_GLOBAL ? 0 : kEraWarps * bs::kWordsW * 32));
     uint8_t *inv_tab = root_tab + 256;
-    {
-        uint32_t x = 1;
-        for (int i = 0; i < 8 * lane; i++) {
-            x <<= 1;
-            if (x & 0x100u)
-                x ^= gf256::kPoly;
-        }
-        for (int i = 8 * lane; i < 8 * lane + 8; i++) { // x = alpha^i
-            if (i != 0) {
-                root_tab[i] = (uint8_t)x;
-                if (i != 255)
-                    inv_tab[255 - i] = (uint8_t)x;
-            }
-            x <<= 1;
-            if (x & 0x100u)
-                x ^= gf256::kPoly;
-        }
-        if (lane == 0) {
-            root_tab[0] = 0;
-            inv_tab[0] = 0;
-            inv_tab[255] = 1; // alpha^0
-        }
-    }
+    era_fill_tables(root_tab, inv_tab, lane);
     __syncthreads(); // (every warp wrote the same tables)
     const uint32_t total = *counter;
     const int pad = 255 - nr - (int)size; // nr = roots of the code = syndromes per row = the most slots a row may declare
@@ -1494,34 +1534,7 @@ rs255_erasure_kernel(int nr, size_t size, const uint32_t *__restrict__ queue, co
                     const size_t cw = entry & 0x3FFFFFFFu;
                     const uint32_t f = era_cnt[cw];
                     const uint32_t *row = era_pos + cw * era_stride;
-                    good = f >= 1u && f <= (uint32_t)nr;
-                    int prev = -1;
-                    // (every slot is defined by the caller, include/poporon_cuda.h: all 32 are read, as quad-words when
-                    // the rows allow)
-                    uint32_t pv[32];
-                    if (vec_rows) {
-#pragma unroll
-                        for (int j = 0; j < 8; j++) {
-                            const uint4 q = __ldg(reinterpret_cast<const uint4 *>(row) + j);
-                            pv[4 * j] = q.x;
-                            pv[4 * j + 1] = q.y;
-                            pv[4 * j + 2] = q.z;
-                            pv[4 * j + 3] = q.w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; j++)
-                            pv[j] = __ldg(row + j);
-                    }
-#pragma unroll
-                    for (int j = 0; j < 32; j++) {
-                        const uint32_t pj = pv[j];
-                        const bool act = (uint32_t)j < f;
-                        good = good && (!act || (pj < (uint32_t)size && (int)pj > prev));
-                        prev = act ? (int)pj : prev;
-                        const uint32_t v = act ? ((pj + (uint32_t)pad + 1u) & 0xFFu) : 0u;
-                        w[j >> 2] |= v << (8 * (j & 3));
-                    }
+                    good = era_row_list(row, vec_rows, f, (uint32_t)size, pad, nr, w);
                     if (good)
                         maxf = (int)f > maxf ? (int)f : maxf;
                 }
@@ -1594,6 +1607,220 @@ rs255_erasure_kernel(int nr, size_t size, const uint32_t *__restrict__ queue, co
                     ok[cw] = 1;
                 if (corrected)
                     corrected[cw] = k;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Erasure mode, second bitsliced stage (rs255_erasure_core.h, ee_lane): the rows the erasure-only kernel declined because
+// their syndromes need errors OUTSIDE the declared positions.  The queue comes ordered by declared count again, and a
+// warp works only when all its regular rows declare the same number F of positions (everything else - and every row
+// whose sigma the plain solver would decline - goes on to the literal stage): sigma by the plain Berlekamp-Massey on
+// the Forney syndromes, its roots by the plain Chien transform, then the magnitudes of the merged, location-ordered
+// list of declared positions and found roots; the i-th of them is XORed into the caller's i-th SLOT, as the reference
+// does (src/decode.c:211-214; slots past the row and positions past the message are skipped, as in rs_correct.cuh).
+// ---------------------------------------------------------------------------------------------------
+constexpr int kEeWarps = 8;
+constexpr int kEeScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsEL + 8 * bs::kNL + bs::kWordsM + 32 + bs::kWordsW;
+static_assert(kEeWarps * kEeScratchWords <= kEraWarps * kEraScratchWords, "the erasure kernel's scratch serves both");
+__global__ void __launch_bounds__(32 * kEeWarps, 1)
+rs255_ee_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ counter,
+                const uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue3,
+                uint32_t *__restrict__ counter3, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data,
+                size_t data_stride, const uint32_t *__restrict__ era_pos, size_t era_stride,
+                const uint32_t *__restrict__ era_cnt)
+{
+    __shared__ uint8_t tabs[512];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t gw = blockIdx.x * kEeWarps + (uint32_t)warp, nw = gridDim.x * kEeWarps;
+    uint32_t *gs = scratch + (size_t)gw * (kEeScratchWords * 32) + lane;
+    const bs::Mem<32> SP{gs}; // (the block behind it, Gamma_0, is read - and not used - by the shifted BM)
+    const bs::Mem<32> G{gs + bs::kWordsS * 32};
+    const bs::Mem<32> EL{gs + (bs::kWordsS + bs::kWordsG) * 32};
+    const bs::Mem<32> SG{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsEL) * 32};
+    const bs::Mem<32> MK{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsEL + 8 * bs::kNL) * 32};
+    const bs::Mem<32> Qs{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsEL + 8 * bs::kNL + bs::kWordsM) * 32};
+    const bs::Mem<32> S{gs + (bs::kWordsS + bs::kWordsG + bs::kWordsEL + 8 * bs::kNL + bs::kWordsM + 32) * 32};
+    uint8_t *root_tab = tabs, *inv_tab = tabs + 256;
+    era_fill_tables(root_tab, inv_tab, lane);
+    __syncthreads();
+    const uint32_t total = *counter;
+    const int pad = 255 - 32 - (int)size;
+    const bool vec_rows = (((uintptr_t)era_pos | (era_stride * 4u)) & 15u) == 0;
+    const uint32_t rounds = (total + nw * 1024u - 1u) / (nw * 1024u);
+    for (uint32_t it = 0; it < rounds; it++) {
+        const uint32_t g0 = (it * nw + gw) * 1024u;
+        if (g0 < total) {
+            {
+                uint32_t ent[32];
+#pragma unroll
+                for (int c = 0; c < 32; c++) {
+                    const uint32_t q = g0 + 32u * (uint32_t)c + (uint32_t)lane;
+                    ent[c] = q < total ? queue[q] : 0xFFFFFFFFu;
+                }
+#pragma unroll
+                for (int c = 0; c < 32; c++)
+                    Qs.st(c, ent[c]);
+                solve_load_syndromes(ent, syn_raw, SP);
+            }
+            uint32_t regular = 0, present = 0;
+            int fmin = 64, fmax = 0;
+#pragma unroll 1
+            for (int c = 0; c < 32; c++) {
+                const uint32_t entry = Qs.ld(c);
+                uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                bool good = false;
+                if (entry != 0xFFFFFFFFu) {
+                    present |= 1u << c;
+                    const size_t cw = entry & 0x3FFFFFFFu;
+                    const uint32_t f = era_cnt[cw];
+                    good = era_row_list(era_pos + cw * era_stride, vec_rows, f, (uint32_t)size, pad, 32, w) && f <= 30u;
+                    if (good) {
+                        fmin = (int)f < fmin ? (int)f : fmin;
+                        fmax = (int)f > fmax ? (int)f : fmax;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    EL.st(8 * c + k, good ? w[k] : 0u);
+                regular |= good ? 1u << c : 0u;
+            }
+            const int wfmin = (int)__reduce_min_sync(0xFFFFFFFFu, (unsigned)fmin);
+            const int wfmax = (int)__reduce_max_sync(0xFFFFFFFFu, (unsigned)fmax);
+            uint32_t accept = 0;
+            int lmax = 0;
+            if (wfmax != 0 && wfmin == wfmax) { // (warp-uniform)
+                const int F = wfmax;
+                bs::LaneOut out;
+                bs::NoHook idle;
+                bs::ee_lane<32, 32>(SP, EL, G, SG, MK, S, inv_tab, F, pad, out, idle);
+                // outcome of sigma per codeword; the merged rank list replaces the slot list
+#pragma unroll 1
+                for (int c = 0; c < 32; c++) {
+                    if (!((regular >> c) & 1u))
+                        continue;
+                    int nroots = 0;
+                    int st = bs::classify<32>(S, out, c, nroots, 32 - F);
+                    uint32_t m[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                    if (st == bs::kOk) {
+                        // merge (both ascending); a found root ON a declared position is a double root of the locator:
+                        // the reference's search then finds fewer roots than the degree and fails
+                        uint32_t lw[8], rw[4];
+#pragma unroll
+                        for (int k = 0; k < 8; k++)
+                            lw[k] = EL.ld(8 * c + k);
+#pragma unroll
+                        for (int k = 0; k < 4; k++)
+                            rw[k] = S.ld(bs::kListBase + 4 * c + k);
+                        int a = 0, b = 0, k = 0;
+                        while (a < F || b < nroots) {
+                            uint32_t va = 256u, vb = 256u;
+#pragma unroll
+                            for (int q = 0; q < 8; q++)
+                                if (q == (a >> 2) && a < F)
+                                    va = (lw[q] >> (8 * (a & 3))) & 0xFFu;
+#pragma unroll
+                            for (int q = 0; q < 4; q++)
+                                if (q == (b >> 2) && b < nroots)
+                                    vb = (rw[q] >> (8 * (b & 3))) & 0xFFu;
+                            if (va == vb) {
+                                st = bs::kFail;
+                                break;
+                            }
+                            const uint32_t v = va < vb ? va : vb;
+                            a += va < vb ? 1 : 0;
+                            b += va < vb ? 0 : 1;
+#pragma unroll
+                            for (int q = 0; q < 8; q++)
+                                if (q == (k >> 2))
+                                    m[q] |= v << (8 * (k & 3));
+                            k++;
+                        }
+                    }
+                    if (st == bs::kOk) {
+                        accept |= 1u << c;
+                        lmax = nroots > lmax ? nroots : lmax;
+#pragma unroll
+                        for (int k = 0; k < 8; k++)
+                            EL.st(8 * c + k, m[k]);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 8; k++)
+                            EL.st(8 * c + k, 0u);
+                        if (st == bs::kFail) { // the reference returns false before it counts anything
+                            const size_t cw = Qs.ld(c) & 0x3FFFFFFFu;
+                            if (ok)
+                                ok[cw] = 0;
+                            if (corrected)
+                                corrected[cw] = 0;
+                            present &= ~(1u << c);
+                        }
+                    }
+                }
+                const int wlmax = (int)__reduce_max_sync(0xFFFFFFFFu, (unsigned)lmax);
+                if (wlmax) {
+                    bs::ee_products<32>(SP, G, SG, wlmax);
+                    uint32_t nz[6] = {0u, 0u, 0u, 0u, 0u, 0u};
+#pragma unroll 1
+                    for (int w = 0; 4 * w < F + wlmax; w++) {
+                        bs::erasure_forney<32, 32>(EL, G, SP, S, w, root_tab, nz);
+                        uint32_t X[32];
+                        bs::magnitude_words<32>(S, X);
+#pragma unroll 1
+                        for (int c0 = 0; c0 < 32; c0 += 8) {
+#pragma unroll
+                            for (int u = 0; u < 8; u++) {
+                                const uint32_t xc = c0 == 0 ? X[u] : c0 == 8 ? X[8 + u] : c0 == 16 ? X[16 + u] : X[24 + u];
+                                if (!((accept >> (c0 + u)) & 1u) || xc == 0u)
+                                    continue;
+                                const size_t cw = Qs.ld(c0 + u) & 0x3FFFFFFFu;
+                                const uint32_t *row = era_pos + cw * era_stride;
+#pragma unroll
+                                for (int y = 0; y < 4; y++) {
+                                    const uint32_t mag = (xc >> (8 * y)) & 0xFFu;
+                                    const size_t slot = (size_t)(4 * w + y);
+                                    if (mag && slot < era_stride) { // rank -> the caller's slot of that number
+                                        const uint32_t pj = __ldg(row + slot);
+                                        if (pj < (uint32_t)size) {
+                                            const uintptr_t a = (uintptr_t)data + cw * data_stride + pj;
+                                            asm volatile("red.relaxed.gpu.global.xor.b32 [%0], %1;" ::"l"(a & ~(uintptr_t)3),
+                                                         "r"(mag << (8u * (unsigned)(a & 3u)))
+                                                         : "memory");
+                                        }
+                                    }
+                                }
+                            }
+                        }
+                    }
+#pragma unroll 1
+                    for (int c = 0; c < 32; c++) {
+                        if (!((accept >> c) & 1u))
+                            continue;
+                        const size_t cw = Qs.ld(c) & 0x3FFFFFFFu;
+                        uint32_t k = 0;
+#pragma unroll
+                        for (int b = 0; b < 6; b++)
+                            k |= ((nz[b] >> c) & 1u) << b;
+                        if (ok)
+                            ok[cw] = 1;
+                        if (corrected)
+                            corrected[cw] = k;
+                    }
+                }
+            }
+            // everything else goes to the literal stage (one reservation per lane)
+            {
+                uint32_t rest = present & ~accept;
+                if (rest) {
+                    uint32_t at = atomicAdd(counter3, (uint32_t)__popc(rest));
+                    while (rest) {
+                        const int c = __ffs((int)rest) - 1;
+                        rest &= rest - 1;
+                        queue3[at++] = Qs.ld(c);
+                    }
+                }
             }
         }
         __syncthreads();
@@ -1756,6 +1983,8 @@ int rs255_init(poporon_cuda_rs *ctx)
     {
         const char *e = getenv("PP_RS255_NO_ERASURE_KERNEL"); // A/B: erasure mode on the plain solver + the literal stage only
         ctx->no_erasure_kernel = e && e[0] == '1';
+        e = getenv("PP_RS255_NO_EE_KERNEL"); // A/B: without the second bitsliced stage of erasure mode
+        ctx->no_ee_kernel = e && e[0] == '1';
     }
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_correct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCorrectSmem));
     {
@@ -1928,6 +2157,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
     // larger than one wave would leave a thin second wave behind the grid-stride loop
     const unsigned cblocks = (unsigned)(ctx->sm_count * ctx->correct_ctas_per_sm);
     const uint32_t *cq = ctx->d_queue, *cc = ctx->d_counters;
+    const uint32_t *era_counter = ctx->d_counters + 1; // rows for the literal stage
     {
         // bitsliced solver first (erasure mode: for the rows it can prove equal to plain decoding, see erasure_row_covers_roots) (with the caller's syndromes error_correction_u8 runs exactly as in plain mode); what it declines lands in queue2 for the literal stage below
         uint32_t *queue2 = dmask + tiles * 64;
@@ -1946,13 +2176,34 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
                                                                       ctx->d_counters + kCntCursor, queue2);
                 ctx->launches += 2;
             }
-            ProfScope prof(ctx, PROF_ERASURE, stream);
-            const size_t ecap = (size_t)ctx->sm_count * kEraWarps;
-            const size_t warps = groups < ecap ? groups : ecap;
-            rs255_erasure_kernel<<<(unsigned)((warps + kEraWarps - 1) / kEraWarps), 32 * kEraWarps,
-                                   kEraSmem, stream>>>(nr, size, queue2, ctx->d_counters, ctx->d_rem, scratch, ctx->d_queue,
-                                                       ctx->d_counters + 1, ok, corrected, data, data_stride, pos,
-                                                       pos_stride, cnt);
+            {
+                ProfScope prof(ctx, PROF_ERASURE, stream);
+                const size_t ecap = (size_t)ctx->sm_count * kEraWarps;
+                const size_t warps = groups < ecap ? groups : ecap;
+                rs255_erasure_kernel<<<(unsigned)((warps + kEraWarps - 1) / kEraWarps), 32 * kEraWarps, kEraSmem, stream>>>(
+                    nr, size, queue2, ctx->d_counters, ctx->d_rem, scratch, ctx->d_queue, ctx->d_counters + 1, ok, corrected,
+                    data, data_stride, pos, pos_stride, cnt);
+            }
+            // what it declined (now in the buffer of the first queue, counted in counters[1]), ordered by declared count
+            // again, goes through the second bitsliced stage; what that declines ends up in the first buffer once more
+            if (!ctx->no_ee_kernel && nr == 32) {
+                uint32_t *sorted = queue2; // (the ordered queue of the erasure kernel is dead)
+                {
+                    ProfScope prof2(ctx, PROF_COMPACT, stream);
+                    const unsigned sblocks = (unsigned)ctx->sm_count * 8u;
+                    rs255_era_hist_kernel<<<sblocks, 256, 0, stream>>>(ctx->d_queue, ctx->d_counters + 1, cnt, ctx->d_counters + kCntHist2);
+                    rs255_era_scatter_kernel<<<sblocks, 256, 0, stream>>>(ctx->d_queue, ctx->d_counters + 1, cnt, ctx->d_counters + kCntHist2,
+                                                                          ctx->d_counters + kCntCursor2, sorted);
+                    ctx->launches += 2;
+                }
+                ProfScope prof3(ctx, PROF_EE, stream);
+                const size_t ewarps = groups < (size_t)ctx->sm_count * kEeWarps ? groups : (size_t)ctx->sm_count * kEeWarps;
+                rs255_ee_kernel<<<(unsigned)((ewarps + kEeWarps - 1) / kEeWarps), 32 * kEeWarps, 0, stream>>>(
+                    size, sorted, ctx->d_counters + 1, ctx->d_rem, scratch, ctx->d_queue, ctx->d_counters + 2, ok, corrected, data,
+                    data_stride, pos, pos_stride, cnt);
+                ctx->launches += 1;
+                era_counter = ctx->d_counters + 2;
+            }
             queue2 = ctx->d_queue; // (the literal stage reads what was declined)
         } else {
             ProfScope prof(ctx, PROF_SOLVE, stream);
@@ -1964,7 +2215,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
                 mode == POPORON_CUDA_MODE_ERASURE ? cnt : nullptr);
         }
         cq = queue2;
-        cc = ctx->d_counters + 1;
+        cc = era_counter;
         ctx->launches += 1;
     }
     {
