@@ -97,6 +97,7 @@ struct poporon_cuda_rs {
     cudaEvent_t busy;         // recorded after the last kernel that uses the scratch above; the next call's stream waits on it
     int correct_ctas_per_sm;  // resident CTAs of the general correction stage (per device, rs255_init)
     int no_fuse;              // PP_RS255_NOFUSE=1: compaction kernel instead of the fused zero-syndrome exit (A/B runs)
+    uint32_t ee_min_rows;     // PP_RS255_EE_MIN_ROWS: see rs255_ee_kernel
     int no_ee_kernel;         // PP_RS255_NO_EE_KERNEL=1: erasure mode without its second bitsliced stage (A/B runs)
     int no_erasure_kernel;    // PP_RS255_NO_ERASURE_KERNEL=1: erasure mode without the bitsliced erasure-only kernel (A/B runs)
     int use_lfsr;             // PP_RS255_LFSR=1: the round-1 LFSR kernels instead of the transform kernels (A/B runs)

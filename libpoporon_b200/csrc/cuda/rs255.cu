@@ -1630,7 +1630,7 @@ rs255_ee_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t 
                 const uint8_t *__restrict__ syn_raw, uint32_t *__restrict__ scratch, uint32_t *__restrict__ queue3,
                 uint32_t *__restrict__ counter3, uint8_t *__restrict__ ok, uint32_t *__restrict__ corrected, uint8_t *data,
                 size_t data_stride, const uint32_t *__restrict__ era_pos, size_t era_stride,
-                const uint32_t *__restrict__ era_cnt)
+                const uint32_t *__restrict__ era_cnt, uint32_t min_rows)
 {
     __shared__ uint8_t tabs[512];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1647,6 +1647,17 @@ rs255_ee_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t 
     era_fill_tables(root_tab, inv_tab, lane);
     __syncthreads();
     const uint32_t total = *counter;
+    if (total < min_rows) {
+        // A tile costs a warp the better part of a millisecond whatever the batch: with few rows the per-thread literal
+        // stage is faster (64 Ki rows: 0.26 against 0.8 ms).  Everything is handed on.
+        if (blockIdx.x == 0) {
+            for (uint32_t q = threadIdx.x; q < total; q += blockDim.x)
+                queue3[q] = queue[q];
+            if (threadIdx.x == 0)
+                *counter3 = total;
+        }
+        return;
+    }
     const int pad = 255 - 32 - (int)size;
     const bool vec_rows = (((uintptr_t)era_pos | (era_stride * 4u)) & 15u) == 0;
     const uint32_t rounds = (total + nw * 1024u - 1u) / (nw * 1024u);
@@ -1985,6 +1996,8 @@ int rs255_init(poporon_cuda_rs *ctx)
         ctx->no_erasure_kernel = e && e[0] == '1';
         e = getenv("PP_RS255_NO_EE_KERNEL"); // A/B: without the second bitsliced stage of erasure mode
         ctx->no_ee_kernel = e && e[0] == '1';
+        e = getenv("PP_RS255_EE_MIN_ROWS"); // rows below which that stage hands everything to the literal one (tests: 0)
+        ctx->ee_min_rows = e ? (uint32_t)strtoul(e, nullptr, 10) : 131072u;
     }
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_correct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCorrectSmem));
     {
@@ -2200,7 +2213,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
                 const size_t ewarps = groups < (size_t)ctx->sm_count * kEeWarps ? groups : (size_t)ctx->sm_count * kEeWarps;
                 rs255_ee_kernel<<<(unsigned)((ewarps + kEeWarps - 1) / kEeWarps), 32 * kEeWarps, 0, stream>>>(
                     size, sorted, ctx->d_counters + 1, ctx->d_rem, scratch, ctx->d_queue, ctx->d_counters + 2, ok, corrected, data,
-                    data_stride, pos, pos_stride, cnt);
+                    data_stride, pos, pos_stride, cnt, ctx->ee_min_rows);
                 ctx->launches += 1;
                 era_counter = ctx->d_counters + 2;
             }

@@ -690,6 +690,36 @@ def test_erasure_mode_of_the_shorter_codes(gpu_device, orc, nr):
             _assert_same(got, want, f"erasure nr={nr} size={size} stride={stride}")
 
 
+@pytest.mark.parametrize("size,F", [(223, 1), (223, 10), (223, 23), (223, 30), (60, 7), (9, 4)])
+def test_erasure_rows_with_undeclared_errors(gpu_device, orc, monkeypatch, size, F):
+    """rs255_ee_kernel: every row declares the same number F of positions (so that its warps accept their tiles) and has
+    errors outside them - few enough to decode, one too many, or none; the slots beyond F hold stale positions, through
+    which the reference applies the magnitudes of the roots it finds beyond the F-th (src/decode.c:211-214)."""
+    rng = np.random.default_rng(7000 + 31 * size + F)
+    n = 3 * 1024 + 500
+    monkeypatch.setenv("PP_RS255_EE_MIN_ROWS", "0")  # (read when the handle is created: small batches skip the kernel)
+    with api.Poporon.rs_default() as h:
+        msg = rng.integers(0, 256, (n, size), dtype=np.uint8)
+        par = _gpu_encode(h, msg, 32)
+        cw = np.concatenate([msg, par], 1)
+        pos = np.zeros((n, 32), np.uint32)
+        cnt = np.full(n, F, np.uint32)
+        emax = (32 - F) // 2
+        for i in range(n):
+            pp = np.sort(rng.choice(size, F, replace=False))
+            pos[i, :F] = pp
+            pos[i, F:] = rng.integers(0, size, 32 - F)
+            cw[i, pp] ^= rng.integers(0, 256, F, dtype=np.uint8)
+            e = int(rng.integers(0, emax + 2))
+            others = np.setdiff1d(np.arange(size + 32), pp)
+            q = rng.choice(others, min(e, len(others)), replace=False)
+            cw[i, q] ^= rng.integers(1, 256, len(q), dtype=np.uint8)
+        got = _gpu_decode(h, cw[:, :size], cw[:, size:], MODE_ERASURE, pos, cnt)
+        want = orc.rs_decode(cw[:, :size], cw[:, size:], RS_DEFAULT, MODE_ERASURE, pos, cnt)
+        _assert_same(got, want, f"erasure + errors size={size} F={F}")
+        assert (want[2] == 1).sum() > n // 4
+
+
 def test_modes_alternate_on_one_handle(gpu_device, orc):
     """plain -> erasure -> plain -> erasure with growing batches on ONE handle: the decode scratch is sized by mode and
     by batch (the erasure kernel's is larger) and regrown in between"""
