@@ -1622,6 +1622,9 @@ rs255_erasure_kernel(int nr, size_t size, const uint32_t *__restrict__ queue, co
 // list of declared positions and found roots; the i-th of them is XORed into the caller's i-th SLOT, as the reference
 // does (src/decode.c:211-214; slots past the row and positions past the message are skipped, as in rs_correct.cuh).
 // ---------------------------------------------------------------------------------------------------
+#ifndef PP_EE_B_SMEM
+#define PP_EE_B_SMEM 1 // BM's B in shared memory (16 KB per warp), the rest of the work area in the scratch
+#endif
 constexpr int kEeWarps = 8;
 constexpr int kEeScratchWords = bs::kWordsS + bs::kWordsG + bs::kWordsEL + 8 * bs::kNL + bs::kWordsM + 32 + bs::kWordsW;
 static_assert(kEeWarps * kEeScratchWords <= kEraWarps * kEraScratchWords, "the erasure kernel's scratch serves both");
@@ -1633,6 +1636,9 @@ rs255_ee_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t 
                 const uint32_t *__restrict__ era_cnt, uint32_t min_rows)
 {
     __shared__ uint8_t tabs[512];
+#if PP_EE_B_SMEM
+    extern __shared__ __align__(16) uint32_t solve_smem[];
+#endif
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t gw = blockIdx.x * kEeWarps + (uint32_t)warp, nw = gridDim.x * kEeWarps;
     uint32_t *gs = scratch + (size_t)gw * (kEeScratchWords * 32) + lane;
@@ -1706,7 +1712,11 @@ rs255_ee_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t 
                 const int F = wfmax;
                 bs::LaneOut out;
                 bs::NoHook idle;
+#if PP_EE_B_SMEM
+                bs::ee_lane<32, 32>(SP, EL, G, SG, MK, S, inv_tab, F, pad, out, idle, solve_smem + warp * (128 * 32) + lane);
+#else
                 bs::ee_lane<32, 32>(SP, EL, G, SG, MK, S, inv_tab, F, pad, out, idle);
+#endif
                 // outcome of sigma per codeword; the merged rank list replaces the slot list
 #pragma unroll 1
                 for (int c = 0; c < 32; c++) {
@@ -1991,6 +2001,8 @@ int rs255_init(poporon_cuda_rs *ctx)
                                      kPairs * kSmemScreen));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
     PP_CUDA_TRY(cudaFuncSetAttribute(rs255_erasure_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEraSmem));
+    if (PP_EE_B_SMEM)
+        PP_CUDA_TRY(cudaFuncSetAttribute(rs255_ee_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEeWarps * 128 * 128));
     {
         const char *e = getenv("PP_RS255_NO_ERASURE_KERNEL"); // A/B: erasure mode on the plain solver + the literal stage only
         ctx->no_erasure_kernel = e && e[0] == '1';
@@ -2211,7 +2223,7 @@ int rs255_decode(poporon_cuda_rs *ctx, int mode, uint8_t *data, size_t data_stri
                 }
                 ProfScope prof3(ctx, PROF_EE, stream);
                 const size_t ewarps = groups < (size_t)ctx->sm_count * kEeWarps ? groups : (size_t)ctx->sm_count * kEeWarps;
-                rs255_ee_kernel<<<(unsigned)((ewarps + kEeWarps - 1) / kEeWarps), 32 * kEeWarps, 0, stream>>>(
+                rs255_ee_kernel<<<(unsigned)((ewarps + kEeWarps - 1) / kEeWarps), 32 * kEeWarps, PP_EE_B_SMEM ? kEeWarps * 128 * 128 : 0, stream>>>(
                     size, sorted, ctx->d_counters + 1, ctx->d_rem, scratch, ctx->d_queue, ctx->d_counters + 2, ok, corrected, data,
                     data_stride, pos, pos_stride, cnt, ctx->ee_min_rows);
                 ctx->launches += 1;

@@ -183,12 +183,14 @@ BS_FN void erasure_forney(const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, co
 // classify(W, out, c, nroots, 32 - F) gives the outcome of sigma for codeword c.
 template <int STRIDE, int SO, class Hook>
 BS_FN void ee_lane(const Mem<SO> SP, const Mem<SO> EL, const Mem<SO> G, const Mem<SO> SG, const Mem<SO> MK,
-                   const Mem<STRIDE> W, const uint8_t *inv_tab, int F, int pad, LaneOut &out, Hook &hook)
+                   const Mem<STRIDE> W, const uint8_t *inv_tab, int F, int pad, LaneOut &out, Hook &hook,
+                   uint32_t *bm_area = nullptr)
 {
     erasure_locator<STRIDE, SO>(EL, G, W, inv_tab, F);
     erasure_product<SO>(SP, G, F, kES);
     const Mem<SO> T{SP.base + 8 * F * SO};
-    const Mem<STRIDE> B{W.base + kListBase * STRIDE};
+    // B of Berlekamp-Massey: 128 words, by default the list area of W (filled only afterwards)
+    const Mem<STRIDE> B{bm_area ? bm_area : W.base + kListBase * STRIDE};
     ribm_mem<STRIDE, SO>(T, B, SG, out.K, kES - F);
 #pragma unroll
     for (int j = 0; j < kNL; j++) {
