@@ -1560,11 +1560,14 @@ rs255_erasure_kernel(int nr, size_t size, const uint32_t *__restrict__ queue, co
                 }
             }
             uint32_t nz[6] = {0u, 0u, 0u, 0u, 0u, 0u};
+            // (no row of the warp declares more than wmaxf positions: Gamma and omega end there, and so do Forney's
+            // Horner chains - at the next even number, at least 4)
+            const int teff = wmaxf <= 4 ? 4 : ((wmaxf + 1) & ~1) < nr ? ((wmaxf + 1) & ~1) : nr;
 #pragma unroll 1
             for (int w = 0; 4 * w < nr; w++) {
                 if (!__any_sync(0xFFFFFFFFu, accept != 0u && maxf > 4 * w))
                     break;
-                bs::erasure_forney<32, 32>(EL, G, Syn, S, w, root_tab, nz, nr);
+                bs::erasure_forney<32, 32>(EL, G, Syn, S, w, root_tab, nz, teff);
                 uint32_t X[32];
                 bs::magnitude_words<32>(S, X);
                 // eight codewords per trip: their queue entries and list words (L2) are all on their way before the
@@ -1784,9 +1787,11 @@ rs255_ee_kernel(size_t size, const uint32_t *__restrict__ queue, const uint32_t 
                 if (wlmax) {
                     bs::ee_products<32>(SP, G, SG, wlmax);
                     uint32_t nz[6] = {0u, 0u, 0u, 0u, 0u, 0u};
+                    const int dmax = F + wlmax; // the largest degree of Gamma * sigma in the warp (<= 31)
+                    const int teff = dmax <= 4 ? 4 : (dmax + 1) & ~1;
 #pragma unroll 1
                     for (int w = 0; 4 * w < F + wlmax; w++) {
-                        bs::erasure_forney<32, 32>(EL, G, SP, S, w, root_tab, nz);
+                        bs::erasure_forney<32, 32>(EL, G, SP, S, w, root_tab, nz, teff);
                         uint32_t X[32];
                         bs::magnitude_words<32>(S, X);
 #pragma unroll 1

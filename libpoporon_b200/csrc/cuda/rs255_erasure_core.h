@@ -160,11 +160,13 @@ BS_FN uint32_t erasure_lane(const Mem<SO> SP, const Mem<SO> EL, const Mem<SO> G,
 // (magnitude_words() turns them into one word per codeword), cnt (6 bit-planes) has counted the non-zero ones.
 // root_tab[list byte] = alpha^(location + 1), the root of Gamma that belongs to the slot.
 template <int STRIDE, int SO>
+// teff: an even number >= 4 and >= the degree of every locator of the lane (its coefficients and those of omega are
+// zero from there on): the Horner chains start at teff - 1.
 BS_FN void erasure_forney(const Mem<SO> EL, const Mem<SO> G, const Mem<SO> P, const Mem<STRIDE> S, int w,
-                          const uint8_t *root_tab, uint32_t (&cnt)[6], int ns = kES)
+                          const uint8_t *root_tab, uint32_t (&cnt)[6], int teff = kES)
 {
     stage_slots<STRIDE, SO>(EL, S, w, root_tab);
-    forney_math<STRIDE, SO, 6>(G, P, S, cnt, ns);
+    forney_math<STRIDE, SO, 6>(G, P, S, cnt, teff);
 }
 
 // ---- errors on top of the erasures -------------------------------------------------------------------------------

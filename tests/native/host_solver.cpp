@@ -115,8 +115,9 @@ static int host_erasure_ns(const uint8_t *syn, const uint8_t *lists, size_t n, i
         const uint32_t badmask = bs::erasure_lane<1, 1>(Synm, ELm, Gm, Sm, inv_tab, nslots, ns);
         uint32_t nz[6] = {0, 0, 0, 0, 0, 0};
         memset(mags + g * 32, 0, cnt * 32);
+        const int teff = nslots <= 4 ? 4 : ((nslots + 1) & ~1) < ns ? ((nslots + 1) & ~1) : ns; // as the kernel bounds it
         for (int w = 0; 4 * w < ns; w++) {
-            bs::erasure_forney<1, 1>(ELm, Gm, Synm, Sm, w, root_tab, nz, ns);
+            bs::erasure_forney<1, 1>(ELm, Gm, Synm, Sm, w, root_tab, nz, teff);
             uint32_t X[32];
             bs::magnitude_words<1>(Sm, X);
             for (size_t c = 0; c < cnt; c++)
@@ -206,8 +207,9 @@ extern "C" int host_ee(const uint8_t *syn /* [n][32] */, const uint8_t *lists /*
         }
         bs::ee_products<1>(SPm, Gm, SGm, lmax);
         uint32_t nz[6] = {0, 0, 0, 0, 0, 0};
+        const int dmax = F + lmax, teff = dmax <= 4 ? 4 : (dmax + 1) & ~1; // as the kernel bounds it
         for (int w = 0; w < 8; w++) {
-            bs::erasure_forney<1, 1>(ELm, Gm, SPm, Wm, w, root_tab, nz);
+            bs::erasure_forney<1, 1>(ELm, Gm, SPm, Wm, w, root_tab, nz, teff);
             uint32_t X[32];
             bs::magnitude_words<1>(Wm, X);
             for (size_t c = 0; c < cnt; c++)
