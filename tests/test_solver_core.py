@@ -263,3 +263,15 @@ def test_errors_on_top_of_erasures_core(solver):
                     fixed[pos[i, r]] ^= mags[i, r]
             assert (fixed == wd[i]).all() and (cw[i, size:] == wp[i]).all(), i
             assert count[i] == wcor[i], (i, count[i], wcor[i])
+
+
+def test_cores_under_address_sanitizer():
+    """The three bitsliced cores (plain solver, erasure-only, errors on top of erasures; 32 / 16 / 8 roots) on random
+    syndromes and slot lists under -fsanitize=address,undefined (tests/native/asan_main.cpp): no access outside their
+    areas whatever the data (compute-sanitizer is not available on the GPU pool)."""
+    exe = os.path.join(os.path.dirname(OUT), "asan_solver")
+    main = os.path.join(ROOT, "tests", "native", "asan_main.cpp")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-fsanitize=address,undefined", "-fno-omit-frame-pointer", f"-I{INC}",
+                    "-o", exe, main, SRC], check=True)
+    run = subprocess.run([exe], capture_output=True, text=True)
+    assert run.returncode == 0 and "asan run done" in run.stdout, run.stderr[-2000:]
