@@ -1281,11 +1281,15 @@ rs255_solve_kernel(int nr, size_t size, uint32_t *queue, const uint32_t *__restr
 
         // Forney on four list slots at a time; the magnitude words go to the error records
         uint32_t nzc[5] = {0u, 0u, 0u, 0u, 0u};
+        // (no decodable codeword of the warp has more roots - a locator of higher degree, a longer evaluator - than
+        // wroots: the Horner chains start at the next even number, at least 4)
+        const int wroots = (int)__reduce_max_sync(0xFFFFFFFFu, (unsigned)maxroots);
+        const int teff = wroots <= 4 ? 4 : ((wroots + 1) & ~1) < (nr >> 1) ? ((wroots + 1) & ~1) : (nr >> 1);
 #pragma unroll 1
         for (int w = 0; w < 4; w++) {
-            if (!__any_sync(0xFFFFFFFFu, maxroots > 4 * w))
+            if (4 * w >= wroots)
                 break;
-            bs::forney_slots<32, 32>(Syn, B, S, w, root_tab, nzc, nr >> 1);
+            bs::forney_slots<32, 32>(Syn, B, S, w, root_tab, nzc, teff);
             uint32_t X[32];
             bs::magnitude_words<32>(S, X);
 #pragma unroll
